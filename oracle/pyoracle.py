@@ -1,0 +1,387 @@
+"""TEST INFRASTRUCTURE — ctypes views of the parity oracles.  NOT part of the product.
+
+Two checkers live under oracle/:
+  * libse_oracle.so      our plain-C restatement (oracle/se_oracle.c), built anywhere with gcc;
+  * _ref/libref_*.so     the reference's OWN sources compiled in place from /root/reference
+                         (oracle/Makefile `make ref`); built in the dev container, travels prebuilt.
+
+Only tests/, __graft_entry__.smoke() and bench.py's cpu_baseline / --impl reference legs import this.
+"""
+import ctypes as C
+import os
+import subprocess
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+REF_DIR = os.path.join(HERE, "_ref")
+REFERENCE_ROOT = os.environ.get("SE_REFERENCE_ROOT", "/root/reference")
+
+_vp = C.c_void_p
+
+
+def _p(a):
+    return None if a is None else a.ctypes.data_as(_vp)
+
+
+def build_oracle(force=False):
+    so = os.path.join(HERE, "libse_oracle.so")
+    src = os.path.join(HERE, "se_oracle.c")
+    if force or not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(src):
+        subprocess.check_call(["make", "-s", "-C", HERE, "libse_oracle.so"])
+    return so
+
+
+def build_ref():
+    """Compile oracle/_ref from the reference sources where they lie (only where they exist)."""
+    if os.path.isdir(REFERENCE_ROOT):
+        subprocess.check_call(["make", "-s", "-C", HERE, "ref", "REF=" + REFERENCE_ROOT])
+        return True
+    return False
+
+
+def have_ref(name="libref_etsi.so"):
+    return os.path.exists(os.path.join(REF_DIR, name))
+
+
+class InfoStruct(C.Structure):
+    _fields_ = [("produced", C.c_int), ("stage0_ran", C.c_int), ("stage1_ran", C.c_int),
+                ("flag_vad", C.c_int), ("hang_over", C.c_int), ("nb_speech", C.c_int),
+                ("nb_frame0", C.c_int), ("nb_frame1", C.c_int),
+                ("sp_var", C.c_int), ("sp_spec", C.c_int), ("sp_mel", C.c_int), ("sp_vadns", C.c_int),
+                ("mean_en", C.c_float), ("alfa_gf", C.c_float), ("low_snr", C.c_float), ("den_en", C.c_float),
+                ("gains", C.c_float * 25)]
+
+
+INFO_DTYPE = np.dtype([("produced", "i4"), ("stage0_ran", "i4"), ("stage1_ran", "i4"), ("flag_vad", "i4"),
+                       ("hang_over", "i4"), ("nb_speech", "i4"), ("nb_frame0", "i4"), ("nb_frame1", "i4"),
+                       ("sp_var", "i4"), ("sp_spec", "i4"), ("sp_mel", "i4"), ("sp_vadns", "i4"),
+                       ("mean_en", "f4"), ("alfa_gf", "f4"), ("low_snr", "f4"), ("den_en", "f4"),
+                       ("gains", "f4", (25,))])
+assert INFO_DTYPE.itemsize == C.sizeof(InfoStruct)
+
+
+class Oracle:
+    """Plain-C restatement (oracle/se_oracle.c)."""
+
+    def __init__(self, fast=False):
+        if fast:
+            so = os.path.join(HERE, "libse_oracle_fast.so")
+            if not os.path.exists(so):
+                subprocess.check_call(["make", "-s", "-C", HERE, "libse_oracle_fast.so"])
+        else:
+            so = build_oracle()
+        L = self.L = C.CDLL(so)
+        L.so_ns_create.restype = _vp
+        L.so_ns_create.argtypes = [C.c_int]
+        L.so_ns_destroy.argtypes = [_vp]
+        L.so_ns_block.argtypes = [_vp, _vp, _vp, _vp]
+        L.so_ns_spectrum.restype = C.POINTER(C.c_float)
+        L.so_ns_spectrum.argtypes = [_vp, C.c_int]
+        L.so_ns_tables.argtypes = [_vp] * 7
+        L.so_etsi_denoise.restype = C.c_long
+        L.so_etsi_denoise.argtypes = [_vp, C.c_long, _vp, _vp, _vp, _vp, _vp]
+        L.so_p16_func_wiener.argtypes = [_vp, _vp, C.c_int] + [_vp] * 7
+        L.so_gammatone.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_float, C.c_long]
+        L.so_haircell.argtypes = [_vp, _vp, C.c_long]
+        L.so_subband.argtypes = [_vp, C.c_long, _vp]
+        L.so_addnoise.argtypes = [_vp, _vp, _vp, C.c_long, C.c_int]
+        L.so_resynth_num_frames.argtypes = [C.c_long, C.c_int]
+        L.so_resynth.argtypes = [_vp, C.c_long, _vp, C.c_int, C.c_int, _vp, _vp]
+        L.so_ibm_num_frames.restype = C.c_long
+        L.so_ibm_num_frames.argtypes = [C.c_long]
+        L.so_single_ibm.argtypes = [_vp, _vp, C.c_long, _vp, _vp]
+        L.so_rfft.argtypes = [_vp, C.c_int, C.c_int]
+        L.so_rfft_cxx.argtypes = [_vp, C.c_int, C.c_int]
+
+    # ---- primitives
+    def rfft(self, x, m, cxx=False):
+        y = np.ascontiguousarray(x, np.float32).copy()
+        (self.L.so_rfft_cxx if cxx else self.L.so_rfft)(_p(y), len(y), m)
+        return y
+
+    # ---- P8
+    def etsi_denoise(self, x, with_ceps=False, trace=False):
+        x = np.ascontiguousarray(x, np.int16)
+        n = len(x)
+        den = np.zeros(n, np.int16)
+        denf = np.zeros(n, np.float32)
+        ncalls = n // 80
+        ceps = np.zeros((max(ncalls, 1), 14), np.float32) if with_ceps else None
+        nceps = C.c_long(0)
+        info = np.zeros(max(ncalls, 1), INFO_DTYPE) if trace else None
+        calls = self.L.so_etsi_denoise(_p(x), n, _p(den), _p(denf), _p(ceps), C.byref(nceps), _p(info))
+        out = {"den_i16": den, "den_f32": denf, "calls": calls}
+        if with_ceps:
+            out["ceps"] = ceps[:nceps.value].copy()
+        if trace:
+            out["info"] = info[:calls]
+        return out
+
+    def comp_ceps(self, frame201):
+        f = np.ascontiguousarray(frame201, np.float32)
+        o = np.zeros(14, np.float32)
+        self.L.so_comp_ceps(_p(f), _p(o))
+        return o
+
+    def cc_tables(self):
+        ham = np.zeros(100, np.float32); dct = np.zeros((12, 23), np.float32)
+        st = np.zeros(23, np.int32); ln = np.zeros(23, np.int32); tri = np.zeros((23, 129), np.float32)
+        self.L.so_cc_tables(_p(ham), _p(dct), _p(st), _p(ln), _p(tri))
+        return dict(hamming=ham, dct=dct, start=st, len=ln, tri=tri)
+
+    def ns_tables(self, profile):
+        h = self.L.so_ns_create(profile)
+        fl, w = (200, 65) if profile == 8 else (480, 128)
+        sw = np.zeros(fl, np.float32); ir = np.zeros(17, np.float32); bank = np.zeros((25, w), np.float32)
+        st = np.zeros(25, np.int32); ln = np.zeros(25, np.int32); idct = np.zeros((25, 25), np.float32)
+        self.L.so_ns_tables(h, _p(sw), _p(ir), _p(bank), _p(st), _p(ln), _p(idct))
+        self.L.so_ns_destroy(h)
+        return dict(sig_window=sw, ir_window=ir, bank=bank, bank_start=st, bank_len=ln, idct=idct)
+
+    # ---- P16
+    def p16_stream(self):
+        return _OracleP16(self)
+
+    # ---- G64
+    def channel_params(self):
+        cf = np.zeros(64, np.float32); bw = np.zeros(64, np.float32); mid = np.zeros(64, np.float32)
+        self.L.so_channel_params(_p(cf), _p(bw), _p(mid))
+        return cf, bw, mid
+
+    def gammatone(self, x, cf, bw, mid):
+        x = np.ascontiguousarray(x, np.float32); y = np.zeros_like(x)
+        self.L.so_gammatone(_p(x), _p(y), float(cf), float(bw), float(mid), len(x))
+        return y
+
+    def haircell(self, x):
+        x = np.ascontiguousarray(x, np.float32); y = np.zeros_like(x)
+        self.L.so_haircell(_p(x), _p(y), len(x))
+        return y
+
+    def subband(self, wav):
+        wav = np.ascontiguousarray(wav, np.int16)
+        out = np.zeros((64, len(wav)), np.int16)
+        self.L.so_subband(_p(wav), len(wav), _p(out))
+        return out
+
+    def addnoise(self, pure, noise, db):
+        pure = np.ascontiguousarray(pure, np.int16); noise = np.ascontiguousarray(noise, np.int16).copy()
+        noisy = np.zeros_like(pure)
+        self.L.so_addnoise(_p(pure), _p(noise), _p(noisy), len(pure), int(db))
+        return noise, noisy
+
+    def resynth_num_frames(self, n, mode):
+        return self.L.so_resynth_num_frames(n, mode)
+
+    def resynth(self, wav, mask, mode, want_f32=False):
+        wav = np.ascontiguousarray(wav, np.int16)
+        m = np.ascontiguousarray(mask, np.float32).copy()
+        out = np.zeros(len(wav), np.int16)
+        of = np.zeros(len(wav), np.float32) if want_f32 else None
+        self.L.so_resynth(_p(wav), len(wav), _p(m), m.shape[0], mode, _p(out), _p(of))
+        return (out, of, m) if want_f32 else (out, m)
+
+    def single_ibm(self, pure64, noise64):
+        pure64 = np.ascontiguousarray(pure64, np.int16); noise64 = np.ascontiguousarray(noise64, np.int16)
+        n = pure64.shape[1]
+        fr = self.L.so_ibm_num_frames(n)
+        irm = np.zeros((fr, 64), np.float32); ibm = np.zeros((fr, 64), np.uint8)
+        self.L.so_single_ibm(_p(pure64), _p(noise64), n, _p(irm), _p(ibm))
+        return irm, ibm
+
+
+class _OracleP16:
+    def __init__(self, o):
+        self.o = o
+        self.h = o.L.so_ns_create(16)
+
+    def close(self):
+        if self.h:
+            self.o.L.so_ns_destroy(self.h)
+            self.h = None
+
+    def func_wiener(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        n = len(x); nb = n // 160
+        out = np.zeros(n, np.float32)
+        fl = [np.zeros(max(nb, 1), np.int32) for _ in range(5)]
+        gains = np.zeros((max(nb, 1), 25), np.float32)
+        rows = self.o.L.so_p16_func_wiener(self.h, _p(x), n, _p(out), *[_p(f) for f in fl], _p(gains))
+        return dict(out=out, sp_var=fl[0][:nb], sp_spec=fl[1][:nb], sp_mel=fl[2][:nb], sp_vadns=fl[3][:nb],
+                    frame_counter=fl[4][:nb], gains=gains[:rows].copy())
+
+    def spectrum(self, which, n=129):
+        ptr = self.o.L.so_ns_spectrum(self.h, which)
+        return np.ctypeslib.as_array(ptr, (n,)).copy()
+
+
+# ------------------------------------------------------------------------------------------
+# oracle/_ref : the reference's own code
+# ------------------------------------------------------------------------------------------
+class TraceStruct(C.Structure):
+    _fields_ = [(k, _vp) for k in ("ret", "flag_vad", "hang_over", "nb_speech", "nb_frame0", "nb_frame1",
+                                   "sp_var", "sp_spec", "sp_mel", "sp_vadns", "mean_en", "alfa_gf", "low_snr",
+                                   "den_en", "nsig1", "noise1", "den1", "nsig2", "noise2", "den2", "out_f32")]
+
+
+class RefEtsi:
+    def __init__(self, fast=False):
+        self.L = L = C.CDLL(os.path.join(REF_DIR, "libref_etsi_fast.so" if fast else "libref_etsi.so"))
+        L.ref_etsi_denoise.argtypes = [_vp, _vp, C.c_long, C.c_int]
+        L.ref_etsi_trace.restype = C.c_long
+        L.ref_etsi_trace.argtypes = [_vp, C.c_long, _vp, _vp, _vp, _vp]
+        L.ref_rfft.argtypes = [_vp, C.c_int, C.c_int]
+        L.ref_comp_ceps.argtypes = [_vp, _vp]
+
+    def rfft(self, x, m):
+        y = np.ascontiguousarray(x, np.float32).copy()
+        self.L.ref_rfft(_p(y), len(y), m)
+        return y
+
+    def etsi_denoise(self, x):
+        x = np.ascontiguousarray(x, np.int16).copy()
+        out = np.zeros_like(x)
+        rc = self.L.ref_etsi_denoise(_p(x), _p(out), len(x), 1)
+        return out, rc
+
+    def trace(self, x, with_ceps=True):
+        x = np.ascontiguousarray(x, np.int16)
+        n = len(x); nc = max(n // 80, 1)
+        den = np.zeros(n, np.int16)
+        ceps = np.zeros((nc, 14), np.float32) if with_ceps else None
+        nceps = C.c_long(0)
+        ints = {k: np.zeros(nc, np.int32) for k in ("ret", "flag_vad", "hang_over", "nb_speech", "nb_frame0",
+                                                    "nb_frame1", "sp_var", "sp_spec", "sp_mel", "sp_vadns")}
+        fl = {k: np.zeros(nc, np.float32) for k in ("mean_en", "alfa_gf", "low_snr", "den_en")}
+        sp = {k: np.zeros((nc, 65), np.float32) for k in ("nsig1", "noise1", "den1", "nsig2", "noise2", "den2")}
+        outf = np.zeros((nc, 80), np.float32)
+        tr = TraceStruct()
+        for k, v in list(ints.items()) + list(fl.items()) + list(sp.items()) + [("out_f32", outf)]:
+            setattr(tr, k, v.ctypes.data)
+        calls = self.L.ref_etsi_trace(_p(x), n, _p(den), _p(ceps), C.byref(nceps), C.byref(tr))
+        res = {"den_i16": den, "calls": calls, "out_f32": outf[:calls]}
+        if with_ceps:
+            res["ceps"] = ceps[:nceps.value].copy()
+        for d in (ints, fl, sp):
+            for k, v in d.items():
+                res[k] = v[:calls]
+        return res
+
+    def comp_ceps(self, frame201):
+        f = np.ascontiguousarray(frame201, np.float32); o = np.zeros(14, np.float32)
+        self.L.ref_comp_ceps(_p(f), _p(o))
+        return o
+
+    def tables(self):
+        sw = np.zeros(200, np.float32); ir = np.zeros(17, np.float32)
+        ms = np.zeros(25, np.int32); ml = np.zeros(25, np.int32); md = np.zeros((25, 65), np.float32)
+        idct = np.zeros((25, 25), np.float32); ham = np.zeros(100, np.float32); dct = np.zeros((12, 23), np.float32)
+        cs = np.zeros(23, np.int32); cl = np.zeros(23, np.int32); cd = np.zeros((23, 129), np.float32)
+        self.L.ref_etsi_tables(*[_p(a) for a in (sw, ir, ms, ml, md, idct, ham, dct, cs, cl, cd)])
+        return dict(sig_window=sw, ir_window=ir, bank_start=ms, bank_len=ml, bank=md, idct=idct,
+                    hamming=ham, dct=dct, cc_start=cs, cc_len=cl, cc_tri=cd)
+
+
+class RefP16:
+    def __init__(self, fast=False):
+        self.L = L = C.CDLL(os.path.join(REF_DIR, "libref_p16_fast.so" if fast else "libref_p16.so"))
+        L.ref_p16_create.restype = _vp
+        L.ref_p16_destroy.argtypes = [_vp]
+        L.ref_p16_func_wiener.argtypes = [_vp, _vp, C.c_int] + [_vp] * 8 + [_vp, C.c_long]
+        L.ref_p16_state.argtypes = [_vp] * 9
+        L.ref_p16_tables.argtypes = [_vp] * 6
+        L.ref_p16_rfft.argtypes = [_vp, C.c_int, C.c_int]
+        self.h = L.ref_p16_create()
+
+    def close(self):
+        if self.h:
+            self.L.ref_p16_destroy(self.h)
+            self.h = None
+
+    def rfft(self, x, m):
+        y = np.ascontiguousarray(x, np.float32).copy()
+        self.L.ref_p16_rfft(_p(y), len(y), m)
+        return y
+
+    def func_wiener(self, x, want_text=False):
+        x = np.ascontiguousarray(x, np.float32).copy()
+        n = len(x); nb = n // 160
+        out = np.zeros(n, np.float32)
+        fl = [np.zeros(max(nb, 1), np.int32) for _ in range(5)]
+        gains = np.zeros((max(nb, 1), 25), np.float32)
+        rows = C.c_int(0)
+        cap = 25 * 12 * max(nb, 1) + 16
+        text = C.create_string_buffer(cap) if want_text else None
+        self.L.ref_p16_func_wiener(self.h, _p(x), n, _p(out), *[_p(f) for f in fl], _p(gains), C.byref(rows),
+                                   text, cap if want_text else 0)
+        r = dict(out=out, sp_var=fl[0][:nb], sp_spec=fl[1][:nb], sp_mel=fl[2][:nb], sp_vadns=fl[3][:nb],
+                 frame_counter=fl[4][:nb], gains=gains[:rows.value].copy())
+        if want_text:
+            r["text"] = text.value.decode()
+        return r
+
+    def state(self):
+        sp = [np.zeros(129, np.float32) for _ in range(6)]
+        sc = np.zeros(8, np.float32); isc = np.zeros(8, np.int32)
+        self.L.ref_p16_state(self.h, *[_p(a) for a in sp], _p(sc), _p(isc))
+        return sp, sc, isc
+
+    def tables(self):
+        sw = np.zeros(480, np.float32); ir = np.zeros(17, np.float32); g = np.zeros((25, 128), np.float32)
+        gs = np.zeros(25, np.int32); idct = np.zeros((25, 25), np.float32)
+        self.L.ref_p16_tables(self.h, _p(sw), _p(ir), _p(g), _p(gs), _p(idct))
+        return dict(sig_window=sw, ir_window=ir, bank=g, bank_start=gs, idct=idct)
+
+
+class RefG64:
+    """variant in {'subband','resynth_ibm','resynth_ori','resynth_1dnn'}"""
+
+    def __init__(self, variant, fast=False):
+        name = "libref_%s%s.so" % (variant, "_fast" if fast else "")
+        self.L = L = C.CDLL(os.path.join(REF_DIR, name))
+        self.variant = variant
+        L.ref_gammatone.argtypes = [_vp, _vp, C.c_float, C.c_float, C.c_float, C.c_long]
+        L.ref_haircell.argtypes = [_vp, _vp, C.c_long]
+        L.ref_channel_params.argtypes = [_vp, _vp, _vp]
+        if variant == "subband":
+            L.ref_subband.argtypes = [_vp, C.c_long, _vp]
+            L.ref_addnoise.argtypes = [_vp, _vp, _vp, C.c_long, C.c_int]
+        else:
+            L.ref_resynth.argtypes = [_vp, C.c_long, _vp, C.c_int, _vp]
+
+    def channel_params(self):
+        cf = np.zeros(64, np.float32); bw = np.zeros(64, np.float32); mid = np.zeros(64, np.float32)
+        self.L.ref_channel_params(_p(cf), _p(bw), _p(mid))
+        return cf, bw, mid
+
+    def gammatone(self, x, cf, bw, mid):
+        x = np.ascontiguousarray(x, np.float32).copy(); y = np.zeros_like(x)
+        self.L.ref_gammatone(_p(x), _p(y), float(cf), float(bw), float(mid), len(x))
+        return y
+
+    def haircell(self, x):
+        x = np.ascontiguousarray(x, np.float32).copy(); y = np.zeros_like(x)
+        self.L.ref_haircell(_p(x), _p(y), len(x))
+        return y
+
+    def subband(self, wav):
+        wav = np.ascontiguousarray(wav, np.int16).copy()
+        out = np.zeros((64, len(wav)), np.int16)
+        rc = self.L.ref_subband(_p(wav), len(wav), _p(out))
+        assert rc == 0
+        return out
+
+    def addnoise(self, pure, noise, db):
+        pure = np.ascontiguousarray(pure, np.int16).copy(); noise = np.ascontiguousarray(noise, np.int16).copy()
+        noisy = np.zeros_like(pure)
+        self.L.ref_addnoise(_p(pure), _p(noise), _p(noisy), len(pure), int(db))
+        return noise, noisy
+
+    def resynth(self, wav, mask):
+        wav = np.ascontiguousarray(wav, np.int16).copy()
+        m = np.ascontiguousarray(mask, np.float32).copy()
+        out = np.zeros(len(wav), np.int16)
+        rc = self.L.ref_resynth(_p(wav), len(wav), _p(m), m.shape[0], _p(out))
+        assert rc == 0
+        return out, m
