@@ -1,0 +1,147 @@
+/* se_b200.h — C ABI of libse_b200.so, the B200 (sm_100a) implementation of the frame-level
+ * speech-enhancement hot path of guokiddo1/speech_enhancement.
+ *
+ * Plain C: pointers and sizes only, no C++/torch types.  Every entry point returns 0 on success or a
+ * negative SE_E* code and never exits the process (the reference fprintf+exit(0)s on allocation
+ * failure, etsi/cpp/NoiseSup.c:983-987).  se_last_error() returns a thread-local message.
+ *
+ * There is NO CPU fallback: every compute entry point fails with SE_ENODEVICE if no CUDA device is
+ * usable.  The reference-named drop-in entry points (etsi_denoise, rfft, etsi_denoise_mapping_*, ...)
+ * are declared in se_reference_api.h and are thin adapters over the *_batch calls below.
+ *
+ * Batches are ragged: `samples` holds the utterances back to back and offsets[u]..offsets[u+1]
+ * (n_utts+1 entries, in samples) delimits utterance u.  `mem` says where ALL data pointers of the call
+ * live: SE_MEM_HOST (the library stages H2D/D2H itself) or SE_MEM_DEVICE (pointers are device
+ * pointers on the context's GPU; nothing is copied, the call is asynchronous on the context stream
+ * until se_ctx_sync()).  offsets / frame-offset arrays are always HOST arrays.
+ */
+#ifndef SE_B200_H
+#define SE_B200_H
+#include <stdint.h>
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+#define SE_OK          0
+#define SE_EINVAL     -1
+#define SE_ENODEVICE  -2   /* no CUDA device / driver: the product has no CPU path            */
+#define SE_ECUDA      -3   /* CUDA runtime error, see se_last_error()                          */
+#define SE_ENOMEM     -4
+#define SE_EUNSUPPORTED -5
+
+#define SE_MEM_HOST    0
+#define SE_MEM_DEVICE  1
+
+typedef struct se_ctx se_ctx;
+
+const char *se_last_error(void);
+int  se_device_count(void);
+/* One context per GPU (reference analogue: one "thread instance" per worker,
+ * function/.../aurora_etsi/NoiseSupExports.h:36).  Owns a stream, constant tables and scratch. */
+int  se_ctx_create(int device, se_ctx **out);
+void se_ctx_destroy(se_ctx *ctx);
+/* Launch on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL restores the own stream. */
+int  se_ctx_set_stream(se_ctx *ctx, void *cuda_stream);
+int  se_ctx_sync(se_ctx *ctx);
+/* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 24 GiB. */
+int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
+
+/* ---- kernel timing (CUDA events on the launching stream) -------------------------------------- */
+#define SE_K_NS_P8     0   /* fused NoiseSup(+CompCeps) stream kernel, 8 kHz profile  */
+#define SE_K_NS_P16    1   /* fused NoiseSup stream kernel, 16 kHz plugin profile     */
+#define SE_K_GT_FWD    2   /* gammatone forward pass (resynth pass 1)                  */
+#define SE_K_GT_BWD    3   /* gammatone reversed pass + mask weights + channel sum     */
+#define SE_K_SUBBAND   4   /* gammatone + hair cell + int16 sub-band writer            */
+#define SE_K_IBM       5   /* fused sub-band -> IRM / IBM                              */
+#define SE_K_ADDNOISE  6
+#define SE_K_COUNT     8
+int se_ctx_profiling(se_ctx *ctx, int enable);          /* record event pairs around own kernels  */
+int se_ctx_kernel_time(se_ctx *ctx, int kernel_id, double *total_ms, int64_t *launches); /* syncs */
+int se_ctx_reset_kernel_times(se_ctx *ctx);
+int64_t se_ctx_launch_count(se_ctx *ctx);               /* kernels launched by this library so far */
+
+/* ---- P8: ETSI NoiseSup (+CompCeps), replaces etsi_denoise (etsi/cpp/AdvFrontEnd.c:125-210) ------
+ * denoised : int16, same layout as samples; the first (Z+4)*80 samples of an utterance are 0 (Z =
+ *            leading all-zero 80-sample frames, etsi/cpp/ParmInterface.c:244-250) and the tail
+ *            len%80 is written as 0 (the reference leaves it untouched).            [required]
+ * ceps     : float [ceps_offsets[u] + m][14] = c1..c12,c0,logE for cepstral frame m, produced by
+ *            the CompCeps step of etsi/cpp/ParmInterface.c:274-293 (shipped commented out in the
+ *            reference; etsi/cpp/CompCeps.c:368-549).  NULL = NoiseSup only.
+ * ceps_offsets : host int64[n_utts+1] frame offsets (se_etsi_num_ceps_frames gives an upper bound).
+ * n_ceps   : int32[n_utts] frames actually produced (same memory kind as data), may be NULL.
+ * den_f32  : optional float denoised stream (before the int16 cast), may be NULL.
+ * vad_trace: optional uint8 per 80-sample call, laid out at offsets[u]/80-ish: trace_offsets[u]+call;
+ *            bit0 flagVAD, bit1 SpeechFoundVar, bit2 Spec, bit3 Mel, bit4 VADNS, bit6 frame
+ *            produced, bit7 zero-frame skipped.  trace_offsets host int64[n_utts+1], may be NULL. */
+int64_t se_etsi_num_ceps_frames(int64_t n_samples);     /* max(0, n/80 - 6)                     */
+int se_etsi_denoise_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                          int16_t *denoised, float *ceps, const int64_t *ceps_offsets, int32_t *n_ceps,
+                          float *den_f32, uint8_t *vad_trace, const int64_t *trace_offsets, int mem);
+
+/* ---- P16: plugin NoiseSup, replaces etsi_denoise_mapping_func_Wiener
+ *      (function/20141106_speech_enhancement/aurora_etsi/NoiseSup.cpp:1140-1407) ------------------
+ * samples are int16 (is_f32=0) or float (is_f32=1, the plugin's own input type).
+ * out_f32  : float denoised, same layout as samples; blocks where nothing is produced are 0.
+ * flags    : int32 [5][total_blocks] = SpeechFoundVar, Spec, Mel, VADNS, FrameCounter, block b of
+ *            utterance u at block_offsets[u]+b; entries of skipped/latency blocks are 0.
+ * gains    : float [block_offsets[u] + row][25], one row per stage-2 frame (the ".wiener" text rows,
+ *            NoiseSup.cpp:1318-1326); n_rows int32[n_utts].
+ * block_offsets : host int64[n_utts+1], block_offsets[u+1]-block_offsets[u] >= len_u/160. */
+int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int64_t *offsets, int n_utts,
+                        float *out_f32, int32_t *flags, float *gains, int32_t *n_rows,
+                        const int64_t *block_offsets, int mem);
+
+/* ---- persistent NoiseSup streams (state carried across calls, like the plugin's thread instance
+ *      reused over 64 channel files, function/.../aurora_etsi_test/aurora_etsi_test.cpp:21-141) --- */
+typedef struct se_ns_stream se_ns_stream;
+int  se_ns_stream_create(se_ctx *ctx, int profile /*8|16*/, se_ns_stream **out);
+void se_ns_stream_destroy(se_ns_stream *s);
+int  se_ns_stream_reset(se_ns_stream *s);
+/* Push n_blocks*shift float samples (HOST pointers).  P8: out receives shift floats per block, valid
+ * where produced[b]!=0 (DoNoiseSup's BOOLEAN, etsi/cpp/NoiseSup.c:1436-1439).  P16: func_Wiener
+ * semantics incl. zero-block skipping; flags is int32[5][n_blocks], gains float[n_blocks][25]. */
+int  se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out, int32_t *produced,
+                       int32_t *flags, float *gains, int32_t *n_rows);
+
+/* ---- G64: 64-channel gammatone analysis / masks / resynthesis ----------------------------------- */
+#define SE_FLAG_EXACT   1   /* evaluate the IIR recurrences with separately rounded mul/add, in the
+                               reference's order (bit-identical to its float arithmetic); default is
+                               FMA-contracted (faster, ~-120 dB relative difference)               */
+/* subbband (enhancement_extract_subband_linux/cpp/extractwav.cpp:36-97): int16 hair-cell output per
+ * channel; out holds, for utterance u, 64 rows of len_u samples starting at 64*offsets[u]. */
+int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                     int16_t *out, int flags, int mem);
+/* make_single_IBM (enhancement_extract_subband_linux/cpp/show_IBM.cpp:92-213) fused with the two
+ * subbband() calls that feed it: per (frame, channel) IRM = Sp/(Sp+Sn) and IBM = (Sn < Sp).
+ * frames_u = (len_u-320)/160+1.  irm: float[frame_offsets[u]+f][64]; ibm_bits: uint64 per frame
+ * (bit c = channel c).  Either output may be NULL.  Always evaluated in exact mode. */
+int64_t se_ibm_num_frames(int64_t n_samples);
+int se_ibm_batch(se_ctx *ctx, const int16_t *pure, const int16_t *noise, const int64_t *offsets, int n_utts,
+                 float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem);
+/* resynth (resyth_64sub_IBM/cpp/extractwav.cpp:9-132 and its _ori / 1dnn variants).
+ * mask: float[frame_offsets[u]+f][64]; frames_u = se_resynth_num_frames(len_u, mode). */
+#define SE_RESYNTH_IBM   0
+#define SE_RESYNTH_ORI   1
+#define SE_RESYNTH_1DNN  2
+int64_t se_resynth_num_frames(int64_t n_samples, int mode);
+int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                     const float *mask, const int64_t *frame_offsets, int mode, int flags,
+                     int16_t *out, int mem);
+/* addnoise (enhancement_extract_subband_linux/cpp/extractwav.cpp:6-35): noise is scaled IN PLACE. */
+int se_addnoise_batch(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy,
+                      const int64_t *offsets, int n_utts, int db, int mem);
+
+/* ---- primitives exposed for known-answer tests ---------------------------------------------------
+ * Batched rfft exactly as the reference lays it out (Re0..Re(n/2), Im(n/2-1)..Im1;
+ * etsi/cpp/rfft.c:29-30).  (n,m) in {(256,8), (512,8) [the plugin's truncated schedule, SURVEY Q1]}. */
+int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem);
+/* gammaToneFilter (extractwav.cpp:168-212) for `count` signals of length n with per-signal channel. */
+int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
+                       int count, int flags, int mem);
+/* init-time tables as the device sees them (host copies), for table parity tests */
+int se_get_table(se_ctx *ctx, const char *name, float *out, int capacity, int *count);
+
+#ifdef __cplusplus
+}
+#endif
+#endif

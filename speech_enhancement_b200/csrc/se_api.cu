@@ -1,0 +1,299 @@
+// C ABI of libse_b200.so: context, tables upload, staging and the *_batch entry points (se_b200.h).
+#include "se_internal.h"
+#include <cmath>
+#include <cstdarg>
+#include <cstdio>
+#include <cstring>
+
+namespace se {
+
+static thread_local char g_err[512] = "";
+
+void set_error(const char *fmt, ...)
+{
+    va_list ap;
+    va_start(ap, fmt);
+    vsnprintf(g_err, sizeof g_err, fmt, ap);
+    va_end(ap);
+}
+
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line)
+{
+    set_error("CUDA error %d (%s) at %s:%d: %s", (int)e, cudaGetErrorString(e), file, line, what);
+    if (e == cudaErrorNoDevice || e == cudaErrorInsufficientDriver) return SE_ENODEVICE;
+    if (e == cudaErrorMemoryAllocation) return SE_ENOMEM;
+    return SE_ECUDA;
+}
+
+template <typename T> static int upload(se_ctx *ctx, const T *h, size_t count, const T **d)
+{
+    void *p = nullptr;
+    SE_CUDA(cudaMalloc(&p, sizeof(T) * count));
+    ctx->table_allocs.push_back(p);
+    SE_CUDA(cudaMemcpy(p, h, sizeof(T) * count, cudaMemcpyHostToDevice));
+    *d = reinterpret_cast<const T *>(p);
+    return SE_OK;
+}
+
+static int upload_ns(se_ctx *ctx, const NsTables &h, NsDevTables &d, int bank_rows)
+{
+    int rc;
+    if ((rc = upload(ctx, h.sig_window.data(), h.sig_window.size(), &d.sig_window))) return rc;
+    if ((rc = upload(ctx, h.ir_window.data() + 8, 9, &d.fir_window))) return rc;
+    std::vector<float> bankT((size_t)bank_rows * 32, 0.0f);
+    int st[32] = {0}, ln[32] = {0};
+    for (int j = 0; j < kMel; j++) {
+        st[j] = h.bank_start[j];
+        ln[j] = h.bank_len[j];
+        if (h.bank_len[j] > bank_rows) { set_error("filter bank row %d longer than %d", j, bank_rows); return SE_EINVAL; }
+        for (int i = 0; i < h.bank_len[j]; i++) bankT[(size_t)i * 32 + j] = h.bank[(size_t)j * h.bank_w + i];
+    }
+    if ((rc = upload(ctx, bankT.data(), bankT.size(), &d.bankT))) return rc;
+    if ((rc = upload(ctx, st, 32, &d.bank_start))) return rc;
+    if ((rc = upload(ctx, ln, 32, &d.bank_len))) return rc;
+    std::vector<float> idctT(25 * 16, 0.0f);
+    for (int f = 0; f < kMel; f++)
+        for (int t = 0; t < 9; t++) idctT[f * 16 + t] = h.idct[t * kMel + f];
+    if ((rc = upload(ctx, idctT.data(), idctT.size(), &d.idctT))) return rc;
+    std::vector<float> tw(2 * 132, 0.0f);
+    for (int k = 0; k <= 128; k++) {
+        tw[2 * k] = (float)std::cos(6.283185307179586476925287 * k / 256.0);
+        tw[2 * k + 1] = (float)std::sin(6.283185307179586476925287 * k / 256.0);
+    }
+    if ((rc = upload(ctx, tw.data(), tw.size(), &d.tw_half))) return rc;
+    d.eps = h.eps;
+    return SE_OK;
+}
+
+static int upload_cc(se_ctx *ctx)
+{
+    const CcTables &h = ctx->h_cc;
+    CcDevTables &d = ctx->d_cc;
+    int rc;
+    float ham[200];
+    for (int i = 0; i < 100; i++) { ham[i] = h.hamming[i]; ham[199 - i] = h.hamming[i]; }   // Window(), CompCeps.c:115-125
+    if ((rc = upload(ctx, ham, 200, &d.hamming))) return rc;
+    std::vector<float> triT(32 * 32, 0.0f);
+    int st[32] = {0}, ln[32] = {0};
+    for (int j = 0; j < 23; j++) {
+        st[j] = h.start[j];
+        ln[j] = h.len[j];
+        if (h.len[j] > 32) { set_error("CompCeps triangle %d longer than 32", j); return SE_EINVAL; }
+        for (int i = 0; i < h.len[j]; i++) triT[i * 32 + j] = h.tri[j][i];
+    }
+    if ((rc = upload(ctx, triT.data(), triT.size(), &d.triT))) return rc;
+    if ((rc = upload(ctx, st, 32, &d.tri_start))) return rc;
+    if ((rc = upload(ctx, ln, 32, &d.tri_len))) return rc;
+    std::vector<float> dctT(23 * 16, 0.0f);
+    for (int j = 0; j < 23; j++)
+        for (int t = 0; t < 12; t++) dctT[j * 16 + t] = h.dct[t * 23 + j];
+    if ((rc = upload(ctx, dctT.data(), dctT.size(), &d.dctT))) return rc;
+    return SE_OK;
+}
+
+int ensure_stage(se_ctx *ctx, int slot, uint64_t bytes, void **out)
+{
+    if (bytes == 0) bytes = 16;
+    if (ctx->stage_bytes[slot] < bytes) {
+        if (ctx->d_stage[slot]) {
+            SE_CUDA(cudaStreamSynchronize(ctx->stream));
+            SE_CUDA(cudaFree(ctx->d_stage[slot]));
+            ctx->d_stage[slot] = nullptr;
+            ctx->stage_bytes[slot] = 0;
+        }
+        const uint64_t want = bytes + bytes / 8;
+        SE_CUDA(cudaMalloc(&ctx->d_stage[slot], want));
+        ctx->stage_bytes[slot] = want;
+    }
+    *out = ctx->d_stage[slot];
+    return SE_OK;
+}
+
+int ensure_scratch(se_ctx *ctx, uint64_t bytes)
+{
+    if (ctx->scratch_bytes < bytes) {
+        if (ctx->d_scratch) {
+            SE_CUDA(cudaStreamSynchronize(ctx->stream));
+            SE_CUDA(cudaFree(ctx->d_scratch));
+            ctx->d_scratch = nullptr;
+            ctx->scratch_bytes = 0;
+        }
+        SE_CUDA(cudaMalloc(&ctx->d_scratch, bytes));
+        ctx->scratch_bytes = bytes;
+    }
+    return SE_OK;
+}
+
+void prof_begin(se_ctx *ctx, int k)
+{
+    if (!ctx->profiling) return;
+    se_ctx::Ev e;
+    e.k = k;
+    cudaEventCreate(&e.a);
+    cudaEventCreate(&e.b);
+    cudaEventRecord(e.a, ctx->stream);
+    ctx->pending.push_back(e);
+}
+
+void prof_end(se_ctx *ctx, int k)
+{
+    ctx->launches++;
+    (void)k;
+    if (!ctx->profiling) return;
+    cudaEventRecord(ctx->pending.back().b, ctx->stream);
+}
+
+static int drain_events(se_ctx *ctx)
+{
+    for (auto &e : ctx->pending) {
+        float ms = 0.0f;
+        SE_CUDA(cudaEventSynchronize(e.b));
+        SE_CUDA(cudaEventElapsedTime(&ms, e.a, e.b));
+        ctx->k_ms[e.k] += ms;
+        ctx->k_launches[e.k]++;
+        cudaEventDestroy(e.a);
+        cudaEventDestroy(e.b);
+    }
+    ctx->pending.clear();
+    return SE_OK;
+}
+
+}  // namespace se
+
+using namespace se;
+
+extern "C" {
+
+const char *se_last_error(void) { return g_err; }
+
+int se_device_count(void)
+{
+    int n = 0;
+    if (cudaGetDeviceCount(&n) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return n;
+}
+
+int se_ctx_create(int device, se_ctx **out)
+{
+    if (!out) return SE_EINVAL;
+    *out = nullptr;
+    int n = 0;
+    cudaError_t e = cudaGetDeviceCount(&n);
+    if (e != cudaSuccess || n <= 0) {
+        cudaGetLastError();
+        set_error("no CUDA device available (libse_b200 has no CPU path): %s", cudaGetErrorString(e));
+        return SE_ENODEVICE;
+    }
+    if (device < 0 || device >= n) { set_error("device %d out of range (0..%d)", device, n - 1); return SE_EINVAL; }
+    SE_CUDA(cudaSetDevice(device));
+    se_ctx *ctx = new se_ctx();
+    ctx->device = device;
+    ctx->own_stream = ctx->stream = nullptr;
+    ctx->d_work_counter = nullptr;
+    ctx->d_scratch = nullptr;
+    ctx->scratch_bytes = 0;
+    ctx->scratch_limit = 24ull << 30;
+    std::memset(ctx->d_stage, 0, sizeof ctx->d_stage);
+    std::memset(ctx->stage_bytes, 0, sizeof ctx->stage_bytes);
+    ctx->profiling = 0;
+    std::memset(ctx->k_ms, 0, sizeof ctx->k_ms);
+    std::memset(ctx->k_launches, 0, sizeof ctx->k_launches);
+    ctx->launches = 0;
+    cudaDeviceProp prop;
+    SE_CUDA(cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    SE_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    ctx->stream = ctx->own_stream;
+    SE_CUDA(cudaMalloc((void **)&ctx->d_work_counter, sizeof(int)));
+    build_ns_tables_p8(ctx->h_p8);
+    build_ns_tables_p16(ctx->h_p16);
+    build_cc_tables(ctx->h_cc);
+    build_gt_tables(ctx->h_gt);
+    int rc;
+    if ((rc = upload_ns(ctx, ctx->h_p8, ctx->d_p8, 16)) || (rc = upload_ns(ctx, ctx->h_p16, ctx->d_p16, 128)) ||
+        (rc = upload_cc(ctx)) || (rc = upload_g64_tables(ctx))) {
+        se_ctx_destroy(ctx);
+        return rc;
+    }
+    *out = ctx;
+    return SE_OK;
+}
+
+void se_ctx_destroy(se_ctx *ctx)
+{
+    if (!ctx) return;
+    cudaSetDevice(ctx->device);
+    cudaDeviceSynchronize();
+    for (void *p : ctx->table_allocs) cudaFree(p);
+    for (int i = 0; i < 16; i++)
+        if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
+    if (ctx->d_scratch) cudaFree(ctx->d_scratch);
+    if (ctx->d_work_counter) cudaFree(ctx->d_work_counter);
+    for (auto &e : ctx->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
+    if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    delete ctx;
+}
+
+int se_ctx_set_stream(se_ctx *ctx, void *cuda_stream)
+{
+    if (!ctx) return SE_EINVAL;
+    ctx->stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+    return SE_OK;
+}
+
+int se_ctx_sync(se_ctx *ctx)
+{
+    if (!ctx) return SE_EINVAL;
+    SE_CUDA(cudaSetDevice(ctx->device));
+    SE_CUDA(cudaStreamSynchronize(ctx->stream));
+    return SE_OK;
+}
+
+int se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes)
+{
+    if (!ctx || bytes < (1ull << 20)) return SE_EINVAL;
+    ctx->scratch_limit = bytes;
+    return SE_OK;
+}
+
+int se_ctx_profiling(se_ctx *ctx, int enable)
+{
+    if (!ctx) return SE_EINVAL;
+    ctx->profiling = enable ? 1 : 0;
+    return SE_OK;
+}
+
+int se_ctx_kernel_time(se_ctx *ctx, int kernel_id, double *total_ms, int64_t *launches)
+{
+    if (!ctx || kernel_id < 0 || kernel_id >= SE_K_COUNT) return SE_EINVAL;
+    int rc = drain_events(ctx);
+    if (rc) return rc;
+    if (total_ms) *total_ms = ctx->k_ms[kernel_id];
+    if (launches) *launches = ctx->k_launches[kernel_id];
+    return SE_OK;
+}
+
+int se_ctx_reset_kernel_times(se_ctx *ctx)
+{
+    if (!ctx) return SE_EINVAL;
+    int rc = drain_events(ctx);
+    if (rc) return rc;
+    std::memset(ctx->k_ms, 0, sizeof ctx->k_ms);
+    std::memset(ctx->k_launches, 0, sizeof ctx->k_launches);
+    return SE_OK;
+}
+
+int64_t se_ctx_launch_count(se_ctx *ctx) { return ctx ? ctx->launches : 0; }
+
+int64_t se_etsi_num_ceps_frames(int64_t n) { const int64_t c = n / 80 - 6; return c > 0 ? c : 0; }
+int64_t se_ibm_num_frames(int64_t n) { return n >= 320 ? (n - 320) / 160 + 1 : 0; }
+int64_t se_resynth_num_frames(int64_t n, int mode)
+{
+    if (mode == SE_RESYNTH_1DNN) return n / 160;
+    const int64_t f = (n - 320) / 160 + 1;   // C integer division truncates toward zero (extractwav.cpp:67)
+    return f > 0 ? f : 0;
+}
+
+}  // extern "C"
+
+#include "se_api_batch.cuh"

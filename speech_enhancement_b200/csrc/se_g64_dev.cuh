@@ -1,0 +1,82 @@
+// Device building blocks of the 64-channel gammatone path: one IIR step of gammaToneFilter and one
+// step of the Meddis hair cell, written so that the EXACT variants round every product and sum
+// separately, in the reference's order (bit-identical to its float arithmetic), while the fast
+// variants let the compiler contract to FMA.
+#pragma once
+#include <cuda_runtime.h>
+
+namespace se {
+
+struct GtCoef { float f1, f2, gain, mid; };
+struct GtState { float p0, p1, p2, p3, q0, q1, q2, q3; };
+
+__device__ __forceinline__ void gt_reset(GtState &s) { s.p0 = s.p1 = s.p2 = s.p3 = s.q0 = s.q1 = s.q2 = s.q3 = 0.0f; }
+
+// gammaToneFilter inner loop, resyth_64sub_IBM/cpp/extractwav.cpp:191-211.
+// Returns output[n] = p[3]*gain BEFORE the state update (one-sample delay).
+template <bool EXACT> __device__ __forceinline__ float gt_step(GtState &s, const GtCoef &c, float in)
+{
+    float out, x0, x1, x2, x3, y0, y1, y2, y3;
+    if (EXACT) {
+        out = __fmul_rn(s.p3, c.gain);
+        x0 = __fsub_rn(__fmul_rn(c.f1, s.p0), __fmul_rn(c.f2, s.q0));
+        y0 = __fadd_rn(__fmul_rn(c.f2, s.p0), __fmul_rn(c.f1, s.q0));
+        x1 = __fsub_rn(__fmul_rn(c.f1, s.p1), __fmul_rn(c.f2, s.q1));
+        y1 = __fadd_rn(__fmul_rn(c.f2, s.p1), __fmul_rn(c.f1, s.q1));
+        x2 = __fsub_rn(__fmul_rn(c.f1, s.p2), __fmul_rn(c.f2, s.q2));
+        y2 = __fadd_rn(__fmul_rn(c.f2, s.p2), __fmul_rn(c.f1, s.q2));
+        x3 = __fsub_rn(__fmul_rn(c.f1, s.p3), __fmul_rn(c.f2, s.q3));
+        y3 = __fadd_rn(__fmul_rn(c.f2, s.p3), __fmul_rn(c.f1, s.q3));
+        s.p0 = __fadd_rn(__fmul_rn(in, c.f1), x0);
+        s.q0 = __fadd_rn(__fmul_rn(in, c.f2), y0);
+        s.p1 = __fadd_rn(s.p0, x1);
+        s.q1 = __fadd_rn(s.q0, y1);
+        s.p2 = __fadd_rn(__fadd_rn(s.p1, x1), x2);
+        s.q2 = __fadd_rn(__fadd_rn(s.q1, y1), y2);
+        s.p3 = __fadd_rn(__fadd_rn(__fadd_rn(s.p2, x1), __fmul_rn(2.0f, x2)), x3);
+        s.q3 = __fadd_rn(__fadd_rn(__fadd_rn(s.q2, y1), __fmul_rn(2.0f, y2)), y3);
+    } else {
+        out = s.p3 * c.gain;
+        x0 = c.f1 * s.p0 - c.f2 * s.q0; y0 = c.f2 * s.p0 + c.f1 * s.q0;
+        x1 = c.f1 * s.p1 - c.f2 * s.q1; y1 = c.f2 * s.p1 + c.f1 * s.q1;
+        x2 = c.f1 * s.p2 - c.f2 * s.q2; y2 = c.f2 * s.p2 + c.f1 * s.q2;
+        x3 = c.f1 * s.p3 - c.f2 * s.q3; y3 = c.f2 * s.p3 + c.f1 * s.q3;
+        s.p0 = in * c.f1 + x0;
+        s.q0 = in * c.f2 + y0;
+        s.p1 = s.p0 + x1;
+        s.q1 = s.q0 + y1;
+        s.p2 = s.p1 + x1 + x2;
+        s.q2 = s.q1 + y1 + y2;
+        s.p3 = s.p2 + x1 + 2.0f * x2 + x3;
+        s.q3 = s.q2 + y1 + 2.0f * y2 + y3;
+    }
+    return out;
+}
+
+// hairCell, resyth_64sub_IBM/cpp/extractwav.cpp:213-258.  hc[] = {ymdt,xdt,ydt,lplusrdt,rdt,gdt,hdt,c0,q0,w0}.
+struct HcState { float c, q, w; };
+__device__ __forceinline__ void hc_reset(HcState &s, const float *hc) { s.c = hc[7]; s.q = hc[8]; s.w = hc[9]; }
+
+__device__ __forceinline__ float hc_step(HcState &s, const float *hc, float in)
+{
+    // kt is evaluated in double in the reference (MED_A, MED_B are double literals)
+    const double t = (double)in + 3.0;
+    const float kt = (t > 0.0) ? (float)((double)hc[5] * t / (t + 300.0)) : 0.0f;
+    const float replenish = (s.q < 1.0f) ? __fsub_rn(hc[0], __fmul_rn(hc[2], s.q)) : 0.0f;
+    const float eject = __fmul_rn(kt, s.q);
+    const float loss = __fmul_rn(hc[3], s.c);
+    const float reuptake = __fmul_rn(hc[4], s.c);
+    const float reprocess = __fmul_rn(hc[1], s.w);
+    s.q = __fadd_rn(__fsub_rn(__fadd_rn(s.q, replenish), eject), reprocess);
+    if (s.q < 0.0f) s.q = 0.0f;
+    s.c = __fsub_rn(__fadd_rn(s.c, eject), loss);
+    if (s.c < 0.0f) s.c = 0.0f;
+    s.w = __fsub_rn(__fadd_rn(s.w, reuptake), reprocess);
+    if (s.w < 0.0f) s.w = 0.0f;
+    return __fmul_rn(hc[6], s.c);
+}
+
+// (short) of a float as x86 does it: cvttss2si to int32, keep the low 16 bits.
+__device__ __forceinline__ short cast_i16(float v) { return (short)__float2int_rz(v); }
+
+}  // namespace se

@@ -1,0 +1,158 @@
+// Internal declarations shared by the .cu translation units of libse_b200.so.
+#pragma once
+#include <cuda_runtime.h>
+#include <stdint.h>
+#include <string>
+#include <vector>
+#include "../../include/se_b200.h"
+#include "se_tables.h"
+
+namespace se {
+
+void set_error(const char *fmt, ...);
+int cuda_fail(cudaError_t e, const char *what, const char *file, int line);
+
+#define SE_CUDA(call)                                                              \
+    do {                                                                           \
+        cudaError_t e__ = (call);                                                  \
+        if (e__ != cudaSuccess) return ::se::cuda_fail(e__, #call, __FILE__, __LINE__); \
+    } while (0)
+
+// ---------------------------------------------------------------------------------------------
+// Device-resident constant tables of one NoiseSup profile (global memory; each CTA stages what it
+// needs into shared memory once).
+// ---------------------------------------------------------------------------------------------
+struct NsDevTables {
+    const float *sig_window;   // [frame]
+    const float *fir_window;   // [9]  : ir_window[8..16]  (DoFilterWindowing uses the upper half only)
+    const float *bankT;        // P8: [BANK_MAXLEN][32] transposed, zero padded; P16: [128][32]
+    const int *bank_start;     // [32]
+    const int *bank_len;       // [32]
+    const float *idctT;        // [25][16] : idctT[f*16+t] = idct[t][f], t<9
+    const float *tw_half;      // [129] float2 : exp(-2 pi i k / 256), k=0..128 (real-FFT split twiddles)
+    float eps;
+};
+
+struct CcDevTables {
+    const float *hamming;      // [200] full symmetric window
+    const float *triT;         // [TRI_MAXLEN][32]
+    const int *tri_start;      // [32]
+    const int *tri_len;        // [32]
+    const float *dctT;         // [23][16] : dctT[j*16+t] = dct[t][j], t<12
+};
+
+// Per-stream NoiseSup state kept in global memory between launches (persistent streams) —
+// the GPU image of NoiseSupStructX.nsVar (etsi/cpp/NoiseSup.c:117-128).
+constexpr int kNsMaxSpec = 129;
+constexpr int kNsMaxRing = 640;
+struct NsState {
+    int nb_in1, nb_in2, nb_out2;      // BUFFERS counters
+    int nb_frame0, nb_frame1;         // vadNS.nbFrame[2]
+    int flag_vad, hang_over, nb_speech;
+    int onset;                        // FEParamsX.NonZeroFrameOnset (P8)
+    int n_ceps;                       // cepstral frames emitted so far (P8)
+    int n_rows;                       // gain rows emitted so far (P16)
+    int pad0;
+    float mean_en, dc_x, dc_y;
+    float den_en0, den_en1, den_en2, low_snr, alfa_gf;
+    float fd_mel_mean, fd_var_mean, fd_acc_test, fd_spec_mean, fd_mel_val0, fd_mel_val1, fd_spec_val, fd_in_vadq;
+    float noise1[kNsMaxSpec], den1[kNsMaxSpec], prev_psd1[kNsMaxSpec];
+    float noise2[kNsMaxSpec], den2[kNsMaxSpec], prev_psd2[kNsMaxSpec];
+    float ring1[kNsMaxRing], ring2[kNsMaxRing], ring3[kNsMaxRing];
+};
+
+// Arguments of one fused NoiseSup launch (one entry per utterance is derived from offsets).
+struct NsLaunch {
+    const void *samples;         // int16 or float
+    int is_f32;
+    const int64_t *offsets;      // device copy, n_utts+1
+    int n_utts;
+    // P8 outputs
+    int16_t *den_i16;
+    float *den_f32;
+    float *ceps;
+    const int64_t *ceps_offsets; // device
+    int32_t *n_ceps;
+    uint8_t *vad_trace;
+    const int64_t *trace_offsets;
+    // P16 outputs
+    float *out_f32;
+    int32_t *flags;              // [5][total_blocks]
+    int64_t total_blocks;
+    float *gains;
+    int32_t *n_rows;
+    const int64_t *block_offsets;
+    // persistent streams (optional): state[u] loaded at start and stored at the end
+    NsState *state;
+    int load_state;
+    int32_t *produced;           // optional per-block bitmask: 1 = shift output, 2 = stage 0 ran, 4 = skipped
+    int zero_check;              // 0 none (DoNoiseSup), 1 leading frames only (DoAdvProcess), 2 anywhere (func_Wiener)
+    float *spec_trace;           // optional debug [total_blocks][6][spec]
+    // work queue
+    int *work_counter;           // device int, zeroed before launch
+};
+
+struct GtDevTables {
+    float f1[kGtChannels], f2[kGtChannels], gain[kGtChannels], mid[kGtChannels];
+    float hc[16];
+};
+
+}  // namespace se
+
+struct se_ctx {
+    int device;
+    int sm_count;
+    cudaStream_t own_stream, stream;
+    // tables
+    se::NsTables h_p8, h_p16;
+    se::CcTables h_cc;
+    se::GtTables h_gt;
+    se::NsDevTables d_p8, d_p16;
+    se::CcDevTables d_cc;
+    std::vector<void *> table_allocs;
+    // scratch
+    int *d_work_counter;
+    void *d_scratch;
+    uint64_t scratch_bytes, scratch_limit;
+    // staging for host-memory calls
+    void *d_stage[16];
+    uint64_t stage_bytes[16];
+    // profiling
+    int profiling;
+    struct Ev { cudaEvent_t a, b; int k; };
+    std::vector<Ev> pending;
+    double k_ms[SE_K_COUNT];
+    int64_t k_launches[SE_K_COUNT];
+    int64_t launches;
+};
+
+namespace se {
+
+// host helpers (se_api.cu)
+int ensure_stage(se_ctx *ctx, int slot, uint64_t bytes, void **out);
+int ensure_scratch(se_ctx *ctx, uint64_t bytes);
+void prof_begin(se_ctx *ctx, int k);
+void prof_end(se_ctx *ctx, int k);
+
+// kernel launchers
+int launch_ns_p8(se_ctx *ctx, const NsLaunch &a);
+int launch_ns_p16(se_ctx *ctx, const NsLaunch &a);
+int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count);
+
+struct G64Launch {
+    const int16_t *samples, *samples2;   // samples2: noise (IBM kernel)
+    const int64_t *offsets;              // device
+    int utt_begin, utt_count;
+    int flags;
+};
+int launch_subband(se_ctx *ctx, const G64Launch &a, int16_t *out);
+int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, const int64_t *frame_offsets);
+int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, const float *mask,
+                   const int64_t *frame_offsets, int mode, int16_t *out);
+int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n, int count,
+                     int flags);
+int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy, const int64_t *offsets,
+                    int n_utts, int db);
+int upload_g64_tables(se_ctx *ctx);
+
+}  // namespace se

@@ -1,0 +1,243 @@
+// Fused two-stage Wiener-filter noise suppression (+ CompCeps), one warp per utterance stream.
+//
+// Replaces, for a whole ragged batch in ONE launch:
+//   P8  : etsi_denoise -> DoAdvProcess -> DoNoiseSup (+ DoCompCeps)
+//         (etsi/cpp/AdvFrontEnd.c:125, ParmInterface.c:208, NoiseSup.c:1061, CompCeps.c:368)
+//   P16 : etsi_denoise_mapping_func_Wiener (function/.../aurora_etsi/NoiseSup.cpp:1140)
+//
+// Mapping.  The per-frame recursion (noise PSD, decision-directed gain, VAD, gain factorisation) is
+// strictly serial in time, so parallelism comes from utterances: a persistent grid of warps pulls
+// utterance indices from an atomic queue.  Inside a warp: lane l owns PSD bins {l, l+32, ...} in
+// registers (noise / denoised / previous-PSD state for both stages), the FFT is an in-register
+// shuffle FFT (se_warp_fft.cuh), the 4-block sample history of both stages lives in per-warp shared
+// memory rings, filter banks / IDCT / windows are CTA-shared tables in shared memory.  HBM traffic is
+// exactly the algorithmic minimum: each input sample is read once, each output written once.
+#include "se_internal.h"
+#include "se_warp_fft.cuh"
+
+namespace se {
+
+// ------------------------------------------------------------------------------------------------
+// profiles
+// ------------------------------------------------------------------------------------------------
+template <int PROF> struct Prof;
+template <> struct Prof<8> {      // etsi/cpp/NoiseSup.h:28-79
+    static constexpr int S = 80, FL = 200, SPEC = 65, ANA = 60, RB = 320;
+    static constexpr int NB = 3;        // PSD bins per lane (ceil(65/32))
+    static constexpr int CH = 3;        // contiguous output samples per lane (ceil(80/32))
+    static constexpr int NR = 3;        // strided input samples per lane
+    static constexpr int BANKROWS = 16; // max mel triangle length (checked on the host)
+    static constexpr int QVAR = 64;     // NS_FFT_LENGTH/4
+    static constexpr bool CEPS = true;
+};
+template <> struct Prof<16> {     // function/.../aurora_etsi/NoiseSup.h:22-72
+    static constexpr int S = 160, FL = 480, SPEC = 129, ANA = 80, RB = 640;
+    static constexpr int NB = 5, CH = 5, NR = 5;
+    static constexpr int BANKROWS = 128;
+    static constexpr int QVAR = 128;
+    static constexpr bool CEPS = false;
+};
+
+constexpr int kTriRows = 32;     // max CompCeps triangle length (checked on the host)
+
+template <int PROF> struct __align__(16) WarpMem {
+    using P = Prof<PROF>;
+    float ring1[P::RB];
+    float ring2[P::RB];
+    float ring3[P::CEPS ? P::RB : 4];
+    float2 Z[132];
+    float2 Z2[PROF == 16 ? 132 : 2];
+    float raw[PROF == 16 ? 260 : 4];
+    float W[132];
+    float melw[32];
+    float fir[16];
+};
+
+template <int PROF> struct __align__(16) BlockMem {
+    using P = Prof<PROF>;
+    float win[P::FL];
+    float2 twh[132];
+    float bankT[P::BANKROWS * 32];
+    int bank_start[32], bank_len[32];
+    float idctT[25 * 16];
+    float firwin[12];
+    // CompCeps tables (P8 only)
+    float ham[P::CEPS ? 200 : 4];
+    float triT[P::CEPS ? kTriRows * 32 : 4];
+    int tri_start[32], tri_len[32];
+    float dctT[P::CEPS ? 23 * 16 : 4];
+};
+
+// Scalar (warp-uniform) part of the stream state: the GPU image of VAD_DATA_NS, VAD_DATA_FD,
+// GAIN_FACT, DC_FILTER and the BUFFERS counters (etsi/cpp/NoiseSup.c:49-100).
+struct Scal {
+    int nb_in1, nb_in2, nb_out2, nb_frame0, nb_frame1;
+    int flag_vad, hang_over, nb_speech, onset, n_ceps, n_rows;
+    float mean_en, dc_x, dc_y, den_en0, den_en1, den_en2, low_snr, alfa_gf;
+    float fd_mel_mean, fd_var_mean, fd_acc_test, fd_spec_mean, fd_mel_val0, fd_mel_val1, fd_spec_val, fd_in_vadq;
+};
+
+__device__ __forceinline__ void scal_init(Scal &s)
+{
+    // DoNoiseSupInit, etsi/cpp/NoiseSup.c:895-943
+    s.nb_in1 = s.nb_in2 = s.nb_out2 = s.nb_frame0 = s.nb_frame1 = 0;
+    s.flag_vad = s.hang_over = s.nb_speech = s.onset = s.n_ceps = s.n_rows = 0;
+    s.mean_en = s.dc_x = s.dc_y = s.den_en0 = s.den_en1 = s.den_en2 = s.low_snr = 0.0f;
+    s.alfa_gf = 0.8f;
+    s.fd_mel_mean = s.fd_var_mean = s.fd_acc_test = s.fd_spec_mean = 0.0f;
+    s.fd_mel_val0 = s.fd_mel_val1 = s.fd_spec_val = s.fd_in_vadq = 0.0f;
+}
+
+// ------------------------------------------------------------------------------------------------
+// warp-uniform scalar recursions (every lane evaluates the same values; double where the reference
+// promotes to double)
+// ------------------------------------------------------------------------------------------------
+
+// VAD for noise suppression, etsi/cpp/NoiseSup.c:359-430.  frame_sq = sum of the newest-shift squares.
+__device__ __forceinline__ void vad_ns(Scal &s, int fstage, float frame_sq)
+{
+    int nbf = fstage ? s.nb_frame1 : s.nb_frame0;
+    if (nbf < 2147483647) nbf++;
+    if (fstage) { s.nb_frame1 = nbf; return; }
+    s.nb_frame0 = nbf;
+    float lambda = (nbf < 10) ? (1.0f - 1.0f / (float)nbf) : 0.97f;
+    float frame_en = 64.0f + frame_sq;
+    frame_en = (float)(0.5 + (log((double)frame_en / 64.0) / log(2.0)) * 16.0);
+    float mean_en = s.mean_en;
+    if (((frame_en - mean_en) < 20.0f) || (nbf < 10)) {
+        // separately rounded mul/add (no FMA contraction): this recursion feeds the VAD decision
+        if ((frame_en < mean_en) || (nbf < 10))
+            mean_en = __fadd_rn(mean_en, __fmul_rn(1.0f - lambda, __fsub_rn(frame_en, mean_en)));
+        else
+            mean_en = __fadd_rn(mean_en, __fmul_rn(1.0f - 0.99f, __fsub_rn(frame_en, mean_en)));
+        if (mean_en < 80.0f) mean_en = 80.0f;
+    }
+    if (nbf > 4) {
+        if ((frame_en - mean_en) > 15.0f) {
+            s.flag_vad = 1;
+            s.nb_speech++;
+        } else {
+            if (s.nb_speech > 4) s.hang_over = 15;
+            s.nb_speech = 0;
+            if (s.hang_over != 0) { s.hang_over--; s.flag_vad = 1; }
+            else s.flag_vad = 0;
+        }
+    }
+    s.mean_en = mean_en;
+}
+
+// SpeechQVar / SpeechQSpec / SpeechQMel, etsi/cpp/NoiseSup.c:686-839
+__device__ __forceinline__ int q_var(Scal &s, float mean, float var, int ssize)
+{
+    const short fc = (short)s.nb_frame0;
+    const float sv = __fsub_rn(var / (float)ssize, __fmul_rn(mean, mean) / (float)(ssize * ssize));
+    if (fc < 15) s.fd_var_mean = (s.fd_var_mean > sv) ? s.fd_var_mean : sv;
+    if ((double)sv < (double)s.fd_var_mean * 1.5 && (double)sv > (double)s.fd_var_mean * 0.85)
+        s.fd_var_mean = (float)((double)s.fd_var_mean * 0.8 + (double)sv * 0.2);
+    if ((double)sv <= (double)s.fd_var_mean * 0.25)
+        s.fd_var_mean = (float)((double)s.fd_var_mean * 0.97 + (double)sv * 0.03);
+    return ((double)sv > (double)s.fd_var_mean * 1.65) ? 1 : 0;
+}
+
+__device__ __forceinline__ int q_spec(Scal &s)
+{
+    const short fc = (short)s.nb_frame0;
+    const float v = s.fd_spec_val;
+    if (fc == 1) s.fd_spec_mean = v;
+    if (fc < 15) {
+        s.fd_acc_test = (float)(1.1 * (double)__fadd_rn(__fmul_rn(s.fd_acc_test, (float)(fc - 1)), v) / (double)(float)(fc));
+        const float acc = v / s.fd_acc_test;
+        if ((double)acc > 2.5) s.fd_in_vadq = 1.0f;
+        if (s.fd_in_vadq == 0.0f) s.fd_spec_mean = (s.fd_spec_mean > v) ? s.fd_spec_mean : v;
+    }
+    if ((double)v < (double)s.fd_spec_mean * 1.5 && (double)v > (double)s.fd_spec_mean * 0.75)
+        s.fd_spec_mean = (float)((double)s.fd_spec_mean * 0.8 + (double)v * 0.2);
+    if ((double)v <= (double)s.fd_spec_mean * 0.5)
+        s.fd_spec_mean = (float)((double)s.fd_spec_mean * 0.97 + (double)v * 0.03);
+    return ((double)v > (double)s.fd_spec_mean * 1.65) ? 1 : 0;
+}
+
+__device__ __forceinline__ int q_mel(Scal &s)
+{
+    const short fc = (short)s.nb_frame0;
+    const float sm = (float)(0.75 * (double)s.fd_mel_val1 + 0.25 * (double)s.fd_mel_val0);
+    s.fd_mel_val0 = s.fd_mel_val1;
+    if (fc < 15) s.fd_mel_mean = (s.fd_mel_mean > sm) ? s.fd_mel_mean : sm;
+    if ((double)sm < (double)s.fd_mel_mean * 1.5 && (double)sm > (double)s.fd_mel_mean * 0.75)
+        s.fd_mel_mean = (float)((double)s.fd_mel_mean * 0.8 + (double)sm * 0.2);
+    if ((double)sm <= (double)s.fd_mel_mean * 0.5)
+        s.fd_mel_mean = (float)((double)s.fd_mel_mean * 0.97 + (double)sm * 0.03);
+    return ((double)sm > (double)s.fd_mel_mean * 3.25) ? 1 : 0;
+}
+
+// Stage-2 part of DoGainFact, etsi/cpp/NoiseSup.c:600-641 (DoGainFact_IBM, NoiseSup.cpp:653-697).
+// The plugin is C++, where log10(float) is the float overload; the ETSI file is C (double log10).
+template <int PROF> __device__ __forceinline__ void gain_fact_stage2(Scal &s, float noise_en)
+{
+    float aver = (s.den_en0 * s.den_en1 * s.den_en2) / (noise_en * noise_en * noise_en);
+    if ((double)aver > 0.00001) {
+        if (PROF == 16) aver = (float)((double)(20.0f * (float)log10((double)aver)) / 3.0);
+        else aver = (float)((20.0 * log10((double)aver)) / 3.0);
+    } else {
+        aver = (float)(-100.0 / 3.0);
+    }
+    if ((((double)aver - (double)s.low_snr) < 10.0) || (s.nb_frame1 < 10)) {
+        float lambda;
+        if (s.nb_frame1 < 10) lambda = (float)(1.0 - 1.0 / (double)(float)s.nb_frame1);
+        else if (aver < s.low_snr) lambda = (float)0.95;
+        else lambda = (float)0.99;
+        s.low_snr = (float)((double)s.low_snr + (1.0 - (double)lambda) * (double)(aver - s.low_snr));
+    }
+    if (s.den_en2 > 100.0f) {
+        if ((double)aver < ((double)s.low_snr + 3.5)) {
+            s.alfa_gf = (float)((double)s.alfa_gf + 0.15);
+            if ((double)s.alfa_gf > 0.8) s.alfa_gf = (float)0.8;
+        } else {
+            s.alfa_gf = (float)((double)s.alfa_gf - 0.3);
+            if ((double)s.alfa_gf < 0.1) s.alfa_gf = (float)0.1;
+        }
+    }
+}
+
+// Decision-directed Wiener gain of one bin, etsi/cpp/NoiseSup.c:449-563 (FilterCalc).
+// psd: this frame's PSD bin, psd_mean: 2-frame mean.  Returns W; updates noise/den.
+template <int FSTAGE>
+__device__ __forceinline__ float filter_calc_bin(float psd, float psd_mean, float &noise, float &den, int nbf,
+                                                 int flag_vad, float eps)
+{
+    if (FSTAGE == 1) {
+        float n2 = noise * noise;
+        if (nbf < 11) {
+            const float lambda = 1.0f - 1.0f / (float)nbf;
+            n2 = lambda * n2 + (1.0f - lambda) * psd_mean;
+        } else {
+            const float up = (float)(0.9 + 0.1 * (double)(psd_mean / (psd_mean + n2)) *
+                                               (1.0 + 1.0 / (1.0 + 0.1 * (double)(psd_mean / n2))));
+            n2 *= up;
+        }
+        noise = sqrtf(n2);
+        if (noise < eps) noise = eps;
+    }
+    const float nsig = sqrtf(psd);
+    const float pm = sqrtf(psd_mean);
+    if (FSTAGE == 0) {
+        const float lambda = (nbf < 100) ? (1.0f - 1.0f / (float)nbf) : 0.99f;
+        if (flag_vad == 0) {
+            noise = lambda * noise + (1.0f - lambda) * pm;
+            if (noise < eps) noise = eps;
+        }
+    }
+    const float post = (pm / noise) - 1.0f;
+    float prio = 0.98f * (den / noise) + (1.0f - 0.98f) * ((0.0f > post) ? 0.0f : post);
+    float W = prio / (1.0f + prio);
+    prio = W * pm / noise;
+    prio = (prio > 0.079432823f) ? prio : 0.079432823f;
+    W = prio / (1.0f + prio);
+    den = W * nsig;
+    return W;
+}
+
+}  // namespace se
+
+#include "se_ns_stage.cuh"
+#include "se_ns_kernel.cuh"

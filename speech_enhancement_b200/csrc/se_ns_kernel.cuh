@@ -1,0 +1,384 @@
+// Persistent fused NoiseSup kernel + host launchers.  Included by se_ns.cu.
+#pragma once
+
+namespace se {
+
+constexpr int kNsWarpsPerBlock = 8;
+
+template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<PROF> &bm, const NsDevTables &tb,
+                                                                     const CcDevTables &cc)
+{
+    using P = Prof<PROF>;
+    const int tid = threadIdx.x, nt = blockDim.x;
+    for (int i = tid; i < P::FL; i += nt) bm.win[i] = tb.sig_window[i];
+    for (int i = tid; i < 129; i += nt) bm.twh[i] = reinterpret_cast<const float2 *>(tb.tw_half)[i];
+    for (int i = tid; i < P::BANKROWS * 32; i += nt) bm.bankT[i] = tb.bankT[i];
+    for (int i = tid; i < 32; i += nt) { bm.bank_start[i] = tb.bank_start[i]; bm.bank_len[i] = tb.bank_len[i]; }
+    for (int i = tid; i < 25 * 16; i += nt) bm.idctT[i] = tb.idctT[i];
+    for (int i = tid; i < 9; i += nt) bm.firwin[i] = tb.fir_window[i];
+    if constexpr (P::CEPS) {
+        for (int i = tid; i < 200; i += nt) bm.ham[i] = cc.hamming[i];
+        for (int i = tid; i < kTriRows * 32; i += nt) bm.triT[i] = cc.triT[i];
+        for (int i = tid; i < 32; i += nt) { bm.tri_start[i] = cc.tri_start[i]; bm.tri_len[i] = cc.tri_len[i]; }
+        for (int i = tid; i < 23 * 16; i += nt) bm.dctT[i] = cc.dctT[i];
+    }
+}
+
+template <typename T> __device__ __forceinline__ float to_f32(T v) { return (float)v; }
+
+template <int PROF, typename IN_T>
+__global__ void __launch_bounds__(kNsWarpsPerBlock * 32)
+ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
+{
+    using P = Prof<PROF>;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BlockMem<PROF> &bm = *reinterpret_cast<BlockMem<PROF> *>(smem_raw);
+    WarpMem<PROF> *wms = reinterpret_cast<WarpMem<PROF> *>(smem_raw + ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpMem<PROF> &wm = wms[warp];
+
+    load_block_tables<PROF>(bm, tb, cc);
+    __syncthreads();
+
+    FftTw tw;
+    fft_tw_init(tw, lane);
+    const float eps = tb.eps;
+    const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
+
+    for (;;) {
+        int u = 0;
+        if (lane == 0) u = atomicAdd(a.work_counter, 1);
+        u = __shfl_sync(0xffffffffu, u, 0);
+        if (u >= a.n_utts) break;
+
+        const int64_t off0 = a.offsets[u], off1 = a.offsets[u + 1];
+        const int64_t n = off1 - off0;
+        const int nblk = (int)(n / P::S);
+        const IN_T *in = all + off0;
+
+        // ---- stream state -------------------------------------------------------------------
+        Scal s;
+        float noise1[P::NB], den1[P::NB], prev1[P::NB], noise2[P::NB], den2[P::NB], prev2[P::NB];
+        NsState *st = a.state ? a.state + u : nullptr;
+        if (st && a.load_state) {
+            s.nb_in1 = st->nb_in1; s.nb_in2 = st->nb_in2; s.nb_out2 = st->nb_out2;
+            s.nb_frame0 = st->nb_frame0; s.nb_frame1 = st->nb_frame1;
+            s.flag_vad = st->flag_vad; s.hang_over = st->hang_over; s.nb_speech = st->nb_speech;
+            s.onset = st->onset; s.n_ceps = st->n_ceps; s.n_rows = st->n_rows;
+            s.mean_en = st->mean_en; s.dc_x = st->dc_x; s.dc_y = st->dc_y;
+            s.den_en0 = st->den_en0; s.den_en1 = st->den_en1; s.den_en2 = st->den_en2;
+            s.low_snr = st->low_snr; s.alfa_gf = st->alfa_gf;
+            s.fd_mel_mean = st->fd_mel_mean; s.fd_var_mean = st->fd_var_mean; s.fd_acc_test = st->fd_acc_test;
+            s.fd_spec_mean = st->fd_spec_mean; s.fd_mel_val0 = st->fd_mel_val0; s.fd_mel_val1 = st->fd_mel_val1;
+            s.fd_spec_val = st->fd_spec_val; s.fd_in_vadq = st->fd_in_vadq;
+#pragma unroll
+            for (int r = 0; r < P::NB; r++) {
+                const int b = lane + 32 * r;
+                const bool v = b < P::SPEC;
+                noise1[r] = v ? st->noise1[b] : eps; den1[r] = v ? st->den1[b] : 0.0f; prev1[r] = v ? st->prev_psd1[b] : 0.0f;
+                noise2[r] = v ? st->noise2[b] : eps; den2[r] = v ? st->den2[b] : 0.0f; prev2[r] = v ? st->prev_psd2[b] : 0.0f;
+            }
+            for (int i = lane; i < P::RB; i += 32) {
+                wm.ring1[i] = st->ring1[i];
+                wm.ring2[i] = st->ring2[i];
+                if (P::CEPS) wm.ring3[i] = st->ring3[i];
+            }
+        } else {
+            scal_init(s);
+#pragma unroll
+            for (int r = 0; r < P::NB; r++) {
+                noise1[r] = noise2[r] = eps;     // NoiseSup.c:948-953
+                den1[r] = den2[r] = prev1[r] = prev2[r] = 0.0f;
+            }
+            for (int i = lane; i < P::RB; i += 32) {
+                wm.ring1[i] = 0.0f;
+                wm.ring2[i] = 0.0f;
+                if (P::CEPS) wm.ring3[i] = 0.0f;
+            }
+        }
+        __syncwarp();
+
+        const int64_t blk0 = a.block_offsets ? a.block_offsets[u] : 0;
+        const int64_t tr0 = a.trace_offsets ? a.trace_offsets[u] : 0;
+        const int64_t ceps0 = a.ceps_offsets ? a.ceps_offsets[u] : 0;
+        const int64_t ceps_cap = a.ceps_offsets ? a.ceps_offsets[u + 1] - ceps0 : 0;
+
+        // ---- software prefetch of the next shift (strided: coalesced) -------------------------
+        float nx[P::NR];
+#pragma unroll
+        for (int r = 0; r < P::NR; r++) {
+            const int i = lane + 32 * r;
+            nx[r] = (nblk > 0 && i < P::S) ? to_f32(in[i]) : 0.0f;
+        }
+
+        for (int b = 0; b < nblk; b++) {
+            float cur[P::NR];
+            float ss = 0.0f;
+            bool nzl = false;
+#pragma unroll
+            for (int r = 0; r < P::NR; r++) { cur[r] = nx[r]; ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
+            if (b + 1 < nblk) {
+#pragma unroll
+                for (int r = 0; r < P::NR; r++) {
+                    const int i = lane + 32 * r;
+                    if (i < P::S) nx[r] = to_f32(in[(int64_t)(b + 1) * P::S + i]);
+                }
+            }
+            // zero-frame gate: DoAdvProcess (ParmInterface.c:244-250, leading frames only) /
+            // func_Wiener (NoiseSup.cpp:1159-1170, anywhere).  (int)FrameCheck != 0  <=>  energy >= 1.
+            bool process = true;
+            if (a.zero_check) {
+                bool nonzero;
+                if (sizeof(IN_T) == 2) nonzero = __any_sync(0xffffffffu, nzl);
+                else nonzero = !(warp_sum(ss) < 1.0f);
+                if (a.zero_check == 1) { process = nonzero || (s.onset != 0); if (process) s.onset = 1; }
+                else process = nonzero;
+            }
+
+            const int64_t obase = off0 + (int64_t)b * P::S;
+            float o[P::CH];
+            bool produced = false, ran0 = false;
+            StageFlags fl = {0, 0, 0};
+            if (process) {
+                const int nb = (s.nb_in1 & 3) * P::S;
+#pragma unroll
+                for (int r = 0; r < P::NR; r++) {
+                    const int i = lane + 32 * r;
+                    if (i < P::S) wm.ring1[nb + i] = cur[r];
+                }
+                s.nb_in1++;
+                __syncwarp();
+                float *trace = a.spec_trace ? a.spec_trace + (blk0 + b) * 6 * P::SPEC : nullptr;
+                if (s.nb_in1 - s.nb_in2 > 2) {
+                    float o0[P::CH];
+                    ns_stage<PROF, 0>(wm, bm, tw, lane, s, noise1, den1, prev1, eps, o0, fl, nullptr, trace);
+                    ran0 = true;
+                }
+                if (s.nb_in2 - s.nb_out2 > 2) {
+                    float *grow = (PROF == 16 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
+                    ns_stage<PROF, 1>(wm, bm, tw, lane, s, noise2, den2, prev2, eps, o, fl, grow, trace);
+                    s.n_rows++;
+                    produced = true;
+                    dc_offset<PROF>(o, s, lane);
+                }
+            }
+
+            // ---- outputs of this shift --------------------------------------------------------
+            const int i0 = lane * P::CH;
+            if constexpr (PROF == 8) {
+                // float denoised -> ring3 (CompCeps history), then coalesced int16 / float stores
+                float *stage_out = wm.W;     // 80 floats of scratch (W is dead here)
+                if (produced) {
+                    const int nb3 = ((s.nb_out2 - 1) & 3) * P::S;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) { wm.ring3[nb3 + i0 + t] = o[t]; stage_out[i0 + t] = o[t]; }
+                } else {
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) stage_out[i0 + t] = 0.0f;
+                }
+                __syncwarp();
+                if (a.den_i16) {
+                    // (FILE_TYPE) ptDenoised[i], ParmInterface.c:266: C cast = truncation toward zero
+                    for (int i = lane; i < P::S / 2; i += 32) {
+                        const float2 f = *reinterpret_cast<const float2 *>(stage_out + 2 * i);
+                        short2 q;
+                        q.x = (short)__float2int_rz(f.x);
+                        q.y = (short)__float2int_rz(f.y);
+                        if ((obase & 1) == 0) *reinterpret_cast<short2 *>(a.den_i16 + obase + 2 * i) = q;
+                        else { a.den_i16[obase + 2 * i] = q.x; a.den_i16[obase + 2 * i + 1] = q.y; }
+                    }
+                }
+                if (a.den_f32)
+                    for (int i = lane; i < P::S; i += 32) a.den_f32[obase + i] = stage_out[i];
+                if (produced && a.ceps && s.nb_out2 >= 3) {
+                    // third denoised shift onwards: frame m = nb_out2-3 (ParmInterface.c:275-293)
+                    const int m = s.nb_out2 - 3;
+                    if (m < ceps_cap) comp_ceps(wm, bm, tw, lane, (m & 3) * P::S, a.ceps + (ceps0 + m) * 14);
+                    s.n_ceps = m + 1;
+                }
+                if (a.vad_trace && lane == 0) {
+                    unsigned char t = 0;
+                    if (process) {
+                        t = (unsigned char)((s.flag_vad ? 1 : 0) | (fl.var << 1) | (fl.spec << 2) | (fl.mel << 3) |
+                                            ((s.nb_speech > 4 ? 1 : 0) << 4) | (ran0 ? 32 : 0) | (produced ? 64 : 0));
+                    } else {
+                        t = 128;
+                    }
+                    a.vad_trace[tr0 + b] = t;
+                }
+            } else {
+                if (a.out_f32) {
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) a.out_f32[obase + i0 + t] = produced ? o[t] : 0.0f;
+                }
+                if (a.flags && lane == 0) {
+                    int32_t *f = a.flags + blk0 + b;
+                    const int64_t T = a.total_blocks;
+                    f[0 * T] = ran0 ? fl.var : 0;
+                    f[1 * T] = ran0 ? fl.spec : 0;
+                    f[2 * T] = ran0 ? fl.mel : 0;
+                    f[3 * T] = ran0 ? (s.nb_speech > 4 ? 1 : 0) : 0;
+                    f[4 * T] = (ran0 || produced) ? s.nb_frame0 : 0;
+                }
+            }
+            if (a.produced && lane == 0)
+                a.produced[blk0 + b] = (produced ? 1 : 0) | (ran0 ? 2 : 0) | (process ? 0 : 4);
+            __syncwarp();
+        }
+
+        // tail (len % S): the reference leaves it untouched; the batch API defines it as 0
+        if (PROF == 8) {
+            for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) {
+                if (a.den_i16) a.den_i16[off0 + i] = 0;
+                if (a.den_f32) a.den_f32[off0 + i] = 0.0f;
+            }
+        } else if (a.out_f32) {
+            for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
+        }
+        if (lane == 0) {
+            if (a.n_ceps) a.n_ceps[u] = s.n_ceps;
+            if (a.n_rows) a.n_rows[u] = s.n_rows;
+        }
+
+        if (st) {
+            if (lane == 0) {
+                st->nb_in1 = s.nb_in1; st->nb_in2 = s.nb_in2; st->nb_out2 = s.nb_out2;
+                st->nb_frame0 = s.nb_frame0; st->nb_frame1 = s.nb_frame1;
+                st->flag_vad = s.flag_vad; st->hang_over = s.hang_over; st->nb_speech = s.nb_speech;
+                st->onset = s.onset; st->n_ceps = s.n_ceps; st->n_rows = s.n_rows;
+                st->mean_en = s.mean_en; st->dc_x = s.dc_x; st->dc_y = s.dc_y;
+                st->den_en0 = s.den_en0; st->den_en1 = s.den_en1; st->den_en2 = s.den_en2;
+                st->low_snr = s.low_snr; st->alfa_gf = s.alfa_gf;
+                st->fd_mel_mean = s.fd_mel_mean; st->fd_var_mean = s.fd_var_mean; st->fd_acc_test = s.fd_acc_test;
+                st->fd_spec_mean = s.fd_spec_mean; st->fd_mel_val0 = s.fd_mel_val0; st->fd_mel_val1 = s.fd_mel_val1;
+                st->fd_spec_val = s.fd_spec_val; st->fd_in_vadq = s.fd_in_vadq;
+            }
+#pragma unroll
+            for (int r = 0; r < P::NB; r++) {
+                const int b = lane + 32 * r;
+                if (b < P::SPEC) {
+                    st->noise1[b] = noise1[r]; st->den1[b] = den1[r]; st->prev_psd1[b] = prev1[r];
+                    st->noise2[b] = noise2[r]; st->den2[b] = den2[r]; st->prev_psd2[b] = prev2[r];
+                }
+            }
+            for (int i = lane; i < P::RB; i += 32) {
+                st->ring1[i] = wm.ring1[i];
+                st->ring2[i] = wm.ring2[i];
+                if (P::CEPS) st->ring3[i] = wm.ring3[i];
+            }
+        }
+        __syncwarp();
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// test kernel: batched rfft in the reference's output layout (one warp per transform)
+// ------------------------------------------------------------------------------------------------
+__global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
+{
+    __shared__ float2 Zs[4][132], Z2s[4][132];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 4 + warp;
+    if (idx >= count) return;
+    float *p = x + (int64_t)idx * n;
+    const float2 *twh = reinterpret_cast<const float2 *>(tw_half);
+    FftTw tw;
+    fft_tw_init(tw, lane);
+    float2 *Z = Zs[warp], *Z2 = Z2s[warp];
+    if (n == 256) {
+        float2 v[4];
+        for (int j = 0; j < 4; j++) v[j] = reinterpret_cast<const float2 *>(p)[lane + 32 * j];
+        __syncwarp();
+        fft128_warp(v, tw, lane);
+        fft128_store(v, Z, lane);
+        __syncwarp();
+        for (int k = lane; k <= 128; k += 32) {
+            const float2 X = rsplit256(Z, k, twh[k]);
+            p[k] = X.x;
+            if (k > 0 && k < 128) p[256 - k] = X.y;
+        }
+    } else {   // n == 512, m == 8 : the plugin's truncated schedule
+        float2 va[4], vw[4];
+        for (int j = 0; j < 4; j++) {
+            const float4 q = reinterpret_cast<const float4 *>(p)[lane + 32 * j];
+            va[j] = make_float2(q.x, q.z);
+            vw[j] = make_float2(q.y, q.w);
+        }
+        __syncwarp();
+        fft128_warp(va, tw, lane);
+        fft128_warp(vw, tw, lane);
+        fft128_store(va, Z, lane);
+        fft128_store(vw, Z2, lane);
+        __syncwarp();
+        for (int k = lane; k <= 128; k += 32) {
+            const float2 A = rsplit256(Z, k, twh[k]);
+            p[k] = A.x;
+            if (k > 0 && k < 128) p[256 - k] = A.y;
+        }
+        for (int k = lane; k <= 64; k += 32) {
+            float2 B, C;
+            rsplit_pair(Z2, k, B, C);
+            p[256 + k] = B.x;
+            p[384 + k] = C.x;
+            if (k > 0 && k < 64) { p[384 - k] = B.y; p[512 - k] = C.y; }
+        }
+    }
+}
+
+// ------------------------------------------------------------------------------------------------
+// host launchers
+// ------------------------------------------------------------------------------------------------
+template <int PROF> static size_t ns_smem_bytes()
+{
+    return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + kNsWarpsPerBlock * sizeof(WarpMem<PROF>);
+}
+
+template <int PROF, typename IN_T> static int launch_ns(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid)
+{
+    if (a.n_utts <= 0) return SE_OK;
+    const size_t smem = ns_smem_bytes<PROF>();
+    auto kern = ns_stream_kernel<PROF, IN_T>;
+    SE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int per_sm = 0;
+    SE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kNsWarpsPerBlock * 32, smem));
+    if (per_sm < 1) per_sm = 1;
+    int blocks = (a.n_utts + kNsWarpsPerBlock - 1) / kNsWarpsPerBlock;
+    const int cap = ctx->sm_count * per_sm;
+    if (blocks > cap) blocks = cap;
+    SE_CUDA(cudaMemsetAsync(a.work_counter, 0, sizeof(int), ctx->stream));
+    prof_begin(ctx, kid);
+    kern<<<blocks, kNsWarpsPerBlock * 32, smem, ctx->stream>>>(a, tb, ctx->d_cc);
+    prof_end(ctx, kid);
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
+int launch_ns_p8(se_ctx *ctx, const NsLaunch &a)
+{
+    return a.is_f32 ? launch_ns<8, float>(ctx, a, ctx->d_p8, SE_K_NS_P8)
+                    : launch_ns<8, int16_t>(ctx, a, ctx->d_p8, SE_K_NS_P8);
+}
+
+int launch_ns_p16(se_ctx *ctx, const NsLaunch &a)
+{
+    return a.is_f32 ? launch_ns<16, float>(ctx, a, ctx->d_p16, SE_K_NS_P16)
+                    : launch_ns<16, int16_t>(ctx, a, ctx->d_p16, SE_K_NS_P16);
+}
+
+int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count)
+{
+    if (!((n == 256 && m == 8) || (n == 512 && m == 8))) {
+        set_error("se_rfft_batch: only (256,8) and (512,8) are on the hot path");
+        return SE_EUNSUPPORTED;
+    }
+    if (count <= 0) return SE_OK;
+    rfft_kernel<<<(count + 3) / 4, 128, 0, ctx->stream>>>(x, n, count, ctx->d_p8.tw_half);
+    ctx->launches++;
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
+}  // namespace se

@@ -1,0 +1,43 @@
+// Host-side constant tables of the hot path (built once per context, uploaded to the GPU).
+// Each builder restates the reference's init code with the same float/double promotions so the
+// tables are bit-identical to the reference's (checked by tests/test_tables.py against the oracle).
+#pragma once
+#include <vector>
+
+namespace se {
+
+constexpr int kMel = 25;          // WF_MEL_ORDER, etsi/cpp/MelProcExports.h:19
+constexpr int kFir = 17;          // NS_FILTER_LENGTH, etsi/cpp/NoiseSup.h:28
+constexpr int kGtChannels = 64;   // NUMBER_CHANNEL, resyth_64sub_IBM/cpp/HuWang.h:13
+
+struct NsTables {                 // one per NoiseSup profile
+    int shift, frame, nfft, spec, ana, fs;
+    std::vector<float> sig_window;            // Hanning, frame
+    std::vector<float> ir_window;             // Hanning-17
+    int bank_start[kMel], bank_len[kMel];
+    int bank_w;                               // row width of bank (65 for P8 mel, 128 for P16 gamma)
+    std::vector<float> bank;                  // [25][bank_w], zero padded
+    std::vector<float> idct;                  // [25][25]
+    float eps;                                // NS_EPS = (float)exp(-10.0)
+};
+
+struct CcTables {                 // CompCeps, 8 kHz
+    float hamming[100];
+    float dct[12 * 23];
+    int start[23], len[23];
+    float tri[23][129];
+};
+
+struct GtTables {                 // 64-channel gammatone
+    float cf[kGtChannels], bw[kGtChannels], mid[kGtChannels];
+    float f1[kGtChannels], f2[kGtChannels], gain[kGtChannels];
+    float hc[16];                             // hair-cell constants, see build_gt_tables
+    double fall_d[160], rise_d[160];          // raised-cosine halves, double as in the reference
+};
+
+void build_ns_tables_p8(NsTables &t);
+void build_ns_tables_p16(NsTables &t);
+void build_cc_tables(CcTables &t);
+void build_gt_tables(GtTables &t);
+
+}  // namespace se
