@@ -46,6 +46,11 @@ int  se_ctx_sync(se_ctx *ctx);
 /* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 24 GiB. */
 int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
 
+/* Pinned host memory for SE_MEM_HOST callers that want PCIe-rate staging (plain malloc works too,
+ * at pageable-copy speed).  Returns NULL on failure. */
+void *se_host_alloc(uint64_t bytes);
+void  se_host_free(void *p);
+
 /* ---- kernel timing (CUDA events on the launching stream) -------------------------------------- */
 #define SE_K_NS_P8     0   /* fused NoiseSup(+CompCeps) stream kernel, 8 kHz profile  */
 #define SE_K_NS_P16    1   /* fused NoiseSup stream kernel, 16 kHz plugin profile     */
@@ -97,11 +102,18 @@ typedef struct se_ns_stream se_ns_stream;
 int  se_ns_stream_create(se_ctx *ctx, int profile /*8|16*/, se_ns_stream **out);
 void se_ns_stream_destroy(se_ns_stream *s);
 int  se_ns_stream_reset(se_ns_stream *s);
-/* Push n_blocks*shift float samples (HOST pointers).  P8: out receives shift floats per block, valid
- * where produced[b]!=0 (DoNoiseSup's BOOLEAN, etsi/cpp/NoiseSup.c:1436-1439).  P16: func_Wiener
- * semantics incl. zero-block skipping; flags is int32[5][n_blocks], gains float[n_blocks][25]. */
+/* Zero-frame gate applied in front of the stream: 0 none (DoNoiseSup; default for profile 8),
+ * 1 leading all-zero blocks only (DoAdvProcess, etsi/cpp/ParmInterface.c:244-250), 2 anywhere
+ * (func_Wiener, aurora_etsi/NoiseSup.cpp:1159-1170; default for profile 16). */
+int  se_ns_stream_set_zero_gate(se_ns_stream *s, int mode);
+/* Push n_blocks*shift float samples (HOST pointers; the call is synchronous).  out receives shift
+ * floats per block.  produced[b] is a bit mask: 1 = a denoised shift was output for block b
+ * (DoNoiseSup's BOOLEAN, etsi/cpp/NoiseSup.c:1436-1439), 2 = stage 0 ran, 4 = block skipped by the
+ * zero gate.  P16: func_Wiener semantics; flags is int32[5][n_blocks], gains float[n_blocks][25]
+ * (*n_rows rows valid).  P8: ceps float[n_blocks][14], *n_ceps rows valid (the CompCeps step of
+ * ParmInterface.c:274-293).  Any output pointer may be NULL. */
 int  se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out, int32_t *produced,
-                       int32_t *flags, float *gains, int32_t *n_rows);
+                       int32_t *flags, float *gains, int32_t *n_rows, float *ceps, int32_t *n_ceps);
 
 /* ---- G64: 64-channel gammatone analysis / masks / resynthesis ----------------------------------- */
 #define SE_FLAG_EXACT   1   /* evaluate the IIR recurrences with separately rounded mul/add, in the

@@ -1,0 +1,226 @@
+// G64 batch entry points + known-answer primitives of se_b200.h.  Included by se_api_batch.cuh.
+#pragma once
+
+extern "C" {
+
+int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                     int16_t *out, int flags, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_subband_batch"));
+    if (n_utts < 0 || (n_utts > 0 && (!samples || !out))) { set_error("se_subband_batch: bad arguments"); return SE_EINVAL; }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_subband_batch"));
+    if (offsets[0] != 0) { set_error("se_subband_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    const uint64_t total = (uint64_t)offsets[n_utts];
+    G64Launch a;
+    std::memset(&a, 0, sizeof a);
+    const void *d_in = nullptr;
+    void *d_out = nullptr;
+    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
+    SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
+    SE_TRY(stage_out(ctx, kSlotOut, out, sizeof(int16_t) * 64 * total, mem, false, &d_out));
+    a.samples = (const int16_t *)d_in;
+    a.utt_begin = 0;
+    a.utt_count = n_utts;
+    a.flags = flags;
+    SE_TRY(launch_subband(ctx, a, (int16_t *)d_out));
+    SE_TRY(stage_out_copy(ctx, out, d_out, sizeof(int16_t) * 64 * total, mem));
+    return leave(ctx, mem);
+}
+
+int se_ibm_batch(se_ctx *ctx, const int16_t *pure, const int16_t *noise, const int64_t *offsets, int n_utts,
+                 float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_ibm_batch"));
+    if (n_utts < 0 || (n_utts > 0 && (!pure || !noise || !frame_offsets))) { set_error("se_ibm_batch: bad arguments"); return SE_EINVAL; }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_ibm_batch"));
+    if (offsets[0] != 0) { set_error("se_ibm_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    for (int u = 0; u < n_utts; u++)
+        if (frame_offsets[u + 1] - frame_offsets[u] < se_ibm_num_frames(offsets[u + 1] - offsets[u])) {
+            set_error("se_ibm_batch: frame_offsets too small for utterance %d", u);
+            return SE_EINVAL;
+        }
+    const uint64_t total = (uint64_t)offsets[n_utts], frames = (uint64_t)frame_offsets[n_utts];
+    G64Launch a;
+    std::memset(&a, 0, sizeof a);
+    const void *d_p = nullptr, *d_n = nullptr;
+    const int64_t *d_fo = nullptr;
+    void *d_irm = nullptr, *d_bits = nullptr;
+    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
+    SE_TRY(upload_offsets(ctx, kSlotOffsets2, frame_offsets, n_utts + 1, &d_fo));
+    SE_TRY(stage_in(ctx, kSlotIn, pure, sizeof(int16_t) * total, mem, &d_p));
+    SE_TRY(stage_in(ctx, kSlotIn2, noise, sizeof(int16_t) * total, mem, &d_n));
+    SE_TRY(stage_out(ctx, kSlotOut, irm, sizeof(float) * 64 * frames, mem, true, &d_irm));
+    SE_TRY(stage_out(ctx, kSlotOut2, ibm_bits, sizeof(uint64_t) * frames, mem, true, &d_bits));
+    a.samples = (const int16_t *)d_p;
+    a.samples2 = (const int16_t *)d_n;
+    a.utt_begin = 0;
+    a.utt_count = n_utts;
+    a.flags = SE_FLAG_EXACT;
+    SE_TRY(launch_ibm(ctx, a, (float *)d_irm, (uint64_t *)d_bits, d_fo));
+    SE_TRY(stage_out_copy(ctx, irm, d_irm, sizeof(float) * 64 * frames, mem));
+    SE_TRY(stage_out_copy(ctx, ibm_bits, d_bits, sizeof(uint64_t) * frames, mem));
+    return leave(ctx, mem);
+}
+
+int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                     const float *mask, const int64_t *frame_offsets, int mode, int flags,
+                     int16_t *out, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_resynth_batch"));
+    if (n_utts < 0 || (n_utts > 0 && (!samples || !mask || !frame_offsets || !out)) || mode < 0 || mode > 2) {
+        set_error("se_resynth_batch: bad arguments");
+        return SE_EINVAL;
+    }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_resynth_batch"));
+    SE_TRY(check_offsets(frame_offsets, n_utts, "se_resynth_batch(frame_offsets)"));
+    if (offsets[0] != 0) { set_error("se_resynth_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    for (int u = 0; u < n_utts; u++)
+        if (frame_offsets[u + 1] - frame_offsets[u] != se_resynth_num_frames(offsets[u + 1] - offsets[u], mode)) {
+            set_error("se_resynth_batch: utterance %d has %lld mask rows, expected %lld", u,
+                      (long long)(frame_offsets[u + 1] - frame_offsets[u]),
+                      (long long)se_resynth_num_frames(offsets[u + 1] - offsets[u], mode));
+            return SE_EINVAL;
+        }
+    const uint64_t total = (uint64_t)offsets[n_utts], frames = (uint64_t)frame_offsets[n_utts];
+    G64Launch a;
+    std::memset(&a, 0, sizeof a);
+    const void *d_in = nullptr, *d_mask = nullptr;
+    const int64_t *d_fo = nullptr;
+    void *d_out = nullptr;
+    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
+    SE_TRY(upload_offsets(ctx, kSlotOffsets2, frame_offsets, n_utts + 1, &d_fo));
+    SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
+    SE_TRY(stage_in(ctx, kSlotIn2, mask, sizeof(float) * 64 * frames, mem, &d_mask));
+    SE_TRY(stage_out(ctx, kSlotOut, out, sizeof(int16_t) * total, mem, false, &d_out));
+    a.samples = (const int16_t *)d_in;
+    a.utt_begin = 0;
+    a.utt_count = n_utts;
+    a.flags = flags;
+    SE_TRY(launch_resynth(ctx, a, offsets, (const float *)d_mask, d_fo, mode, (int16_t *)d_out));
+    SE_TRY(stage_out_copy(ctx, out, d_out, sizeof(int16_t) * total, mem));
+    return leave(ctx, mem);
+}
+
+int se_addnoise_batch(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy,
+                      const int64_t *offsets, int n_utts, int db, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_addnoise_batch"));
+    if (n_utts < 0 || (n_utts > 0 && (!pure || !noise || !noisy))) { set_error("se_addnoise_batch: bad arguments"); return SE_EINVAL; }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_addnoise_batch"));
+    if (offsets[0] != 0) { set_error("se_addnoise_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    const uint64_t bytes = sizeof(int16_t) * (uint64_t)offsets[n_utts];
+    const int64_t *d_off = nullptr;
+    const void *d_p = nullptr, *d_nz_in = nullptr;
+    void *d_noisy = nullptr;
+    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &d_off));
+    SE_TRY(stage_in(ctx, kSlotIn, pure, bytes, mem, &d_p));
+    SE_TRY(stage_in(ctx, kSlotIn2, noise, bytes, mem, &d_nz_in));
+    SE_TRY(stage_out(ctx, kSlotOut, noisy, bytes, mem, false, &d_noisy));
+    int16_t *d_nz = const_cast<int16_t *>((const int16_t *)d_nz_in);   // scaled in place
+    SE_TRY(launch_addnoise(ctx, (const int16_t *)d_p, d_nz, (int16_t *)d_noisy, d_off, n_utts, db));
+    SE_TRY(stage_out_copy(ctx, noise, d_nz, bytes, mem));
+    SE_TRY(stage_out_copy(ctx, noisy, d_noisy, bytes, mem));
+    return leave(ctx, mem);
+}
+
+int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_rfft_batch"));
+    if (count < 0 || (count > 0 && !x)) { set_error("se_rfft_batch: bad arguments"); return SE_EINVAL; }
+    if (!((n == 256 && m == 8) || (n == 512 && m == 8))) {
+        set_error("se_rfft_batch: only (256,8) and (512,8) are on the hot path");
+        return SE_EUNSUPPORTED;
+    }
+    if (count == 0) return SE_OK;
+    const uint64_t bytes = sizeof(float) * (uint64_t)n * (uint64_t)count;
+    const void *d_in = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, x, bytes, mem, &d_in));
+    float *d = const_cast<float *>((const float *)d_in);
+    SE_TRY(launch_rfft(ctx, d, n, m, count));
+    SE_TRY(stage_out_copy(ctx, x, d, bytes, mem));
+    return leave(ctx, mem);
+}
+
+int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
+                       int count, int flags, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_gammatone_batch"));
+    if (count < 0 || n < 0 || (count > 0 && (!in || !out || !channel))) { set_error("se_gammatone_batch: bad arguments"); return SE_EINVAL; }
+    if (count == 0 || n == 0) return SE_OK;
+    if (mem == SE_MEM_HOST)
+        for (int i = 0; i < count; i++)
+            if (channel[i] < 0 || channel[i] >= kGtChannels) { set_error("se_gammatone_batch: channel[%d] out of range", i); return SE_EINVAL; }
+    const uint64_t bytes = sizeof(float) * (uint64_t)n * (uint64_t)count;
+    const void *d_in = nullptr, *d_ch = nullptr;
+    void *d_out = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, in, bytes, mem, &d_in));
+    SE_TRY(stage_in(ctx, kSlotIn2, channel, sizeof(int32_t) * (uint64_t)count, mem, &d_ch));
+    SE_TRY(stage_out(ctx, kSlotOut, out, bytes, mem, false, &d_out));
+    SE_TRY(launch_gammatone(ctx, (const float *)d_in, (float *)d_out, (const int32_t *)d_ch, n, count, flags));
+    SE_TRY(stage_out_copy(ctx, out, d_out, bytes, mem));
+    return leave(ctx, mem);
+}
+
+// Host copies of the init-time tables (built on the host, identical to what the kernels read).
+// ctx may be NULL: the tables are then built on the fly (no GPU needed — used by the CPU table tests).
+int se_get_table(se_ctx *ctx, const char *name, float *out, int capacity, int *count)
+{
+    if (!name || !count) { set_error("se_get_table: bad arguments"); return SE_EINVAL; }
+    std::vector<float> v;
+    const std::string key(name);
+    NsTables p8l, p16l; CcTables ccl; GtTables gtl;
+    const NsTables *ns = nullptr;
+    std::string field;
+    if (key.rfind("p8.", 0) == 0) {
+        if (ctx) ns = &ctx->h_p8; else { build_ns_tables_p8(p8l); ns = &p8l; }
+        field = key.substr(3);
+    } else if (key.rfind("p16.", 0) == 0) {
+        if (ctx) ns = &ctx->h_p16; else { build_ns_tables_p16(p16l); ns = &p16l; }
+        field = key.substr(4);
+    }
+    if (ns) {
+        if (field == "sig_window") v = ns->sig_window;
+        else if (field == "ir_window") v = ns->ir_window;
+        else if (field == "bank") v = ns->bank;
+        else if (field == "idct") v = ns->idct;
+        else if (field == "bank_start") v.assign(ns->bank_start, ns->bank_start + kMel);
+        else if (field == "bank_len") v.assign(ns->bank_len, ns->bank_len + kMel);
+        else if (field == "eps") v.assign(1, ns->eps);
+        else { set_error("se_get_table: unknown table %s", name); return SE_EINVAL; }
+    } else if (key.rfind("cc.", 0) == 0) {
+        const CcTables *cc = &ccl;
+        if (ctx) cc = &ctx->h_cc; else build_cc_tables(ccl);
+        field = key.substr(3);
+        if (field == "hamming") v.assign(cc->hamming, cc->hamming + 100);
+        else if (field == "dct") v.assign(cc->dct, cc->dct + 12 * 23);
+        else if (field == "start") v.assign(cc->start, cc->start + 23);
+        else if (field == "len") v.assign(cc->len, cc->len + 23);
+        else if (field == "tri") v.assign(&cc->tri[0][0], &cc->tri[0][0] + 23 * 129);
+        else { set_error("se_get_table: unknown table %s", name); return SE_EINVAL; }
+    } else if (key.rfind("gt.", 0) == 0) {
+        const GtTables *gt = &gtl;
+        if (ctx) gt = &ctx->h_gt; else build_gt_tables(gtl);
+        field = key.substr(3);
+        const float *src = nullptr;
+        if (field == "cf") src = gt->cf; else if (field == "bw") src = gt->bw; else if (field == "mid") src = gt->mid;
+        else if (field == "f1") src = gt->f1; else if (field == "f2") src = gt->f2; else if (field == "gain") src = gt->gain;
+        if (src) v.assign(src, src + kGtChannels);
+        else if (field == "hc") v.assign(gt->hc, gt->hc + 16);
+        else { set_error("se_get_table: unknown table %s", name); return SE_EINVAL; }
+    } else {
+        set_error("se_get_table: unknown table %s", name);
+        return SE_EINVAL;
+    }
+    *count = (int)v.size();
+    if (out) {
+        if (capacity < (int)v.size()) { set_error("se_get_table: capacity %d < %d", capacity, (int)v.size()); return SE_EINVAL; }
+        std::memcpy(out, v.data(), sizeof(float) * v.size());
+    }
+    return SE_OK;
+}
+
+}  // extern "C"

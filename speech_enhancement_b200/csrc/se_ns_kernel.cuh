@@ -64,7 +64,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             s.nb_in1 = st->nb_in1; s.nb_in2 = st->nb_in2; s.nb_out2 = st->nb_out2;
             s.nb_frame0 = st->nb_frame0; s.nb_frame1 = st->nb_frame1;
             s.flag_vad = st->flag_vad; s.hang_over = st->hang_over; s.nb_speech = st->nb_speech;
-            s.onset = st->onset; s.n_ceps = st->n_ceps; s.n_rows = st->n_rows;
+            s.onset = st->onset; s.n_ceps = st->n_ceps;
+            s.n_rows = 0;     // rows are counted per push (gains rows of this call start at 0)
             s.mean_en = st->mean_en; s.dc_x = st->dc_x; s.dc_y = st->dc_y;
             s.den_en0 = st->den_en0; s.den_en1 = st->den_en1; s.den_en2 = st->den_en2;
             s.low_snr = st->low_snr; s.alfa_gf = st->alfa_gf;
@@ -97,6 +98,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             }
         }
         __syncwarp();
+        // cepstral rows are numbered per launch: a resumed stream continues at row 0 of this push
+        const int ceps_row0 = (st && a.load_state && s.nb_out2 > 2) ? s.nb_out2 - 2 : 0;
 
         const int64_t blk0 = a.block_offsets ? a.block_offsets[u] : 0;
         const int64_t tr0 = a.trace_offsets ? a.trace_offsets[u] : 0;
@@ -195,7 +198,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 if (produced && a.ceps && s.nb_out2 >= 3) {
                     // third denoised shift onwards: frame m = nb_out2-3 (ParmInterface.c:275-293)
                     const int m = s.nb_out2 - 3;
-                    if (m < ceps_cap) comp_ceps(wm, bm, tw, lane, (m & 3) * P::S, a.ceps + (ceps0 + m) * 14);
+                    if (m - ceps_row0 < ceps_cap)
+                        comp_ceps(wm, bm, tw, lane, (m & 3) * P::S, a.ceps + (ceps0 + m - ceps_row0) * 14);
                     s.n_ceps = m + 1;
                 }
                 if (a.vad_trace && lane == 0) {
@@ -239,7 +243,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
         }
         if (lane == 0) {
-            if (a.n_ceps) a.n_ceps[u] = s.n_ceps;
+            if (a.n_ceps) a.n_ceps[u] = s.n_ceps - ceps_row0;
             if (a.n_rows) a.n_rows[u] = s.n_rows;
         }
 

@@ -1,0 +1,283 @@
+// libse_b200_dropin.so — the reference's function names for the hot path, implemented as thin
+// adapters over libse_b200.so (include/se_reference_api.h cites what each one replaces).
+// Host C++ only; no arithmetic of the path lives here except int16<->float conversions and the
+// text formatting the reference does around its kernels.
+#include "se_b200.h"
+#include "se_reference_api.h"
+#include <cstdio>
+#include <cstdlib>
+#include <cstring>
+#include <mutex>
+#include <vector>
+
+#define SE_EXPORT extern "C" __attribute__((visibility("default")))
+
+namespace {
+
+std::mutex g_mu;
+se_ctx *g_ctx = nullptr;
+
+// One process-wide context (the reference's entry points carry no handle).  Fails loudly without a GPU.
+se_ctx *default_ctx(const char *who)
+{
+    std::lock_guard<std::mutex> lk(g_mu);
+    if (!g_ctx) {
+        int dev = 0;
+        if (const char *e = std::getenv("SE_B200_DEVICE")) dev = std::atoi(e);
+        int rc = se_ctx_create(dev, &g_ctx);
+        if (rc != SE_OK) {
+            std::fprintf(stderr, "%s: libse_b200 cannot run (%d): %s\n", who, rc, se_last_error());
+            g_ctx = nullptr;
+        }
+    }
+    return g_ctx;
+}
+
+int report(const char *who, int rc)
+{
+    if (rc != SE_OK) std::fprintf(stderr, "%s: error %d: %s\n", who, rc, se_last_error());
+    return rc;
+}
+
+}  // namespace
+
+// ---------------------------------------------------------------------------------------------
+// etsi/cpp/AdvFrontEnd.h
+// ---------------------------------------------------------------------------------------------
+SE_EXPORT int etsi_denoise(short *p_data, short *p_denoised, long i_frame)
+{
+    se_ctx *ctx = default_ctx("etsi_denoise");
+    if (!ctx || !p_data || !p_denoised || i_frame < 0) return 1;
+    const long body = i_frame - i_frame % 80;       // the tail is never read nor written (AdvFrontEnd.c:96-97)
+    if (body == 0) return 0;
+    const int64_t off[2] = {0, body};
+    int rc = se_etsi_denoise_batch(ctx, p_data, off, 1, p_denoised, nullptr, nullptr, nullptr, nullptr, nullptr,
+                                   nullptr, SE_MEM_HOST);
+    return report("etsi_denoise", rc) == SE_OK ? 0 : 1;
+}
+
+SE_EXPORT int etsi_denoise_synchronization(short *p_data, short *p_denoised, long i_frame)
+{
+    // AdvFrontEnd.c:213-226, quirks included: copies only when etsi_denoise returned TRUE (failure),
+    // and the length is in BYTES.
+    if (i_frame < 0) return 1;
+    short *tmp = (short *)std::calloc((size_t)(i_frame > 0 ? i_frame : 1), sizeof(short));
+    if (!tmp) return 1;
+    const int flag = etsi_denoise(p_data, tmp, i_frame);
+    if (flag && i_frame > 320) {
+        std::memset(p_denoised, 0, (size_t)i_frame * sizeof(short));
+        std::memcpy(p_denoised, tmp + 320, (size_t)(i_frame - 320));
+    }
+    std::free(tmp);
+    return flag;
+}
+
+SE_EXPORT int etsi_denoise_16k(short *, short *, long)
+{
+    std::fprintf(stderr, "etsi_denoise_16k: unsupported (16 kHz ETSI mode is outside the accelerated path)\n");
+    return 1;
+}
+
+SE_EXPORT int etsi_denoise_16k_synchronization(short *, short *, long)
+{
+    std::fprintf(stderr, "etsi_denoise_16k_synchronization: unsupported (16 kHz ETSI mode is outside the accelerated path)\n");
+    return 1;
+}
+
+SE_EXPORT void rfft(float *x, int n, int m)
+{
+    se_ctx *ctx = default_ctx("rfft");
+    if (!ctx) return;
+    report("rfft", se_rfft_batch(ctx, x, n, m, 1, SE_MEM_HOST));
+}
+
+// ---------------------------------------------------------------------------------------------
+// etsi/cpp/ParmInterface.h: AdvProcessAlloc / Init / DoAdvProcess / Delete on an opaque handle
+// ---------------------------------------------------------------------------------------------
+struct FEParamsX {
+    se_ns_stream *ns;
+    int feat_ready;
+};
+
+SE_EXPORT FEParamsX *AdvProcessAlloc(int SamplingFrequency)
+{
+    if (SamplingFrequency != 8000) {
+        std::fprintf(stderr, "AdvProcessAlloc: only 8000 Hz is on the accelerated path (got %d)\n", SamplingFrequency);
+        return nullptr;
+    }
+    se_ctx *ctx = default_ctx("AdvProcessAlloc");
+    if (!ctx) return nullptr;
+    FEParamsX *p = new FEParamsX();
+    p->ns = nullptr;
+    p->feat_ready = 0;
+    if (report("AdvProcessAlloc", se_ns_stream_create(ctx, 8, &p->ns)) != SE_OK) { delete p; return nullptr; }
+    se_ns_stream_set_zero_gate(p->ns, 1);        // DoAdvProcess skips leading all-zero frames
+    return p;
+}
+
+SE_EXPORT void AdvProcessInit(FEParamsX *This)
+{
+    if (This) { se_ns_stream_reset(This->ns); This->feat_ready = 0; }
+}
+
+SE_EXPORT int DoAdvProcess(short *CurrentFrame, short *OutBuf, float *FeatBuf, FEParamsX *This)
+{
+    if (!This || !CurrentFrame) return 0;
+    float in[80], out[80], ceps[14];
+    for (int i = 0; i < 80; i++) in[i] = (float)CurrentFrame[i];      // ParmInterface.c:239-242
+    int32_t produced = 0, n_ceps = 0;
+    This->feat_ready = 0;
+    if (report("DoAdvProcess", se_ns_stream_push(This->ns, in, 1, out, &produced, nullptr, nullptr, nullptr,
+                                                 FeatBuf ? ceps : nullptr, &n_ceps)) != SE_OK)
+        return 0;
+    if (!(produced & 1)) return 0;
+    if (OutBuf)
+        for (int i = 0; i < 80; i++) OutBuf[i] = (short)(int)out[i];   // ParmInterface.c:264-268: C cast
+    if (FeatBuf && n_ceps > 0) { std::memcpy(FeatBuf, ceps, sizeof ceps); This->feat_ready = 1; }
+    return 1;
+}
+
+SE_EXPORT int se_adv_feature_ready(FEParamsX *This) { return This ? This->feat_ready : 0; }
+
+SE_EXPORT void AdvProcessDelete(FEParamsX **This)
+{
+    if (!This || !*This) return;
+    se_ns_stream_destroy((*This)->ns);
+    delete *This;
+    *This = nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------
+// function/.../aurora_etsi/NoiseSupExports.h: the plugin API
+// ---------------------------------------------------------------------------------------------
+namespace {
+struct GlobalImpl { int SamplingFrequency; };
+}
+
+SE_EXPORT int32s etsi_denoise_mapping_global_init(PINSTANCE sm_glb_pins, INSTANCE)
+{
+    if (!sm_glb_pins) return 0;
+    GlobalImpl *g = new GlobalImpl();
+    g->SamplingFrequency = 16000;                  // NoiseSup.cpp:918
+    *sm_glb_pins = g;
+    return 1;
+}
+
+SE_EXPORT int32s etsi_denoise_mapping_thread_init(PINSTANCE sm_thd_pins, INSTANCE sm_glb_ins)
+{
+    if (!sm_thd_pins || !sm_glb_ins) return 0;     // NoiseSup.cpp:941-944
+    se_ctx *ctx = default_ctx("etsi_denoise_mapping_thread_init");
+    if (!ctx) return 0;
+    se_ns_stream *s = nullptr;
+    if (report("etsi_denoise_mapping_thread_init", se_ns_stream_create(ctx, 16, &s)) != SE_OK) return 0;
+    *sm_thd_pins = s;
+    return 1;
+}
+
+SE_EXPORT int32s etsi_denoise_mapping_func_Wiener(INSTANCE, INSTANCE sm_thd_ins, INSTANCE in_ins, INSTANCE out_ins,
+                                                  INSTANCE fp_Wiener)
+{
+    se_ns_stream *s = (se_ns_stream *)sm_thd_ins;
+    esti_denoise_in *in = (esti_denoise_in *)in_ins;
+    esti_denoise_out *po = (esti_denoise_out *)out_ins;
+    if (!s || !in || !po) return 1;
+    const int nb = in->dataNum / 160;
+    if (nb <= 0) return 0;
+    std::vector<float> out((size_t)nb * 160), gains((size_t)nb * 25);
+    std::vector<int32_t> produced(nb), flags((size_t)nb * 5);
+    int32_t rows = 0;
+    if (report("etsi_denoise_mapping_func_Wiener",
+               se_ns_stream_push(s, in->inData, nb, out.data(), produced.data(), flags.data(), gains.data(), &rows,
+                                 nullptr, nullptr)) != SE_OK)
+        return 1;
+    for (int b = 0; b < nb; b++) {
+        const int p = produced[b];
+        if (p & 4) continue;                                          // zero block: nothing touched (:1166-1170)
+        if ((p & 1) && po->outData) std::memcpy(po->outData + (size_t)b * 160, out.data() + (size_t)b * 160, 160 * sizeof(float));
+        if (p & 2) {
+            if (po->pSpeechFoundVar) po->pSpeechFoundVar[b] = flags[0 * (size_t)nb + b];
+            if (po->pSpeechFoundSpec) po->pSpeechFoundSpec[b] = flags[1 * (size_t)nb + b];
+            if (po->pSpeechFoundMel) po->pSpeechFoundMel[b] = flags[2 * (size_t)nb + b];
+            if (po->pSpeechFoundVADNS) po->pSpeechFoundVADNS[b] = flags[3 * (size_t)nb + b];
+        }
+        if ((p & 3) && po->pFrameCounter) po->pFrameCounter[b] = flags[4 * (size_t)nb + b];
+    }
+    if (FILE *fp = (FILE *)fp_Wiener) {
+        for (int r = 0; r < rows; r++) {                              // NoiseSup.cpp:1318-1326
+            for (int i = 0; i < 25; i++) std::fprintf(fp, "%f ", gains[(size_t)r * 25 + i]);
+            std::fprintf(fp, "\n");
+        }
+    }
+    return 0;
+}
+
+SE_EXPORT void etsi_denoise_mapping_thread_release(PINSTANCE sm_thd_pins)
+{
+    if (!sm_thd_pins || !*sm_thd_pins) return;
+    se_ns_stream_destroy((se_ns_stream *)*sm_thd_pins);
+    *sm_thd_pins = nullptr;
+}
+
+SE_EXPORT void etsi_denoise_mapping_global_release(PINSTANCE sm_glb_pins)
+{
+    if (!sm_glb_pins || !*sm_glb_pins) return;
+    delete (GlobalImpl *)*sm_glb_pins;
+    *sm_glb_pins = nullptr;
+}
+
+// ---------------------------------------------------------------------------------------------
+// */cpp/extractwav.cpp C twins
+// ---------------------------------------------------------------------------------------------
+SE_EXPORT int se_subband(const short *wav, long n, short *out64xn)
+{
+    se_ctx *ctx = default_ctx("se_subband");
+    if (!ctx) return SE_ENODEVICE;
+    if (n <= 0) return SE_OK;
+    const int64_t off[2] = {0, n};
+    return report("se_subband", se_subband_batch(ctx, wav, off, 1, out64xn, SE_FLAG_EXACT, SE_MEM_HOST));
+}
+
+SE_EXPORT int se_resynth(const short *wav, long n, float *mask, int num_frame, int mode, short *out)
+{
+    se_ctx *ctx = default_ctx("se_resynth");
+    if (!ctx) return SE_ENODEVICE;
+    if (n <= 0) return SE_OK;
+    const int64_t off[2] = {0, n}, fo[2] = {0, num_frame};
+    int rc = report("se_resynth", se_resynth_batch(ctx, wav, off, 1, mask, fo, mode, SE_FLAG_EXACT, out, SE_MEM_HOST));
+    if (rc == SE_OK && mode == SE_RESYNTH_IBM && mask)
+        for (long i = 0; i < (long)num_frame * 64; i++)
+            if (mask[i] > 0.5f) mask[i] = 1.0f;                       // resyth_64sub_IBM/cpp/extractwav.cpp:99
+    return rc;
+}
+
+SE_EXPORT int se_single_ibm(const short *pure, const short *noise, long n, float *irm, unsigned char *ibm)
+{
+    se_ctx *ctx = default_ctx("se_single_ibm");
+    if (!ctx) return SE_ENODEVICE;
+    const int64_t frames = se_ibm_num_frames(n);
+    if (frames <= 0) return SE_OK;
+    const int64_t off[2] = {0, n}, fo[2] = {0, frames};
+    std::vector<uint64_t> bits(ibm ? (size_t)frames : 0);
+    int rc = report("se_single_ibm", se_ibm_batch(ctx, pure, noise, off, 1, irm, ibm ? bits.data() : nullptr, fo, SE_MEM_HOST));
+    if (rc == SE_OK && ibm)
+        for (int64_t f = 0; f < frames; f++)
+            for (int c = 0; c < 64; c++) ibm[f * 64 + c] = (unsigned char)((bits[(size_t)f] >> c) & 1u);
+    return rc;
+}
+
+SE_EXPORT int se_addnoise(const short *pure, short *noise, short *noisy, long n, int db)
+{
+    se_ctx *ctx = default_ctx("se_addnoise");
+    if (!ctx) return SE_ENODEVICE;
+    if (n <= 0) return SE_OK;
+    const int64_t off[2] = {0, n};
+    return report("se_addnoise", se_addnoise_batch(ctx, pure, noise, noisy, off, 1, db, SE_MEM_HOST));
+}
+
+SE_EXPORT int se_gammatone_filter(const float *input, float *output, int channel, long sigLength)
+{
+    se_ctx *ctx = default_ctx("se_gammatone_filter");
+    if (!ctx) return SE_ENODEVICE;
+    const int32_t ch = channel;
+    return report("se_gammatone_filter", se_gammatone_batch(ctx, input, output, &ch, sigLength, 1, SE_FLAG_EXACT, SE_MEM_HOST));
+}
