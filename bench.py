@@ -1,0 +1,477 @@
+#!/usr/bin/env python
+"""bench.py — audio-seconds per second (xRT) of the speech-enhancement hot path on B200.
+
+  python bench.py [--gpus N --steps K --warmup W]            our arm (CUDA, through the C ABI)
+  python bench.py --impl reference [...]                     the reference's own CPU code (oracle/_ref)
+
+A "step" is one pass of the hot path over one batch of synthetic utterances.  Headline workload =
+BASELINE.json configs[1]: 10k synthetic 16 kHz noisy utterances (ragged 2-10 s) through the plugin
+NoiseSup (framed rfft + two-stage Wiener filter, etsi_denoise_mapping_func_Wiener) -> denoised stream,
+25 band gains per frame, frame-dropping flags.  The P8 NoiseSup+CompCeps path and the 64-sub IBM
+resynthesis are measured on smaller batches and reported under "other_workloads".
+
+Weak scaling: every rank (one per GPU) processes its own batch of the same size; there is no
+collective on the data path (utterances are independent).  torch is used for device memory, the
+stream/events and torch.distributed only.
+"""
+import argparse
+import json
+import os
+import subprocess
+import sys
+import threading
+import time
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.abspath(__file__))
+sys.path.insert(0, ROOT)
+
+P16_BYTES_PER_BLOCK = 320 + 640 + 100 + 20      # int16 in, f32 denoised out, 25 f32 gains, 5 int32 flags
+P8_BYTES_PER_HOP = 160 + 160 + 56               # int16 in, int16 out, 14 f32 cepstra
+G64_BYTES_PER_SAMPLE = 2 + 2 + 64 * 4 / 160.0   # int16 in, int16 out, float mask row per 160 samples
+
+
+def parse():
+    ap = argparse.ArgumentParser()
+    ap.add_argument("--gpus", type=int, default=1)
+    ap.add_argument("--steps", type=int, default=5)
+    ap.add_argument("--warmup", type=int, default=3)
+    ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
+    ap.add_argument("--utts", type=int, default=10000, help="utterances per GPU in the headline batch")
+    ap.add_argument("--no-extra", action="store_true", help="skip the other_workloads section")
+    ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    return ap.parse_args()
+
+
+def make_corpus(first_u, count, fs, min_s, max_s, seconds=None, components=False):
+    """Ragged synthetic corpus, generated with all host threads (the C generator releases the GIL)."""
+    from speech_enhancement_b200 import synth
+    lens = np.array([int(seconds * fs) if seconds else synth.ragged_length(first_u + i, fs, min_s, max_s)
+                     for i in range(count)], np.int64)
+    offsets = np.zeros(count + 1, np.int64)
+    offsets[1:] = np.cumsum(lens)
+    total = int(offsets[-1])
+    noisy = np.empty(total, np.int16)
+    L = synth._load()
+
+    def gen(i):
+        L.se_synth_utterance(first_u + i, fs, int(lens[i]), noisy[offsets[i]:].ctypes.data, None, None)
+
+    with ThreadPoolExecutor(max_workers=max(1, min(32, os.cpu_count() or 1))) as ex:
+        list(ex.map(gen, range(count)))
+    return noisy, offsets
+
+
+class ClockSampler:
+    """nvidia-smi clocks / throttle reasons sampled DURING the timed region."""
+    Q = ("clocks.sm,clocks.max.sm,clocks_event_reasons.hw_slowdown,clocks_event_reasons.hw_thermal_slowdown,"
+         "clocks_event_reasons.sw_thermal_slowdown,clocks_event_reasons.sw_power_cap")
+
+    def __init__(self, index):
+        self.index = index
+        self.rows = []
+        self.stop = threading.Event()
+        self.th = threading.Thread(target=self._run, daemon=True)
+
+    def _run(self):
+        while not self.stop.is_set():
+            try:
+                out = subprocess.run(["nvidia-smi", "-i", str(self.index), "--query-gpu=" + self.Q,
+                                      "--format=csv,noheader,nounits"], capture_output=True, text=True, timeout=5).stdout
+                self.rows.append([c.strip() for c in out.strip().split(",")])
+            except Exception:
+                pass
+            self.stop.wait(0.1)
+
+    def __enter__(self):
+        self.th.start()
+        return self
+
+    def __exit__(self, *a):
+        self.stop.set()
+        self.th.join(timeout=6)
+
+    def summary(self):
+        sm, mx, reasons = [], 0, set()
+        names = ["hw_slowdown", "hw_thermal_slowdown", "sw_thermal_slowdown", "sw_power_cap"]
+        for r in self.rows:
+            if len(r) < 6:
+                continue
+            try:
+                sm.append(float(r[0]))
+                mx = max(mx, float(r[1]))
+            except ValueError:
+                continue
+            for n, v in zip(names, r[2:6]):
+                if v.lower().startswith("active"):
+                    reasons.add(n)
+        return {"sm_mhz": float(np.median(sm)) if sm else None, "sm_max_mhz": mx or None,
+                "reasons": sorted(reasons), "samples": len(sm)}
+
+
+def peaks():
+    p = os.path.join(ROOT, "MEASURED_PEAKS.json")
+    if os.path.exists(p):
+        return float(json.load(open(p))["hbm_gbs"]), "measured (MEASURED_PEAKS.json)"
+    return 6650.0, "fallback (B200_PROFILING.md)"
+
+
+# ------------------------------------------------------------------------------------------------
+# our arm
+# ------------------------------------------------------------------------------------------------
+class Dist:
+    """torch.distributed plumbing (barrier + max over ranks); a no-op at N=1 without torchrun."""
+
+    def __init__(self, torch, n_gpus):
+        self.torch = torch
+        self.world = int(os.environ.get("WORLD_SIZE", "1"))
+        self.rank = int(os.environ.get("RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.on = self.world > 1
+        if self.on:
+            import torch.distributed as dist
+            self.dist = dist
+            os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
+
+    def barrier(self):
+        if self.on:
+            self.dist.barrier()
+
+    def max(self, v):
+        if not self.on:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.MAX)
+        return float(t.item())
+
+    def sum(self, v):
+        if not self.on:
+            return v
+        t = self.torch.tensor([v], dtype=self.torch.float64, device="cuda")
+        self.dist.all_reduce(t, op=self.dist.ReduceOp.SUM)
+        return float(t.item())
+
+    def close(self):
+        if self.on:
+            self.dist.destroy_process_group()
+
+
+def timed_steps(torch, dist, stream, step, warmup, steps):
+    """W untimed + exactly K timed steps, CUDA events on the launching stream, barrier+sync both sides;
+    returns total milliseconds (max over ranks)."""
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    e0, e1 = torch.cuda.Event(enable_timing=True), torch.cuda.Event(enable_timing=True)
+    e0.record(stream)
+    for _ in range(steps):
+        step()
+    e1.record(stream)
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    return dist.max(e0.elapsed_time(e1))
+
+
+def host_timed_steps(torch, dist, step, warmup, steps):
+    """Same bracket for the end-to-end leg (synchronous host-buffer calls): wall clock between syncs."""
+    for _ in range(warmup):
+        step()
+    torch.cuda.synchronize()
+    dist.barrier()
+    torch.cuda.synchronize()
+    t0 = time.perf_counter()
+    for _ in range(steps):
+        step()
+    torch.cuda.synchronize()
+    t1 = time.perf_counter()
+    dist.barrier()
+    return dist.max((t1 - t0) * 1e3)
+
+
+def dev(torch, a):
+    return torch.from_numpy(a).cuda()
+
+
+def pinned(api, a):
+    p = api.PinnedArray(a.shape, a.dtype)
+    p.array[...] = a
+    return p
+
+
+def bench_p16(args, torch, api, ctx, dist, stream, first_u):
+    """Headline: BASELINE configs[1]."""
+    samples, offsets = make_corpus(first_u, args.utts, 16000, 2.0, 10.0)
+    nu = args.utts
+    bo = np.zeros(nu + 1, np.int64)
+    bo[1:] = np.cumsum(np.diff(offsets) // 160)
+    tb, total = int(bo[-1]), int(offsets[-1])
+    audio_s = total / 16000.0
+    d_in = dev(torch, samples)
+    d_out = torch.empty(total, dtype=torch.float32, device="cuda")
+    d_flags = torch.empty(5 * tb, dtype=torch.int32, device="cuda")
+    d_gains = torch.empty(tb * 25, dtype=torch.float32, device="cuda")
+    d_rows = torch.empty(nu, dtype=torch.int32, device="cuda")
+
+    def step():
+        ctx.p16_wiener_raw(d_in.data_ptr(), 0, offsets, nu, d_out.data_ptr(), d_flags.data_ptr(), d_gains.data_ptr(),
+                           d_rows.data_ptr(), bo, mem=api.SE_MEM_DEVICE)
+
+    ctx.profiling(False)
+    for _ in range(args.warmup):
+        step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    l0 = ctx.launch_count()
+    with ClockSampler(dist.local) as clk:
+        ms = timed_steps(torch, dist, stream, step, 0, args.steps)
+    launches = ctx.launch_count() - l0
+    k_ms, k_n = ctx.kernel_time(api.K_NS_P16)
+    ctx.profiling(False)
+    rows_total = int(d_rows.sum().item())
+
+    # end to end: pinned host buffers through the same C-ABI call, H2D + D2H inside the timed region
+    h_in = pinned(api, samples)
+    h_out = api.PinnedArray(total, np.float32)
+    h_flags = api.PinnedArray(5 * tb, np.int32)
+    h_gains = api.PinnedArray(tb * 25, np.float32)
+    h_rows = api.PinnedArray(nu, np.int32)
+
+    def step_e2e():
+        ctx.p16_wiener_raw(h_in.ptr, 0, offsets, nu, h_out.ptr, h_flags.ptr, h_gains.ptr, h_rows.ptr, bo,
+                           mem=api.SE_MEM_HOST)
+
+    e2e_ms = host_timed_steps(torch, dist, step_e2e, 1, args.steps)
+    same = bool(np.array_equal(h_rows.array, d_rows.cpu().numpy()))
+    h2d = samples.nbytes
+    d2h = h_out.array.nbytes + h_flags.array.nbytes + h_gains.array.nbytes + h_rows.array.nbytes
+    for p in (h_in, h_out, h_flags, h_gains, h_rows):
+        p.free()
+    del d_in, d_out, d_flags, d_gains, d_rows
+    torch.cuda.empty_cache()
+    return dict(audio_s=audio_s, ms=ms, launches=launches, k_ms=k_ms, k_n=k_n, blocks=tb, rows=rows_total,
+                e2e_ms=e2e_ms, h2d=h2d, d2h=d2h, clocks=clk.summary(), e2e_matches_device=same,
+                samples=samples, offsets=offsets)
+
+
+def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=2000):
+    """P8: ETSI NoiseSup + CompCeps on 10 s 8 kHz utterances (C1-type work, batched)."""
+    samples, offsets = make_corpus(first_u, n_utts, 8000, 0, 0, seconds=10.0)
+    total = int(offsets[-1])
+    co = np.zeros(n_utts + 1, np.int64)
+    co[1:] = np.cumsum(np.maximum(np.diff(offsets) // 80 - 6, 0))
+    d_in = dev(torch, samples)
+    d_den = torch.empty(total, dtype=torch.int16, device="cuda")
+    d_ceps = torch.empty(int(co[-1]) * 14, dtype=torch.float32, device="cuda")
+    d_nc = torch.empty(n_utts, dtype=torch.int32, device="cuda")
+
+    def step():
+        ctx.etsi_denoise_raw(d_in.data_ptr(), offsets, n_utts, d_den.data_ptr(), d_ceps.data_ptr(), co, d_nc.data_ptr(),
+                             mem=api.SE_MEM_DEVICE)
+
+    for _ in range(args.warmup):
+        step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    ms = timed_steps(torch, dist, stream, step, 0, args.steps)
+    k_ms, k_n = ctx.kernel_time(api.K_NS_P8)
+    ctx.profiling(False)
+    audio_s = total / 8000.0
+    hops = total // 80
+    hbm, _ = peaks()
+    gbs = hops * P8_BYTES_PER_HOP / (k_ms / max(k_n, 1) * 1e-3) / 1e9
+    return {"workload": "P8 etsi NoiseSup+CompCeps, %d x 10 s 8 kHz" % n_utts, "xrt": audio_s * args.steps / (ms * 1e-3),
+            "ms_per_step": ms / args.steps, "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
+
+
+def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
+    """G64: resyth_64sub_IBM on 10 s 16 kHz utterances (BASELINE configs[2] shape)."""
+    samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
+    total = int(offsets[-1])
+    nf = api.resynth_num_frames(160000, api.RESYNTH_IBM)
+    fo = np.arange(n_utts + 1, dtype=np.int64) * nf
+    rng = np.random.default_rng(first_u)
+    mask = (rng.random((n_utts * nf, 64)) > 0.45).astype(np.float32)
+    d_in, d_mask = dev(torch, samples), dev(torch, mask)
+    d_out = torch.empty(total, dtype=torch.int16, device="cuda")
+
+    def step():
+        ctx.resynth_raw(d_in.data_ptr(), offsets, n_utts, d_mask.data_ptr(), fo, api.RESYNTH_IBM, 0, d_out.data_ptr(),
+                        mem=api.SE_MEM_DEVICE)
+
+    w = min(args.warmup, 1)
+    for _ in range(w):
+        step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    steps = min(args.steps, 2)
+    ms = timed_steps(torch, dist, stream, step, 0, steps)
+    f_ms, f_n = ctx.kernel_time(api.K_GT_FWD)
+    b_ms, b_n = ctx.kernel_time(api.K_GT_BWD)
+    ctx.profiling(False)
+    audio_s = total / 16000.0
+    hbm, _ = peaks()
+    k = (f_ms + b_ms) / steps
+    gbs = total * G64_BYTES_PER_SAMPLE / (k * 1e-3) / 1e9
+    return {"workload": "G64 resyth_64sub_IBM, %d x 10 s 16 kHz" % n_utts, "xrt": audio_s * steps / (ms * 1e-3),
+            "ms_per_step": ms / steps, "kernel_ms": {"gt_fwd": f_ms / steps, "gt_bwd": b_ms / steps},
+            "achieved_gbs": gbs, "frac": gbs / hbm}
+
+
+# ------------------------------------------------------------------------------------------------
+# the reference's own CPU code (oracle/_ref, or the plain-C port when _ref is absent)
+# ------------------------------------------------------------------------------------------------
+_W = {}
+
+
+def _cpu_init(kind):
+    from oracle import pyoracle
+    if kind == "reference":
+        _W["h"] = pyoracle.RefP16(fast=True)
+    else:
+        _W["h"] = pyoracle.Oracle(fast=True)
+    _W["kind"] = kind
+
+
+def _cpu_one(x):
+    """One utterance through etsi_denoise_mapping_func_Wiener on a fresh thread instance."""
+    from oracle import pyoracle
+    xf = x.astype(np.float32)
+    if _W["kind"] == "reference":
+        h = _W["h"]
+        h.close()
+        h.h = h.L.ref_p16_create()
+        r = h.func_wiener(xf)
+    else:
+        s = _W["h"].p16_stream()
+        r = s.func_wiener(xf)
+        s.close()
+    return len(r["gains"])
+
+
+def cpu_p16(samples, offsets, n_utts, cores):
+    """Times the CPU implementation on the first n_utts utterances with `cores` worker processes."""
+    import multiprocessing as mp
+    from oracle import pyoracle
+    kind = "reference" if pyoracle.have_ref("libref_p16_fast.so") else "port"
+    xs = [samples[offsets[u]:offsets[u + 1]] for u in range(n_utts)]
+    audio_s = float(offsets[n_utts] - offsets[0]) / 16000.0
+    ctx = mp.get_context("fork")
+    with ctx.Pool(cores, initializer=_cpu_init, initargs=(kind,)) as pool:
+        pool.map(_cpu_one, xs[:cores])          # warm the workers (library load, table init)
+        t0 = time.perf_counter()
+        rows = pool.map(_cpu_one, xs, chunksize=max(1, n_utts // (cores * 8)))
+        dt = time.perf_counter() - t0
+    return dict(kind=kind, audio_s=audio_s, seconds=dt, rows=int(sum(rows)), cores=cores)
+
+
+METRIC = "audio-sec/sec (xRT) per B200 for NoiseSup+CompCeps & 64-sub IBM resynth, 1/2/4/8 GPU"
+UNIT = "audio-s/s"
+
+
+def workload_name(utts):
+    return ("configs[1]: enhancement_extract_subband batch, %d synthetic 16 kHz noisy utterances (ragged 2-10 s), "
+            "framed rfft+NoiseSup features (etsi_denoise_mapping_func_Wiener)" % utts)
+
+
+def run_reference(args):
+    """--impl reference: the reference's own CPU implementation, all host threads, bounded sample per step."""
+    rank = int(os.environ.get("RANK", "0"))
+    if rank != 0:
+        return
+    cores = os.cpu_count() or 1
+    n = max(cores * 32, 64)                        # utterances per step: a bounded sample of the workload
+    samples, offsets = make_corpus(0, n, 16000, 2.0, 10.0)
+    for _ in range(max(args.warmup, 0) and 1):
+        cpu_p16(samples, offsets, min(n, cores), cores)
+    t_total, audio = 0.0, 0.0
+    kind = "port"
+    for _ in range(args.steps):
+        r = cpu_p16(samples, offsets, n, cores)
+        t_total += r["seconds"]
+        audio += r["audio_s"]
+        kind = r["kind"]
+    v = audio / t_total
+    line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": t_total / args.steps * 1e3, "higher_is_better": True,
+            "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.utts), "sample": "%d utterances per step" % n},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
+                             "sample": "first %d utterances of the workload per step, %d steps" % (n, args.steps)},
+            "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
+    print(json.dumps(line), flush=True)
+
+
+def run_ours(args):
+    import torch
+    from speech_enhancement_b200 import api
+    local = int(os.environ.get("LOCAL_RANK", "0"))
+    rank = int(os.environ.get("RANK", "0"))
+    first_u = rank * 1000003                        # every rank gets its own utterances (weak scaling)
+
+    # CPU baseline first (rank 0, N=1 only), before any CUDA context exists in this process (fork-safe)
+    cpu = None
+    if rank == 0 and args.gpus == 1 and not args.no_cpu:
+        cores = os.cpu_count() or 1
+        n = max(cores * 64, 64)
+        s, o = make_corpus(first_u, n, 16000, 2.0, 10.0)
+        r = cpu_p16(s, o, n, cores)
+        cpu = {"value": r["audio_s"] / r["seconds"], "unit": UNIT, "cores": cores, "kind": r["kind"],
+               "sample": "first %d utterances of the workload (%.0f audio-s), %.1f s wall on %d worker processes"
+                         % (n, r["audio_s"], r["seconds"], cores)}
+
+    torch.cuda.set_device(local)
+    dist = Dist(torch, args.gpus)
+    stream = torch.cuda.Stream()
+    ctx = api.Context(local)
+    ctx.set_stream(stream.cuda_stream)
+    hbm, peak_src = peaks()
+
+    with torch.cuda.stream(stream):
+        r = bench_p16(args, torch, api, ctx, dist, stream, first_u)
+        extra = None
+        if not args.no_extra and args.gpus == 1:
+            extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000),
+                     bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000)]
+    audio_all = dist.sum(r["audio_s"])
+    value = audio_all * args.steps / (r["ms"] * 1e-3)
+    e2e = audio_all * args.steps / (r["e2e_ms"] * 1e-3)
+    k_avg_ms = r["k_ms"] / max(r["k_n"], 1)
+    alg_bytes = r["blocks"] * P16_BYTES_PER_BLOCK
+    achieved = alg_bytes / (k_avg_ms * 1e-3) / 1e9
+    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
+            "vs_baseline": None, "dtype": "f32", "data": "synthetic",
+            "config": {"workload": workload_name(args.utts), "audio_s_per_gpu_per_step": r["audio_s"],
+                       "l2": "inputs larger than L2 (%.2f GB int16 per step)" % (r["h2d"] / 1e9),
+                       "parallelism": "utterance-sharded, %d rank(s), no collective" % args.gpus},
+            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+                         "traffic": None, "peak_source": peak_src, "kernel": "ns_stream_kernel<16,int16>",
+                         "kernel_ms": k_avg_ms, "algorithmic_bytes_per_launch": alg_bytes},
+            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                    "ms_per_step": r["e2e_ms"] / args.steps, "matches_device_path": r["e2e_matches_device"]},
+            "gpu_launches": r["launches"], "clocks": r["clocks"]}
+    if cpu:
+        line["cpu_baseline"] = cpu
+    if extra:
+        line["other_workloads"] = extra
+    if rank == 0:
+        print(json.dumps(line), flush=True)
+    ctx.close()
+    dist.close()
+
+
+if __name__ == "__main__":
+    a = parse()
+    if a.impl == "reference":
+        run_reference(a)
+    else:
+        run_ours(a)

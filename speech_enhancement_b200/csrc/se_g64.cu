@@ -13,6 +13,7 @@ namespace se {
 __constant__ GtDevTables c_gt;
 __constant__ float c_ibm_win[320];     // Hamming-320 of our SpecInfo restatement (se_oracle.c)
 __constant__ float c_w_fall[160], c_w_rise[160], c_w_both[160];   // resynth() raised-cosine halves
+__constant__ double c_w_fall_d[160], c_w_rise_d[160];              // the same halves as the reference's double expressions
 
 constexpr int kTile = 64;
 

@@ -23,6 +23,8 @@ int upload_g64_tables(se_ctx *ctx)
     SE_CUDA(cudaMemcpyToSymbol(c_w_fall, wf, sizeof wf));
     SE_CUDA(cudaMemcpyToSymbol(c_w_rise, wr, sizeof wr));
     SE_CUDA(cudaMemcpyToSymbol(c_w_both, wb, sizeof wb));
+    SE_CUDA(cudaMemcpyToSymbol(c_w_fall_d, h.fall_d, sizeof h.fall_d));
+    SE_CUDA(cudaMemcpyToSymbol(c_w_rise_d, h.rise_d, sizeof h.rise_d));
     return SE_OK;
 }
 

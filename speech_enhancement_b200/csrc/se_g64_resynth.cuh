@@ -74,9 +74,16 @@ __global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const int64_
                 if (MODE == SE_RESYNTH_IBM) {
                     w = (m_h != 0.0f) ? ((m_h1 != 0.0f) ? c_w_both[r] : c_w_fall[r]) : ((m_h1 != 0.0f) ? c_w_rise[r] : 0.0f);
                 } else {
+                    // weight_e[] (float) += 0.5*(1+cos(..)) * v_erm : a double product added to a float
+                    // (resyth_64sub_ori/cpp/extractwav.cpp:101-104); falling half of frame h first
                     w = 0.0f;
-                    if (m_h != 0.0f) w = __fmul_rn(c_w_fall[r], m_h);
-                    if (m_h1 != 0.0f) w = __fadd_rn(w, __fmul_rn(c_w_rise[r], m_h1));
+                    if (EXACT) {
+                        if (m_h != 0.0f) w = (float)(c_w_fall_d[r] * (double)m_h);
+                        if (m_h1 != 0.0f) w = (float)((double)w + c_w_rise_d[r] * (double)m_h1);
+                    } else {
+                        if (m_h != 0.0f) w = c_w_fall[r] * m_h;
+                        if (m_h1 != 0.0f) w += c_w_rise[r] * m_h1;
+                    }
                 }
                 tile[buf][t][c] = __fmul_rn(w, v);
                 if (--r < 0) { r = 159; h--; m_h1 = m_h; m_h = m_prev; m_prev = gate(h - 1); }

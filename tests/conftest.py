@@ -44,3 +44,16 @@ def rel_err(ref, test, floor):
     ref = np.asarray(ref, np.float64)
     test = np.asarray(test, np.float64)
     return np.abs(ref - test) / np.maximum(np.maximum(np.abs(ref), np.abs(test)), floor)
+
+
+def ceps_err(ref, test):
+    """Cepstral parity metric: |a-b| / max(|a|, |b|, s) with s = the frame's largest |c1..c12| (for c1..c12)
+    or 1e-3 (for c0, logE).  c1..c12 are DCT sums of 23 log-band energies with cancellation; element-wise
+    relative error of a coefficient that happens to be near zero says nothing about parity (the
+    reference's own float FFT carries the same rounding noise), so the scale is the frame's vector."""
+    ref = np.asarray(ref, np.float64).reshape(-1, 14)
+    test = np.asarray(test, np.float64).reshape(-1, 14)
+    floor = np.full(ref.shape, 1e-3)
+    if len(ref):
+        floor[:, :12] = np.maximum(np.max(np.abs(ref[:, :12]), axis=1, keepdims=True), 1e-3)
+    return np.abs(ref - test) / np.maximum(np.maximum(np.abs(ref), np.abs(test)), floor)

@@ -1,0 +1,135 @@
+"""The reference-named entry points of libse_b200_dropin.so (include/se_reference_api.h), driven the way
+the reference's own drivers drive them (etsi/cpp/main.cpp:55-66, aurora_etsi_test.cpp:16-141)."""
+import ctypes as C
+
+import numpy as np
+import pytest
+
+from conftest import ceps_err, rel_err, snr_db
+from speech_enhancement_b200 import api, synth
+
+pytestmark = pytest.mark.gpu
+_vp = C.c_void_p
+
+
+@pytest.fixture(scope="module")
+def dropin(ctx):
+    L = C.CDLL(api.DROPIN_PATH)
+    L.etsi_denoise.argtypes = [_vp, _vp, C.c_long]
+    L.etsi_denoise_synchronization.argtypes = [_vp, _vp, C.c_long]
+    L.rfft.argtypes = [_vp, C.c_int, C.c_int]
+    L.rfft.restype = None
+    L.AdvProcessAlloc.restype = _vp
+    L.AdvProcessAlloc.argtypes = [C.c_int]
+    L.AdvProcessInit.argtypes = [_vp]
+    L.DoAdvProcess.argtypes = [_vp, _vp, _vp, _vp]
+    L.se_adv_feature_ready.argtypes = [_vp]
+    L.AdvProcessDelete.argtypes = [C.POINTER(_vp)]
+    L.etsi_denoise_mapping_global_init.argtypes = [C.POINTER(_vp), _vp]
+    L.etsi_denoise_mapping_thread_init.argtypes = [C.POINTER(_vp), _vp]
+    L.etsi_denoise_mapping_func_Wiener.argtypes = [_vp] * 5
+    L.etsi_denoise_mapping_thread_release.argtypes = [C.POINTER(_vp)]
+    L.etsi_denoise_mapping_global_release.argtypes = [C.POINTER(_vp)]
+    L.se_resynth.argtypes = [_vp, C.c_long, _vp, C.c_int, C.c_int, _vp]
+    L.se_subband.argtypes = [_vp, C.c_long, _vp]
+    return L
+
+
+def test_etsi_denoise_signature_and_tail(dropin, oracle):
+    x = synth.utterance(1, 8000, 80 * 120 + 33)
+    out = np.full(len(x), 12345, np.int16)
+    rc = dropin.etsi_denoise(x.ctypes.data, out.ctypes.data, len(x))
+    assert rc == 0                                     # FALSE = success (AdvFrontEnd.c:205)
+    ref = oracle.etsi_denoise(x)
+    body = 80 * 120
+    assert np.abs(out[:body].astype(np.int32) - ref["den_i16"][:body]).max() <= 1
+    assert np.all(out[:320] == 0)                      # 4-call latency
+    assert np.all(out[body:] == 12345)                 # tail untouched, like the reference
+    assert dropin.etsi_denoise_16k(x.ctypes.data, out.ctypes.data, len(x)) == 1
+
+
+def test_rfft_in_place(dropin, oracle):
+    rng = np.random.default_rng(0)
+    x = (rng.standard_normal(256) * 500).astype(np.float32)
+    y = x.copy()
+    dropin.rfft(y.ctypes.data, 256, 8)
+    ref = oracle.rfft(x, 8)
+    assert np.max(np.abs(ref - y)) <= 1e-4 * np.max(np.abs(ref))
+
+
+def test_do_adv_process_frame_by_frame(dropin, oracle):
+    x = synth.utterance(2, 8000, 80 * 40)
+    ref = oracle.etsi_denoise(x, with_ceps=True)
+    h = _vp(dropin.AdvProcessAlloc(8000))
+    assert h.value
+    dropin.AdvProcessInit(h)
+    outs, feats, rets = [], [], []
+    for b in range(40):
+        frame = np.ascontiguousarray(x[b * 80:(b + 1) * 80])
+        out = np.zeros(80, np.int16)
+        feat = np.zeros(14, np.float32)
+        rets.append(dropin.DoAdvProcess(frame.ctypes.data, out.ctypes.data, feat.ctypes.data, h))
+        outs.append(out)
+        if dropin.se_adv_feature_ready(h):
+            feats.append(feat)
+    dropin.AdvProcessDelete(C.byref(h))
+    assert h.value is None
+    assert rets == [0] * 4 + [1] * 36                  # TRUE once a shift is output (NoiseSup.c:1436-1439)
+    got = np.concatenate(outs)
+    assert np.abs(got.astype(np.int32) - ref["den_i16"]).max() <= 1
+    assert len(feats) == len(ref["ceps"]) == 34
+    assert ceps_err(ref["ceps"], np.array(feats)).max() <= 1e-4
+
+
+def test_plugin_api_like_extract_wiener(dropin, oracle, tmp_path):
+    glb, thd = _vp(), _vp()
+    assert dropin.etsi_denoise_mapping_global_init(C.byref(glb), None) == 1
+    assert dropin.etsi_denoise_mapping_thread_init(C.byref(thd), glb) == 1
+
+    class In(C.Structure):
+        _fields_ = [("inData", _vp), ("dataNum", C.c_int)]
+
+    class Out(C.Structure):
+        _fields_ = [("outData", _vp)] + [(k, _vp) for k in ("var", "spec", "mel", "vadns", "fc")]
+
+    libc = C.CDLL(None)
+    libc.fopen.restype = _vp
+    libc.fopen.argtypes = [C.c_char_p, C.c_char_p]
+    libc.fclose.argtypes = [_vp]
+    s = oracle.p16_stream()
+    for chan in range(2):                              # state carries over between channel files
+        wav = synth.utterance(40 + chan, 16000, 160 * 30 + 17)
+        num = len(wav) - len(wav) % 160                # "wipe the tail", aurora_etsi_test.cpp:100-101
+        x = wav[:num].astype(np.float32)
+        nb = num // 160
+        out = np.zeros(num, np.float32)
+        fl = [np.zeros(nb, np.int32) for _ in range(5)]
+        path = str(tmp_path / ("c%d.wiener" % chan)).encode()
+        fp = libc.fopen(path, b"w")
+        i, o = In(x.ctypes.data, num), Out(out.ctypes.data, *[f.ctypes.data for f in fl])
+        rc = dropin.etsi_denoise_mapping_func_Wiener(glb, thd, C.addressof(i), C.addressof(o), fp)
+        libc.fclose(fp)
+        assert rc == 0
+        ref = s.func_wiener(x)
+        assert snr_db(ref["out"], out) >= 60.0
+        assert np.array_equal(fl[4], ref["frame_counter"])
+        rows = [l.split() for l in open(path.decode()).read().strip().split("\n")]
+        assert len(rows) == len(ref["gains"]) and all(len(r) == 25 for r in rows)
+        txt = np.array(rows, np.float64)
+        assert np.abs(txt - ref["gains"]).max() <= 2e-6 + 1e-4 * np.abs(ref["gains"]).max()
+    s.close()
+    dropin.etsi_denoise_mapping_thread_release(C.byref(thd))
+    dropin.etsi_denoise_mapping_global_release(C.byref(glb))
+    assert thd.value is None and glb.value is None
+
+
+def test_resynth_c_twin_marks_mask(dropin, oracle):
+    x = synth.utterance(3, 16000, 3200)
+    nf = api.resynth_num_frames(len(x), 0)
+    m = np.random.default_rng(5).random((nf, 64)).astype(np.float32)
+    m0 = m.copy()
+    out = np.zeros(len(x), np.int16)
+    assert dropin.se_resynth(x.ctypes.data, len(x), m.ctypes.data, nf, 0, out.ctypes.data) == 0
+    ref, mref = oracle.resynth(x, m0, 0)
+    assert np.array_equal(out, ref)
+    assert np.array_equal(m, mref)                     # > 0.5 entries overwritten with 1.0 (extractwav.cpp:99)
