@@ -51,6 +51,13 @@ int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
 void *se_host_alloc(uint64_t bytes);
 void  se_host_free(void *p);
 
+/* ---- multi-GPU sharding (host-side, no device work) ---------------------------------------------
+ * Utterances are independent, so a batch shards by contiguous utterance ranges with no collective
+ * (the reference's own N-worker model: one work item = one file,
+ * function/.../aurora_speech_enhancement/aurora_speech_enhancement.cpp:110-120).  first_utt gets
+ * n_shards+1 entries; shard k = utterances [first_utt[k], first_utt[k+1]), balanced by sample count. */
+int se_shard_plan(const int64_t *offsets, int n_utts, int n_shards, int32_t *first_utt);
+
 /* ---- kernel timing (CUDA events on the launching stream) -------------------------------------- */
 #define SE_K_NS_P8     0   /* fused NoiseSup(+CompCeps) stream kernel, 8 kHz profile  */
 #define SE_K_NS_P16    1   /* fused NoiseSup stream kernel, 16 kHz plugin profile     */

@@ -68,6 +68,7 @@ def lib():
         L.se_addnoise_batch.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int]
         L.se_rfft_batch.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int]
         L.se_gammatone_batch.argtypes = [_vp, _vp, _vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int]
+        L.se_shard_plan.argtypes = [_vp, C.c_int, C.c_int, _vp]
         L.se_get_table.argtypes = [_vp, C.c_char_p, _vp, C.c_int, C.POINTER(C.c_int)]
         _lib = L
     return _lib
@@ -98,6 +99,14 @@ def get_table(name, ctx=None):
     _check(L.se_get_table(h, name.encode(), None, 0, C.byref(cnt)), "se_get_table")
     out = np.zeros(cnt.value, np.float32)
     _check(L.se_get_table(h, name.encode(), out.ctypes.data, cnt.value, C.byref(cnt)), "se_get_table")
+    return out
+
+
+def shard_plan(offsets, n_shards):
+    """Contiguous utterance ranges balanced by sample count: int32[n_shards+1] (host-side only)."""
+    offsets = _i64(offsets)
+    out = np.zeros(n_shards + 1, np.int32)
+    _check(lib().se_shard_plan(offsets.ctypes.data, len(offsets) - 1, int(n_shards), out.ctypes.data), "se_shard_plan")
     return out
 
 

@@ -285,6 +285,22 @@ int se_ctx_reset_kernel_times(se_ctx *ctx)
 
 int64_t se_ctx_launch_count(se_ctx *ctx) { return ctx ? ctx->launches : 0; }
 
+int se_shard_plan(const int64_t *offsets, int n_utts, int n_shards, int32_t *first_utt)
+{
+    if (!offsets || !first_utt || n_utts < 0 || n_shards < 1) { set_error("se_shard_plan: bad arguments"); return SE_EINVAL; }
+    const int64_t base = offsets[0], total = offsets[n_utts] - base;
+    first_utt[0] = 0;
+    int u = 0;
+    for (int k = 1; k < n_shards; k++) {
+        const int64_t target = base + (int64_t)((__int128)total * k / n_shards);
+        while (u < n_utts && offsets[u] < target) u++;           // first boundary at or after the target
+        if (u > first_utt[k - 1] && offsets[u] - target > target - offsets[u - 1]) u--;   // nearest boundary
+        first_utt[k] = u;
+    }
+    first_utt[n_shards] = n_utts;
+    return SE_OK;
+}
+
 int64_t se_etsi_num_ceps_frames(int64_t n) { const int64_t c = n / 80 - 6; return c > 0 ? c : 0; }
 int64_t se_ibm_num_frames(int64_t n) { return n >= 320 ? (n - 320) / 160 + 1 : 0; }
 int64_t se_resynth_num_frames(int64_t n, int mode)

@@ -1,0 +1,89 @@
+"""Generates tests/golden/*.npz from oracle/_ref = the reference's OWN sources compiled in place from
+/root/reference (oracle/Makefile `make ref`).  Run in the dev container (needs /root/reference):
+
+    python tests/golden/make_golden.py
+
+The vectors pin the plain-C oracle (tests/test_oracle_golden.py) and, on the GPU box where
+/root/reference does not exist, the CUDA path (tests/test_gpu_golden.py).
+Inputs come from the deterministic generator speech_enhancement_b200/csrc/synth.c.
+"""
+import os
+import sys
+
+import numpy as np
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(os.path.dirname(HERE))
+sys.path.insert(0, ROOT)
+
+from oracle import pyoracle as po  # noqa: E402
+from speech_enhancement_b200 import synth  # noqa: E402
+
+
+def main():
+    assert po.build_ref(), "needs /root/reference"
+    rng = np.random.default_rng(20141106)
+
+    # ---- P8: etsi_denoise + re-enabled CompCeps step, with the per-call VAD trace ------------------
+    r = po.RefEtsi()
+    x = synth.utterance(3, 8000, 8000 + 33)                 # 1 s + ragged tail
+    t = r.trace(x, with_ceps=True)
+    out, rc = r.etsi_denoise(x)
+    assert rc == 0 and np.array_equal(out[:8000], t["den_i16"][:8000])
+    xz = synth.utterance(7, 8000, 4000)                      # utterance with 50 ms of leading zeros
+    tz = r.trace(xz, with_ceps=True)
+    keys = ("den_i16", "ceps", "ret", "flag_vad", "hang_over", "nb_speech", "nb_frame0", "nb_frame1", "sp_var",
+            "sp_spec", "sp_mel", "sp_vadns", "mean_en", "alfa_gf", "out_f32")
+    np.savez_compressed(os.path.join(HERE, "p8_etsi.npz"), x=x, xz=xz,
+                        **{k: t[k] for k in keys}, **{"z_" + k: tz[k] for k in keys},
+                        noise1_last=t["noise1"][-1], den2_last=t["den2"][-1])
+    tb = r.tables()
+    np.savez_compressed(os.path.join(HERE, "p8_tables.npz"), **tb)
+    fx = (rng.standard_normal((4, 256)) * 1000).astype(np.float32)
+    np.savez_compressed(os.path.join(HERE, "rfft.npz"), x256=fx, y256=np.stack([r.rfft(v, 8) for v in fx]))
+
+    # ---- P16: plugin func_Wiener, two calls on one thread instance (state carry-over) --------------
+    p = po.RefP16()
+    a = synth.utterance(5, 16000, 16000).astype(np.float32)
+    a[160 * 20:160 * 22] = 0.0                               # zero blocks in the middle
+    b = synth.utterance(6, 16000, 8000).astype(np.float32)
+    ra, rb = p.func_wiener(a, want_text=True), p.func_wiener(b)
+    fx5 = (rng.standard_normal((4, 512)) * 1000).astype(np.float32)
+    y5 = np.stack([p.rfft(v, 8) for v in fx5])               # the truncated (512, 8) schedule, SURVEY Q1
+    np.savez_compressed(os.path.join(HERE, "p16_wiener.npz"), a=a, b=b, text_a=np.array(ra["text"]),
+                        x512=fx5, y512=y5,
+                        **{"a_" + k: v for k, v in ra.items() if k != "text"},
+                        **{"b_" + k: v for k, v in rb.items()})
+    np.savez_compressed(os.path.join(HERE, "p16_tables.npz"), **p.tables())
+    p.close()
+
+    # ---- G64: channel parameters, gammatone, hair cell, subband, addnoise, resynth x3 --------------
+    g = po.RefG64("subband")
+    cf, bw, mid = g.channel_params()
+    w = synth.utterance(9, 16000, 1600)
+    imp = np.zeros(600, np.float32)
+    imp[0] = 1000.0
+    chans = [0, 17, 40, 63]
+    gt = np.stack([g.gammatone(imp, cf[c], bw[c], mid[c]) for c in chans])
+    hc = g.haircell(gt[1] * 50)
+    sub = g.subband(w)
+    _, clean, noise = synth.utterance(10, 16000, 1600, components=True)
+    an, ay = g.addnoise(clean, noise, 5)
+    res = {}
+    for name, mode in (("resynth_ibm", 0), ("resynth_ori", 1), ("resynth_1dnn", 2)):
+        gg = po.RefG64(name)
+        nf = 1600 // 160 if mode == 2 else (1600 - 320) // 160 + 1
+        m = rng.random((nf, 64)).astype(np.float32)
+        if mode:
+            m[rng.random((nf, 64)) < 0.25] = 0.0
+        o, m_after = gg.resynth(w, m)
+        res["mask%d" % mode], res["out%d" % mode], res["mask_after%d" % mode] = m, o, m_after
+    np.savez_compressed(os.path.join(HERE, "g64.npz"), cf=cf, bw=bw, mid=mid, w=w, imp=imp, chans=np.array(chans),
+                        gt=gt, hc=hc, sub=sub, clean=clean, noise=noise, an=an, ay=ay, **res)
+    for f in sorted(os.listdir(HERE)):
+        if f.endswith(".npz"):
+            print(f, os.path.getsize(os.path.join(HERE, f)))
+
+
+if __name__ == "__main__":
+    main()
