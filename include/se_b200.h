@@ -43,6 +43,11 @@ void se_ctx_destroy(se_ctx *ctx);
 /* Launch on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL restores the own stream. */
 int  se_ctx_set_stream(se_ctx *ctx, void *cuda_stream);
 int  se_ctx_sync(se_ctx *ctx);
+/* SE_MEM_HOST batch calls are pipelined: the batch is cut into contiguous utterance chunks of about
+ * chunk_bytes of input+output (default 512 MiB) but never fewer than min_utts utterances (default 1024,
+ * enough to keep the persistent warps busy); H2D, kernels and D2H of successive chunks overlap.
+ * Results do not depend on the chunking (utterances are independent). */
+int  se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts);
 /* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 24 GiB. */
 int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
 

@@ -46,6 +46,7 @@ def lib():
         L.se_ctx_sync.argtypes = [_vp]
         L.se_ctx_set_scratch_limit.argtypes = [_vp, C.c_uint64]
         L.se_ctx_profiling.argtypes = [_vp, C.c_int]
+        L.se_ctx_set_pipeline.argtypes = [_vp, C.c_uint64, C.c_int]
         L.se_ctx_kernel_time.argtypes = [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
         L.se_ctx_reset_kernel_times.argtypes = [_vp]
         L.se_ctx_launch_count.restype = C.c_int64
@@ -171,6 +172,9 @@ class Context:
 
     def set_scratch_limit(self, nbytes):
         _check(self.L.se_ctx_set_scratch_limit(self.h, int(nbytes)), "se_ctx_set_scratch_limit")
+
+    def set_pipeline(self, chunk_bytes, min_utts):
+        _check(self.L.se_ctx_set_pipeline(self.h, int(chunk_bytes), int(min_utts)), "se_ctx_set_pipeline")
 
     def profiling(self, on):
         _check(self.L.se_ctx_profiling(self.h, 1 if on else 0), "se_ctx_profiling")

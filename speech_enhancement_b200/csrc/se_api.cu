@@ -1,5 +1,6 @@
 // C ABI of libse_b200.so: context, tables upload, staging and the *_batch entry points (se_b200.h).
 #include "se_internal.h"
+#include <algorithm>
 #include <cmath>
 #include <cstdarg>
 #include <cstdio>
@@ -94,18 +95,18 @@ static int upload_cc(se_ctx *ctx)
 int ensure_stage(se_ctx *ctx, int slot, uint64_t bytes, void **out)
 {
     if (bytes == 0) bytes = 16;
-    if (ctx->stage_bytes[slot] < bytes) {
-        if (ctx->d_stage[slot]) {
-            SE_CUDA(cudaStreamSynchronize(ctx->stream));
-            SE_CUDA(cudaFree(ctx->d_stage[slot]));
-            ctx->d_stage[slot] = nullptr;
-            ctx->stage_bytes[slot] = 0;
+    if (ctx->cur->stage_bytes[slot] < bytes) {
+        if (ctx->cur->d_stage[slot]) {
+            SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
+            SE_CUDA(cudaFree(ctx->cur->d_stage[slot]));
+            ctx->cur->d_stage[slot] = nullptr;
+            ctx->cur->stage_bytes[slot] = 0;
         }
         const uint64_t want = bytes + bytes / 8;
-        SE_CUDA(cudaMalloc(&ctx->d_stage[slot], want));
-        ctx->stage_bytes[slot] = want;
+        SE_CUDA(cudaMalloc(&ctx->cur->d_stage[slot], want));
+        ctx->cur->stage_bytes[slot] = want;
     }
-    *out = ctx->d_stage[slot];
+    *out = ctx->cur->d_stage[slot];
     return SE_OK;
 }
 
@@ -113,7 +114,7 @@ int ensure_scratch(se_ctx *ctx, uint64_t bytes)
 {
     if (ctx->scratch_bytes < bytes) {
         if (ctx->d_scratch) {
-            SE_CUDA(cudaStreamSynchronize(ctx->stream));
+            SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
             SE_CUDA(cudaFree(ctx->d_scratch));
             ctx->d_scratch = nullptr;
             ctx->scratch_bytes = 0;
@@ -131,7 +132,7 @@ void prof_begin(se_ctx *ctx, int k)
     e.k = k;
     cudaEventCreate(&e.a);
     cudaEventCreate(&e.b);
-    cudaEventRecord(e.a, ctx->stream);
+    cudaEventRecord(e.a, ctx->cur->stream);
     ctx->pending.push_back(e);
 }
 
@@ -140,7 +141,7 @@ void prof_end(se_ctx *ctx, int k)
     ctx->launches++;
     (void)k;
     if (!ctx->profiling) return;
-    cudaEventRecord(ctx->pending.back().b, ctx->stream);
+    cudaEventRecord(ctx->pending.back().b, ctx->cur->stream);
 }
 
 static int drain_events(se_ctx *ctx)
@@ -188,13 +189,14 @@ int se_ctx_create(int device, se_ctx **out)
     SE_CUDA(cudaSetDevice(device));
     se_ctx *ctx = new se_ctx();
     ctx->device = device;
-    ctx->own_stream = ctx->stream = nullptr;
-    ctx->d_work_counter = nullptr;
+    ctx->own_stream = nullptr;
+    std::memset(ctx->lanes, 0, sizeof ctx->lanes);
+    ctx->cur = &ctx->lanes[0];
     ctx->d_scratch = nullptr;
     ctx->scratch_bytes = 0;
     ctx->scratch_limit = 24ull << 30;
-    std::memset(ctx->d_stage, 0, sizeof ctx->d_stage);
-    std::memset(ctx->stage_bytes, 0, sizeof ctx->stage_bytes);
+    ctx->chunk_bytes = 512ull << 20;
+    ctx->chunk_min_utts = 1024;
     ctx->profiling = 0;
     std::memset(ctx->k_ms, 0, sizeof ctx->k_ms);
     std::memset(ctx->k_launches, 0, sizeof ctx->k_launches);
@@ -203,8 +205,12 @@ int se_ctx_create(int device, se_ctx **out)
     SE_CUDA(cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     SE_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
-    ctx->stream = ctx->own_stream;
-    SE_CUDA(cudaMalloc((void **)&ctx->d_work_counter, sizeof(int)));
+    ctx->lanes[0].stream = ctx->own_stream;
+    for (int l = 0; l < kLanes; l++) {
+        if (l > 0) SE_CUDA(cudaStreamCreateWithFlags(&ctx->lanes[l].stream, cudaStreamNonBlocking));
+        SE_CUDA(cudaMalloc((void **)&ctx->lanes[l].d_work_counter, sizeof(int)));
+        SE_CUDA(cudaEventCreateWithFlags(&ctx->lanes[l].done, cudaEventDisableTiming));
+    }
     build_ns_tables_p8(ctx->h_p8);
     build_ns_tables_p16(ctx->h_p16);
     build_cc_tables(ctx->h_cc);
@@ -225,10 +231,15 @@ void se_ctx_destroy(se_ctx *ctx)
     cudaSetDevice(ctx->device);
     cudaDeviceSynchronize();
     for (void *p : ctx->table_allocs) cudaFree(p);
-    for (int i = 0; i < 16; i++)
-        if (ctx->d_stage[i]) cudaFree(ctx->d_stage[i]);
+    for (int l = 0; l < kLanes; l++) {
+        se_lane &ln = ctx->lanes[l];
+        for (int i = 0; i < 16; i++)
+            if (ln.d_stage[i]) cudaFree(ln.d_stage[i]);
+        if (ln.d_work_counter) cudaFree(ln.d_work_counter);
+        if (ln.done) cudaEventDestroy(ln.done);
+        if (l > 0 && ln.stream) cudaStreamDestroy(ln.stream);
+    }
     if (ctx->d_scratch) cudaFree(ctx->d_scratch);
-    if (ctx->d_work_counter) cudaFree(ctx->d_work_counter);
     for (auto &e : ctx->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
     delete ctx;
@@ -237,7 +248,7 @@ void se_ctx_destroy(se_ctx *ctx)
 int se_ctx_set_stream(se_ctx *ctx, void *cuda_stream)
 {
     if (!ctx) return SE_EINVAL;
-    ctx->stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
+    ctx->lanes[0].stream = cuda_stream ? reinterpret_cast<cudaStream_t>(cuda_stream) : ctx->own_stream;
     return SE_OK;
 }
 
@@ -245,7 +256,7 @@ int se_ctx_sync(se_ctx *ctx)
 {
     if (!ctx) return SE_EINVAL;
     SE_CUDA(cudaSetDevice(ctx->device));
-    SE_CUDA(cudaStreamSynchronize(ctx->stream));
+    SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
     return SE_OK;
 }
 
@@ -253,6 +264,14 @@ int se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes)
 {
     if (!ctx || bytes < (1ull << 20)) return SE_EINVAL;
     ctx->scratch_limit = bytes;
+    return SE_OK;
+}
+
+int se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts)
+{
+    if (!ctx || chunk_bytes == 0 || min_utts < 1) return SE_EINVAL;
+    ctx->chunk_bytes = chunk_bytes;
+    ctx->chunk_min_utts = min_utts;
     return SE_OK;
 }
 

@@ -4,7 +4,7 @@
 
 namespace se {
 
-// Staging slots (ctx->d_stage).  One call uses each slot for at most one array.
+// Staging slots (ctx->cur->d_stage).  One call uses each slot for at most one array.
 enum {
     kSlotOffsets = 0, kSlotOffsets2 = 1, kSlotOffsets3 = 2, kSlotIn = 3, kSlotIn2 = 4,
     kSlotOut = 5, kSlotOut2 = 6, kSlotOut3 = 7, kSlotOut4 = 8, kSlotOut5 = 9, kSlotOut6 = 10,
@@ -19,7 +19,7 @@ static int upload_offsets(se_ctx *ctx, int slot, const int64_t *h, int count, co
     void *p = nullptr;
     int rc = ensure_stage(ctx, slot, sizeof(int64_t) * (size_t)count, &p);
     if (rc) return rc;
-    SE_CUDA(cudaMemcpyAsync(p, h, sizeof(int64_t) * (size_t)count, cudaMemcpyHostToDevice, ctx->stream));
+    SE_CUDA(cudaMemcpyAsync(p, h, sizeof(int64_t) * (size_t)count, cudaMemcpyHostToDevice, ctx->cur->stream));
     *d = reinterpret_cast<const int64_t *>(p);
     return SE_OK;
 }
@@ -41,7 +41,7 @@ static int stage_in(se_ctx *ctx, int slot, const void *p, uint64_t bytes, int me
     void *s = nullptr;
     int rc = ensure_stage(ctx, slot, bytes, &s);
     if (rc) return rc;
-    if (bytes) SE_CUDA(cudaMemcpyAsync(s, p, bytes, cudaMemcpyHostToDevice, ctx->stream));
+    if (bytes) SE_CUDA(cudaMemcpyAsync(s, p, bytes, cudaMemcpyHostToDevice, ctx->cur->stream));
     *d = s;
     return SE_OK;
 }
@@ -57,14 +57,14 @@ static int stage_out(se_ctx *ctx, int slot, void *p, uint64_t bytes, int mem, bo
         int rc = ensure_stage(ctx, slot, bytes, d);
         if (rc) return rc;
     }
-    if (zero && bytes) SE_CUDA(cudaMemsetAsync(*d, 0, bytes, ctx->stream));
+    if (zero && bytes) SE_CUDA(cudaMemsetAsync(*d, 0, bytes, ctx->cur->stream));
     return SE_OK;
 }
 
 static int stage_out_copy(se_ctx *ctx, void *host, const void *dev, uint64_t bytes, int mem)
 {
     if (!host || mem == SE_MEM_DEVICE || bytes == 0) return SE_OK;
-    SE_CUDA(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->stream));
+    SE_CUDA(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
     return SE_OK;
 }
 
@@ -78,11 +78,141 @@ static int enter(se_ctx *ctx, int mem, const char *what)
 
 static int leave(se_ctx *ctx, int mem)
 {
-    if (mem == SE_MEM_HOST) SE_CUDA(cudaStreamSynchronize(ctx->stream));
+    if (mem == SE_MEM_HOST) SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
     return SE_OK;
 }
 
 #define SE_TRY(expr) do { int rc__ = (expr); if (rc__) return rc__; } while (0)
+
+
+// ------------------------------------------------------------------------------------------------
+// Shared driver of the two NoiseSup batch calls.
+//
+// SE_MEM_DEVICE: one launch on the context stream, pointers used as given.
+// SE_MEM_HOST  : the batch is cut into contiguous utterance chunks (balanced by samples); chunk c runs
+//                H2D -> kernel -> D2H in order on lane c % kLanes, so the copies of one chunk overlap the
+//                kernels of its neighbours (PCIe both directions + SMs busy at once).
+// In both modes utterances are queued longest-first inside a launch so the persistent warps finish
+// together (the reference's one-file-at-a-time loop has no such concern).
+// ------------------------------------------------------------------------------------------------
+enum { kIdxSample = 0, kIdxAux1 = 1, kIdxAux2 = 2 };
+struct NsOut {
+    void *host;            // caller's array (host or device pointer), may be NULL
+    uint64_t elem;         // bytes per indexed element
+    int index;             // which offsets array indexes it
+    bool zero;             // clear before the launch (rows the kernel may leave unwritten)
+    bool planes5;          // int32 [5][total(aux1)] layout (P16 flags)
+    int slot;
+    size_t field;          // offsetof(NsLaunch, <pointer field>)
+};
+constexpr int kSlotOrder = 11, kSlotCounts = 12;
+
+static void set_field(NsLaunch &a, size_t field, void *p) { *reinterpret_cast<void **>(reinterpret_cast<char *>(&a) + field) = p; }
+
+static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *samples, uint64_t in_elem,
+                        const int64_t *offsets, const int64_t *aux1, const int64_t *aux2, int n_utts,
+                        NsOut *outs, int n_outs, int32_t *counts, size_t counts_field, int mem)
+{
+    const int64_t *idx[3] = {offsets, aux1, aux2};
+    se_lane *lane0 = &ctx->lanes[0];
+    ctx->cur = lane0;
+    // queue order: longest utterance first within each chunk
+    uint64_t io_bytes = in_elem * (uint64_t)offsets[n_utts];
+    for (int k = 0; k < n_outs; k++)
+        if (outs[k].host) io_bytes += outs[k].elem * (uint64_t)idx[outs[k].index][n_utts] * (outs[k].planes5 ? 5 : 1);
+    int n_chunks = 1;
+    if (mem == SE_MEM_HOST) {
+        const uint64_t by_bytes = io_bytes / ctx->chunk_bytes, by_utts = (uint64_t)n_utts / (uint64_t)ctx->chunk_min_utts;
+        n_chunks = (int)std::max<uint64_t>(1, std::min<uint64_t>(std::min(by_bytes, by_utts), 32));
+    }
+    std::vector<int32_t> first(n_chunks + 1), order(n_utts);
+    SE_TRY(se_shard_plan(offsets, n_utts, n_chunks, first.data()));
+    for (int u = 0; u < n_utts; u++) order[u] = u;
+    for (int c = 0; c < n_chunks; c++)
+        std::stable_sort(order.begin() + first[c], order.begin() + first[c + 1], [&](int32_t x, int32_t y) {
+            return offsets[x + 1] - offsets[x] > offsets[y + 1] - offsets[y];
+        });
+    // whole-batch index arrays + per-utterance counters live on lane 0
+    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
+    const int64_t *d_aux1 = nullptr, *d_aux2 = nullptr;
+    SE_TRY(upload_offsets(ctx, kSlotOffsets2, aux1, n_utts + 1, &d_aux1));
+    SE_TRY(upload_offsets(ctx, kSlotOffsets3, aux2, n_utts + 1, &d_aux2));
+    if (profile == 8) { a.ceps_offsets = d_aux1; a.trace_offsets = d_aux2; } else a.block_offsets = d_aux1;
+    void *d_order = nullptr, *d_counts = nullptr;
+    SE_TRY(ensure_stage(ctx, kSlotOrder, sizeof(int32_t) * (size_t)n_utts, &d_order));
+    SE_CUDA(cudaMemcpyAsync(d_order, order.data(), sizeof(int32_t) * (size_t)n_utts, cudaMemcpyHostToDevice, lane0->stream));
+    a.order = (const int32_t *)d_order;
+    if (counts) {
+        if (mem == SE_MEM_DEVICE) d_counts = counts;
+        else SE_TRY(ensure_stage(ctx, kSlotCounts, sizeof(int32_t) * (size_t)n_utts, &d_counts));
+        set_field(a, counts_field, d_counts);
+    }
+    if (n_chunks > 1) {
+        SE_CUDA(cudaEventRecord(lane0->done, lane0->stream));
+        for (int l = 1; l < kLanes; l++) SE_CUDA(cudaStreamWaitEvent(ctx->lanes[l].stream, lane0->done, 0));
+    }
+    int rc = SE_OK;
+    for (int c = 0; c < n_chunks && rc == SE_OK; c++) {
+        const int u0 = first[c], u1 = first[c + 1];
+        if (u1 == u0) continue;
+        ctx->cur = &ctx->lanes[n_chunks > 1 ? c % kLanes : 0];
+        NsLaunch b = a;
+        b.utt_begin = u0;
+        b.n_utts = u1 - u0;
+        b.work_counter = ctx->cur->d_work_counter;
+        const int64_t lo[3] = {offsets[u0], aux1 ? aux1[u0] : 0, aux2 ? aux2[u0] : 0};
+        const int64_t hi[3] = {offsets[u1], aux1 ? aux1[u1] : 0, aux2 ? aux2[u1] : 0};
+        void *d_out[8] = {nullptr};
+        auto body = [&]() -> int {
+            if (mem == SE_MEM_HOST) {
+                b.sample_base = lo[0];
+                if (profile == 8) { b.ceps_base = lo[1]; b.trace_base = lo[2]; } else b.block_base = lo[1];
+                b.total_blocks = hi[1] - lo[1];
+                SE_TRY(stage_in(ctx, kSlotIn, (const char *)samples + in_elem * (uint64_t)lo[0],
+                                in_elem * (uint64_t)(hi[0] - lo[0]), mem, &b.samples));
+            } else {
+                b.samples = samples;
+            }
+            for (int k = 0; k < n_outs; k++) {
+                const NsOut &o = outs[k];
+                if (!o.host) continue;
+                const uint64_t cnt = (uint64_t)(hi[o.index] - lo[o.index]) * (o.planes5 ? 5 : 1);
+                if (mem == SE_MEM_HOST) SE_TRY(stage_out(ctx, o.slot, o.host, o.elem * cnt, mem, o.zero, &d_out[k]));
+                else d_out[k] = o.host;          // device arrays are written in place (caller zeroes nothing)
+                set_field(b, o.field, d_out[k]);
+            }
+            SE_TRY(profile == 8 ? launch_ns_p8(ctx, b) : launch_ns_p16(ctx, b));
+            if (mem != SE_MEM_HOST) return SE_OK;
+            for (int k = 0; k < n_outs; k++) {
+                const NsOut &o = outs[k];
+                if (!o.host) continue;
+                const uint64_t cnt = (uint64_t)(hi[o.index] - lo[o.index]);
+                if (cnt == 0) continue;
+                if (o.planes5) {
+                    const uint64_t T = (uint64_t)idx[o.index][n_utts];
+                    SE_CUDA(cudaMemcpy2DAsync((char *)o.host + o.elem * (uint64_t)lo[o.index], o.elem * T, d_out[k],
+                                              o.elem * cnt, o.elem * cnt, 5, cudaMemcpyDeviceToHost, ctx->cur->stream));
+                } else {
+                    SE_CUDA(cudaMemcpyAsync((char *)o.host + o.elem * (uint64_t)lo[o.index], d_out[k], o.elem * cnt,
+                                            cudaMemcpyDeviceToHost, ctx->cur->stream));
+                }
+            }
+            return SE_OK;
+        };
+        rc = body();
+    }
+    ctx->cur = lane0;
+    if (n_chunks > 1) {
+        for (int l = 1; l < kLanes; l++) {
+            cudaEventRecord(ctx->lanes[l].done, ctx->lanes[l].stream);
+            cudaStreamWaitEvent(lane0->stream, ctx->lanes[l].done, 0);
+        }
+    }
+    if (rc) { cudaStreamSynchronize(lane0->stream); return rc; }
+    if (counts && mem == SE_MEM_HOST)
+        SE_CUDA(cudaMemcpyAsync(counts, d_counts, sizeof(int32_t) * (size_t)n_utts, cudaMemcpyDeviceToHost, lane0->stream));
+    return leave(ctx, mem);
+}
 
 }  // namespace se
 
@@ -114,38 +244,27 @@ int se_etsi_denoise_batch(se_ctx *ctx, const int16_t *samples, const int64_t *of
     SE_TRY(check_offsets(offsets, n_utts, "se_etsi_denoise_batch"));
     if (ceps && !ceps_offsets) { set_error("se_etsi_denoise_batch: ceps needs ceps_offsets"); return SE_EINVAL; }
     if (vad_trace && !trace_offsets) { set_error("se_etsi_denoise_batch: vad_trace needs trace_offsets"); return SE_EINVAL; }
-    const int64_t base = offsets[0], total = offsets[n_utts] - base;
-    if (base != 0) { set_error("se_etsi_denoise_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    if (offsets[0] != 0) { set_error("se_etsi_denoise_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    if (ceps) SE_TRY(check_offsets(ceps_offsets, n_utts, "se_etsi_denoise_batch(ceps_offsets)"));
+    if (vad_trace) {
+        SE_TRY(check_offsets(trace_offsets, n_utts, "se_etsi_denoise_batch(trace_offsets)"));
+        for (int u = 0; u < n_utts; u++)
+            if (trace_offsets[u + 1] - trace_offsets[u] < (offsets[u + 1] - offsets[u]) / 80) {
+                set_error("se_etsi_denoise_batch: trace_offsets too small for utterance %d", u);
+                return SE_EINVAL;
+            }
+    }
     NsLaunch a;
     std::memset(&a, 0, sizeof a);
-    const uint64_t ceps_bytes = ceps ? sizeof(float) * 14 * (uint64_t)ceps_offsets[n_utts] : 0;
-    const uint64_t trace_bytes = vad_trace ? (uint64_t)trace_offsets[n_utts] : 0;
-    void *d_den = nullptr, *d_ceps = nullptr, *d_nceps = nullptr, *d_denf = nullptr, *d_trace = nullptr;
-    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
-    SE_TRY(upload_offsets(ctx, kSlotOffsets2, ceps ? ceps_offsets : nullptr, n_utts + 1, &a.ceps_offsets));
-    SE_TRY(upload_offsets(ctx, kSlotOffsets3, vad_trace ? trace_offsets : nullptr, n_utts + 1, &a.trace_offsets));
-    SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * (uint64_t)total, mem, &a.samples));
-    SE_TRY(stage_out(ctx, kSlotOut, denoised, sizeof(int16_t) * (uint64_t)total, mem, false, &d_den));
-    SE_TRY(stage_out(ctx, kSlotOut2, ceps, ceps_bytes, mem, true, &d_ceps));
-    SE_TRY(stage_out(ctx, kSlotOut3, n_ceps, sizeof(int32_t) * (uint64_t)n_utts, mem, false, &d_nceps));
-    SE_TRY(stage_out(ctx, kSlotOut4, den_f32, sizeof(float) * (uint64_t)total, mem, false, &d_denf));
-    SE_TRY(stage_out(ctx, kSlotOut5, vad_trace, trace_bytes, mem, true, &d_trace));
-    a.is_f32 = 0;
-    a.n_utts = n_utts;
-    a.den_i16 = (int16_t *)d_den;
-    a.ceps = (float *)d_ceps;
-    a.n_ceps = (int32_t *)d_nceps;
-    a.den_f32 = (float *)d_denf;
-    a.vad_trace = (uint8_t *)d_trace;
     a.zero_check = 1;
-    a.work_counter = ctx->d_work_counter;
-    SE_TRY(launch_ns_p8(ctx, a));
-    SE_TRY(stage_out_copy(ctx, denoised, d_den, sizeof(int16_t) * (uint64_t)total, mem));
-    SE_TRY(stage_out_copy(ctx, ceps, d_ceps, ceps_bytes, mem));
-    SE_TRY(stage_out_copy(ctx, n_ceps, d_nceps, sizeof(int32_t) * (uint64_t)n_utts, mem));
-    SE_TRY(stage_out_copy(ctx, den_f32, d_denf, sizeof(float) * (uint64_t)total, mem));
-    SE_TRY(stage_out_copy(ctx, vad_trace, d_trace, trace_bytes, mem));
-    return leave(ctx, mem);
+    NsOut outs[] = {
+        {denoised, sizeof(int16_t), kIdxSample, false, false, kSlotOut, offsetof(NsLaunch, den_i16)},
+        {ceps, sizeof(float) * 14, kIdxAux1, true, false, kSlotOut2, offsetof(NsLaunch, ceps)},
+        {den_f32, sizeof(float), kIdxSample, false, false, kSlotOut4, offsetof(NsLaunch, den_f32)},
+        {vad_trace, 1, kIdxAux2, true, false, kSlotOut5, offsetof(NsLaunch, vad_trace)},
+    };
+    return ns_batch_run(ctx, 8, a, samples, sizeof(int16_t), offsets, ceps ? ceps_offsets : nullptr,
+                        vad_trace ? trace_offsets : nullptr, n_utts, outs, 4, n_ceps, offsetof(NsLaunch, n_ceps), mem);
 }
 
 int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int64_t *offsets, int n_utts,
@@ -158,40 +277,26 @@ int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int6
     SE_TRY(check_offsets(offsets, n_utts, "se_p16_wiener_batch"));
     if ((flags || gains) && !block_offsets) { set_error("se_p16_wiener_batch: flags/gains need block_offsets"); return SE_EINVAL; }
     if (offsets[0] != 0) { set_error("se_p16_wiener_batch: offsets[0] must be 0"); return SE_EINVAL; }
-    if (block_offsets)
+    if (block_offsets) {
+        SE_TRY(check_offsets(block_offsets, n_utts, "se_p16_wiener_batch(block_offsets)"));
         for (int u = 0; u < n_utts; u++)
             if (block_offsets[u + 1] - block_offsets[u] < (offsets[u + 1] - offsets[u]) / 160) {
                 set_error("se_p16_wiener_batch: block_offsets too small for utterance %d", u);
                 return SE_EINVAL;
             }
-    const int64_t total = offsets[n_utts];
-    const int64_t total_blocks = block_offsets ? block_offsets[n_utts] : 0;
-    const uint64_t in_bytes = (is_f32 ? sizeof(float) : sizeof(int16_t)) * (uint64_t)total;
+    }
     NsLaunch a;
     std::memset(&a, 0, sizeof a);
-    void *d_out = nullptr, *d_flags = nullptr, *d_gains = nullptr, *d_rows = nullptr;
-    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
-    SE_TRY(upload_offsets(ctx, kSlotOffsets2, block_offsets, n_utts + 1, &a.block_offsets));
-    SE_TRY(stage_in(ctx, kSlotIn, samples, in_bytes, mem, &a.samples));
-    SE_TRY(stage_out(ctx, kSlotOut, out_f32, sizeof(float) * (uint64_t)total, mem, false, &d_out));
-    SE_TRY(stage_out(ctx, kSlotOut2, flags, sizeof(int32_t) * 5 * (uint64_t)total_blocks, mem, true, &d_flags));
-    SE_TRY(stage_out(ctx, kSlotOut3, gains, sizeof(float) * 25 * (uint64_t)total_blocks, mem, true, &d_gains));
-    SE_TRY(stage_out(ctx, kSlotOut4, n_rows, sizeof(int32_t) * (uint64_t)n_utts, mem, false, &d_rows));
     a.is_f32 = is_f32 ? 1 : 0;
-    a.n_utts = n_utts;
-    a.out_f32 = (float *)d_out;
-    a.flags = (int32_t *)d_flags;
-    a.total_blocks = total_blocks;
-    a.gains = (float *)d_gains;
-    a.n_rows = (int32_t *)d_rows;
     a.zero_check = 2;
-    a.work_counter = ctx->d_work_counter;
-    SE_TRY(launch_ns_p16(ctx, a));
-    SE_TRY(stage_out_copy(ctx, out_f32, d_out, sizeof(float) * (uint64_t)total, mem));
-    SE_TRY(stage_out_copy(ctx, flags, d_flags, sizeof(int32_t) * 5 * (uint64_t)total_blocks, mem));
-    SE_TRY(stage_out_copy(ctx, gains, d_gains, sizeof(float) * 25 * (uint64_t)total_blocks, mem));
-    SE_TRY(stage_out_copy(ctx, n_rows, d_rows, sizeof(int32_t) * (uint64_t)n_utts, mem));
-    return leave(ctx, mem);
+    a.total_blocks = block_offsets ? block_offsets[n_utts] : 0;
+    NsOut outs[] = {
+        {out_f32, sizeof(float), kIdxSample, false, false, kSlotOut, offsetof(NsLaunch, out_f32)},
+        {flags, sizeof(int32_t), kIdxAux1, true, true, kSlotOut2, offsetof(NsLaunch, flags)},
+        {gains, sizeof(float) * 25, kIdxAux1, true, false, kSlotOut3, offsetof(NsLaunch, gains)},
+    };
+    return ns_batch_run(ctx, 16, a, samples, is_f32 ? sizeof(float) : sizeof(int16_t), offsets, block_offsets, nullptr,
+                        n_utts, outs, 3, n_rows, offsetof(NsLaunch, n_rows), mem);
 }
 
 }  // extern "C"

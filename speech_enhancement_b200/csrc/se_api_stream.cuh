@@ -18,7 +18,7 @@ static int stream_reserve(se_ns_stream *s, uint64_t n_blocks)
 {
     if (n_blocks <= s->cap_blocks) return SE_OK;
     se_ctx *ctx = s->ctx;
-    SE_CUDA(cudaStreamSynchronize(ctx->stream));
+    SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
     void **bufs[] = {&s->d_in, &s->d_out, &s->d_produced, &s->d_flags, &s->d_gains, &s->d_ceps};
     for (void **b : bufs) { if (*b) cudaFree(*b); *b = nullptr; }
     s->cap_blocks = 0;
@@ -64,7 +64,7 @@ void se_ns_stream_destroy(se_ns_stream *s)
 {
     if (!s) return;
     cudaSetDevice(s->ctx->device);
-    cudaStreamSynchronize(s->ctx->stream);
+    cudaStreamSynchronize(s->ctx->cur->stream);
     void *bufs[] = {s->d_state, s->d_in, s->d_out, s->d_produced, s->d_flags, s->d_gains, s->d_rows, s->d_offsets, s->d_ceps};
     for (void *b : bufs)
         if (b) cudaFree(b);
@@ -98,8 +98,8 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
     const int shift = s->profile == 8 ? 80 : 160;
     const int64_t n = (int64_t)n_blocks * shift;
     const int64_t h_off[2] = {0, n};
-    SE_CUDA(cudaMemcpyAsync(s->d_offsets, h_off, sizeof h_off, cudaMemcpyHostToDevice, ctx->stream));
-    SE_CUDA(cudaMemcpyAsync(s->d_in, in, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, ctx->stream));
+    SE_CUDA(cudaMemcpyAsync(s->d_offsets, h_off, sizeof h_off, cudaMemcpyHostToDevice, ctx->cur->stream));
+    SE_CUDA(cudaMemcpyAsync(s->d_in, in, sizeof(float) * (size_t)n, cudaMemcpyHostToDevice, ctx->cur->stream));
     NsLaunch a;
     std::memset(&a, 0, sizeof a);
     a.samples = s->d_in;
@@ -109,7 +109,7 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
     a.state = s->d_state;
     a.load_state = s->fresh ? 0 : 1;
     a.produced = (int32_t *)s->d_produced;
-    a.work_counter = ctx->d_work_counter;
+    a.work_counter = ctx->cur->d_work_counter;
     if (s->profile == 8) {
         a.den_f32 = (float *)s->d_out;
         a.zero_check = s->zero_gate;
@@ -127,26 +127,26 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
         a.n_rows = (int32_t *)s->d_rows;
         a.block_offsets = (const int64_t *)s->d_offsets;   // {0, ...}: rows and flags start at 0
         a.zero_check = s->zero_gate;
-        SE_CUDA(cudaMemsetAsync(s->d_gains, 0, sizeof(float) * 25 * (size_t)n_blocks, ctx->stream));
+        SE_CUDA(cudaMemsetAsync(s->d_gains, 0, sizeof(float) * 25 * (size_t)n_blocks, ctx->cur->stream));
         SE_TRY(launch_ns_p16(ctx, a));
     }
     s->fresh = 0;
-    if (out) SE_CUDA(cudaMemcpyAsync(out, s->d_out, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->stream));
+    if (out) SE_CUDA(cudaMemcpyAsync(out, s->d_out, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->cur->stream));
     if (produced)
-        SE_CUDA(cudaMemcpyAsync(produced, s->d_produced, sizeof(int32_t) * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->stream));
+        SE_CUDA(cudaMemcpyAsync(produced, s->d_produced, sizeof(int32_t) * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
     if (s->profile == 8 && ceps) {
-        SE_CUDA(cudaMemcpyAsync(ceps, s->d_ceps, sizeof(float) * 14 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->stream));
-        if (n_ceps) SE_CUDA(cudaMemcpyAsync(n_ceps, s->d_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+        SE_CUDA(cudaMemcpyAsync(ceps, s->d_ceps, sizeof(float) * 14 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
+        if (n_ceps) SE_CUDA(cudaMemcpyAsync(n_ceps, s->d_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->cur->stream));
     }
     if (s->profile == 16) {
         if (flags)
-            SE_CUDA(cudaMemcpyAsync(flags, s->d_flags, sizeof(int32_t) * 5 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->stream));
+            SE_CUDA(cudaMemcpyAsync(flags, s->d_flags, sizeof(int32_t) * 5 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
         if (gains)
-            SE_CUDA(cudaMemcpyAsync(gains, s->d_gains, sizeof(float) * 25 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->stream));
+            SE_CUDA(cudaMemcpyAsync(gains, s->d_gains, sizeof(float) * 25 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
         if (n_rows)
-            SE_CUDA(cudaMemcpyAsync(n_rows, s->d_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->stream));
+            SE_CUDA(cudaMemcpyAsync(n_rows, s->d_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->cur->stream));
     }
-    SE_CUDA(cudaStreamSynchronize(ctx->stream));
+    SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
     return SE_OK;
 }
 

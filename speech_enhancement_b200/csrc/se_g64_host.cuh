@@ -32,8 +32,8 @@ int launch_subband(se_ctx *ctx, const G64Launch &a, int16_t *out)
 {
     if (a.utt_count <= 0) return SE_OK;
     prof_begin(ctx, SE_K_SUBBAND);
-    if (a.flags & SE_FLAG_EXACT) subband_kernel<true><<<a.utt_count, 64, 0, ctx->stream>>>(a.samples, a.offsets, a.utt_begin, out);
-    else subband_kernel<false><<<a.utt_count, 64, 0, ctx->stream>>>(a.samples, a.offsets, a.utt_begin, out);
+    if (a.flags & SE_FLAG_EXACT) subband_kernel<true><<<a.utt_count, 64, 0, ctx->cur->stream>>>(a.samples, a.offsets, a.utt_begin, out);
+    else subband_kernel<false><<<a.utt_count, 64, 0, ctx->cur->stream>>>(a.samples, a.offsets, a.utt_begin, out);
     prof_end(ctx, SE_K_SUBBAND);
     SE_CUDA(cudaGetLastError());
     return SE_OK;
@@ -43,7 +43,7 @@ int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, cons
 {
     if (a.utt_count <= 0) return SE_OK;
     prof_begin(ctx, SE_K_IBM);
-    ibm_kernel<<<a.utt_count, 64, 0, ctx->stream>>>(a.samples, a.samples2, a.offsets, a.utt_begin, irm,
+    ibm_kernel<<<a.utt_count, 64, 0, ctx->cur->stream>>>(a.samples, a.samples2, a.offsets, a.utt_begin, irm,
                                                      reinterpret_cast<uint32_t *>(bits), frame_offsets);
     prof_end(ctx, SE_K_IBM);
     SE_CUDA(cudaGetLastError());
@@ -55,9 +55,9 @@ static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const i
                        int64_t base, const float *mask, const int64_t *fo, int16_t *out)
 {
     if (mode == SE_RESYNTH_IBM)
-        gt_bwd_kernel<EXACT, SE_RESYNTH_IBM><<<count, 64, 0, ctx->stream>>>(Y, offsets, utt_begin, base, mask, fo, out);
+        gt_bwd_kernel<EXACT, SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, offsets, utt_begin, base, mask, fo, out);
     else
-        gt_bwd_kernel<EXACT, SE_RESYNTH_ORI><<<count, 64, 0, ctx->stream>>>(Y, offsets, utt_begin, base, mask, fo, out);
+        gt_bwd_kernel<EXACT, SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, offsets, utt_begin, base, mask, fo, out);
 }
 
 // h_offsets: host copy of the sample offsets (to chunk the batch against the scratch limit).
@@ -81,8 +81,8 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
             float *Y = reinterpret_cast<float *>(ctx->d_scratch);
             const int64_t base = h_offsets[u];
             prof_begin(ctx, SE_K_GT_FWD);
-            if (exact) gt_fwd_kernel<true><<<v - u, 64, 0, ctx->stream>>>(a.samples, a.offsets, u, base, Y);
-            else gt_fwd_kernel<false><<<v - u, 64, 0, ctx->stream>>>(a.samples, a.offsets, u, base, Y);
+            if (exact) gt_fwd_kernel<true><<<v - u, 64, 0, ctx->cur->stream>>>(a.samples, a.offsets, u, base, Y);
+            else gt_fwd_kernel<false><<<v - u, 64, 0, ctx->cur->stream>>>(a.samples, a.offsets, u, base, Y);
             prof_end(ctx, SE_K_GT_FWD);
             prof_begin(ctx, SE_K_GT_BWD);
             if (exact) launch_bwd<true>(ctx, mode, v - u, Y, a.offsets, u, base, mask, frame_offsets, out);
@@ -98,8 +98,8 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
 int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n, int count, int flags)
 {
     if (count <= 0) return SE_OK;
-    if (flags & SE_FLAG_EXACT) gammatone_kernel<true><<<(count + 63) / 64, 64, 0, ctx->stream>>>(in, out, channel, n, count);
-    else gammatone_kernel<false><<<(count + 63) / 64, 64, 0, ctx->stream>>>(in, out, channel, n, count);
+    if (flags & SE_FLAG_EXACT) gammatone_kernel<true><<<(count + 63) / 64, 64, 0, ctx->cur->stream>>>(in, out, channel, n, count);
+    else gammatone_kernel<false><<<(count + 63) / 64, 64, 0, ctx->cur->stream>>>(in, out, channel, n, count);
     ctx->launches++;
     SE_CUDA(cudaGetLastError());
     return SE_OK;
@@ -114,8 +114,8 @@ int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *n
     if (rc) return rc;
     const float db_lin = (float)std::pow(10.0, db / 10.0);
     prof_begin(ctx, SE_K_ADDNOISE);
-    addnoise_gain_kernel<<<(n_utts + 63) / 64, 64, 0, ctx->stream>>>(pure, noise, offsets, n_utts, db_lin, (float *)g);
-    addnoise_mix_kernel<<<dim3(64, n_utts), 256, 0, ctx->stream>>>(pure, noise, noisy, offsets, (const float *)g);
+    addnoise_gain_kernel<<<(n_utts + 63) / 64, 64, 0, ctx->cur->stream>>>(pure, noise, offsets, n_utts, db_lin, (float *)g);
+    addnoise_mix_kernel<<<dim3(64, n_utts), 256, 0, ctx->cur->stream>>>(pure, noise, noisy, offsets, (const float *)g);
     prof_end(ctx, SE_K_ADDNOISE);
     SE_CUDA(cudaGetLastError());
     return SE_OK;

@@ -65,8 +65,13 @@ struct NsState {
 struct NsLaunch {
     const void *samples;         // int16 or float
     int is_f32;
-    const int64_t *offsets;      // device copy, n_utts+1
-    int n_utts;
+    const int64_t *offsets;      // device copy of the WHOLE batch's offsets
+    int n_utts;                  // utterances in this launch: queue slots [utt_begin, utt_begin + n_utts)
+    int utt_begin;
+    const int32_t *order;        // optional: queue slot -> utterance index (longest first), device
+    // a launch may cover a chunk of the batch whose data pointers address chunk-local staging buffers:
+    // element index = global offset - base
+    int64_t sample_base, block_base, ceps_base, trace_base;
     // P8 outputs
     int16_t *den_i16;
     float *den_f32;
@@ -99,10 +104,26 @@ struct GtDevTables {
 
 }  // namespace se
 
+// One in-order pipeline lane: a stream with its own staging buffers and work-queue counter.  Lane 0
+// is the context's visible stream (se_ctx_set_stream); lanes 1.. exist so that SE_MEM_HOST calls can
+// overlap H2D, kernels and D2H of successive utterance chunks.
+constexpr int kLanes = 3;
+struct se_lane {
+    cudaStream_t stream;
+    int *d_work_counter;
+    void *d_stage[16];
+    uint64_t stage_bytes[16];
+    cudaEvent_t done;
+};
+
 struct se_ctx {
     int device;
     int sm_count;
-    cudaStream_t own_stream, stream;
+    cudaStream_t own_stream;
+    se_lane lanes[kLanes];
+    se_lane *cur;               // lane the launch helpers currently target
+    uint64_t chunk_bytes;       // SE_MEM_HOST pipelining: target I/O bytes per chunk
+    int chunk_min_utts;         // ... and the fewest utterances worth a launch of their own
     // tables
     se::NsTables h_p8, h_p16;
     se::CcTables h_cc;
@@ -111,12 +132,8 @@ struct se_ctx {
     se::CcDevTables d_cc;
     std::vector<void *> table_allocs;
     // scratch
-    int *d_work_counter;
     void *d_scratch;
     uint64_t scratch_bytes, scratch_limit;
-    // staging for host-memory calls
-    void *d_stage[16];
-    uint64_t stage_bytes[16];
     // profiling
     int profiling;
     struct Ev { cudaEvent_t a, b; int k; };

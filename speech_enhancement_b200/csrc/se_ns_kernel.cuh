@@ -50,9 +50,11 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         if (lane == 0) u = atomicAdd(a.work_counter, 1);
         u = __shfl_sync(0xffffffffu, u, 0);
         if (u >= a.n_utts) break;
+        u += a.utt_begin;
+        if (a.order) u = a.order[u];
 
-        const int64_t off0 = a.offsets[u], off1 = a.offsets[u + 1];
-        const int64_t n = off1 - off0;
+        const int64_t off0 = a.offsets[u] - a.sample_base;
+        const int64_t n = a.offsets[u + 1] - a.offsets[u];
         const int nblk = (int)(n / P::S);
         const IN_T *in = all + off0;
 
@@ -101,10 +103,10 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         // cepstral rows are numbered per launch: a resumed stream continues at row 0 of this push
         const int ceps_row0 = (st && a.load_state && s.nb_out2 > 2) ? s.nb_out2 - 2 : 0;
 
-        const int64_t blk0 = a.block_offsets ? a.block_offsets[u] : 0;
-        const int64_t tr0 = a.trace_offsets ? a.trace_offsets[u] : 0;
-        const int64_t ceps0 = a.ceps_offsets ? a.ceps_offsets[u] : 0;
-        const int64_t ceps_cap = a.ceps_offsets ? a.ceps_offsets[u + 1] - ceps0 : 0;
+        const int64_t blk0 = a.block_offsets ? a.block_offsets[u] - a.block_base : 0;
+        const int64_t tr0 = a.trace_offsets ? a.trace_offsets[u] - a.trace_base : 0;
+        const int64_t ceps0 = a.ceps_offsets ? a.ceps_offsets[u] - a.ceps_base : 0;
+        const int64_t ceps_cap = a.ceps_offsets ? a.ceps_offsets[u + 1] - a.ceps_offsets[u] : 0;
 
         // ---- software prefetch of the next shift (strided: coalesced) -------------------------
         float nx[P::NR];
@@ -352,9 +354,9 @@ template <int PROF, typename IN_T> static int launch_ns(se_ctx *ctx, const NsLau
     int blocks = (a.n_utts + kNsWarpsPerBlock - 1) / kNsWarpsPerBlock;
     const int cap = ctx->sm_count * per_sm;
     if (blocks > cap) blocks = cap;
-    SE_CUDA(cudaMemsetAsync(a.work_counter, 0, sizeof(int), ctx->stream));
+    SE_CUDA(cudaMemsetAsync(a.work_counter, 0, sizeof(int), ctx->cur->stream));
     prof_begin(ctx, kid);
-    kern<<<blocks, kNsWarpsPerBlock * 32, smem, ctx->stream>>>(a, tb, ctx->d_cc);
+    kern<<<blocks, kNsWarpsPerBlock * 32, smem, ctx->cur->stream>>>(a, tb, ctx->d_cc);
     prof_end(ctx, kid);
     SE_CUDA(cudaGetLastError());
     return SE_OK;
@@ -379,7 +381,7 @@ int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count)
         return SE_EUNSUPPORTED;
     }
     if (count <= 0) return SE_OK;
-    rfft_kernel<<<(count + 3) / 4, 128, 0, ctx->stream>>>(x, n, count, ctx->d_p8.tw_half);
+    rfft_kernel<<<(count + 3) / 4, 128, 0, ctx->cur->stream>>>(x, n, count, ctx->d_p8.tw_half);
     ctx->launches++;
     SE_CUDA(cudaGetLastError());
     return SE_OK;

@@ -93,3 +93,22 @@ def test_stream_carries_state_across_pushes(ctx, oracle):
         assert snr_db(ref["out"], got["out"]) >= SNR_MIN_DB
         assert rel_err(ref["gains"], got["gains"], 1e-3).max() <= GAIN_REL
         assert np.array_equal(got["flags"][4], ref["frame_counter"])
+
+
+def test_pipelined_chunks_do_not_change_results(ctx):
+    """SE_MEM_HOST calls are cut into overlapping H2D/kernel/D2H chunks on several streams; forcing tiny
+    chunks must give bit-identical outputs (P16 and P8)."""
+    samples, offsets = synth.corpus(400, 37, 16000, min_s=0.3, max_s=1.5)
+    a = ctx.p16_wiener(samples, offsets)
+    s8, o8 = synth.corpus(500, 41, 8000, min_s=0.3, max_s=1.5)
+    a8 = ctx.etsi_denoise(s8, o8, ceps=True, den_f32=True, trace=True)
+    ctx.set_pipeline(64 << 10, 3)
+    try:
+        b = ctx.p16_wiener(samples, offsets)
+        b8 = ctx.etsi_denoise(s8, o8, ceps=True, den_f32=True, trace=True)
+    finally:
+        ctx.set_pipeline(512 << 20, 1024)
+    for k in ("out", "flags", "gains", "n_rows"):
+        assert np.array_equal(a[k], b[k]), k
+    for k in ("den_i16", "ceps", "n_ceps", "den_f32", "trace"):
+        assert np.array_equal(a8[k], b8[k]), k
