@@ -27,10 +27,13 @@ __device__ __forceinline__ float warp_sum(float v)
     return v;
 }
 
-// Per-lane twiddles, computed once per kernel.
+// Per-lane twiddles, computed once per kernel.  The inter-lane stage twiddles are pre-selected per
+// lane: the lower lane of a butterfly pair keeps (a + b) and gets twiddle 1, the upper lane keeps
+// (b - a) * w, so every lane executes the same  t = b + sgn * a ;  a = t * w'  (no select, no branch).
 struct FftTw {
     float2 q1, q2, q3;        // exp(-2 pi i * lane*q / 128)
-    float2 s16, s8, s4, s2;   // exp(-2 pi i * (lane & (s-1)) / (2 s))
+    float2 s16, s8, s4, s2;   // upper lane of the span: exp(-2 pi i * (lane & (s-1)) / (2 s)); lower lane: 1
+    unsigned sign;            // bit k set: lane is the upper one at span 2^k (k = 0..4)
 };
 
 __device__ __forceinline__ float2 expmi(float frac_of_pi)   // exp(-i * pi * frac)
@@ -42,22 +45,24 @@ __device__ __forceinline__ float2 expmi(float frac_of_pi)   // exp(-i * pi * fra
 
 __device__ __forceinline__ void fft_tw_init(FftTw &t, int lane)
 {
+    const float2 one = make_float2(1.0f, 0.0f);
     t.q1 = expmi((float)lane * (1.0f / 64.0f));
     t.q2 = expmi((float)(2 * lane) * (1.0f / 64.0f));
     t.q3 = expmi((float)(3 * lane) * (1.0f / 64.0f));
-    t.s16 = expmi((float)(lane & 15) * (1.0f / 16.0f));
-    t.s8 = expmi((float)(lane & 7) * (1.0f / 8.0f));
-    t.s4 = expmi((float)(lane & 3) * (1.0f / 4.0f));
-    t.s2 = expmi((float)(lane & 1) * (1.0f / 2.0f));
+    t.s16 = (lane & 16) ? expmi((float)(lane & 15) * (1.0f / 16.0f)) : one;
+    t.s8 = (lane & 8) ? expmi((float)(lane & 7) * (1.0f / 8.0f)) : one;
+    t.s4 = (lane & 4) ? expmi((float)(lane & 3) * (1.0f / 4.0f)) : one;
+    t.s2 = (lane & 2) ? expmi((float)(lane & 1) * (1.0f / 2.0f)) : one;
+    t.sign = (unsigned)lane;
 }
 
 template <int SPAN>
-__device__ __forceinline__ void bfly(float2 &a, const float2 w, const bool upper)
+__device__ __forceinline__ void bfly(float2 &a, const float2 w, const float sgn)
 {
     const float2 b = shfl_xor2(a, SPAN);
-    const float2 sum = cadd(a, b);
-    const float2 dif = csub(b, a);     // on the upper lane: x[i] - x[i+span]
-    a = upper ? (SPAN == 1 ? dif : cmul(dif, w)) : sum;
+    // lower lane: a + b ; upper lane: (partner - own) = x[i] - x[i+span]
+    const float2 t = make_float2(fmaf(sgn, a.x, b.x), fmaf(sgn, a.y, b.y));
+    a = (SPAN == 1) ? t : cmul(t, w);
 }
 
 // In: v[j] = z[lane + 32 j].  Out: v[q] = Z[q + 4*bitrev5(lane)].
@@ -75,14 +80,18 @@ __device__ __forceinline__ void fft128_warp(float2 (&v)[4], const FftTw &t, int 
     v[2] = cmul(y2, t.q2);
     v[3] = cmul(y3, t.q3);
     // 32-point DIF across lanes
+    const float g16 = (lane & 16) ? -1.0f : 1.0f, g8 = (lane & 8) ? -1.0f : 1.0f, g4 = (lane & 4) ? -1.0f : 1.0f,
+                g2 = (lane & 2) ? -1.0f : 1.0f, g1 = (lane & 1) ? -1.0f : 1.0f;
 #pragma unroll
-    for (int q = 0; q < 4; q++) {
-        bfly<16>(v[q], t.s16, (lane & 16) != 0);
-        bfly<8>(v[q], t.s8, (lane & 8) != 0);
-        bfly<4>(v[q], t.s4, (lane & 4) != 0);
-        bfly<2>(v[q], t.s2, (lane & 2) != 0);
-        bfly<1>(v[q], t.s2, (lane & 1) != 0);
-    }
+    for (int q = 0; q < 4; q++) bfly<16>(v[q], t.s16, g16);
+#pragma unroll
+    for (int q = 0; q < 4; q++) bfly<8>(v[q], t.s8, g8);
+#pragma unroll
+    for (int q = 0; q < 4; q++) bfly<4>(v[q], t.s4, g4);
+#pragma unroll
+    for (int q = 0; q < 4; q++) bfly<2>(v[q], t.s2, g2);
+#pragma unroll
+    for (int q = 0; q < 4; q++) bfly<1>(v[q], t.s2, g1);
 }
 
 // Conflict-free padded index for the 128-entry spectrum scratch (132 float2).
