@@ -47,7 +47,13 @@ static int upload_ns(se_ctx *ctx, const NsTables &h, NsDevTables &d, int bank_ro
         st[j] = h.bank_start[j];
         ln[j] = h.bank_len[j];
         if (h.bank_len[j] > bank_rows) { set_error("filter bank row %d longer than %d", j, bank_rows); return SE_EINVAL; }
-        for (int i = 0; i < h.bank_len[j]; i++) bankT[(size_t)i * 32 + j] = h.bank[(size_t)j * h.bank_w + i];
+        if (bank_rows == 128) {
+            // P16 dense Gamma bank: float4 per (band, lane) = the lane's 4 bins {lane, lane+32, lane+64, lane+96}
+            for (int l = 0; l < 32; l++)
+                for (int r = 0; r < 4; r++) bankT[((size_t)j * 32 + l) * 4 + r] = h.bank[(size_t)j * h.bank_w + l + 32 * r];
+        } else {
+            for (int i = 0; i < h.bank_len[j]; i++) bankT[(size_t)i * 32 + j] = h.bank[(size_t)j * h.bank_w + i];
+        }
     }
     if ((rc = upload(ctx, bankT.data(), bankT.size(), &d.bankT))) return rc;
     if ((rc = upload(ctx, st, 32, &d.bank_start))) return rc;

@@ -42,9 +42,10 @@ constexpr int kTriRows = 32;     // max CompCeps triangle length (checked on the
 
 template <int PROF> struct __align__(16) WarpMem {
     using P = Prof<PROF>;
-    float ring1[P::RB];
-    float ring2[P::RB];
+    float ring1[P::RB + 16];          // 8 guard samples either side, see ring_store()
+    float ring2[P::RB + 16];
     float ring3[P::CEPS ? P::RB : 4];
+    float prev[2 * P::NB * 32];       // previous-frame PSD of both stages, [stage][r][lane]
     float2 Z[132];
     float2 Z2[PROF == 16 ? 132 : 2];
     float raw[PROF == 16 ? 260 : 4];
@@ -57,7 +58,7 @@ template <int PROF> struct __align__(16) BlockMem {
     using P = Prof<PROF>;
     float win[P::FL];
     float2 twh[132];
-    float bankT[P::BANKROWS * 32];
+    float bankT[PROF == 16 ? 25 * 32 * 4 : P::BANKROWS * 32];
     int bank_start[32], bank_len[32];
     float idctT[25 * 16];
     float firwin[12];
@@ -209,7 +210,9 @@ template <int PROF> __device__ __forceinline__ void gain_fact_stage2(Scal &s, fl
 __device__ __forceinline__ float fdiv(float a, float b)
 {
 #if SE_NS_FAST_MATH
-    return __fdividef(a, b);
+    float r;                       // MUFU.RCP + FMUL; every divisor here is >= 2e-9 (eps^2) and finite
+    asm("rcp.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(b));
+    return a * r;
 #else
     return a / b;
 #endif
@@ -218,7 +221,7 @@ __device__ __forceinline__ float fsqrt(float a)
 {
 #if SE_NS_FAST_MATH
     float r;
-    asm("sqrt.approx.f32 %0, %1;" : "=f"(r) : "f"(a));
+    asm("sqrt.approx.ftz.f32 %0, %1;" : "=f"(r) : "f"(a));
     return r;
 #else
     return sqrtf(a);
@@ -227,11 +230,10 @@ __device__ __forceinline__ float fsqrt(float a)
 
 // Decision-directed Wiener gain of one bin, etsi/cpp/NoiseSup.c:449-563 (FilterCalc).
 // psd: this frame's PSD bin, psd_mean: 2-frame mean.  Returns W; updates noise/den.
-template <int FSTAGE>
-__device__ __forceinline__ float filter_calc_bin(float psd, float psd_mean, float &noise, float &den, int nbf,
-                                                 int flag_vad, float eps)
+__device__ __forceinline__ float filter_calc_bin(const int fstage, float psd, float psd_mean, float &noise, float &den,
+                                                 int nbf, int flag_vad, float eps)
 {
-    if (FSTAGE == 1) {
+    if (fstage == 1) {
         float n2 = noise * noise;
         if (nbf < 11) {
             const float lambda = 1.0f - 1.0f / (float)nbf;
@@ -246,7 +248,7 @@ __device__ __forceinline__ float filter_calc_bin(float psd, float psd_mean, floa
     }
     const float nsig = fsqrt(psd);
     const float pm = fsqrt(psd_mean);
-    if (FSTAGE == 0) {
+    if (fstage == 0) {
         const float lambda = (nbf < 100) ? (1.0f - 1.0f / (float)nbf) : 0.99f;
         if (flag_vad == 0) {
             noise = lambda * noise + (1.0f - lambda) * pm;

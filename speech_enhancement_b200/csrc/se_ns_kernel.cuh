@@ -12,7 +12,7 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
     const int tid = threadIdx.x, nt = blockDim.x;
     for (int i = tid; i < P::FL; i += nt) bm.win[i] = tb.sig_window[i];
     for (int i = tid; i < 129; i += nt) bm.twh[i] = reinterpret_cast<const float2 *>(tb.tw_half)[i];
-    for (int i = tid; i < P::BANKROWS * 32; i += nt) bm.bankT[i] = tb.bankT[i];
+    for (int i = tid; i < (int)(sizeof(bm.bankT) / sizeof(float)); i += nt) bm.bankT[i] = tb.bankT[i];
     for (int i = tid; i < 32; i += nt) { bm.bank_start[i] = tb.bank_start[i]; bm.bank_len[i] = tb.bank_len[i]; }
     for (int i = tid; i < 25 * 16; i += nt) bm.idctT[i] = tb.idctT[i];
     for (int i = tid; i < 9; i += nt) bm.firwin[i] = tb.fir_window[i];
@@ -27,7 +27,7 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
 template <typename T> __device__ __forceinline__ float to_f32(T v) { return (float)v; }
 
 template <int PROF, typename IN_T>
-__global__ void __launch_bounds__(kNsWarpsPerBlock * 32)
+__global__ void __launch_bounds__(kNsWarpsPerBlock * 32, 2)
 ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 {
     using P = Prof<PROF>;
@@ -42,6 +42,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 
     FftTw tw;
     fft_tw_init(tw, lane);
+    IdctRegs ic;
+    idct_regs_init(ic, bm.idctT, bm.firwin, lane);
     const float eps = tb.eps;
     const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
 
@@ -60,7 +62,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 
         // ---- stream state -------------------------------------------------------------------
         Scal s;
-        float noise1[P::NB], den1[P::NB], prev1[P::NB], noise2[P::NB], den2[P::NB], prev2[P::NB];
+        float noise1[P::NB], den1[P::NB], noise2[P::NB], den2[P::NB];
+        float *ring1 = wm.ring1 + 8, *ring2 = wm.ring2 + 8;
         NsState *st = a.state ? a.state + u : nullptr;
         if (st && a.load_state) {
             s.nb_in1 = st->nb_in1; s.nb_in2 = st->nb_in2; s.nb_out2 = st->nb_out2;
@@ -78,26 +81,33 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             for (int r = 0; r < P::NB; r++) {
                 const int b = lane + 32 * r;
                 const bool v = b < P::SPEC;
-                noise1[r] = v ? st->noise1[b] : eps; den1[r] = v ? st->den1[b] : 0.0f; prev1[r] = v ? st->prev_psd1[b] : 0.0f;
-                noise2[r] = v ? st->noise2[b] : eps; den2[r] = v ? st->den2[b] : 0.0f; prev2[r] = v ? st->prev_psd2[b] : 0.0f;
+                noise1[r] = v ? st->noise1[b] : eps; den1[r] = v ? st->den1[b] : 0.0f;
+                noise2[r] = v ? st->noise2[b] : eps; den2[r] = v ? st->den2[b] : 0.0f;
+                wm.prev[r * 32 + lane] = v ? st->prev_psd1[b] : 0.0f;
+                wm.prev[(P::NB + r) * 32 + lane] = v ? st->prev_psd2[b] : 0.0f;
             }
-            for (int i = lane; i < P::RB; i += 32) {
-                wm.ring1[i] = st->ring1[i];
-                wm.ring2[i] = st->ring2[i];
-                if (P::CEPS) wm.ring3[i] = st->ring3[i];
+            for (int i = lane - 8; i < P::RB + 8; i += 32) {      // core + both guards
+                const int src = wrap<P::RB>(i);
+                ring1[i] = st->ring1[src];
+                ring2[i] = st->ring2[src];
             }
+            if (P::CEPS)
+                for (int i = lane; i < P::RB; i += 32) wm.ring3[i] = st->ring3[i];
         } else {
             scal_init(s);
 #pragma unroll
             for (int r = 0; r < P::NB; r++) {
                 noise1[r] = noise2[r] = eps;     // NoiseSup.c:948-953
-                den1[r] = den2[r] = prev1[r] = prev2[r] = 0.0f;
+                den1[r] = den2[r] = 0.0f;
+                wm.prev[r * 32 + lane] = 0.0f;
+                wm.prev[(P::NB + r) * 32 + lane] = 0.0f;
             }
-            for (int i = lane; i < P::RB; i += 32) {
+            for (int i = lane; i < P::RB + 16; i += 32) {
                 wm.ring1[i] = 0.0f;
                 wm.ring2[i] = 0.0f;
-                if (P::CEPS) wm.ring3[i] = 0.0f;
             }
+            if (P::CEPS)
+                for (int i = lane; i < P::RB; i += 32) wm.ring3[i] = 0.0f;
         }
         __syncwarp();
         // cepstral rows are numbered per launch: a resumed stream continues at row 0 of this push
@@ -145,26 +155,41 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             bool produced = false, ran0 = false;
             StageFlags fl = {0, 0, 0};
             if (process) {
-                const int nb = (s.nb_in1 & 3) * P::S;
+                const int slot = s.nb_in1 & 3;
 #pragma unroll
                 for (int r = 0; r < P::NR; r++) {
                     const int i = lane + 32 * r;
-                    if (i < P::S) wm.ring1[nb + i] = cur[r];
+                    if (i < P::S) ring_store<PROF>(ring1, slot, i, cur[r]);
                 }
                 s.nb_in1++;
                 __syncwarp();
                 float *trace = a.spec_trace ? a.spec_trace + (blk0 + b) * 6 * P::SPEC : nullptr;
-                if (s.nb_in1 - s.nb_in2 > 2) {
-                    float o0[P::CH];
-                    ns_stage<PROF, 0>(wm, bm, tw, lane, s, noise1, den1, prev1, eps, o0, fl, nullptr, trace);
-                    ran0 = true;
-                }
-                if (s.nb_in2 - s.nb_out2 > 2) {
-                    float *grow = (PROF == 16 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
-                    ns_stage<PROF, 1>(wm, bm, tw, lane, s, noise2, den2, prev2, eps, o, fl, grow, trace);
-                    s.n_rows++;
-                    produced = true;
-                    dc_offset<PROF>(o, s, lane);
+#pragma unroll 1
+                for (int fstage = 0; fstage < 2; fstage++) {
+                    // stage 0 runs from the 3rd block on, stage 1 from the 3rd stage-0 output on
+                    // (NS_NB_FRAMES_LATENCY, NoiseSup.c:1144-1196); stage 1 sees stage 0's update of nb_in2
+                    const bool run = fstage == 0 ? (s.nb_in1 - s.nb_in2 > 2) : (s.nb_in2 - s.nb_out2 > 2);
+                    if (!run) continue;
+                    float noise[P::NB], den[P::NB];
+#pragma unroll
+                    for (int r = 0; r < P::NB; r++) {
+                        noise[r] = fstage ? noise2[r] : noise1[r];
+                        den[r] = fstage ? den2[r] : den1[r];
+                    }
+                    float *grow = (PROF == 16 && fstage == 1 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
+                    ns_stage<PROF>(wm, bm, tw, ic, lane, s, noise, den, eps, fstage, o, fl, grow, trace);
+#pragma unroll
+                    for (int r = 0; r < P::NB; r++) {
+                        if (fstage) { noise2[r] = noise[r]; den2[r] = den[r]; }
+                        else { noise1[r] = noise[r]; den1[r] = den[r]; }
+                    }
+                    if (fstage == 0) {
+                        ran0 = true;
+                    } else {
+                        s.n_rows++;
+                        produced = true;
+                        dc_offset<PROF>(o, s, lane);
+                    }
                 }
             }
 
@@ -266,13 +291,13 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             for (int r = 0; r < P::NB; r++) {
                 const int b = lane + 32 * r;
                 if (b < P::SPEC) {
-                    st->noise1[b] = noise1[r]; st->den1[b] = den1[r]; st->prev_psd1[b] = prev1[r];
-                    st->noise2[b] = noise2[r]; st->den2[b] = den2[r]; st->prev_psd2[b] = prev2[r];
+                    st->noise1[b] = noise1[r]; st->den1[b] = den1[r]; st->prev_psd1[b] = wm.prev[r * 32 + lane];
+                    st->noise2[b] = noise2[r]; st->den2[b] = den2[r]; st->prev_psd2[b] = wm.prev[(P::NB + r) * 32 + lane];
                 }
             }
             for (int i = lane; i < P::RB; i += 32) {
-                st->ring1[i] = wm.ring1[i];
-                st->ring2[i] = wm.ring2[i];
+                st->ring1[i] = ring1[i];
+                st->ring2[i] = ring2[i];
                 if (P::CEPS) st->ring3[i] = wm.ring3[i];
             }
         }

@@ -122,15 +122,43 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
 
 struct StageFlags { int var, spec, mel; };
 
-template <int PROF, int FSTAGE>
-__device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, int lane, Scal &s,
-                                         float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
-                                         float (&prev)[Prof<PROF>::NB], float eps, float (&o)[Prof<PROF>::CH],
-                                         StageFlags &fl, float *gains_row, float *spec_trace)
+// Sample rings: 4 shifts of history per stage, stored with 8 guard samples on either side (a copy of the
+// other end) so the 17-tap filter reads its S+16 window with plain contiguous addresses.
+// ring points at the core: ring[-8..0) mirrors ring[RB-8..RB), ring[RB..RB+8) mirrors ring[0..8).
+template <int PROF> __device__ __forceinline__ void ring_store(float *ring, int slot, int i, float v)
 {
     using P = Prof<PROF>;
-    float *ring = FSTAGE == 0 ? wm.ring1 : wm.ring2;
-    const int cnt = FSTAGE == 0 ? s.nb_in1 : s.nb_in2;   // blocks written to this ring so far
+    ring[slot * P::S + i] = v;
+    if (slot == 3 && i >= P::S - 8) ring[i - P::S] = v;
+    if (slot == 0 && i < 8) ring[P::RB + i] = v;
+}
+
+// Per-lane registers of the 25x9 IDCT (DoMelIDCT restricted to the 9 taps DoFilterWindowing keeps):
+// lane L = t + 9 g (t < 9 taps, g < 3 groups) owns bands f = 9 g + i, i < 9.
+struct IdctRegs { float c[9]; float firwin; };
+
+__device__ __forceinline__ void idct_regs_init(IdctRegs &ic, const float *idctT /*[25][16]*/, const float *firwin9, int lane)
+{
+    const int t = lane % 9, g = lane / 9;
+#pragma unroll
+    for (int i = 0; i < 9; i++) {
+        const int f = 9 * g + i;
+        ic.c[i] = (g < 3 && f < kMel) ? idctT[f * 16 + t] : 0.0f;
+    }
+    ic.firwin = firwin9[t];
+}
+
+// One Wiener-filter stage (fstage is warp-uniform at run time: both stages share one copy of the code,
+// which halves the kernel's instruction footprint).
+template <int PROF>
+__device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, const IdctRegs &ic,
+                                         int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
+                                         float eps, const int fstage, float (&o)[Prof<PROF>::CH], StageFlags &fl,
+                                         float *gains_row, float *spec_trace)
+{
+    using P = Prof<PROF>;
+    float *ring = fstage == 0 ? wm.ring1 + 8 : wm.ring2 + 8;
+    const int cnt = fstage == 0 ? s.nb_in1 : s.nb_in2;   // blocks written to this ring so far
     const int slot_old = cnt & 3;                        // buffer[0..S)      = prvFrame
     const int cur_base = ((cnt + 1) & 3) * P::S;         // buffer[S..2S)     = curFrame
 
@@ -139,7 +167,7 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
 
     // VAD (stage 0 only looks at the signal)
     float frame_sq = 0.0f;
-    if (FSTAGE == 0) {
+    if (fstage == 0) {
 #pragma unroll
         for (int r = 0; r < P::NR; r++) {
             const int i = lane + 32 * r;
@@ -147,56 +175,73 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
         }
         frame_sq = warp_sum(frame_sq);
     }
-    vad_ns(s, FSTAGE, frame_sq);
-    const int nbf = (int)(short)(FSTAGE == 0 ? s.nb_frame0 : s.nb_frame1);   // Q2: read through int16
+    vad_ns(s, fstage, frame_sq);
+    const int nbf = (int)(short)(fstage == 0 ? s.nb_frame0 : s.nb_frame1);   // Q2: read through int16
 
     // PSDMean (NoiseSup.c:289-303) + FilterCalc per owned bin
+    float W[P::NB];
+    float *prev = wm.prev + fstage * (P::NB * 32);
     float wsum = 0.0f, wsq = 0.0f, den_sum = 0.0f, noise_sum = 0.0f;
 #pragma unroll
     for (int r = 0; r < P::NB; r++) {
         const int b = lane + 32 * r;
+        W[r] = 0.0f;
         if (b < P::SPEC) {
-            const float pm = (prev[r] + psd[r]) * 0.5f;
-            prev[r] = psd[r];
-            const float W = filter_calc_bin<FSTAGE>(psd[r], pm, noise[r], den[r], nbf, s.flag_vad, eps);
-            wm.W[b] = W;
-            if (r < P::NB - 1) { wsum += W; wsq += W * W; }
+            const float pm = (prev[r * 32 + lane] + psd[r]) * 0.5f;
+            prev[r * 32 + lane] = psd[r];
+            W[r] = filter_calc_bin(fstage, psd[r], pm, noise[r], den[r], nbf, s.flag_vad, eps);
+            if (PROF == 8) wm.W[b] = W[r];
+            if (r < P::NB - 1) { wsum += W[r]; wsq += W[r] * W[r]; }
             den_sum += den[r];
             noise_sum += noise[r];
             if (spec_trace) {
-                spec_trace[(3 * FSTAGE + 0) * P::SPEC + b] = sqrtf(psd[r]);
-                spec_trace[(3 * FSTAGE + 1) * P::SPEC + b] = noise[r];
-                spec_trace[(3 * FSTAGE + 2) * P::SPEC + b] = den[r];
+                spec_trace[(3 * fstage + 0) * P::SPEC + b] = sqrtf(psd[r]);
+                spec_trace[(3 * fstage + 1) * P::SPEC + b] = noise[r];
+                spec_trace[(3 * fstage + 2) * P::SPEC + b] = den[r];
             }
         }
     }
-    if (FSTAGE == 0) {
+    if (fstage == 0) {
         wsum = warp_sum(wsum);
         wsq = warp_sum(wsq);
         fl.var = q_var(s, wsum, wsq, P::QVAR);
     }
-    __syncwarp();
 
     // DoMelFB (etsi/cpp/MelProc.c:82-104) / DoGamma (aurora_etsi/MelProc.cpp:119-141, ignores StartingPoint)
     float mw = 0.0f;
     if constexpr (PROF == 8) {
+        __syncwarp();
         const int st = bm.bank_start[lane], len = bm.bank_len[lane];
 #pragma unroll 4
         for (int i = 0; i < P::BANKROWS; i++)
             if (i < len) mw += wm.W[st + i] * bm.bankT[i * 32 + lane];
     } else {
-#pragma unroll 4
-        for (int i = 0; i < 128; i += 4) {
-            const float4 w4 = *reinterpret_cast<const float4 *>(wm.W + i);
-            mw += w4.x * bm.bankT[(i + 0) * 32 + lane];
-            mw += w4.y * bm.bankT[(i + 1) * 32 + lane];
-            mw += w4.z * bm.bankT[(i + 2) * 32 + lane];
-            mw += w4.w * bm.bankT[(i + 3) * 32 + lane];
+        // dense 25 x 128: every lane multiplies its own 4 bins (registers) into 25 partial sums, then a
+        // butterfly reduce-scatter leaves band j's total on lane j (31 shuffles instead of 25 x 5)
+        float p[32];
+        const float4 *bank4 = reinterpret_cast<const float4 *>(bm.bankT);
+#pragma unroll
+        for (int j = 0; j < kMel; j++) {
+            const float4 c = bank4[j * 32 + lane];
+            p[j] = W[0] * c.x + W[1] * c.y + W[2] * c.z + W[3] * c.w;
         }
+#pragma unroll
+        for (int j = kMel; j < 32; j++) p[j] = 0.0f;
+#pragma unroll
+        for (int sp = 16; sp >= 1; sp >>= 1) {
+            const bool up = (lane & sp) != 0;
+#pragma unroll
+            for (int i = 0; i < sp; i++) {
+                const float send = up ? p[i] : p[i + sp];
+                const float keep = up ? p[i + sp] : p[i];
+                p[i] = keep + __shfl_xor_sync(0xffffffffu, send, sp);
+            }
+        }
+        mw = p[0];
     }
     if (lane >= kMel) mw = 0.0f;
 
-    if (FSTAGE == 0) {
+    if (fstage == 0) {
         // frame-dropping VAD statistics, NoiseSup.c:1268-1281
         const float te = warp_sum(mw);
         s.fd_spec_val = (float)((double)(te * te) - 3.0);
@@ -215,25 +260,26 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
         if (gains_row && lane < kMel) gains_row[lane] = mw;
     }
 
-    // DoMelIDCT (MelProc.c:357-378): only taps 0..8 survive DoFilterWindowing (NoiseSup.c:660-669)
-    wm.melw[lane] = mw;
-    __syncwarp();
-    if (lane < 9) {
+    // DoMelIDCT (MelProc.c:357-378): only taps 0..8 survive DoFilterWindowing (NoiseSup.c:660-669).
+    // lane t + 9 g accumulates bands 9 g .. 9 g + 8 of tap t; three partials are folded with two shuffles.
+    float h[9];
+    {
+        const int g9 = (lane / 9) * 9;
         float acc = 0.0f;
 #pragma unroll
-        for (int f = 0; f < kMel; f++) acc += wm.melw[f] * bm.idctT[f * 16 + lane];
-        wm.fir[lane] = acc * bm.firwin[lane];
-    }
-    __syncwarp();
-    float h[9];
+        for (int i = 0; i < 9; i++) acc += __shfl_sync(0xffffffffu, mw, (g9 + i) & 31) * ic.c[i];
+        acc += __shfl_down_sync(0xffffffffu, acc, 9) + __shfl_down_sync(0xffffffffu, acc, 18);
+        acc *= ic.firwin;
 #pragma unroll
-    for (int t = 0; t < 9; t++) h[t] = wm.fir[t];
+        for (int t = 0; t < 9; t++) h[t] = __shfl_sync(0xffffffffu, acc, t);
+    }
 
     // ApplyWF, NoiseSup.c:324-340: 17-tap symmetric FIR over curFrame with prv/next context
     float x[P::CH + 16];
     const int i0 = lane * P::CH;
+    const float *xin = ring + cur_base + i0 - 8;        // guard samples make this window contiguous
 #pragma unroll
-    for (int d = 0; d < P::CH + 16; d++) x[d] = ring[wrap<P::RB>(cur_base + i0 + d - 8)];
+    for (int d = 0; d < P::CH + 16; d++) x[d] = xin[d];
 #pragma unroll
     for (int t = 0; t < P::CH; t++) {
         float acc = 0.0f;
@@ -242,11 +288,11 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
         o[t] = acc;
     }
 
-    if (FSTAGE == 0) {
-        const int nb = (s.nb_in2 & 3) * P::S;
+    if (fstage == 0) {
+        const int slot = s.nb_in2 & 3;
 #pragma unroll
         for (int t = 0; t < P::CH; t++)
-            if (i0 + t < P::S) wm.ring2[nb + i0 + t] = o[t];
+            if (i0 + t < P::S) ring_store<PROF>(wm.ring2 + 8, slot, i0 + t, o[t]);
         s.nb_in2++;
     } else {
         s.nb_out2++;
