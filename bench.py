@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--utts", type=int, default=10000, help="utterances per GPU in the headline batch")
     ap.add_argument("--no-extra", action="store_true", help="skip the other_workloads section")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--profile-only", default="", choices=["", "p8", "resynth"],
+                    help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
 
 
@@ -435,6 +437,13 @@ def run_ours(args):
     ctx.set_stream(stream.cuda_stream)
     hbm, peak_src = peaks()
 
+    if args.profile_only:
+        with torch.cuda.stream(stream):
+            fn = bench_p8 if args.profile_only == "p8" else bench_resynth
+            print(json.dumps(fn(args, torch, api, ctx, dist, stream, first_u + 500000)), flush=True)
+        ctx.close()
+        dist.close()
+        return
     with torch.cuda.stream(stream):
         r = bench_p16(args, torch, api, ctx, dist, stream, first_u)
         extra = None

@@ -48,7 +48,7 @@ int  se_ctx_sync(se_ctx *ctx);
  * enough to keep the persistent warps busy); H2D, kernels and D2H of successive chunks overlap.
  * Results do not depend on the chunking (utterances are independent). */
 int  se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts);
-/* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 24 GiB. */
+/* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 48 GiB. */
 int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
 
 /* Pinned host memory for SE_MEM_HOST callers that want PCIe-rate staging (plain malloc works too,

@@ -200,7 +200,7 @@ int se_ctx_create(int device, se_ctx **out)
     ctx->cur = &ctx->lanes[0];
     ctx->d_scratch = nullptr;
     ctx->scratch_bytes = 0;
-    ctx->scratch_limit = 24ull << 30;
+    ctx->scratch_limit = 48ull << 30;
     ctx->chunk_bytes = 512ull << 20;
     ctx->chunk_min_utts = 1024;
     ctx->profiling = 0;

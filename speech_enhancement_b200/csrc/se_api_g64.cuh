@@ -91,7 +91,6 @@ int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
     const int64_t *d_fo = nullptr;
     void *d_out = nullptr;
     SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
-    SE_TRY(upload_offsets(ctx, kSlotOffsets2, frame_offsets, n_utts + 1, &d_fo));
     SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
     SE_TRY(stage_in(ctx, kSlotIn2, mask, sizeof(float) * 64 * frames, mem, &d_mask));
     SE_TRY(stage_out(ctx, kSlotOut, out, sizeof(int16_t) * total, mem, false, &d_out));
@@ -99,7 +98,7 @@ int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
     a.utt_begin = 0;
     a.utt_count = n_utts;
     a.flags = flags;
-    SE_TRY(launch_resynth(ctx, a, offsets, (const float *)d_mask, d_fo, mode, (int16_t *)d_out));
+    SE_TRY(launch_resynth(ctx, a, offsets, (const float *)d_mask, frame_offsets, mode, (int16_t *)d_out));
     SE_TRY(stage_out_copy(ctx, out, d_out, sizeof(int16_t) * total, mem));
     return leave(ctx, mem);
 }

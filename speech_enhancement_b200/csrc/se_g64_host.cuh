@@ -1,6 +1,8 @@
 // Host launchers of the G64 kernels.  Included by se_g64.cu (via se_g64_resynth.cuh).
 #pragma once
+#include <algorithm>
 #include <cmath>
+#include <vector>
 
 namespace se {
 
@@ -51,48 +53,71 @@ int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, cons
 }
 
 template <bool EXACT>
-static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const int64_t *offsets, int utt_begin,
-                       int64_t base, const float *mask, const int64_t *fo, int16_t *out)
+static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const GtItem *items, const float *mask, int16_t *out)
 {
     if (mode == SE_RESYNTH_IBM)
-        gt_bwd_kernel<EXACT, SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, offsets, utt_begin, base, mask, fo, out);
+        gt_bwd_kernel<EXACT, SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, items, mask, out);
     else
-        gt_bwd_kernel<EXACT, SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, offsets, utt_begin, base, mask, fo, out);
+        gt_bwd_kernel<EXACT, SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, items, mask, out);
 }
 
-// h_offsets: host copy of the sample offsets (to chunk the batch against the scratch limit).
+// h_offsets / h_frame_offsets: host copies (work items are planned on the host and grouped against the
+// scratch limit: one group = one forward + one reversed launch).
 int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, const float *mask,
-                   const int64_t *frame_offsets, int mode, int16_t *out)
+                   const int64_t *h_frame_offsets, int mode, int16_t *out)
 {
     const bool exact = (a.flags & SE_FLAG_EXACT) != 0;
-    int u = a.utt_begin;
     const int end = a.utt_begin + a.utt_count;
-    const uint64_t max_samples = ctx->scratch_limit / (64 * sizeof(float));
-    while (u < end) {
-        int v = u;
-        uint64_t samples = 0;
-        while (v < end && (v == u || samples + (uint64_t)(h_offsets[v + 1] - h_offsets[v]) <= max_samples)) {
-            samples += (uint64_t)(h_offsets[v + 1] - h_offsets[v]);
-            v++;
+    const int64_t max_rows = (int64_t)(ctx->scratch_limit / (64 * sizeof(float)));
+    std::vector<GtItem> items;
+    int64_t rows = 0;
+    auto flush = [&]() -> int {
+        if (items.empty()) return SE_OK;
+        int rc = ensure_scratch(ctx, (uint64_t)rows * 64 * sizeof(float));
+        if (rc) return rc;
+        void *d_items = nullptr;
+        rc = ensure_stage(ctx, 14, sizeof(GtItem) * items.size(), &d_items);
+        if (rc) return rc;
+        SE_CUDA(cudaMemcpyAsync(d_items, items.data(), sizeof(GtItem) * items.size(), cudaMemcpyHostToDevice, ctx->cur->stream));
+        SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));      // items is a host vector about to be reused
+        float *Y = reinterpret_cast<float *>(ctx->d_scratch);
+        const GtItem *it = reinterpret_cast<const GtItem *>(d_items);
+        const int count = (int)items.size();
+        prof_begin(ctx, SE_K_GT_FWD);
+        if (exact) gt_fwd_kernel<true><<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
+        else gt_fwd_kernel<false><<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
+        prof_end(ctx, SE_K_GT_FWD);
+        prof_begin(ctx, SE_K_GT_BWD);
+        if (exact) launch_bwd<true>(ctx, mode, count, Y, it, mask, out);
+        else launch_bwd<false>(ctx, mode, count, Y, it, mask, out);
+        prof_end(ctx, SE_K_GT_BWD);
+        SE_CUDA(cudaGetLastError());
+        items.clear();
+        rows = 0;
+        return SE_OK;
+    };
+    for (int u = a.utt_begin; u < end; u++) {
+        const int64_t n = h_offsets[u + 1] - h_offsets[u];
+        if (n <= 0) continue;
+        if (n > 0x7fffffff) { set_error("se_resynth_batch: utterance %d longer than 2^31 samples", u); return SE_EINVAL; }
+        const int64_t step = exact ? n : kGtChunk;
+        for (int64_t ca = 0; ca < n; ca += step) {
+            GtItem it;
+            it.sample_off = h_offsets[u];
+            it.frame_off = h_frame_offsets[u];
+            it.frames = (int32_t)(h_frame_offsets[u + 1] - h_frame_offsets[u]);
+            it.a = (int32_t)ca;
+            it.b = (int32_t)std::min<int64_t>(n, ca + step);
+            it.fs = exact ? 0 : (int32_t)std::max<int64_t>(0, ca - kGtWarm);
+            it.fe = exact ? (int32_t)n : (int32_t)std::min<int64_t>(n, (int64_t)it.b + kGtWarm);
+            const int64_t need = it.fe - it.fs;
+            if (rows + need > max_rows && !items.empty()) { int rc = flush(); if (rc) return rc; }
+            it.y_off = rows;
+            rows += need;
+            items.push_back(it);
         }
-        if (samples > 0) {
-            int rc = ensure_scratch(ctx, samples * 64 * sizeof(float));
-            if (rc) return rc;
-            float *Y = reinterpret_cast<float *>(ctx->d_scratch);
-            const int64_t base = h_offsets[u];
-            prof_begin(ctx, SE_K_GT_FWD);
-            if (exact) gt_fwd_kernel<true><<<v - u, 64, 0, ctx->cur->stream>>>(a.samples, a.offsets, u, base, Y);
-            else gt_fwd_kernel<false><<<v - u, 64, 0, ctx->cur->stream>>>(a.samples, a.offsets, u, base, Y);
-            prof_end(ctx, SE_K_GT_FWD);
-            prof_begin(ctx, SE_K_GT_BWD);
-            if (exact) launch_bwd<true>(ctx, mode, v - u, Y, a.offsets, u, base, mask, frame_offsets, out);
-            else launch_bwd<false>(ctx, mode, v - u, Y, a.offsets, u, base, mask, frame_offsets, out);
-            prof_end(ctx, SE_K_GT_BWD);
-            SE_CUDA(cudaGetLastError());
-        }
-        u = v;
     }
-    return SE_OK;
+    return flush();
 }
 
 int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n, int count, int flags)

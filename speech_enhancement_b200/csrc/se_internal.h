@@ -165,7 +165,7 @@ struct G64Launch {
 int launch_subband(se_ctx *ctx, const G64Launch &a, int16_t *out);
 int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, const int64_t *frame_offsets);
 int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, const float *mask,
-                   const int64_t *frame_offsets, int mode, int16_t *out);
+                   const int64_t *h_frame_offsets, int mode, int16_t *out);
 int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n, int count,
                      int flags);
 int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy, const int64_t *offsets,
