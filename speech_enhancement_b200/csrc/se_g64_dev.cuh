@@ -53,6 +53,27 @@ template <bool EXACT> __device__ __forceinline__ float gt_step(GtState &s, const
     return out;
 }
 
+// Default-mode step: same recurrence with FMA contraction, returns p[3] BEFORE the update without the gain
+// (callers fold gain / midEar into one scale factor).
+__device__ __forceinline__ float gt_step_raw(GtState &s, const GtCoef &c, float in)
+{
+    const float out = s.p3;
+    const float x0 = c.f1 * s.p0 - c.f2 * s.q0, y0 = c.f2 * s.p0 + c.f1 * s.q0;
+    const float x1 = c.f1 * s.p1 - c.f2 * s.q1, y1 = c.f2 * s.p1 + c.f1 * s.q1;
+    const float x2 = c.f1 * s.p2 - c.f2 * s.q2, y2 = c.f2 * s.p2 + c.f1 * s.q2;
+    const float x3 = c.f1 * s.p3 - c.f2 * s.q3, y3 = c.f2 * s.p3 + c.f1 * s.q3;
+    s.p0 = fmaf(in, c.f1, x0);
+    s.q0 = fmaf(in, c.f2, y0);
+    s.p1 = s.p0 + x1;
+    s.q1 = s.q0 + y1;
+    const float ax = x1 + x2, ay = y1 + y2;
+    s.p2 = s.p1 + ax;
+    s.q2 = s.q1 + ay;
+    s.p3 = (s.p2 + ax) + (x2 + x3);
+    s.q3 = (s.q2 + ay) + (y2 + y3);
+    return out;
+}
+
 // hairCell, resyth_64sub_IBM/cpp/extractwav.cpp:213-258.  hc[] = {ymdt,xdt,ydt,lplusrdt,rdt,gdt,hdt,c0,q0,w0}.
 struct HcState { float c, q, w; };
 __device__ __forceinline__ void hc_reset(HcState &s, const float *hc) { s.c = hc[7]; s.q = hc[8]; s.w = hc[9]; }

@@ -85,11 +85,12 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
         const int count = (int)items.size();
         prof_begin(ctx, SE_K_GT_FWD);
         if (exact) gt_fwd_kernel<true><<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
-        else gt_fwd_kernel<false><<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
+        else gt_fwd_fast_kernel<<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
         prof_end(ctx, SE_K_GT_FWD);
         prof_begin(ctx, SE_K_GT_BWD);
         if (exact) launch_bwd<true>(ctx, mode, count, Y, it, mask, out);
-        else launch_bwd<false>(ctx, mode, count, Y, it, mask, out);
+        else if (mode == SE_RESYNTH_IBM) gt_bwd_fast_kernel<SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out);
+        else gt_bwd_fast_kernel<SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out);
         prof_end(ctx, SE_K_GT_BWD);
         SE_CUDA(cudaGetLastError());
         items.clear();

@@ -120,6 +120,107 @@ __global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem
     }
 }
 
+// ---- default-mode kernels (same work items; FMA-contracted arithmetic, gain/midEar folded) --------
+__global__ void __launch_bounds__(64) gt_fwd_fast_kernel(const int16_t *samples, const GtItem *items, float *Y)
+{
+    __shared__ float s_in[2][kTile];
+    const GtItem it = items[blockIdx.x];
+    const int c = threadIdx.x;
+    const int16_t *x = samples + it.sample_off + it.fs;
+    float *y = Y + it.y_off * 64 + c;
+    const GtCoef k = load_coef(c);
+    const float scale = k.gain / k.mid;
+    GtState g; gt_reset(g);
+    const int n = it.fe - it.fs;
+    int buf = 0;
+    if (c < n) s_in[0][c] = (float)x[c];
+    for (int t0 = 0; t0 < n; t0 += kTile, buf ^= 1) {
+        const int len = (n - t0 < kTile) ? (n - t0) : kTile;
+        __syncthreads();
+        if (t0 + kTile + c < n) s_in[buf ^ 1][c] = (float)x[t0 + kTile + c];     // next tile, other buffer
+        float *yp = y + (int64_t)t0 * 64;
+        if (len == kTile) {
+#pragma unroll 16
+            for (int t = 0; t < kTile; t++) yp[t * 64] = gt_step_raw(g, k, s_in[buf][t]) * scale;
+        } else {
+            for (int t = 0; t < len; t++) yp[t * 64] = gt_step_raw(g, k, s_in[buf][t]) * scale;
+        }
+    }
+}
+
+// Reversed pass.  Tiles of 32 samples are aligned so that every tile lies inside one 160-sample hop
+// (160 = 5 x 32): the two mask values that weight a hop are fetched once per tile, and the raised-cosine
+// weight is  w = m[h+1] + (m[h] - m[h+1]) * fall[r]   (fall[r] + rise[r] = 1).
+template <int MODE>
+__global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const GtItem *items, const float *mask, int16_t *out)
+{
+    constexpr int T = 32;
+    __shared__ float tile[2][T][65];
+    const GtItem it = items[blockIdx.x];
+    const int c = threadIdx.x;
+    const float *y = Y + it.y_off * 64 + c;
+    const int frames = it.frames;
+    const float *mk = mask + it.frame_off * 64 + c;
+    int16_t *o = out + it.sample_off;
+    const GtCoef k = load_coef(c);
+    const float scale = k.gain / k.mid;                // this pass's own gain and midEar division
+    GtState g; gt_reset(g);
+
+    auto gate = [&](int f) -> float {
+        if (f < 0 || f >= frames) return 0.0f;
+        const float m = mk[(int64_t)f * 64];
+        if (MODE == SE_RESYNTH_IBM) return (m > 0.5f) ? 1.0f : 0.0f;
+        return (m > 0.0f) ? m : 0.0f;
+    };
+    // run-in over [b, fe): state only
+    int pos = it.fe - 1;
+    while (pos >= it.b) {
+        const int len = (pos - it.b + 1 < 16) ? (pos - it.b + 1) : 16;
+        const float *yp = y + (int64_t)(pos - it.fs) * 64;
+        float in[16];
+#pragma unroll
+        for (int t = 0; t < 16; t++) in[t] = (t < len) ? yp[-t * 64] : 0.0f;
+#pragma unroll
+        for (int t = 0; t < 16; t++)
+            if (t < len) (void)gt_step_raw(g, k, in[t]);
+        pos -= len;
+    }
+    int buf = 0;
+    int len = (pos >= it.a) ? (pos & 31) + 1 : 0;      // first tile ends on a multiple of 32
+    while (pos >= it.a) {
+        if (len > pos - it.a + 1) len = pos - it.a + 1;
+        const int h = pos / 160, r_top = pos - h * 160;
+        const float m_h = gate(h), m_h1 = gate(h + 1);
+        const float wa = (m_h - m_h1) * scale, wb = m_h1 * scale;
+        const float *yp = y + (int64_t)(pos - it.fs) * 64;
+        float in[T];
+        if (len == T) {
+#pragma unroll
+            for (int t = 0; t < T; t++) in[t] = yp[-t * 64];
+#pragma unroll
+            for (int t = 0; t < T; t++) {
+                const float v = gt_step_raw(g, k, in[t]);
+                tile[buf][t][c] = fmaf(wa, c_w_fall[r_top - t], wb) * v;
+            }
+        } else {
+            for (int t = 0; t < len; t++) {
+                const float v = gt_step_raw(g, k, yp[-t * 64]);
+                tile[buf][t][c] = fmaf(wa, c_w_fall[r_top - t], wb) * v;
+            }
+        }
+        __syncthreads();
+        if (c < len) {
+            float acc = 0.0f;
+#pragma unroll 16
+            for (int ch = 0; ch < 64; ch++) acc += tile[buf][c][ch];
+            o[pos - c] = cast_i16(acc);
+        }
+        pos -= len;
+        len = T;
+        buf ^= 1;
+    }
+}
+
 // ---- known-answer kernel: gammaToneFilter on float signals, one thread per signal ---------------
 template <bool EXACT>
 __global__ void gammatone_kernel(const float *in, float *out, const int32_t *channel, int64_t n, int count)
