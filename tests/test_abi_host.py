@@ -29,8 +29,9 @@ def test_c_abi_exports_every_declared_symbol():
 
 def test_dropin_exports_reference_names():
     L = C.CDLL(api.DROPIN_PATH)
-    names = _declared("se_reference_api.h")
-    for must in ("etsi_denoise", "rfft", "DoAdvProcess", "etsi_denoise_mapping_func_Wiener", "se_resynth", "se_subband"):
+    names = sorted(set(_declared("se_reference_api.h") + _declared("se_io.h")))
+    for must in ("etsi_denoise", "rfft", "DoAdvProcess", "etsi_denoise_mapping_func_Wiener", "se_resynth", "se_subband", "se_wav_read",
+                 "se_mask_reader_rows", "se_write_kaldi_matrix"):
         assert must in names
     for n in names:
         assert hasattr(L, n), "libse_b200_dropin.so does not export %s" % n
