@@ -42,6 +42,8 @@ def parse():
     ap.add_argument("--utts", type=int, default=10000, help="utterances per GPU in the headline batch")
     ap.add_argument("--no-extra", action="store_true", help="skip the other_workloads section")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
+    ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
+    ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
     ap.add_argument("--profile-only", default="", choices=["", "p8", "resynth"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
@@ -435,6 +437,8 @@ def run_ours(args):
     stream = torch.cuda.Stream()
     ctx = api.Context(local)
     ctx.set_stream(stream.cuda_stream)
+    if args.chunk_mb or args.chunk_utts:
+        ctx.set_pipeline((args.chunk_mb or 512) << 20, args.chunk_utts or 1024)
     hbm, peak_src = peaks()
 
     if args.profile_only:

@@ -24,6 +24,13 @@ __device__ __forceinline__ GtCoef load_coef(int c)
     return k;
 }
 
+__device__ __forceinline__ GtRot load_rot(int c)
+{
+    GtRot k;
+    k.rho = c_gt.rho[c]; k.rho2 = 2.0f * k.rho; k.rc = c_gt.rot_c[c]; k.rs = c_gt.rot_s[c]; k.turns = c_gt.turns[c];
+    return k;
+}
+
 // ------------------------------------------------------------------------------------------------
 // subbband(): gammatone -> hair cell -> (short), 64 channel-major rows per utterance
 // (enhancement_extract_subband_linux/cpp/extractwav.cpp:36-97)

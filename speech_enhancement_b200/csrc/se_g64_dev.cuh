@@ -74,6 +74,50 @@ __device__ __forceinline__ float gt_step_raw(GtState &s, const GtCoef &c, float 
     return out;
 }
 
+// Rotating-frame form of the same recurrence for the default mode.  With c_k = p_k + i q_k and the pole
+// z = rho e^{i theta}, substitute c_k[n] = e^{i theta n} d_k[n]: the four complex rotations z * c_k (16 real
+// operations per sample) become four real scalings by rho that fold into the binomial sums as FMAs, at the
+// price of modulating the input and demodulating the output with the phasor e^{-+ i theta n}:
+//   d0' = rho (x e^{-i theta n} + d0);  d1' = d0' + rho d1;  d2' = d1' + rho d1 + rho d2;
+//   d3' = d2' + rho d1 + 2 rho d2 + rho d3;  out[n] = Re(e^{i theta n} d3[n])
+// 22 FP32 operations per sample instead of 31.  The phasor is advanced by one complex multiply per sample
+// and re-seeded from a double-precision angle at every tile start (gt_rot_seed), so it cannot drift.
+struct GtRot { float rho, rho2, rc, rs; double turns; };
+struct GtStateR { float d0r, d0i, d1r, d1i, d2r, d2i, d3r, d3i, pr, pi; };
+
+__device__ __forceinline__ void gtr_reset(GtStateR &s)
+{
+    s.d0r = s.d0i = s.d1r = s.d1i = s.d2r = s.d2i = s.d3r = s.d3i = 0.0f;
+    s.pr = 1.0f;
+    s.pi = 0.0f;
+}
+
+// phasor (cos, sin)(theta * n) for step index n since the filter was started from rest
+__device__ __forceinline__ void gt_rot_seed(GtStateR &s, const GtRot &k, int n)
+{
+    const double x = k.turns * (double)n;
+    const float frac = (float)(x - floor(x));
+    sincospif(2.0f * frac, &s.pi, &s.pr);
+}
+
+// returns d3 demodulated BEFORE the update (the one-sample delay of the reference), without the gain
+__device__ __forceinline__ float gt_step_rot(GtStateR &s, const GtRot &k, float in)
+{
+    const float out = s.pr * s.d3r - s.pi * s.d3i;
+    const float n0r = k.rho * fmaf(in, s.pr, s.d0r);
+    const float n0i = k.rho * fmaf(-in, s.pi, s.d0i);
+    const float n1r = fmaf(k.rho, s.d1r, n0r), n1i = fmaf(k.rho, s.d1i, n0i);
+    const float n2r = fmaf(k.rho, s.d2r, fmaf(k.rho, s.d1r, n1r));
+    const float n2i = fmaf(k.rho, s.d2i, fmaf(k.rho, s.d1i, n1i));
+    const float n3r = fmaf(k.rho, s.d3r, fmaf(k.rho2, s.d2r, fmaf(k.rho, s.d1r, n2r)));
+    const float n3i = fmaf(k.rho, s.d3i, fmaf(k.rho2, s.d2i, fmaf(k.rho, s.d1i, n2i)));
+    s.d0r = n0r; s.d0i = n0i; s.d1r = n1r; s.d1i = n1i; s.d2r = n2r; s.d2i = n2i; s.d3r = n3r; s.d3i = n3i;
+    const float pr = s.pr * k.rc - s.pi * k.rs;
+    s.pi = s.pr * k.rs + s.pi * k.rc;
+    s.pr = pr;
+    return out;
+}
+
 // hairCell, resyth_64sub_IBM/cpp/extractwav.cpp:213-258.  hc[] = {ymdt,xdt,ydt,lplusrdt,rdt,gdt,hdt,c0,q0,w0}.
 struct HcState { float c, q, w; };
 __device__ __forceinline__ void hc_reset(HcState &s, const float *hc) { s.c = hc[7]; s.q = hc[8]; s.w = hc[9]; }

@@ -12,6 +12,14 @@ int upload_g64_tables(se_ctx *ctx)
     GtDevTables d;
     for (int c = 0; c < kGtChannels; c++) { d.f1[c] = h.f1[c]; d.f2[c] = h.f2[c]; d.gain[c] = h.gain[c]; d.mid[c] = h.mid[c]; }
     for (int i = 0; i < 16; i++) d.hc[i] = h.hc[i];
+    for (int c = 0; c < kGtChannels; c++) {
+        const double re = (double)h.f1[c], im = (double)h.f2[c];
+        const double r = std::hypot(re, im), th = std::atan2(im, re);
+        d.rho[c] = (float)r;
+        d.rot_c[c] = (float)(re / r);
+        d.rot_s[c] = (float)(im / r);
+        d.turns[c] = th / 6.283185307179586476925287;
+    }
     SE_CUDA(cudaMemcpyToSymbol(c_gt, &d, sizeof d));
     float win[320], wf[160], wr[160], wb[160];
     // Hamming-320 of the SpecInfo restatement: 0.54 - 0.46 cos(2 pi k / 319)

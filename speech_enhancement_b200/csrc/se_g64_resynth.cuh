@@ -128,9 +128,9 @@ __global__ void __launch_bounds__(64) gt_fwd_fast_kernel(const int16_t *samples,
     const int c = threadIdx.x;
     const int16_t *x = samples + it.sample_off + it.fs;
     float *y = Y + it.y_off * 64 + c;
-    const GtCoef k = load_coef(c);
-    const float scale = k.gain / k.mid;
-    GtState g; gt_reset(g);
+    const GtRot k = load_rot(c);
+    const float scale = c_gt.gain[c] / c_gt.mid[c];
+    GtStateR g; gtr_reset(g);
     const int n = it.fe - it.fs;
     int buf = 0;
     if (c < n) s_in[0][c] = (float)x[c];
@@ -139,11 +139,12 @@ __global__ void __launch_bounds__(64) gt_fwd_fast_kernel(const int16_t *samples,
         __syncthreads();
         if (t0 + kTile + c < n) s_in[buf ^ 1][c] = (float)x[t0 + kTile + c];     // next tile, other buffer
         float *yp = y + (int64_t)t0 * 64;
+        gt_rot_seed(g, k, t0);
         if (len == kTile) {
 #pragma unroll 16
-            for (int t = 0; t < kTile; t++) yp[t * 64] = gt_step_raw(g, k, s_in[buf][t]) * scale;
+            for (int t = 0; t < kTile; t++) yp[t * 64] = gt_step_rot(g, k, s_in[buf][t]) * scale;
         } else {
-            for (int t = 0; t < len; t++) yp[t * 64] = gt_step_raw(g, k, s_in[buf][t]) * scale;
+            for (int t = 0; t < len; t++) yp[t * 64] = gt_step_rot(g, k, s_in[buf][t]) * scale;
         }
     }
 }
@@ -162,9 +163,10 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
     const int frames = it.frames;
     const float *mk = mask + it.frame_off * 64 + c;
     int16_t *o = out + it.sample_off;
-    const GtCoef k = load_coef(c);
-    const float scale = k.gain / k.mid;                // this pass's own gain and midEar division
-    GtState g; gt_reset(g);
+    const GtRot k = load_rot(c);
+    const float scale = c_gt.gain[c] / c_gt.mid[c];    // this pass's own gain and midEar division
+    GtStateR g; gtr_reset(g);
+    int step = 0;                                      // samples filtered since the start from rest
 
     auto gate = [&](int f) -> float {
         if (f < 0 || f >= frames) return 0.0f;
@@ -180,10 +182,12 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
         float in[16];
 #pragma unroll
         for (int t = 0; t < 16; t++) in[t] = (t < len) ? yp[-t * 64] : 0.0f;
+        gt_rot_seed(g, k, step);
 #pragma unroll
         for (int t = 0; t < 16; t++)
-            if (t < len) (void)gt_step_raw(g, k, in[t]);
+            if (t < len) (void)gt_step_rot(g, k, in[t]);
         pos -= len;
+        step += len;
     }
     int buf = 0;
     int len = (pos >= it.a) ? (pos & 31) + 1 : 0;      // first tile ends on a multiple of 32
@@ -194,17 +198,18 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
         const float wa = (m_h - m_h1) * scale, wb = m_h1 * scale;
         const float *yp = y + (int64_t)(pos - it.fs) * 64;
         float in[T];
+        gt_rot_seed(g, k, step);
         if (len == T) {
 #pragma unroll
             for (int t = 0; t < T; t++) in[t] = yp[-t * 64];
 #pragma unroll
             for (int t = 0; t < T; t++) {
-                const float v = gt_step_raw(g, k, in[t]);
+                const float v = gt_step_rot(g, k, in[t]);
                 tile[buf][t][c] = fmaf(wa, c_w_fall[r_top - t], wb) * v;
             }
         } else {
             for (int t = 0; t < len; t++) {
-                const float v = gt_step_raw(g, k, yp[-t * 64]);
+                const float v = gt_step_rot(g, k, yp[-t * 64]);
                 tile[buf][t][c] = fmaf(wa, c_w_fall[r_top - t], wb) * v;
             }
         }
@@ -216,6 +221,7 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
             o[pos - c] = cast_i16(acc);
         }
         pos -= len;
+        step += len;
         len = T;
         buf ^= 1;
     }

@@ -100,6 +100,10 @@ struct NsLaunch {
 struct GtDevTables {
     float f1[kGtChannels], f2[kGtChannels], gain[kGtChannels], mid[kGtChannels];
     float hc[16];
+    // polar form of the pole z = f1 + i f2 (taken from the FLOAT f1, f2 the reference filters with):
+    // radius, unit rotation (cos, sin) and angle in turns, for the rotating-frame default-mode kernels
+    float rho[kGtChannels], rot_c[kGtChannels], rot_s[kGtChannels];
+    double turns[kGtChannels];
 };
 
 }  // namespace se
