@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
     ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
-    ap.add_argument("--profile-only", default="", choices=["", "p8", "resynth"],
+    ap.add_argument("--profile-only", default="", choices=["", "p8", "resynth", "ibm"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
 
@@ -264,7 +264,7 @@ def bench_p16(args, torch, api, ctx, dist, stream, first_u):
                 samples=samples, offsets=offsets)
 
 
-def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=2000):
+def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000):
     """P8: ETSI NoiseSup + CompCeps on 10 s 8 kHz utterances (C1-type work, batched)."""
     samples, offsets = make_corpus(first_u, n_utts, 8000, 0, 0, seconds=10.0)
     total = int(offsets[-1])
@@ -293,6 +293,46 @@ def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=2000):
     gbs = hops * P8_BYTES_PER_HOP / (k_ms / max(k_n, 1) * 1e-3) / 1e9
     return {"workload": "P8 etsi NoiseSup+CompCeps, %d x 10 s 8 kHz" % n_utts, "xrt": audio_s * args.steps / (ms * 1e-3),
             "ms_per_step": ms / args.steps, "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
+
+
+def bench_ibm(args, torch, api, ctx, dist, stream, first_u, n_utts=2000, seconds=5.0):
+    """G64: fused subbband(pure) + subbband(noise) + make_single_IBM -> IRM + packed IBM bits (exact mode)."""
+    from speech_enhancement_b200 import synth
+    n = int(seconds * 16000)
+    offsets = np.arange(n_utts + 1, dtype=np.int64) * n
+    pure = np.empty(n_utts * n, np.int16)
+    noise = np.empty(n_utts * n, np.int16)
+    L = synth._load()
+
+    def gen(i):
+        L.se_synth_utterance(first_u + i, 16000, n, None, pure[i * n:].ctypes.data, noise[i * n:].ctypes.data)
+
+    with ThreadPoolExecutor(max_workers=max(1, min(32, os.cpu_count() or 1))) as ex:
+        list(ex.map(gen, range(n_utts)))
+    nf = api.ibm_num_frames(n)
+    fo = np.arange(n_utts + 1, dtype=np.int64) * nf
+    d_p, d_n = dev(torch, pure), dev(torch, noise)
+    d_irm = torch.empty(n_utts * nf * 64, dtype=torch.float32, device="cuda")
+    d_bits = torch.empty(n_utts * nf, dtype=torch.int64, device="cuda")
+
+    def step():
+        ctx.ibm_raw(d_p.data_ptr(), d_n.data_ptr(), offsets, n_utts, d_irm.data_ptr(), d_bits.data_ptr(), fo,
+                    mem=api.SE_MEM_DEVICE)
+
+    step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    steps = min(args.steps, 2)
+    ms = timed_steps(torch, dist, stream, step, 0, steps)
+    k_ms, k_n = ctx.kernel_time(api.K_IBM)
+    ctx.profiling(False)
+    audio_s = n_utts * seconds
+    hbm, _ = peaks()
+    gbs = (2 * 2 * n_utts * n + n_utts * nf * (256 + 8)) / (k_ms / max(k_n, 1) * 1e-3) / 1e9
+    return {"workload": "G64 subband x2 + make_single_IBM (exact), %d x %.0f s 16 kHz" % (n_utts, seconds),
+            "xrt": audio_s * steps / (ms * 1e-3), "ms_per_step": ms / steps, "kernel_ms": k_ms / max(k_n, 1),
+            "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
 def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
@@ -443,7 +483,7 @@ def run_ours(args):
 
     if args.profile_only:
         with torch.cuda.stream(stream):
-            fn = bench_p8 if args.profile_only == "p8" else bench_resynth
+            fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm}[args.profile_only]
             print(json.dumps(fn(args, torch, api, ctx, dist, stream, first_u + 500000)), flush=True)
         ctx.close()
         dist.close()
@@ -453,7 +493,8 @@ def run_ours(args):
         extra = None
         if not args.no_extra and args.gpus == 1:
             extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000),
-                     bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000)]
+                     bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000),
+                     bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000)]
     audio_all = dist.sum(r["audio_s"])
     value = audio_all * args.steps / (r["ms"] * 1e-3)
     e2e = audio_all * args.steps / (r["e2e_ms"] * 1e-3)
