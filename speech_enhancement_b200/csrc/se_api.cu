@@ -46,7 +46,10 @@ static int upload_ns(se_ctx *ctx, const NsTables &h, NsDevTables &d, int bank_ro
     for (int j = 0; j < kMel; j++) {
         st[j] = h.bank_start[j];
         ln[j] = h.bank_len[j];
-        if (h.bank_len[j] > bank_rows) { set_error("filter bank row %d longer than %d", j, bank_rows); return SE_EINVAL; }
+        if (h.bank_len[j] > bank_rows || (bank_rows != 128 && h.bank_len[j] > 10)) {   // kMelTaps (se_ns_stage.cuh)
+            set_error("filter bank row %d too long (%d)", j, h.bank_len[j]);
+            return SE_EINVAL;
+        }
         if (bank_rows == 128) {
             // P16 dense Gamma bank: float4 per (band, lane) = the lane's 4 bins {lane, lane+32, lane+64, lane+96}
             for (int l = 0; l < 32; l++)
@@ -85,7 +88,10 @@ static int upload_cc(se_ctx *ctx)
     for (int j = 0; j < 23; j++) {
         st[j] = h.start[j];
         ln[j] = h.len[j];
-        if (h.len[j] > 32) { set_error("CompCeps triangle %d longer than 32", j); return SE_EINVAL; }
+        if (h.len[j] > 32 || h.len[j] > (j >= 14 ? 24 : 12)) {   // 2 x kTriTaps for the bands that are split over two lanes
+            set_error("CompCeps triangle %d too long (%d)", j, h.len[j]);
+            return SE_EINVAL;
+        }
         for (int i = 0; i < h.len[j]; i++) triT[i * 32 + j] = h.tri[j][i];
     }
     if ((rc = upload(ctx, triT.data(), triT.size(), &d.triT))) return rc;

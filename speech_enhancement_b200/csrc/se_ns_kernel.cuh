@@ -44,6 +44,10 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     fft_tw_init(tw, lane);
     IdctRegs ic;
     idct_regs_init(ic, bm.idctT, bm.firwin, lane);
+    BankRegs br;
+    if constexpr (PROF == 8) bank_regs_init(br, bm, lane);
+    else { br.mel_st = br.tri_st = 0; }
+    for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;       // zero-weight taps may read past the spectrum
     const float eps = tb.eps;
     const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
 
@@ -177,7 +181,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         den[r] = fstage ? den2[r] : den1[r];
                     }
                     float *grow = (PROF == 16 && fstage == 1 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
-                    ns_stage<PROF>(wm, bm, tw, ic, lane, s, noise, den, eps, fstage, o, fl, grow, trace);
+                    ns_stage<PROF>(wm, bm, tw, ic, br, lane, s, noise, den, eps, fstage, o, fl, grow, trace);
 #pragma unroll
                     for (int r = 0; r < P::NB; r++) {
                         if (fstage) { noise2[r] = noise[r]; den2[r] = den[r]; }
@@ -226,7 +230,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     // third denoised shift onwards: frame m = nb_out2-3 (ParmInterface.c:275-293)
                     const int m = s.nb_out2 - 3;
                     if (m - ceps_row0 < ceps_cap)
-                        comp_ceps(wm, bm, tw, lane, (m & 3) * P::S, a.ceps + (ceps0 + m - ceps_row0) * 14);
+                        comp_ceps(wm, bm, tw, br, lane, (m & 3) * P::S, a.ceps + (ceps0 + m - ceps_row0) * 14);
                     s.n_ceps = m + 1;
                 }
                 if (a.vad_trace && lane == 0) {

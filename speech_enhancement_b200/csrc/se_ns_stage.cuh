@@ -148,11 +148,34 @@ __device__ __forceinline__ void idct_regs_init(IdctRegs &ic, const float *idctT 
     ic.firwin = firwin9[t];
 }
 
+// Sparse filter banks of the 8 kHz profile held as per-lane tap registers (weights zero-padded, so the
+// loops need no predicate): the 25 NoiseSup mel triangles (<= 10 taps, lane = band) and the 23 CompCeps
+// triangles (<= 22 taps: lane j < 23 takes taps 0..11 of band j, lane j + 9 (23..31) takes taps 12..23 of
+// bands 14..22; one shuffle folds the halves).
+constexpr int kMelTaps = 10, kTriTaps = 12;
+struct BankRegs {
+    int mel_st, tri_st;
+    float mel[kMelTaps], tri[kTriTaps];
+};
+
+__device__ __forceinline__ void bank_regs_init(BankRegs &br, const BlockMem<8> &bm, int lane)
+{
+    br.mel_st = bm.bank_start[lane];
+    const int ml = bm.bank_len[lane];
+#pragma unroll
+    for (int i = 0; i < kMelTaps; i++) br.mel[i] = (i < ml) ? bm.bankT[i * 32 + lane] : 0.0f;
+    const int band = lane < 23 ? lane : lane - 9, t0 = lane < 23 ? 0 : kTriTaps;
+    br.tri_st = bm.tri_start[band] + t0;
+    const int tl = bm.tri_len[band];
+#pragma unroll
+    for (int i = 0; i < kTriTaps; i++) br.tri[i] = (t0 + i < tl) ? bm.triT[(t0 + i) * 32 + band] : 0.0f;
+}
+
 // One Wiener-filter stage (fstage is warp-uniform at run time: both stages share one copy of the code,
 // which halves the kernel's instruction footprint).
 template <int PROF>
 __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, const IdctRegs &ic,
-                                         int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
+                                         const BankRegs &br, int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
                                          float eps, const int fstage, float (&o)[Prof<PROF>::CH], StageFlags &fl,
                                          float *gains_row, float *spec_trace)
 {
@@ -211,10 +234,8 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
     float mw = 0.0f;
     if constexpr (PROF == 8) {
         __syncwarp();
-        const int st = bm.bank_start[lane], len = bm.bank_len[lane];
-#pragma unroll 4
-        for (int i = 0; i < P::BANKROWS; i++)
-            if (i < len) mw += wm.W[st + i] * bm.bankT[i * 32 + lane];
+#pragma unroll
+        for (int i = 0; i < kMelTaps; i++) mw = fmaf(wm.W[br.mel_st + i], br.mel[i], mw);
     } else {
         // dense 25 x 128: every lane multiplies its own 4 bins (registers) into 25 partial sums, then a
         // butterfly reduce-scatter leaves band j's total on lane j (31 shuffles instead of 25 x 5)
@@ -346,7 +367,7 @@ template <int PROF> __device__ __forceinline__ void dc_offset(float (&o)[Prof<PR
 
 // WI8CompCeps (etsi/cpp/CompCeps.c:368-549) on the 200-sample frame that starts `base` (ring3
 // position of frame sample 0); ring3 holds the float denoised stream.
-__device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, int lane, int base,
+__device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, int base,
                                           float *row)
 {
     using P = Prof<8>;
@@ -384,10 +405,11 @@ __device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm,
     __syncwarp();
     // 23 mel triangles (DoMelFB, MelProc.c:82-104), ln with floor (:509-513)
     float fb = 0.0f;
+#pragma unroll
+    for (int i = 0; i < kTriTaps; i++) fb = fmaf(wm.W[br.tri_st + i], br.tri[i], fb);
     {
-        const int st = bm.tri_start[lane], len = bm.tri_len[lane];
-        for (int i = 0; i < kTriRows; i++)
-            if (i < len) fb += wm.W[st + i] * bm.triT[i * 32 + lane];
+        const float hi = __shfl_down_sync(0xffffffffu, fb, 9);      // taps 12.. of bands 14..22 live on lanes 23..31
+        if (lane >= 14 && lane < 23) fb += hi;
     }
     const float floor_fb = 4.5399929762484854e-05f;   // (float)exp(-10.0)
     fb = (fb < floor_fb) ? -10.0f : logf(fb);
