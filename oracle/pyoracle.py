@@ -93,6 +93,9 @@ class Oracle:
         L.so_single_ibm.argtypes = [_vp, _vp, C.c_long, _vp, _vp]
         L.so_rfft.argtypes = [_vp, C.c_int, C.c_int]
         L.so_rfft_cxx.argtypes = [_vp, C.c_int, C.c_int]
+        L.so_wave_proc.argtypes = [_vp]
+        L.so_etsi_features.restype = C.c_long
+        L.so_etsi_features.argtypes = [_vp, C.c_long, _vp, _vp]
 
     # ---- primitives
     def rfft(self, x, m, cxx=False):
@@ -123,6 +126,19 @@ class Oracle:
         o = np.zeros(14, np.float32)
         self.L.so_comp_ceps(_p(f), _p(o))
         return o
+
+    def wave_proc(self, frame200):
+        f = np.ascontiguousarray(frame200, np.float32).copy()
+        self.L.so_wave_proc(_p(f))
+        return f
+
+    def etsi_features(self, x):
+        """NoiseSup -> WaveProc -> CompCeps -> PostProc -> VAD: (feat[rows][15], den_i16)."""
+        x = np.ascontiguousarray(x, np.int16)
+        feat = np.zeros((max(len(x) // 80, 1), 15), np.float32)
+        den = np.zeros(len(x), np.int16)
+        rows = self.L.so_etsi_features(_p(x), len(x), _p(feat), _p(den))
+        return feat[:rows].copy(), den
 
     def cc_tables(self):
         ham = np.zeros(100, np.float32); dct = np.zeros((12, 23), np.float32)
@@ -233,11 +249,26 @@ class RefEtsi:
         L.ref_etsi_trace.argtypes = [_vp, C.c_long, _vp, _vp, _vp, _vp]
         L.ref_rfft.argtypes = [_vp, C.c_int, C.c_int]
         L.ref_comp_ceps.argtypes = [_vp, _vp]
+        L.ref_wave_proc.argtypes = [_vp]
+        L.ref_etsi_features.restype = C.c_long
+        L.ref_etsi_features.argtypes = [_vp, C.c_long, _vp, _vp]
 
     def rfft(self, x, m):
         y = np.ascontiguousarray(x, np.float32).copy()
         self.L.ref_rfft(_p(y), len(y), m)
         return y
+
+    def wave_proc(self, frame200):
+        f = np.ascontiguousarray(frame200, np.float32).copy()
+        self.L.ref_wave_proc(_p(f))
+        return f
+
+    def etsi_features(self, x):
+        x = np.ascontiguousarray(x, np.int16)
+        feat = np.zeros((max(len(x) // 80, 1), 15), np.float32)
+        den = np.zeros(len(x), np.int16)
+        rows = self.L.ref_etsi_features(_p(x), len(x), _p(feat), _p(den))
+        return feat[:rows].copy(), den
 
     def etsi_denoise(self, x):
         x = np.ascontiguousarray(x, np.int16).copy()

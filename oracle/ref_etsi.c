@@ -213,3 +213,70 @@ void ref_comp_ceps(const float *frame201, float *coef14)
     fe->DoCompCeps(tmp + 1, coef14, fe);
     AdvProcessDelete(&fe);
 }
+
+/* ---- full feature pipeline ------------------------------------------------------------------ */
+#include "WaveProcExports.h"
+
+/* DoWaveProc on one 200-sample frame, in place (etsi/cpp/WaveProc.c:386) */
+void ref_wave_proc(float *frame200)
+{
+    FEParamsX *fe = AdvProcessAlloc(8000);
+    AdvProcessInit(fe);
+    fe->DoWaveProc(frame200, fe);
+    AdvProcessDelete(&fe);
+}
+
+/* The DoAdvProcess body with the WHOLE commented-out block re-enabled (ParmInterface.c:274-311:
+ * DoWaveProc -> DoCompCeps -> DoPostProc -> DoVADProc) and the zero-frame branch (:314-328), driven
+ * like etsi_denoise's loop (AdvFrontEnd.c:173-191).  FEParamsX.FrameCounter, which gates DoVADProc
+ * (VAD.c:256), is maintained by DoNoiseSup itself (NoiseSup.c:1366: stage-1 VAD frame count).
+ * feat: [n/80][15] = c1..c12, c0, logE (post-processed), VAD flag.  Returns the number of rows written. */
+long ref_etsi_features(const short *in, long n, float *feat, short *den_i16)
+{
+    FEParamsX *fe = AdvProcessAlloc(8000);
+    X_FLOAT32 frameBuf[FRAME_BUF_SIZE + 8];
+    X_FLOAT32 fb[NUM_CEP_COEFF + 3];
+    short den_buf[80];
+    long start = 0, rows = 0;
+    int i;
+    fe->Noc0 = 0;
+    AdvProcessInit(fe);
+    memset(den_buf, 0, sizeof den_buf);
+    memset(fb, 0, sizeof fb);
+    while (start + 80 <= n) {
+        X_FLOAT32 *pt = BufInShiftToPut(fe->denoisedBuf, fe->FrameShift);
+        float check = 0.0f;
+        int out = 0;
+        for (i = 0; i < 80; i++) {
+            fe->CurFrame[i] = (X_FLOAT32)in[start + i];
+            check += in[start + i] * in[start + i];
+        }
+        if (((int)check != 0) || (fe->NonZeroFrameOnset != 0)) {
+            fe->NonZeroFrameOnset = 1;
+            if (fe->DoNoiseSup(fe->CurFrame, pt, fe)) {
+                for (i = 0; i < 80; i++) den_buf[i] = (FILE_TYPE)pt[i];
+                if (fe->offsetDenoisedFrame < 0) fe->offsetDenoisedFrame += fe->FrameShift;
+                if (fe->offsetDenoisedFrame >= 0) {
+                    BufInGetLast(fe->denoisedBuf, frameBuf, fe->FrameLength + fe->offsetDenoisedFrame + 1);
+                    fe->DoWaveProc(frameBuf + 1, fe);
+                    fe->DoCompCeps(frameBuf + 1, fb, fe);
+                    fe->DoPostProc(fb, fe);
+                    out = fe->DoVADProc(fb, fe) ? 1 : 0;
+                }
+            }
+        } else {
+            fe->ZeroFrameCounter++;
+            for (i = 0; i <= NUM_CEP_COEFF; i++) fb[i] = 0.0;
+            fe->VAD = NON_SPEECH_FRAME;
+            out = 1;
+        }
+        if (out) {
+            memcpy(feat + rows * 15, fb, sizeof(float) * 15);
+            rows++;
+        }
+        if (den_i16) memcpy(den_i16 + start, den_buf, sizeof den_buf);
+        start += 80;
+    }
+    AdvProcessDelete(&fe);
+    return rows;
+}

@@ -731,6 +731,189 @@ long so_etsi_denoise(const int16_t *in, long n, int16_t *den_i16, float *den_f32
     return calls;
 }
 
+/* -------------------------------------------------------------------------------------
+ * Back half of the ETSI feature pipeline: waveform processing,
+ * blind equalisation and the frame-dropping VAD, as DoAdvProcess would chain them
+ * (etsi/cpp/ParmInterface.c:274-311, shipped commented out).
+ * ------------------------------------------------------------------------------------- */
+
+/* argmax over t[lo..hi] (inclusive, ascending scan) where later equal values win (>=), as the
+ * neighbour searches of GetMaximaPositions do (WaveProc.c:107-114, 126-133; they scan offsets 25..79
+ * away from the current maximum, so "later" means farther away).  -1 when every candidate is negative
+ * (only possible after int32 wrap-around of the 9-point sum on full-scale input). */
+static int wp_far_peak(const int32_t *t, int from, int dir, int len)
+{
+    int best = -1, d;
+    int32_t top = 0;
+    for (d = 25; d < 80; d++) {
+        const int p = from + dir * d;
+        if (p < 0 || p >= len) continue;
+        if (t[p] >= top) { top = t[p]; best = p; }
+    }
+    return best;
+}
+
+/* DoWaveProc, etsi/cpp/WaveProc.c:386-453 (TeagerEng :173-184, GetTeagerFilter :204-291,
+ * GetMaximaPositions :74-153).  d = 200 samples, modified in place. */
+void so_wave_proc(float *d)
+{
+    enum { L = 200 };
+    float energy = 0.0f, w[L];
+    int32_t q[L], sm[L];
+    int pos[24], n_pos = 0, i, k;
+    for (i = 0; i < L; i++) energy += d[i] * d[i];
+    if (!(energy >= 100.0)) return;                                   /* :403-404 */
+    /* Teager operator with replicated edges, then round(0.25 * |.|) to int (:222-227) */
+    for (i = 0; i < L; i++) {
+        const float a = d[i > 0 ? i - 1 : 0], b = d[i < L - 1 ? i + 1 : L - 1];
+        const float t = (float)fabs(d[i] * d[i] - a * b);
+        q[i] = (int)floor(t * 0.25 + 0.5);
+    }
+    /* 9-point running sum with replicated edges (:222-254); unsigned = the reference's wrap-around */
+    for (i = 0; i < L; i++) {
+        uint32_t acc = 0;
+        for (k = -4; k <= 4; k++) {
+            int j = i + k;
+            j = j < 0 ? 0 : (j > L - 1 ? L - 1 : j);
+            acc += (uint32_t)q[j];
+        }
+        sm[i] = (int32_t)acc;
+    }
+    /* global maximum (first strict), then neighbours 25..79 samples away on either side (:86-135) */
+    {
+        int32_t top = 0;
+        int g = -1, m, left[12], nl = 0;
+        for (i = 0; i < L; i++)
+            if (sm[i] > top) { top = sm[i]; g = i; }
+        if (g >= 0) {
+            m = g;
+            while (m - 25 > 0) { const int p = wp_far_peak(sm, m, -1, L); if (p < 0) break; left[nl++] = m = p; }
+            for (i = nl - 1; i >= 0; i--) pos[n_pos++] = left[i];
+            pos[n_pos++] = g;
+            m = g;
+            while (m + 25 < L) { const int p = wp_far_peak(sm, m, +1, L); if (p < 0) break; pos[n_pos++] = m = p; }
+        }
+    }
+    /* window: 0.4 everywhere, 0.6 over the first 80 % of every inter-peak gap, starting 4 samples
+     * before the peak (:262-289).  pos[] ascending (sort_it, :44-66). */
+    {
+        const float eps = (float)0.2;
+        const float lo = (float)((1 - eps) / 2.0), hi = (float)((1 + eps) / 2.0);
+        for (i = 0; i < L; i++) w[i] = lo;
+        if (n_pos > 1) {
+            for (k = 0; k < n_pos; k++) {
+                const int gap = (k < n_pos - 1) ? pos[k + 1] - pos[k] : pos[k] - pos[k - 1];
+                const int a = pos[k] - 4, b = a + (80 * gap + 99) / 100;
+                for (i = a; i < b; i++)
+                    if (i >= 0 && i < L) w[i] = hi;
+            }
+        }
+    }
+    for (i = 0; i < L; i++) d[i] *= w[i] + w[i < L - 1 ? i + 1 : i];       /* :430-447 */
+}
+
+/* DoPostProc, etsi/cpp/PostProc.c:117-150 (Noc0 = 0: the energy term is coef[13] = logE) */
+static const float pp_target[12] = {(float)-6.618909, (float)0.198269, (float)-0.740308, (float)0.055132,
+    (float)-0.227086, (float)0.144280, (float)-0.112451, (float)-0.146940, (float)-0.327466, (float)0.134571,
+    (float)0.027884, (float)-0.114905};
+
+void so_post_proc(float *coef14, float *lms12)
+{
+    const float lambda = (float)0.0087890625;
+    float wp = (coef14[13] * 64.0f - 211.0f) / 64.0f;
+    int i;
+    if (wp < 0) wp = 0;
+    else if (wp > 1) wp = lambda;
+    else wp *= lambda;
+    for (i = 0; i < 12; i++) {
+        const float dif = (coef14[i] - lms12[i]) - pp_target[i];
+        coef14[i] = coef14[i] - lms12[i];
+        lms12[i] += dif * wp;
+    }
+}
+
+/* DoVADProc, etsi/cpp/VAD.c:214-330: 7-frame circular delay line + hangover logic.
+ * fb15 in: 14 coefficients; out (when 1 is returned): the frame 6 calls back + its VAD flag. */
+void so_vad_init(so_vad *v)
+{
+    memset(v, 0, sizeof *v);
+    v->hang_over = 23;                                                  /* HANGOVERV, :113 */
+}
+
+int so_vad_proc(so_vad *v, float *fb15, int speech_found, int frame_counter)
+{
+    int i, run = 0, longest = 0;
+    v->focus = (v->focus + 1) % 7;
+    memcpy(v->buf[v->focus], fb15, sizeof(float) * 14);
+    v->buf[v->focus][14] = speech_found ? 1.0f : 0.0f;
+    if (frame_counter <= 10) return 0;                                  /* BUFFER_SIZE + 3, :256 */
+    for (i = 1; i <= 7; i++) {                                          /* oldest -> newest */
+        if (v->buf[(v->focus + i) % 7][14] != 0.0f) { if (++run > longest) longest = run; }
+        else run = 0;
+    }
+    if (longest >= 4) {                                                 /* H_TRIGGER */
+        v->h_count = v->hang_over;
+        if (frame_counter <= 35) v->hang_over = 50;                     /* SANGOVER */
+    }
+    if (v->h_count && longest < 3) v->h_count--;
+    if (longest >= 3) v->v_count = 5;                                   /* V_TRIGGER / VANGOVER */
+    if (v->v_count && longest < 3) v->v_count--;
+    memcpy(fb15, v->buf[(v->focus + 1) % 7], sizeof(float) * 14);
+    fb15[14] = (v->v_count || v->h_count || longest >= 3) ? 1.0f : 0.0f;
+    return 1;
+}
+
+/* The full per-frame chain, driven like oracle/ref_etsi.c:ref_etsi_features.  The VAD's FrameCounter
+ * is the stage-1 frame count DoNoiseSup publishes (NoiseSup.c:1366).  feat: [n/80][15]; returns rows. */
+long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16)
+{
+    so_ns *s = so_ns_create(SO_PROFILE_P8);
+    so_vad vad;
+    float den_buf[241], cur[80], fb[16], lms[12], frame[201];
+    int16_t out_buf[80];
+    long start = 0, rows = 0;
+    int onset = 0, offset = -200, i;
+    memset(den_buf, 0, sizeof den_buf);
+    memset(out_buf, 0, sizeof out_buf);
+    memset(fb, 0, sizeof fb);
+    memset(lms, 0, sizeof lms);
+    so_vad_init(&vad);
+    while (start + 80 <= n) {
+        float check = 0.0, *pt = den_buf + 241 - 80;
+        so_ns_info info;
+        int out = 0;
+        memmove(den_buf, den_buf + 80, sizeof(float) * (241 - 80));
+        for (i = 0; i < 80; i++) {
+            cur[i] = (float)in[start + i];
+            check += in[start + i] * in[start + i];
+        }
+        memset(&info, 0, sizeof info);
+        if (((int)check != 0) || onset) {
+            onset = 1;
+            if (so_ns_block(s, cur, pt, &info)) {
+                for (i = 0; i < 80; i++) out_buf[i] = (int16_t)pt[i];
+                if (offset < 0) offset += 80;
+                if (offset >= 0) {
+                    memcpy(frame, den_buf + 241 - (200 + offset + 1), sizeof frame);
+                    so_wave_proc(frame + 1);
+                    so_comp_ceps(frame, fb);
+                    so_post_proc(fb, lms);
+                    out = so_vad_proc(&vad, fb, info.sp_spec || info.sp_mel || info.sp_var || info.sp_vadns,
+                                      info.nb_frame0);
+                }
+            }
+        } else {
+            for (i = 0; i < 14; i++) fb[i] = 0.0f;                      /* ParmInterface.c:320-321 */
+            out = 1;
+        }
+        if (out) { memcpy(feat + rows * 15, fb, sizeof(float) * 15); rows++; }
+        if (den_i16) memcpy(den_i16 + start, out_buf, sizeof out_buf);
+        start += 80;
+    }
+    so_ns_destroy(s);
+    return rows;
+}
+
 /* etsi_denoise_mapping_func_Wiener, aurora_etsi/NoiseSup.cpp:1140-1407 */
 int so_p16_func_wiener(so_ns *s, const float *in, int n, float *out, int *sp_var, int *sp_spec,
                        int *sp_mel, int *sp_vadns, int *frame_counter, float *gains)

@@ -56,6 +56,15 @@ long so_etsi_denoise(const int16_t *in, long n, int16_t *den_i16, float *den_f32
 void so_comp_ceps(const float *frame201, float *coef14);   /* etsi/cpp/CompCeps.c:368-549          */
 void so_cc_tables(float *hamming100, float *dct12x23, int *start23, int *len23, float *tri23x129);
 
+/* ---------- P8 back half: WaveProc / PostProc / VAD (etsi/cpp/ParmInterface.c:274-311) ---------- */
+typedef struct { float buf[7][16]; int focus, hang_over, h_count, v_count; } so_vad;
+void so_wave_proc(float *frame200);                          /* etsi/cpp/WaveProc.c:386-453          */
+void so_post_proc(float *coef14, float *lms12);              /* etsi/cpp/PostProc.c:117-150          */
+void so_vad_init(so_vad *v);
+int so_vad_proc(so_vad *v, float *fb15, int speech_found, int frame_counter);   /* VAD.c:214-330    */
+/* NoiseSup -> WaveProc -> CompCeps -> PostProc -> VAD; feat[row][15] = c1..c12,c0,logE,VAD flag. */
+long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16);
+
 /* ---------- P16 plugin entry point ---------- */
 /* etsi_denoise_mapping_func_Wiener (aurora_etsi/NoiseSup.cpp:1140-1407) on an existing stream.
  * out / flag arrays follow the reference contract (caller zeroes; untouched where nothing ran).
