@@ -95,6 +95,26 @@ int se_etsi_denoise_batch(se_ctx *ctx, const int16_t *samples, const int64_t *of
                           int16_t *denoised, float *ceps, const int64_t *ceps_offsets, int32_t *n_ceps,
                           float *den_f32, uint8_t *vad_trace, const int64_t *trace_offsets, int mem);
 
+/* ---- P8: the whole ETSI feature chain, DoAdvProcess with the block the reference ships commented out
+ *      re-enabled (etsi/cpp/ParmInterface.c:274-311): DoNoiseSup -> DoWaveProc (WaveProc.c:386) ->
+ *      DoCompCeps (CompCeps.c:368) -> DoPostProc (PostProc.c:117) -> DoVADProc (VAD.c:214), plus the
+ *      null vectors of leading all-zero frames (ParmInterface.c:314-327).  No flush at the end of an
+ *      utterance (FlushAdvProcess is never called by the reference's drivers either).
+ * features : float [feat_offsets[u] + row][15] = c1..c12, c0, logE after blind equalisation, VAD flag
+ *            (FeatureBuffer[0..14]); rows come out in call order: Z null rows, then cepstral frame
+ *            m at processed call m+12 (6 calls of NoiseSup/framing latency + the VAD's 7-frame delay
+ *            line): max(0, len/80 - Z - 12) rows.                                      [required]
+ * feat_offsets : host int64[n_utts+1]; capacity per utterance >= se_etsi_num_feature_rows(len).
+ * n_rows   : int32[n_utts] rows written (same memory kind as data), may be NULL.
+ * denoised : optional int16 denoised stream, as se_etsi_denoise_batch. */
+int64_t se_etsi_num_feature_rows(int64_t n_samples);    /* n/80: upper bound                    */
+int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                           float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised,
+                           int mem);
+
+/* Known-answer entry: DoWaveProc (etsi/cpp/WaveProc.c:386-453) on n frames of 200 floats, in place. */
+int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem);
+
 /* ---- P16: plugin NoiseSup, replaces etsi_denoise_mapping_func_Wiener
  *      (function/20141106_speech_enhancement/aurora_etsi/NoiseSup.cpp:1140-1407) ------------------
  * samples are int16 (is_f32=0) or float (is_f32=1, the plugin's own input type).

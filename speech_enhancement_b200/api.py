@@ -51,12 +51,14 @@ def lib():
         L.se_ctx_reset_kernel_times.argtypes = [_vp]
         L.se_ctx_launch_count.restype = C.c_int64
         L.se_ctx_launch_count.argtypes = [_vp]
-        for f in ("se_etsi_num_ceps_frames", "se_ibm_num_frames"):
+        for f in ("se_etsi_num_ceps_frames", "se_etsi_num_feature_rows", "se_ibm_num_frames"):
             getattr(L, f).restype = C.c_int64
             getattr(L, f).argtypes = [C.c_int64]
         L.se_resynth_num_frames.restype = C.c_int64
         L.se_resynth_num_frames.argtypes = [C.c_int64, C.c_int]
         L.se_etsi_denoise_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]
+        L.se_wave_proc_batch.argtypes = [_vp, _vp, C.c_int, C.c_int]
+        L.se_etsi_features_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
         L.se_p16_wiener_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
         L.se_ns_stream_create.argtypes = [_vp, C.c_int, C.POINTER(_vp)]
         L.se_ns_stream_destroy.argtypes = [_vp]
@@ -198,6 +200,12 @@ class Context:
                                             _ptr(ceps_offsets), _ptr(n_ceps), _ptr(den_f32), _ptr(vad_trace),
                                             _ptr(trace_offsets), mem), "se_etsi_denoise_batch")
 
+    def etsi_features_raw(self, samples, offsets, n_utts, features, feat_offsets, n_rows=None, denoised=None,
+                          mem=SE_MEM_HOST):
+        _check(self.L.se_etsi_features_batch(self.h, _ptr(samples), _ptr(offsets), n_utts, _ptr(features),
+                                             _ptr(feat_offsets), _ptr(n_rows), _ptr(denoised), mem),
+               "se_etsi_features_batch")
+
     def p16_wiener_raw(self, samples, is_f32, offsets, n_utts, out_f32, flags, gains, n_rows, block_offsets,
                        mem=SE_MEM_HOST):
         _check(self.L.se_p16_wiener_batch(self.h, _ptr(samples), int(is_f32), _ptr(offsets), n_utts, _ptr(out_f32),
@@ -240,6 +248,25 @@ class Context:
         self.etsi_denoise_raw(samples, offsets, nu, out["den_i16"], out.get("ceps"), co, out.get("n_ceps"),
                               out.get("den_f32"), out.get("trace"), to)
         return out
+
+    def wave_proc(self, frames):
+        f = np.ascontiguousarray(frames, np.float32).reshape(-1, 200).copy()
+        _check(self.L.se_wave_proc_batch(self.h, _ptr(f), len(f), SE_MEM_HOST), "se_wave_proc_batch")
+        return f
+
+    def etsi_features(self, samples, offsets, denoised=False):
+        """Full ETSI feature chain: list of per-utterance [rows][15] arrays (+ int16 denoised stream)."""
+        samples = np.ascontiguousarray(samples, np.int16)
+        offsets = _i64(offsets)
+        nu = len(offsets) - 1
+        fo = np.zeros(nu + 1, np.int64)
+        fo[1:] = np.cumsum(np.diff(offsets) // 80)
+        feat = np.zeros((max(int(fo[-1]), 1), 15), np.float32)
+        rows = np.zeros(max(nu, 1), np.int32)
+        den = np.zeros(len(samples), np.int16) if denoised else None
+        self.etsi_features_raw(samples, offsets, nu, feat, fo, rows, den)
+        per_utt = [feat[fo[u]:fo[u] + rows[u]] for u in range(nu)]
+        return (per_utt, den) if denoised else per_utt
 
     def p16_wiener(self, samples, offsets):
         samples = np.ascontiguousarray(samples)

@@ -333,6 +333,7 @@ int se_shard_plan(const int64_t *offsets, int n_utts, int n_shards, int32_t *fir
 }
 
 int64_t se_etsi_num_ceps_frames(int64_t n) { const int64_t c = n / 80 - 6; return c > 0 ? c : 0; }
+int64_t se_etsi_num_feature_rows(int64_t n) { return n > 0 ? n / 80 : 0; }
 int64_t se_ibm_num_frames(int64_t n) { return n >= 320 ? (n - 320) / 160 + 1 : 0; }
 int64_t se_resynth_num_frames(int64_t n, int mode)
 {

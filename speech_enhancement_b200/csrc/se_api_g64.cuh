@@ -144,6 +144,20 @@ int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem)
     return leave(ctx, mem);
 }
 
+int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_wave_proc_batch"));
+    if (n_frames < 0 || (n_frames > 0 && !frames)) { set_error("se_wave_proc_batch: bad arguments"); return SE_EINVAL; }
+    if (n_frames == 0) return SE_OK;
+    const uint64_t bytes = sizeof(float) * 200u * (uint64_t)n_frames;
+    const void *d_in = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, frames, bytes, mem, &d_in));
+    float *d = const_cast<float *>((const float *)d_in);
+    SE_TRY(launch_wave_proc(ctx, d, n_frames));
+    SE_TRY(stage_out_copy(ctx, frames, d, bytes, mem));
+    return leave(ctx, mem);
+}
+
 int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
                        int count, int flags, int mem)
 {

@@ -75,7 +75,8 @@ struct NsLaunch {
     // P8 outputs
     int16_t *den_i16;
     float *den_f32;
-    float *ceps;
+    float *ceps;                 // [row][14] raw cepstra, or [row][15] feature rows when `features`
+    int features;                // P8: run WaveProc -> CompCeps -> PostProc -> VAD behind NoiseSup
     const int64_t *ceps_offsets; // device
     int32_t *n_ceps;
     uint8_t *vad_trace;
@@ -159,6 +160,7 @@ void prof_end(se_ctx *ctx, int k);
 int launch_ns_p8(se_ctx *ctx, const NsLaunch &a);
 int launch_ns_p16(se_ctx *ctx, const NsLaunch &a);
 int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count);
+int launch_wave_proc(se_ctx *ctx, float *frames, int count);
 
 struct G64Launch {
     const int16_t *samples, *samples2;   // samples2: noise (IBM kernel)

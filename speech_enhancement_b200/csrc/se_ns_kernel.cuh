@@ -26,16 +26,20 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
 
 template <typename T> __device__ __forceinline__ float to_f32(T v) { return (float)v; }
 
-template <int PROF, typename IN_T>
+// FEAT (P8 only): a.ceps receives 15-column feature rows (WaveProc -> CompCeps -> PostProc -> VAD,
+// se_ns_feat.cuh) instead of 14-column raw cepstra; a.n_ceps counts released rows.
+template <int PROF, typename IN_T, bool FEAT>
 __global__ void __launch_bounds__(kNsWarpsPerBlock * 32, 2)
 ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 {
     using P = Prof<PROF>;
+    static_assert(!FEAT || PROF == 8, "the feature chain exists for the 8 kHz profile only");
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BlockMem<PROF> &bm = *reinterpret_cast<BlockMem<PROF> *>(smem_raw);
     WarpMem<PROF> *wms = reinterpret_cast<WarpMem<PROF> *>(smem_raw + ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpMem<PROF> &wm = wms[warp];
+    FeatMem &fm = reinterpret_cast<FeatMem *>(wms + kNsWarpsPerBlock)[FEAT ? warp : 0];
 
     load_block_tables<PROF>(bm, tb, cc);
     __syncthreads();
@@ -113,6 +117,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             if (P::CEPS)
                 for (int i = lane; i < P::RB; i += 32) wm.ring3[i] = 0.0f;
         }
+        FeatState fs;
+        if constexpr (FEAT) feat_state_init(fs, fm, lane);
         __syncwarp();
         // cepstral rows are numbered per launch: a resumed stream continues at row 0 of this push
         const int ceps_row0 = (st && a.load_state && s.nb_out2 > 2) ? s.nb_out2 - 2 : 0;
@@ -226,7 +232,26 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 }
                 if (a.den_f32)
                     for (int i = lane; i < P::S; i += 32) a.den_f32[obase + i] = stage_out[i];
-                if (produced && a.ceps && s.nb_out2 >= 3) {
+                if constexpr (FEAT) {
+                    bool emit = false;
+                    float c = 0.0f;
+                    if (!process) {
+                        emit = true;                     // null feature vector, ParmInterface.c:314-327
+                    } else if (produced && s.nb_out2 >= 3) {
+                        const int base = ((s.nb_out2 - 3) & 3) * P::S;
+                        for (int i = lane; i < 201; i += 32) fm.frame[i] = wm.ring3[wrap<P::RB>(base + i - 1)];
+                        __syncwarp();
+                        wave_proc_warp(fm, lane);
+                        c = comp_ceps_core(wm, bm, tw, br, lane, [&](int i) { return fm.frame[1 + i]; });
+                        c = post_proc_warp(c, fs, lane);
+                        const bool speech = fl.spec || fl.mel || fl.var || (s.nb_speech > 4);
+                        emit = vad_proc_warp(c, fs, fm, lane, speech, s.nb_frame0);
+                    }
+                    if (emit) {
+                        if (a.ceps && fs.rows < ceps_cap && lane < kFeatCols) a.ceps[(ceps0 + fs.rows) * kFeatCols + lane] = c;
+                        fs.rows++;
+                    }
+                } else if (produced && a.ceps && s.nb_out2 >= 3) {
                     // third denoised shift onwards: frame m = nb_out2-3 (ParmInterface.c:275-293)
                     const int m = s.nb_out2 - 3;
                     if (m - ceps_row0 < ceps_cap)
@@ -274,7 +299,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
         }
         if (lane == 0) {
-            if (a.n_ceps) a.n_ceps[u] = s.n_ceps - ceps_row0;
+            if (a.n_ceps) a.n_ceps[u] = FEAT ? fs.rows : s.n_ceps - ceps_row0;
             if (a.n_rows) a.n_rows[u] = s.n_rows;
         }
 
@@ -363,19 +388,37 @@ __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
     }
 }
 
+// test kernel: DoWaveProc on independent frames (one warp per frame)
+__global__ void wave_proc_kernel(float *frames, int count)
+{
+    __shared__ FeatMem fms[4];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 4 + warp;
+    if (idx >= count) return;
+    FeatMem &fm = fms[warp];
+    float *p = frames + (int64_t)idx * 200;
+    for (int i = lane; i < 200; i += 32) fm.frame[1 + i] = p[i];
+    if (lane == 0) fm.frame[0] = 0.0f;
+    __syncwarp();
+    wave_proc_warp(fm, lane);
+    for (int i = lane; i < 200; i += 32) p[i] = fm.frame[1 + i];
+}
+
 // ------------------------------------------------------------------------------------------------
 // host launchers
 // ------------------------------------------------------------------------------------------------
-template <int PROF> static size_t ns_smem_bytes()
+template <int PROF, bool FEAT> static size_t ns_smem_bytes()
 {
-    return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + kNsWarpsPerBlock * sizeof(WarpMem<PROF>);
+    return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + kNsWarpsPerBlock * sizeof(WarpMem<PROF>) +
+           (FEAT ? kNsWarpsPerBlock * sizeof(FeatMem) : 0);
 }
 
-template <int PROF, typename IN_T> static int launch_ns(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid)
+template <int PROF, typename IN_T, bool FEAT = false>
+static int launch_ns(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid)
 {
     if (a.n_utts <= 0) return SE_OK;
-    const size_t smem = ns_smem_bytes<PROF>();
-    auto kern = ns_stream_kernel<PROF, IN_T>;
+    const size_t smem = ns_smem_bytes<PROF, FEAT>();
+    auto kern = ns_stream_kernel<PROF, IN_T, FEAT>;
     SE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
     SE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kNsWarpsPerBlock * 32, smem));
@@ -393,6 +436,10 @@ template <int PROF, typename IN_T> static int launch_ns(se_ctx *ctx, const NsLau
 
 int launch_ns_p8(se_ctx *ctx, const NsLaunch &a)
 {
+    if (a.features) {
+        if (a.is_f32 || a.state) { set_error("feature chain: int16 batch input only"); return SE_EUNSUPPORTED; }
+        return launch_ns<8, int16_t, true>(ctx, a, ctx->d_p8, SE_K_NS_P8);
+    }
     return a.is_f32 ? launch_ns<8, float>(ctx, a, ctx->d_p8, SE_K_NS_P8)
                     : launch_ns<8, int16_t>(ctx, a, ctx->d_p8, SE_K_NS_P8);
 }
@@ -401,6 +448,15 @@ int launch_ns_p16(se_ctx *ctx, const NsLaunch &a)
 {
     return a.is_f32 ? launch_ns<16, float>(ctx, a, ctx->d_p16, SE_K_NS_P16)
                     : launch_ns<16, int16_t>(ctx, a, ctx->d_p16, SE_K_NS_P16);
+}
+
+int launch_wave_proc(se_ctx *ctx, float *frames, int count)
+{
+    if (count <= 0) return SE_OK;
+    wave_proc_kernel<<<(count + 3) / 4, 128, 0, ctx->cur->stream>>>(frames, count);
+    ctx->launches++;
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
 }
 
 int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count)

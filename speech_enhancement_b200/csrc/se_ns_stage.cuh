@@ -367,11 +367,11 @@ template <int PROF> __device__ __forceinline__ void dc_offset(float (&o)[Prof<PR
 
 // WI8CompCeps (etsi/cpp/CompCeps.c:368-549) on the 200-sample frame that starts `base` (ring3
 // position of frame sample 0); ring3 holds the float denoised stream.
-__device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, int base,
-                                          float *row)
+// `ld(i)` returns frame sample i, -1 <= i < 200.  Returns this lane's coefficient (lanes 0..11 = c1..c12,
+// lane 12 = c0, lane 13 = logE, 0 elsewhere).
+template <class LD>
+__device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, LD ld)
 {
-    using P = Prof<8>;
-    const float *d = wm.ring3;
     float e = 0.0f;
     float2 v[4];
 #pragma unroll
@@ -379,9 +379,9 @@ __device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm,
         const int i2 = 2 * (lane + 32 * j);
         v[j] = make_float2(0.0f, 0.0f);
         if (i2 < 200) {
-            const float dm1 = d[wrap<P::RB>(base + i2 - 1)];
-            const float d0 = d[wrap<P::RB>(base + i2)];
-            const float d1 = d[wrap<P::RB>(base + i2 + 1)];
+            const float dm1 = ld(i2 - 1);
+            const float d0 = ld(i2);
+            const float d1 = ld(i2 + 1);
             e += d0 * d0 + d1 * d1;
             // pre-emphasis 0.9 (:427-429) and Hamming (:434)
             v[j] = make_float2((d0 - 0.9f * dm1) * bm.ham[i2], (d1 - 0.9f * d0) * bm.ham[i2 + 1]);
@@ -427,8 +427,17 @@ __device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm,
         const float floor_e = 1.9287498479639178e-22f;   // (float)exp(-50.0)
         out = (e < floor_e) ? -50.0f : logf(e);
     }
-    if (lane < 14) row[lane] = out;
     __syncwarp();
+    return out;
+}
+
+__device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, int base,
+                                          float *row)
+{
+    using P = Prof<8>;
+    const float *d = wm.ring3;
+    const float out = comp_ceps_core(wm, bm, tw, br, lane, [&](int i) { return d[wrap<P::RB>(base + i)]; });
+    if (lane < 14) row[lane] = out;
 }
 
 }  // namespace se

@@ -20,8 +20,29 @@ from oracle import pyoracle as po  # noqa: E402
 from speech_enhancement_b200 import synth  # noqa: E402
 
 
+def features():
+    """Full feature chain (WaveProc -> CompCeps -> PostProc -> VAD, ParmInterface.c:274-311) + DoWaveProc alone."""
+    assert po.build_ref(), "needs /root/reference"
+    r = po.RefEtsi()
+    x = synth.utterance(3, 8000, 8000 + 33)
+    xz = synth.utterance(7, 8000, 4000)                      # 5 leading all-zero frames -> 5 null vectors
+    f, d = r.etsi_features(x)
+    fz, dz = r.etsi_features(xz)
+    rng = np.random.default_rng(386)
+    n = np.arange(200)
+    frames = np.stack([(rng.standard_normal(200) * 2000).astype(np.float32),
+                       (3000 * np.sin(2 * np.pi * n / 61.0) * (1 + 0.5 * np.sin(2 * np.pi * n / 57))).astype(np.float32),
+                       np.round(rng.standard_normal(200) * 0.5).astype(np.float32),     # below the energy gate
+                       rng.integers(-32768, 32768, 200).astype(np.float32)])           # int32 wrap-around case
+    np.savez_compressed(os.path.join(HERE, "p8_features.npz"), x=x, xz=xz, feat=f, z_feat=fz, den=d, z_den=dz,
+                        frames=frames, wp=np.stack([r.wave_proc(v) for v in frames]))
+
+
 def main():
     assert po.build_ref(), "needs /root/reference"
+    if "--only-features" in sys.argv:
+        return features()
+    features()
     rng = np.random.default_rng(20141106)
 
     # ---- P8: etsi_denoise + re-enabled CompCeps step, with the per-call VAD trace ------------------

@@ -44,6 +44,20 @@ def test_p8_etsi_golden(oracle, prefix, xkey):
     assert len(r["ceps"]) == n_ceps
 
 
+def test_p8_features_golden(oracle):
+    """WaveProc -> CompCeps -> PostProc -> VAD behind NoiseSup: bit-exact rows against the reference build."""
+    g = load("p8_features.npz")
+    for xk, fk, dk in (("x", "feat", "den"), ("xz", "z_feat", "z_den")):
+        f, d = oracle.etsi_features(g[xk])
+        assert f.shape == g[fk].shape and np.array_equal(f, g[fk])
+        assert np.array_equal(d, g[dk])
+    assert len(g["feat"]) == 100 - 12 and len(g["z_feat"]) == 5 + (50 - 5 - 12)
+    assert not g["z_feat"][:5].any() and g["feat"][0, :14].all()        # null vectors, then real frames
+    for v, w in zip(g["frames"], g["wp"]):
+        assert np.array_equal(oracle.wave_proc(v), w)
+    assert np.array_equal(g["wp"][2], g["frames"][2])                    # low-energy frames pass untouched
+
+
 def test_rfft_golden(oracle):
     g = load("rfft.npz")
     for x, y in zip(g["x256"], g["y256"]):
@@ -126,6 +140,8 @@ def test_oracle_vs_reference_build_live():
     a, b = o.etsi_denoise(x, with_ceps=True), po.RefEtsi().trace(x)
     n = len(x) // 80 * 80
     assert np.array_equal(a["den_i16"][:n], b["den_i16"][:n]) and np.array_equal(a["ceps"], b["ceps"])
+    fa, fb = o.etsi_features(x), po.RefEtsi().etsi_features(x)
+    assert np.array_equal(fa[0], fb[0]) and np.array_equal(fa[1], fb[1]) and fa[0][:, 14].any()
     x16 = synth.utterance(22, 16000, 16000 + 77).astype(np.float32)
     s, R = o.p16_stream(), po.RefP16()
     A, B = s.func_wiener(x16), R.func_wiener(x16)
