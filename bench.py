@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
     ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
-    ap.add_argument("--profile-only", default="", choices=["", "p8", "resynth", "ibm"],
+    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "resynth", "ibm"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
 
@@ -264,20 +264,25 @@ def bench_p16(args, torch, api, ctx, dist, stream, first_u):
                 samples=samples, offsets=offsets)
 
 
-def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000):
-    """P8: ETSI NoiseSup + CompCeps on 10 s 8 kHz utterances (C1-type work, batched)."""
+def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features=False):
+    """P8: ETSI NoiseSup + CompCeps on 10 s 8 kHz utterances (C1-type work, batched); features=True runs the
+    whole feature chain (WaveProc -> CompCeps -> PostProc -> VAD, 15-column rows) behind NoiseSup."""
     samples, offsets = make_corpus(first_u, n_utts, 8000, 0, 0, seconds=10.0)
     total = int(offsets[-1])
     co = np.zeros(n_utts + 1, np.int64)
-    co[1:] = np.cumsum(np.maximum(np.diff(offsets) // 80 - 6, 0))
+    co[1:] = np.cumsum(np.diff(offsets) // 80 if features else np.maximum(np.diff(offsets) // 80 - 6, 0))
     d_in = dev(torch, samples)
     d_den = torch.empty(total, dtype=torch.int16, device="cuda")
-    d_ceps = torch.empty(int(co[-1]) * 14, dtype=torch.float32, device="cuda")
+    d_ceps = torch.empty(int(co[-1]) * (15 if features else 14), dtype=torch.float32, device="cuda")
     d_nc = torch.empty(n_utts, dtype=torch.int32, device="cuda")
 
     def step():
-        ctx.etsi_denoise_raw(d_in.data_ptr(), offsets, n_utts, d_den.data_ptr(), d_ceps.data_ptr(), co, d_nc.data_ptr(),
-                             mem=api.SE_MEM_DEVICE)
+        if features:
+            ctx.etsi_features_raw(d_in.data_ptr(), offsets, n_utts, d_ceps.data_ptr(), co, d_nc.data_ptr(),
+                                  d_den.data_ptr(), mem=api.SE_MEM_DEVICE)
+        else:
+            ctx.etsi_denoise_raw(d_in.data_ptr(), offsets, n_utts, d_den.data_ptr(), d_ceps.data_ptr(), co,
+                                 d_nc.data_ptr(), mem=api.SE_MEM_DEVICE)
 
     for _ in range(args.warmup):
         step()
@@ -290,8 +295,9 @@ def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000):
     audio_s = total / 8000.0
     hops = total // 80
     hbm, _ = peaks()
-    gbs = hops * P8_BYTES_PER_HOP / (k_ms / max(k_n, 1) * 1e-3) / 1e9
-    return {"workload": "P8 etsi NoiseSup+CompCeps, %d x 10 s 8 kHz" % n_utts, "xrt": audio_s * args.steps / (ms * 1e-3),
+    gbs = hops * (P8_BYTES_PER_HOP + (4 if features else 0)) / (k_ms / max(k_n, 1) * 1e-3) / 1e9
+    name = "P8 etsi NoiseSup+WaveProc+CompCeps+PostProc+VAD" if features else "P8 etsi NoiseSup+CompCeps"
+    return {"workload": "%s, %d x 10 s 8 kHz" % (name, n_utts), "xrt": audio_s * args.steps / (ms * 1e-3),
             "ms_per_step": ms / args.steps, "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
@@ -483,7 +489,8 @@ def run_ours(args):
 
     if args.profile_only:
         with torch.cuda.stream(stream):
-            fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm}[args.profile_only]
+            fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm,
+                  "p8feat": lambda *a: bench_p8(*a, features=True)}[args.profile_only]
             print(json.dumps(fn(args, torch, api, ctx, dist, stream, first_u + 500000)), flush=True)
         ctx.close()
         dist.close()
@@ -493,6 +500,7 @@ def run_ours(args):
         extra = None
         if not args.no_extra and args.gpus == 1:
             extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000),
+                     bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000, features=True),
                      bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000),
                      bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000)]
     audio_all = dist.sum(r["audio_s"])

@@ -14,7 +14,7 @@ constexpr int kFeatCols = 15;    // c1..c12, c0, logE, VAD flag (FeatureBuffer[0
 struct __align__(16) FeatMem {
     float frame[208];            // [0] = sample -1 (pre-emphasis history), [1..200] = the frame
     int q[208];                  // rounded Teager energy with 4 replicated samples either side
-    int sm[200];                 // 9-point sums; later the 0.4 / 0.6 window (as float bits)
+    int sm[200];                 // 9-point sums of q
     float vad[7 * 16];           // the VAD's 7-frame delay line (OutBuffer)
 };
 
@@ -33,128 +33,115 @@ __device__ __forceinline__ void feat_state_init(FeatState &f, FeatMem &fm, int l
     for (int i = lane; i < 7 * 16; i += 32) fm.vad[i] = 0.0f;       // calloc'ed OutBuffer, VAD.c:150
 }
 
-// (value, tag) arg-max over the warp; larger tag wins ties.  Returns the winning tag on every lane
-// (-1 when no lane holds a valid candidate; invalid candidates carry tag < 0).
-__device__ __forceinline__ int warp_argmax_tag(int val, int tag, int &best_val)
-{
-#pragma unroll
-    for (int d = 16; d >= 1; d >>= 1) {
-        const int ov = __shfl_xor_sync(0xffffffffu, val, d);
-        const int ot = __shfl_xor_sync(0xffffffffu, tag, d);
-        const bool take = (ot >= 0) && (tag < 0 || ov > val || (ov == val && ot > tag));
-        if (take) { val = ov; tag = ot; }
-    }
-    best_val = val;
-    return tag;
-}
-
-// DoWaveProc on fm.frame[1..200], in place.
+// DoWaveProc on fm.frame[1..200], in place.  Lane l owns the 7 consecutive samples [7l, 7l+7) (lanes 0..28),
+// so Teager energy, the 9-point sums and the window all come from registers; only the rounded energies and
+// their sums pass through shared memory (stride-7 words: conflict-free).  Warp-wide maxima use redux.sync.
 __device__ __forceinline__ void wave_proc_warp(FeatMem &fm, int lane)
 {
-    constexpr int L = 200;
+    constexpr int L = 200, T = 7;
+    constexpr unsigned FULL = 0xffffffffu;
     float *d = fm.frame + 1;
+    const int s0 = lane * T;
+    float x[T + 2];                               // x[t] = d[s0 - 1 + t], frame edges replicated
+#pragma unroll
+    for (int t = 0; t < T + 2; t++) x[t] = d[min(max(s0 - 1 + t, 0), L - 1)];
     // low-energy check (:400-404).  The reference sums sequentially; a frame whose energy sits within
     // float rounding of 100.0 may take the other branch here.
     float e = 0.0f;
 #pragma unroll
-    for (int j = 0; j < 7; j++) {
-        const int i = lane + 32 * j;
-        if (i < L) e = fmaf(d[i], d[i], e);
-    }
+    for (int t = 0; t < T; t++)
+        if (s0 + t < L) e = fmaf(x[t + 1], x[t + 1], e);
     e = warp_sum(e);
     if (!(e >= 100.0f)) return;
 
-    // Teager energy with replicated edges, scaled by 0.25 and rounded to int (:173-184, :222-227)
+    // Teager energy, scaled by 0.25 and rounded to int (:173-184, :222-227)
 #pragma unroll
-    for (int j = 0; j < 7; j++) {
-        const int i = lane + 32 * j;
+    for (int t = 0; t < T; t++) {
+        const int i = s0 + t;
         if (i < L) {
-            const float c = d[i], a = d[i > 0 ? i - 1 : 0], b = d[i < L - 1 ? i + 1 : L - 1];
-            const float t = fabsf(__fsub_rn(__fmul_rn(c, c), __fmul_rn(a, b)));
-            const int qi = __double2int_rd((double)t * 0.25 + 0.5);
+            const float tg = fabsf(__fsub_rn(__fmul_rn(x[t + 1], x[t + 1]), __fmul_rn(x[t], x[t + 2])));
+            const int qi = __double2int_rd((double)tg * 0.25 + 0.5);
             fm.q[4 + i] = qi;
             if (i == 0) fm.q[0] = fm.q[1] = fm.q[2] = fm.q[3] = qi;
             if (i == L - 1) fm.q[204] = fm.q[205] = fm.q[206] = fm.q[207] = qi;
         }
     }
     __syncwarp();
-    // 9-point sum (:228-254), wrap-around arithmetic like the reference's running int32 sum
-    int gv = 0, gi = -1;
+    // 9-point sums as a sliding window (:228-254), wrap-around arithmetic like the reference's int32 sum
+    int gv = 0, gi = 0;
+    {
+        unsigned qq[T + 8];
 #pragma unroll
-    for (int j = 0; j < 7; j++) {
-        const int i = lane + 32 * j;
-        if (i < L) {
-            unsigned acc = 0;
+        for (int t = 0; t < T + 8; t++) qq[t] = (unsigned)fm.q[min(s0 + t, 207)];
+        unsigned acc = 0;
 #pragma unroll
-            for (int k = 0; k < 9; k++) acc += (unsigned)fm.q[i + k];
+        for (int k = 0; k < 9; k++) acc += qq[k];
+#pragma unroll
+        for (int t = 0; t < T; t++) {
+            if (t > 0) acc += qq[t + 8] - qq[t - 1];
             const int v = (int)acc;
-            fm.sm[i] = v;
-            if (v > gv) { gv = v; gi = i; }       // first strict maximum of this lane's (ascending) samples
+            if (s0 + t < L) {
+                fm.sm[s0 + t] = v;
+                if (v > gv) { gv = v; gi = s0 + t; }      // first strict maximum of this lane's samples
+            }
         }
     }
     __syncwarp();
-    // global maximum: largest value, smallest index (:86-93); tag = L-1-i turns "smallest" into "largest"
-    int top;
-    int g = warp_argmax_tag(gv, gi < 0 ? -1 : L - 1 - gi, top);
+    // global maximum: largest value, smallest index, must be > 0 (:86-93)
+    const int top = __reduce_max_sync(FULL, gv);
     int n_pos = 0, my_pos = 0;
-    if (g >= 0) {
-        g = L - 1 - g;
+    if (top > 0) {
+        const int g = __reduce_min_sync(FULL, gv == top ? gi : L);
         // neighbours 25..79 samples away, farthest wins ties, only non-negative sums qualify (:97-135)
         int left_reg = 0, right_reg = 0, nl = 0, nr = 0;
+#pragma unroll 1
         for (int dir = -1; dir <= 1; dir += 2) {
             int m = g;
             while (dir < 0 ? (m - 25 > 0) : (m + 25 < L)) {
-                int bv = 0, bt = -1;
+                int bv = -1, bt = -1;
 #pragma unroll
                 for (int h = 0; h < 2; h++) {
                     const int dd = 25 + lane + 32 * h;
                     const int p = m + dir * dd;
                     if (dd < 80 && p >= 0 && p < L) {
                         const int v = fm.sm[p];
-                        if (v >= 0 && (bt < 0 || v >= bv)) { bv = v; bt = dd; }
+                        if (v >= 0 && v >= bv) { bv = v; bt = dd; }
                     }
                 }
-                const int w = warp_argmax_tag(bv, bt, top);
-                if (w < 0) break;
-                m += dir * w;
+                const int best = __reduce_max_sync(FULL, bv);
+                if (best < 0) break;
+                m += dir * __reduce_max_sync(FULL, bv == best ? bt : -1);
                 if (dir < 0) { if (lane == nl) left_reg = m; nl++; }
                 else { if (lane == nr) right_reg = m; nr++; }
             }
         }
         n_pos = nl + 1 + nr;
         // ascending list on lanes 0..n_pos-1 (sort_it, :44-66)
-        const int from_left = __shfl_sync(0xffffffffu, left_reg, (nl - 1 - lane) & 31);
-        const int from_right = __shfl_sync(0xffffffffu, right_reg, (lane - nl - 1) & 31);
+        const int from_left = __shfl_sync(FULL, left_reg, (nl - 1 - lane) & 31);
+        const int from_right = __shfl_sync(FULL, right_reg, (lane - nl - 1) & 31);
         my_pos = lane < nl ? from_left : (lane == nl ? g : from_right);
     }
-    __syncwarp();
-    // window (:259-289): 0.4 everywhere, 0.6 over the first 80 % of each inter-peak gap from 4 before the peak
+    // window (:259-289): 0.4 everywhere, 0.6 over the first 80 % of each inter-peak gap from 4 before the peak.
+    // bit t of `hib` = window of sample s0+t is high (t = 0..7: own samples + the next one)
     const float lo = (float)((1.0f - 0.2f) / 2.0), hi = (float)((1.0f + 0.2f) / 2.0);
-    const int nxt = __shfl_down_sync(0xffffffffu, my_pos, 1), prv = __shfl_up_sync(0xffffffffu, my_pos, 1);
+    const int nxt = __shfl_down_sync(FULL, my_pos, 1), prv = __shfl_up_sync(FULL, my_pos, 1);
     const int gap = (lane < n_pos - 1) ? nxt - my_pos : my_pos - prv;
     const int ia = my_pos - 4, ib = ia + (80 * gap + 99) / 100;
-    unsigned hibits = 0;
+    unsigned hib = 0;
     if (n_pos > 1) {
         for (int k = 0; k < n_pos; k++) {
-            const int A = __shfl_sync(0xffffffffu, ia, k), B = __shfl_sync(0xffffffffu, ib, k);
-#pragma unroll
-            for (int j = 0; j < 7; j++) {
-                const int i = lane + 32 * j;
-                if (i >= A && i < B) hibits |= 1u << j;
-            }
+            const int A = max(__shfl_sync(FULL, ia, k) - s0, 0), B = min(__shfl_sync(FULL, ib, k) - s0, T + 1);
+            if (B > A) hib |= ((1u << B) - 1u) & ~((1u << A) - 1u);
         }
     }
-    float *w = reinterpret_cast<float *>(fm.sm);
 #pragma unroll
-    for (int j = 0; j < 7; j++) {
-        const int i = lane + 32 * j;
-        if (i < L) w[i] = ((hibits >> j) & 1u) ? hi : lo;
-    }
-    __syncwarp();
-#pragma unroll
-    for (int j = 0; j < 7; j++) {
-        const int i = lane + 32 * j;
-        if (i < L) d[i] = __fmul_rn(d[i], __fadd_rn(w[i], w[i < L - 1 ? i + 1 : i]));      // :430-447
+    for (int t = 0; t < T; t++) {
+        const int i = s0 + t;
+        if (i < L) {
+            const int tn = (i == L - 1) ? t : t + 1;
+            const float w0 = ((hib >> t) & 1u) ? hi : lo, w1 = ((hib >> tn) & 1u) ? hi : lo;
+            d[i] = __fmul_rn(x[t + 1], __fadd_rn(w0, w1));                              // :430-447
+        }
     }
     __syncwarp();
 }

@@ -3,7 +3,12 @@
 
 namespace se {
 
-constexpr int kNsWarpsPerBlock = 8;
+// warps (= concurrent utterances) per CTA; 2 CTAs per SM.  The feature-chain variant keeps more state live
+// per warp, so it trades occupancy (12 instead of 16 warps/SM) for 168 registers per thread.
+#ifndef SE_NS_WARPS
+#define SE_NS_WARPS 8
+#endif
+template <bool FEAT> struct NsWarps { static constexpr int value = FEAT ? 6 : SE_NS_WARPS; };
 
 template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<PROF> &bm, const NsDevTables &tb,
                                                                      const CcDevTables &cc)
@@ -29,7 +34,7 @@ template <typename T> __device__ __forceinline__ float to_f32(T v) { return (flo
 // FEAT (P8 only): a.ceps receives 15-column feature rows (WaveProc -> CompCeps -> PostProc -> VAD,
 // se_ns_feat.cuh) instead of 14-column raw cepstra; a.n_ceps counts released rows.
 template <int PROF, typename IN_T, bool FEAT>
-__global__ void __launch_bounds__(kNsWarpsPerBlock * 32, 2)
+__global__ void __launch_bounds__(NsWarps<FEAT>::value * 32, 2)
 ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 {
     using P = Prof<PROF>;
@@ -39,7 +44,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     WarpMem<PROF> *wms = reinterpret_cast<WarpMem<PROF> *>(smem_raw + ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpMem<PROF> &wm = wms[warp];
-    FeatMem &fm = reinterpret_cast<FeatMem *>(wms + kNsWarpsPerBlock)[FEAT ? warp : 0];
+    FeatMem &fm = reinterpret_cast<FeatMem *>(wms + NsWarps<FEAT>::value)[FEAT ? warp : 0];
 
     load_block_tables<PROF>(bm, tb, cc);
     __syncthreads();
@@ -299,7 +304,10 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
         }
         if (lane == 0) {
-            if (a.n_ceps) a.n_ceps[u] = FEAT ? fs.rows : s.n_ceps - ceps_row0;
+            if (a.n_ceps) {
+                if constexpr (FEAT) a.n_ceps[u] = fs.rows;
+                else a.n_ceps[u] = s.n_ceps - ceps_row0;
+            }
             if (a.n_rows) a.n_rows[u] = s.n_rows;
         }
 
@@ -409,8 +417,8 @@ __global__ void wave_proc_kernel(float *frames, int count)
 // ------------------------------------------------------------------------------------------------
 template <int PROF, bool FEAT> static size_t ns_smem_bytes()
 {
-    return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + kNsWarpsPerBlock * sizeof(WarpMem<PROF>) +
-           (FEAT ? kNsWarpsPerBlock * sizeof(FeatMem) : 0);
+    return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + NsWarps<FEAT>::value * sizeof(WarpMem<PROF>) +
+           (FEAT ? NsWarps<FEAT>::value * sizeof(FeatMem) : 0);
 }
 
 template <int PROF, typename IN_T, bool FEAT = false>
@@ -421,14 +429,15 @@ static int launch_ns(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int 
     auto kern = ns_stream_kernel<PROF, IN_T, FEAT>;
     SE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
     int per_sm = 0;
-    SE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, kNsWarpsPerBlock * 32, smem));
+    constexpr int warps = NsWarps<FEAT>::value;
+    SE_CUDA(cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, warps * 32, smem));
     if (per_sm < 1) per_sm = 1;
-    int blocks = (a.n_utts + kNsWarpsPerBlock - 1) / kNsWarpsPerBlock;
+    int blocks = (a.n_utts + warps - 1) / warps;
     const int cap = ctx->sm_count * per_sm;
     if (blocks > cap) blocks = cap;
     SE_CUDA(cudaMemsetAsync(a.work_counter, 0, sizeof(int), ctx->cur->stream));
     prof_begin(ctx, kid);
-    kern<<<blocks, kNsWarpsPerBlock * 32, smem, ctx->cur->stream>>>(a, tb, ctx->d_cc);
+    kern<<<blocks, warps * 32, smem, ctx->cur->stream>>>(a, tb, ctx->d_cc);
     prof_end(ctx, kid);
     SE_CUDA(cudaGetLastError());
     return SE_OK;

@@ -1,0 +1,32 @@
+"""How often does the GPU feature chain differ from the oracle by more than 1e-4 of the frame scale?
+(WaveProc peak-position flips on 1-ulp differences of the denoised stream.)  Run on the GPU box."""
+import os
+import sys
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from conftest import ceps_err                      # noqa: E402
+from oracle import pyoracle                        # noqa: E402
+from speech_enhancement_b200 import api, synth     # noqa: E402
+
+n_utts = int(sys.argv[1]) if len(sys.argv) > 1 else 200
+o = pyoracle.Oracle(fast=False)
+ctx = api.Context(0)
+xs = [synth.utterance(5000 + i, 8000, 8000 * 5) for i in range(n_utts)]
+offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
+got = ctx.etsi_features(np.concatenate(xs), offsets)
+errs, vad_diff, rows = [], 0, 0
+for u, x in enumerate(xs):
+    ref, _ = o.etsi_features(x)
+    assert ref.shape == got[u].shape
+    errs.append(ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1))
+    vad_diff += int((ref[:, 14] != got[u][:, 14]).sum())
+    rows += len(ref)
+e = np.concatenate(errs)
+print("rows", rows, "vad flag mismatches", vad_diff)
+for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
+    print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
+print("max err %.4g, median %.3g" % (e.max(), np.median(e)))
