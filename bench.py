@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
     ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
-    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "resynth", "ibm"],
+    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "resynth", "ibm", "subband"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
 
@@ -341,6 +341,31 @@ def bench_ibm(args, torch, api, ctx, dist, stream, first_u, n_utts=2000, seconds
             "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
+def bench_subband(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, seconds=5.0):
+    """G64: subbband() materialised like the reference (64 int16 channel rows per utterance, exact mode)."""
+    samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=seconds)
+    total = int(offsets[-1])
+    d_in = dev(torch, samples)
+    d_out = torch.empty(64 * total, dtype=torch.int16, device="cuda")
+
+    def step():
+        ctx.subband_raw(d_in.data_ptr(), offsets, n_utts, d_out.data_ptr(), api.SE_FLAG_EXACT, mem=api.SE_MEM_DEVICE)
+
+    step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    steps = min(args.steps, 2)
+    ms = timed_steps(torch, dist, stream, step, 0, steps)
+    k_ms, k_n = ctx.kernel_time(api.K_SUBBAND)
+    ctx.profiling(False)
+    hbm, _ = peaks()
+    gbs = (2 + 128) * total / (k_ms / max(k_n, 1) * 1e-3) / 1e9
+    return {"workload": "G64 subbband (64 int16 rows, exact), %d x %.0f s 16 kHz" % (n_utts, seconds),
+            "xrt": total / 16000.0 * steps / (ms * 1e-3), "ms_per_step": ms / steps, "kernel_ms": k_ms / max(k_n, 1),
+            "achieved_gbs": gbs, "frac": gbs / hbm}
+
+
 def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
     """G64: resyth_64sub_IBM on 10 s 16 kHz utterances (BASELINE configs[2] shape)."""
     samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
@@ -489,7 +514,7 @@ def run_ours(args):
 
     if args.profile_only:
         with torch.cuda.stream(stream):
-            fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm,
+            fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm, "subband": lambda *a: bench_subband(*a, n_utts=int(os.environ.get("SE_SUB_UTTS", "1000")), seconds=float(os.environ.get("SE_SUB_SEC", "5"))),
                   "p8feat": lambda *a: bench_p8(*a, features=True)}[args.profile_only]
             print(json.dumps(fn(args, torch, api, ctx, dist, stream, first_u + 500000)), flush=True)
         ctx.close()
@@ -502,7 +527,8 @@ def run_ours(args):
             extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000),
                      bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000, features=True),
                      bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000),
-                     bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000)]
+                     bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000),
+                     bench_subband(args, torch, api, ctx, dist, stream, first_u + 900000)]
     audio_all = dist.sum(r["audio_s"])
     value = audio_all * args.steps / (r["ms"] * 1e-3)
     e2e = audio_all * args.steps / (r["e2e_ms"] * 1e-3)

@@ -186,6 +186,31 @@ int se_device_count(void)
     return n;
 }
 
+// Device-side part of se_ctx_create; any failure leaves a partially built context for se_ctx_destroy.
+static int ctx_init_device(se_ctx *ctx)
+{
+    const int device = ctx->device;
+    cudaDeviceProp prop;
+    SE_CUDA(cudaGetDeviceProperties(&prop, device));
+    ctx->sm_count = prop.multiProcessorCount;
+    SE_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    ctx->lanes[0].stream = ctx->own_stream;
+    for (int l = 0; l < kLanes; l++) {
+        if (l > 0) SE_CUDA(cudaStreamCreateWithFlags(&ctx->lanes[l].stream, cudaStreamNonBlocking));
+        SE_CUDA(cudaMalloc((void **)&ctx->lanes[l].d_work_counter, sizeof(int)));
+        SE_CUDA(cudaEventCreateWithFlags(&ctx->lanes[l].done, cudaEventDisableTiming));
+    }
+    build_ns_tables_p8(ctx->h_p8);
+    build_ns_tables_p16(ctx->h_p16);
+    build_cc_tables(ctx->h_cc);
+    build_gt_tables(ctx->h_gt);
+    int rc;
+    if ((rc = upload_ns(ctx, ctx->h_p8, ctx->d_p8, 16)) || (rc = upload_ns(ctx, ctx->h_p16, ctx->d_p16, 128)) ||
+        (rc = upload_cc(ctx)) || (rc = upload_g64_tables(ctx)))
+        return rc;
+    return SE_OK;
+}
+
 int se_ctx_create(int device, se_ctx **out)
 {
     if (!out) return SE_EINVAL;
@@ -213,23 +238,8 @@ int se_ctx_create(int device, se_ctx **out)
     std::memset(ctx->k_ms, 0, sizeof ctx->k_ms);
     std::memset(ctx->k_launches, 0, sizeof ctx->k_launches);
     ctx->launches = 0;
-    cudaDeviceProp prop;
-    SE_CUDA(cudaGetDeviceProperties(&prop, device));
-    ctx->sm_count = prop.multiProcessorCount;
-    SE_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
-    ctx->lanes[0].stream = ctx->own_stream;
-    for (int l = 0; l < kLanes; l++) {
-        if (l > 0) SE_CUDA(cudaStreamCreateWithFlags(&ctx->lanes[l].stream, cudaStreamNonBlocking));
-        SE_CUDA(cudaMalloc((void **)&ctx->lanes[l].d_work_counter, sizeof(int)));
-        SE_CUDA(cudaEventCreateWithFlags(&ctx->lanes[l].done, cudaEventDisableTiming));
-    }
-    build_ns_tables_p8(ctx->h_p8);
-    build_ns_tables_p16(ctx->h_p16);
-    build_cc_tables(ctx->h_cc);
-    build_gt_tables(ctx->h_gt);
-    int rc;
-    if ((rc = upload_ns(ctx, ctx->h_p8, ctx->d_p8, 16)) || (rc = upload_ns(ctx, ctx->h_p16, ctx->d_p16, 128)) ||
-        (rc = upload_cc(ctx)) || (rc = upload_g64_tables(ctx))) {
+    const int rc = ctx_init_device(ctx);
+    if (rc) {                       // partially built context: release what exists
         se_ctx_destroy(ctx);
         return rc;
     }
