@@ -151,6 +151,18 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
         SE_CUDA(cudaEventRecord(lane0->done, lane0->stream));
         for (int l = 1; l < kLanes; l++) SE_CUDA(cudaStreamWaitEvent(ctx->lanes[l].stream, lane0->done, 0));
     }
+    // SE_B200_TRACE=1: print the H2D / kernel / D2H completion times of every chunk (debug aid)
+    struct TraceEv { cudaEvent_t e; int chunk; const char *what; };
+    std::vector<TraceEv> trace;
+    const bool tracing = mem == SE_MEM_HOST && std::getenv("SE_B200_TRACE") != nullptr;
+    auto mark = [&](int c, const char *what) {
+        if (!tracing) return;
+        cudaEvent_t e;
+        if (cudaEventCreate(&e) != cudaSuccess) return;
+        cudaEventRecord(e, ctx->cur->stream);
+        trace.push_back({e, c, what});
+    };
+    mark(-1, "start");
     int rc = SE_OK;
     for (int c = 0; c < n_chunks && rc == SE_OK; c++) {
         const int u0 = first[c], u1 = first[c + 1];
@@ -181,7 +193,9 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
                 else d_out[k] = o.host;          // device arrays are written in place (caller zeroes nothing)
                 set_field(b, o.field, d_out[k]);
             }
+            mark(c, "h2d");
             SE_TRY(profile == 8 ? launch_ns_p8(ctx, b) : launch_ns_p16(ctx, b));
+            mark(c, "kernel");
             if (mem != SE_MEM_HOST) return SE_OK;
             for (int k = 0; k < n_outs; k++) {
                 const NsOut &o = outs[k];
@@ -197,6 +211,7 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
                                             cudaMemcpyDeviceToHost, ctx->cur->stream));
                 }
             }
+            mark(c, "d2h");
             return SE_OK;
         };
         rc = body();
@@ -211,7 +226,17 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
     if (rc) { cudaStreamSynchronize(lane0->stream); return rc; }
     if (counts && mem == SE_MEM_HOST)
         SE_CUDA(cudaMemcpyAsync(counts, d_counts, sizeof(int32_t) * (size_t)n_utts, cudaMemcpyDeviceToHost, lane0->stream));
-    return leave(ctx, mem);
+    const int rc_leave = leave(ctx, mem);
+    if (tracing && !trace.empty()) {
+        std::fprintf(stderr, "[se_b200 trace] %d chunks\n", n_chunks);
+        for (size_t i = 1; i < trace.size(); i++) {
+            float ms = 0.0f;
+            cudaEventElapsedTime(&ms, trace[0].e, trace[i].e);
+            std::fprintf(stderr, "[se_b200 trace] chunk %2d %-6s done at %8.3f ms\n", trace[i].chunk, trace[i].what, ms);
+        }
+        for (auto &t : trace) cudaEventDestroy(t.e);
+    }
+    return rc_leave;
 }
 
 }  // namespace se

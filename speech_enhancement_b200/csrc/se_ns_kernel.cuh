@@ -231,7 +231,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         short2 q;
                         q.x = (short)__float2int_rz(f.x);
                         q.y = (short)__float2int_rz(f.y);
-                        if ((obase & 1) == 0) *reinterpret_cast<short2 *>(a.den_i16 + obase + 2 * i) = q;
+                        if ((reinterpret_cast<uintptr_t>(a.den_i16 + obase) & 3) == 0) *reinterpret_cast<short2 *>(a.den_i16 + obase + 2 * i) = q;
                         else { a.den_i16[obase + 2 * i] = q.x; a.den_i16[obase + 2 * i + 1] = q.y; }
                     }
                 }
