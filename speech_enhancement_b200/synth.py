@@ -42,16 +42,26 @@ def ragged_length(u, fs, min_s=2.0, max_s=10.0):
     return int(_load().se_synth_length(u, fs, min_s, max_s))
 
 
-def corpus(first_u, count, fs, seconds=None, min_s=2.0, max_s=10.0):
-    """Concatenated ragged batch: (samples int16[total], offsets int64[count+1])."""
+def corpus(first_u, count, fs, seconds=None, min_s=2.0, max_s=10.0, threads=1):
+    """Concatenated ragged batch: (samples int16[total], offsets int64[count+1]).  threads > 1 generates
+    utterances in parallel (the C generator releases the GIL; results do not depend on the thread count)."""
     L = _load()
     lens = [int(seconds * fs) if seconds is not None else ragged_length(first_u + i, fs, min_s, max_s)
             for i in range(count)]
     offsets = np.zeros(count + 1, np.int64)
     offsets[1:] = np.cumsum(lens)
     samples = np.empty(int(offsets[-1]), np.int16)
-    for i in range(count):
+
+    def gen(i):
         L.se_synth_utterance(first_u + i, fs, lens[i], samples[offsets[i]:].ctypes.data, None, None)
+
+    if threads > 1:
+        from concurrent.futures import ThreadPoolExecutor
+        with ThreadPoolExecutor(max_workers=threads) as ex:
+            list(ex.map(gen, range(count)))
+    else:
+        for i in range(count):
+            gen(i)
     return samples, offsets
 
 
