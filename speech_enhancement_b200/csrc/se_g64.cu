@@ -90,47 +90,52 @@ __device__ __forceinline__ float acc_power(const FrameAcc &a)
     return __fmul_rn(0.5f, t);
 }
 
-__global__ void __launch_bounds__(64) ibm_kernel(const int16_t *pure, const int16_t *noise, const int64_t *offsets,
-                                                 int utt_begin, float *irm, uint32_t *bits,
-                                                 const int64_t *frame_offsets)
+// 128 threads per utterance: thread = (signal, channel), signal 0 = pure (warps 0-1), 1 = noise (warps 2-3), so
+// the two subbband() passes of one utterance run side by side (twice the resident warps per utterance to hide the
+// latency of the serial float/double recurrences).  One tile = one 160-sample hop, so a frame's second half
+// completes exactly at a tile end; the two signals' frame powers meet in shared memory there.
+constexpr int kIbmHop = 160;
+__global__ void __launch_bounds__(128) ibm_kernel(const int16_t *pure, const int16_t *noise, const int64_t *offsets,
+                                                  int utt_begin, float *irm, uint32_t *bits,
+                                                  const int64_t *frame_offsets)
 {
-    __shared__ float s_p[kTile], s_n[kTile];
-    const int u = utt_begin + blockIdx.x, c = threadIdx.x, warp = c >> 5;
+    __shared__ float s_x[2][kIbmHop];
+    __shared__ float s_pow[2][64];
+    const int u = utt_begin + blockIdx.x, sig = threadIdx.x >> 6, c = threadIdx.x & 63, warp = c >> 5;
     const int64_t off = offsets[u], n = offsets[u + 1] - off;
     const int64_t f0 = frame_offsets[u];
     const int64_t frames = (n >= 320) ? (n - 320) / 160 + 1 : 0;
+    const int16_t *x = (sig ? noise : pure) + off;
     const GtCoef k = load_coef(c);
-    GtState gp, gn; gt_reset(gp); gt_reset(gn);
-    HcState hp, hn; hc_reset(hp, c_gt.hc); hc_reset(hn, c_gt.hc);
-    FrameAcc ap_cur, an_cur, ap_old, an_old;   // cur: frame h (window idx r); old: frame h-1 (idx 160+r)
-    acc_reset(ap_cur); acc_reset(an_cur); acc_reset(ap_old); acc_reset(an_old);
-    int r = 0;
+    GtState g; gt_reset(g);
+    HcState hs; hc_reset(hs, c_gt.hc);
+    FrameAcc a_cur, a_old;        // cur: frame h (window idx r); old: frame h-1 (idx 160+r)
+    acc_reset(a_cur); acc_reset(a_old);
     int64_t h = 0;
-    for (int64_t t0 = 0; t0 < n; t0 += kTile) {
-        const int len = (int)((n - t0 < kTile) ? (n - t0) : kTile);
+    for (int64_t t0 = 0; t0 < n; t0 += kIbmHop, h++) {
+        const int len = (int)((n - t0 < kIbmHop) ? (n - t0) : kIbmHop);
         __syncthreads();
-        if (c < len) { s_p[c] = (float)pure[off + t0 + c]; s_n[c] = (float)noise[off + t0 + c]; }
+        for (int i = c; i < len; i += 64) s_x[sig][i] = (float)x[t0 + i];
         __syncthreads();
-        for (int t = 0; t < len; t++) {
-            const float vp = (float)cast_i16(hc_step(hp, c_gt.hc, gt_step<true>(gp, k, s_p[t])));
-            const float vn = (float)cast_i16(hc_step(hn, c_gt.hc, gt_step<true>(gn, k, s_n[t])));
-            const float w0 = c_ibm_win[r], w1 = c_ibm_win[160 + r];
-            acc_add(ap_cur, __fmul_rn(vp, w0), r);
-            acc_add(an_cur, __fmul_rn(vn, w0), r);
-            acc_add(ap_old, __fmul_rn(vp, w1), 160 + r);
-            acc_add(an_old, __fmul_rn(vn, w1), 160 + r);
-            if (++r == 160) {
-                r = 0;
-                if (h >= 1 && h - 1 < frames) {
-                    const float sp = acc_power(ap_old), sn = acc_power(an_old);
-                    const int64_t f = f0 + h - 1;
-                    if (irm) irm[f * 64 + c] = sp / __fadd_rn(sp, sn);
-                    const unsigned b = __ballot_sync(0xffffffffu, sn < sp);
-                    if (bits && (c & 31) == 0) bits[f * 2 + warp] = b;
-                }
-                ap_old = ap_cur; an_old = an_cur;
-                acc_reset(ap_cur); acc_reset(an_cur);
-                h++;
+        const float *xin = s_x[sig];
+        for (int r = 0; r < len; r++) {
+            const float v = (float)cast_i16(hc_step(hs, c_gt.hc, gt_step<true>(g, k, xin[r])));
+            acc_add(a_cur, __fmul_rn(v, c_ibm_win[r]), r);
+            acc_add(a_old, __fmul_rn(v, c_ibm_win[160 + r]), 160 + r);
+        }
+        if (len < kIbmHop) break;                         // ragged tail: no further frame completes
+        const bool emit = h >= 1 && h - 1 < frames;       // uniform over the CTA
+        if (emit) s_pow[sig][c] = acc_power(a_old);
+        a_old = a_cur;
+        acc_reset(a_cur);
+        if (emit) {
+            __syncthreads();
+            if (sig == 0) {
+                const float sp = s_pow[0][c], sn = s_pow[1][c];
+                const int64_t f = f0 + h - 1;
+                if (irm) irm[f * 64 + c] = sp / __fadd_rn(sp, sn);
+                const unsigned b = __ballot_sync(0xffffffffu, sn < sp);
+                if (bits && (c & 31) == 0) bits[f * 2 + warp] = b;
             }
         }
     }

@@ -53,7 +53,7 @@ int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, cons
 {
     if (a.utt_count <= 0) return SE_OK;
     prof_begin(ctx, SE_K_IBM);
-    ibm_kernel<<<a.utt_count, 64, 0, ctx->cur->stream>>>(a.samples, a.samples2, a.offsets, a.utt_begin, irm,
+    ibm_kernel<<<a.utt_count, 128, 0, ctx->cur->stream>>>(a.samples, a.samples2, a.offsets, a.utt_begin, irm,
                                                      reinterpret_cast<uint32_t *>(bits), frame_offsets);
     prof_end(ctx, SE_K_IBM);
     SE_CUDA(cudaGetLastError());
