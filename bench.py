@@ -198,17 +198,34 @@ def host_timed_steps(torch, dist, step, warmup, steps):
     return dist.max((t1 - t0) * 1e3)
 
 
-def measured_traffic(utts, alg_bytes):
-    """roofline.traffic: DRAM bytes per launch of the dominant kernel from the committed ncu capture
-    (profiles/r01_traffic.json); only reported for the workload the capture was taken on."""
+def ncu_capture(utts, alg_bytes):
+    """The committed ncu capture of the dominant kernel (profiles/r01_traffic.json), if it was taken on this
+    workload; None otherwise."""
     try:
         with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
             t = json.load(f)
         if t["workload_utts"] == utts and abs(t["algorithmic_bytes_per_launch"] - alg_bytes) <= 0.001 * alg_bytes:
-            return t["traffic_bytes"]
+            return t
     except (OSError, KeyError, ValueError):
         pass
     return None
+
+
+def measured_traffic(utts, alg_bytes):
+    """roofline.traffic: DRAM bytes per launch of the dominant kernel from that capture."""
+    t = ncu_capture(utts, alg_bytes)
+    return t["traffic_bytes"] if t else None
+
+
+def issue_bound(utts, alg_bytes, kernel_ms, sm_mhz, sm_count=148):
+    """What actually bounds the kernel: executed warp-instructions per launch (ncu) against the
+    issue slots the SMs offered during the live-timed launch (4 schedulers per SM, one instruction per clock)."""
+    t = ncu_capture(utts, alg_bytes)
+    if not t or not sm_mhz:
+        return None
+    slots = sm_count * 4 * sm_mhz * 1e6 * kernel_ms * 1e-3
+    return {"warp_instructions_per_launch": t["inst_executed"], "issue_slots_in_launch": slots,
+            "frac": t["inst_executed"] / slots}
 
 
 def dev(torch, a):
@@ -556,7 +573,8 @@ def run_ours(args):
                        "parallelism": "utterance-sharded, %d rank(s), no collective" % args.gpus},
             "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
                          "traffic": measured_traffic(args.utts, alg_bytes), "peak_source": peak_src, "kernel": "ns_stream_kernel<16,int16>",
-                         "kernel_ms": k_avg_ms, "algorithmic_bytes_per_launch": alg_bytes},
+                         "kernel_ms": k_avg_ms, "algorithmic_bytes_per_launch": alg_bytes,
+                         "issue_bound": issue_bound(args.utts, alg_bytes, k_avg_ms, r["clocks"].get("sm_mhz"))},
             "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
                     "ms_per_step": r["e2e_ms"] / args.steps, "matches_device_path": r["e2e_matches_device"]},
             "gpu_launches": r["launches"], "clocks": r["clocks"]}
