@@ -181,3 +181,34 @@ def test_fuzz_features(ctx, oracle, oracle_fma):
         # of the same noise -- a tie by construction (the reference's two builds differ there too, test_fuzz_p8)
         tie_share = 2e-2 if k == 5 else 2e-3
         assert g_vad[k] <= max(2, tie_share * rows[k], SLACK * s_vad[k], s_under[k]), (k, g_vad[k], s_vad[k], s_under[k])
+
+
+def test_fuzz_g64_exact_modes_stay_bit_exact(ctx, oracle):
+    """EXACT-mode G64 kernels reproduce the reference's float arithmetic operation by operation, so even the
+    degenerate signals must come out bit-identical (sub-band int16 rows, IBM bits, IBM-masked resynthesis);
+    the default FMA mode must still reach +-1 LSB on them."""
+    from speech_enhancement_b200 import api
+    xs = [x for x in _signals(np.random.default_rng(64), 16000, 30, 0.25) if len(x) >= 400]
+    samples, offsets = _batch(xs)
+    sub = ctx.subband(samples, offsets, exact=True)
+    rng = np.random.default_rng(3)
+    for u, x in enumerate(xs):
+        lo, hi = int(offsets[u]), int(offsets[u + 1])
+        ref_sub = oracle.subband(x)
+        assert np.array_equal(sub[64 * lo:64 * hi].reshape(64, len(x)), ref_sub), (u, u % 10)
+        nf = api.resynth_num_frames(len(x), api.RESYNTH_IBM)
+        m = rng.random((nf, 64)).astype(np.float32)
+        ref_i16, _ = oracle.resynth(x, m.copy(), api.RESYNTH_IBM)
+        assert np.array_equal(ctx.resynth(x, [0, len(x)], m, [0, nf], api.RESYNTH_IBM, exact=True), ref_i16), u
+        fast = ctx.resynth(x, [0, len(x)], m, [0, nf], api.RESYNTH_IBM, exact=False)
+        # full-scale inputs wrap the int16 cast (Q4): compare modulo 2^16
+        d = (fast.astype(np.int32) - ref_i16.astype(np.int32) + 32768) % 65536 - 32768
+        assert np.abs(d).max(initial=0) <= 1, (u, u % 10, int(np.abs(d).max()))
+    # IBM bits: clean = signal u, noise = signal u+1 (cut to the same length)
+    for u in range(0, len(xs) - 1, 2):
+        n = min(len(xs[u]), len(xs[u + 1]))
+        p, z = xs[u][:n], xs[u + 1][:n]
+        irm, bits, fo = ctx.ibm(p, z, [0, n])
+        rirm, ribm = oracle.single_ibm(oracle.subband(p), oracle.subband(z))
+        got = ((bits[:, None] >> np.arange(64, dtype=np.uint64)[None, :]) & np.uint64(1)).astype(np.uint8)
+        assert np.array_equal(got, ribm), u
