@@ -223,7 +223,11 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
             cudaStreamWaitEvent(lane0->stream, ctx->lanes[l].done, 0);
         }
     }
-    if (rc) { cudaStreamSynchronize(lane0->stream); return rc; }
+    if (rc) {
+        cudaStreamSynchronize(lane0->stream);
+        for (auto &t : trace) cudaEventDestroy(t.e);
+        return rc;
+    }
     if (counts && mem == SE_MEM_HOST)
         SE_CUDA(cudaMemcpyAsync(counts, d_counts, sizeof(int32_t) * (size_t)n_utts, cudaMemcpyDeviceToHost, lane0->stream));
     const int rc_leave = leave(ctx, mem);
