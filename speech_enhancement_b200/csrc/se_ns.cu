@@ -12,6 +12,7 @@
 // shuffle FFT (se_warp_fft.cuh), the 4-block sample history of both stages lives in per-warp shared
 // memory rings, filter banks / IDCT / windows are CTA-shared tables in shared memory.  HBM traffic is
 // exactly the algorithmic minimum: each input sample is read once, each output written once.
+#include <type_traits>
 #include "se_internal.h"
 #include "se_warp_fft.cuh"
 
