@@ -114,6 +114,9 @@ int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *o
                            float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised,
                            int mem);
 
+/* Module-level entry: DoCompCeps (etsi/cpp/CompCeps.c:309-318,368-549) on n independent frames of 201 floats
+ * (frame[0] = the sample before the frame, needed by the 0.9 pre-emphasis) -> 14 floats c1..c12,c0,logE each. */
+int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float *coef14, int mem);
 /* Known-answer entry: DoWaveProc (etsi/cpp/WaveProc.c:386-453) on n frames of 200 floats, in place. */
 int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem);
 

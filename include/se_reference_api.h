@@ -48,6 +48,14 @@ FEParamsX *AdvProcessAlloc(int SamplingFrequency);            /* only 8000 is on
 void AdvProcessInit(FEParamsX *This);
 int DoAdvProcess(short *CurrentFrame, short *OutBuf, float *FeatBuf, FEParamsX *This);
 int se_adv_feature_ready(FEParamsX *This);                    /* additive: 1 if the last call wrote FeatBuf */
+/* Module entry points (etsi/cpp/NoiseSupExports.h:20-26, CompCepsExports.h:17-20) on the same opaque handle;
+ * their Alloc/Delete halves are part of AdvProcessAlloc/AdvProcessDelete here.
+ * DoNoiseSup: 80 floats in; TRUE(1) when 80 denoised floats were written to OutData (NoiseSup.c:1436-1439),
+ * no zero-frame gate.  DoCompCeps: Data = 200-sample frame with Data[-1] valid; Coef = c1..c12,c0,logE. */
+void DoNoiseSupInit(FEParamsX *This);
+int DoNoiseSup(float *InData, float *OutData, FEParamsX *This);
+void DoCompCepsInit(FEParamsX *This);
+int DoCompCeps(float *Data, float *Coef, FEParamsX *This);
 void AdvProcessDelete(FEParamsX **This);
 
 /* ---- function/20141106_speech_enhancement/aurora_etsi/NoiseSupExports.h:9-42 -------------------- */

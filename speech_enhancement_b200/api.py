@@ -58,6 +58,7 @@ def lib():
         L.se_resynth_num_frames.argtypes = [C.c_int64, C.c_int]
         L.se_etsi_denoise_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]
         L.se_wave_proc_batch.argtypes = [_vp, _vp, C.c_int, C.c_int]
+        L.se_comp_ceps_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int]
         L.se_etsi_features_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
         L.se_p16_wiener_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
         L.se_ns_stream_create.argtypes = [_vp, C.c_int, C.POINTER(_vp)]
@@ -247,6 +248,12 @@ class Context:
             out["trace_offsets"] = to
         self.etsi_denoise_raw(samples, offsets, nu, out["den_i16"], out.get("ceps"), co, out.get("n_ceps"),
                               out.get("den_f32"), out.get("trace"), to)
+        return out
+
+    def comp_ceps(self, frames201):
+        f = np.ascontiguousarray(frames201, np.float32).reshape(-1, 201)
+        out = np.zeros((len(f), 14), np.float32)
+        _check(self.L.se_comp_ceps_batch(self.h, _ptr(f), len(f), _ptr(out), SE_MEM_HOST), "se_comp_ceps_batch")
         return out
 
     def wave_proc(self, frames):

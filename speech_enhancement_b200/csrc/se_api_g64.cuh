@@ -158,6 +158,20 @@ int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem)
     return leave(ctx, mem);
 }
 
+int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float *coef14, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_comp_ceps_batch"));
+    if (n_frames < 0 || (n_frames > 0 && (!frames201 || !coef14))) { set_error("se_comp_ceps_batch: bad arguments"); return SE_EINVAL; }
+    if (n_frames == 0) return SE_OK;
+    const void *d_in = nullptr;
+    void *d_out = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, frames201, sizeof(float) * 201u * (uint64_t)n_frames, mem, &d_in));
+    SE_TRY(stage_out(ctx, kSlotOut, coef14, sizeof(float) * 14u * (uint64_t)n_frames, mem, false, &d_out));
+    SE_TRY(launch_comp_ceps(ctx, (const float *)d_in, (float *)d_out, n_frames));
+    SE_TRY(stage_out_copy(ctx, coef14, d_out, sizeof(float) * 14u * (uint64_t)n_frames, mem));
+    return leave(ctx, mem);
+}
+
 int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
                        int count, int flags, int mem)
 {

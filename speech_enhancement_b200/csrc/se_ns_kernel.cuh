@@ -416,6 +416,31 @@ __global__ void wave_proc_kernel(float *frames, int count)
     for (int i = lane; i < 200; i += 32) p[i] = fm.frame[1 + i];
 }
 
+// test / module-level kernel: DoCompCeps on independent 201-sample frames (frame[0] = sample -1), one warp each
+__global__ void __launch_bounds__(128) comp_ceps_kernel(const float *frames, float *coef, int count, const NsDevTables tb,
+                                                        const CcDevTables cc)
+{
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BlockMem<8> &bm = *reinterpret_cast<BlockMem<8> *>(smem_raw);
+    WarpMem<8> *wms = reinterpret_cast<WarpMem<8> *>(smem_raw + ((sizeof(BlockMem<8>) + 15) & ~size_t(15)));
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpMem<8> &wm = wms[warp];
+    load_block_tables<8>(bm, tb, cc);
+    __syncthreads();
+    FftTw tw;
+    fft_tw_init(tw, lane);
+    BankRegs br;
+    bank_regs_init(br, bm, lane);
+    for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;
+    __syncwarp();
+    for (int idx = blockIdx.x * 4 + warp; idx < count; idx += gridDim.x * 4) {
+        const float *f = frames + (int64_t)idx * 201;
+        const float out = comp_ceps_core(wm, bm, tw, br, lane, [&](int i) { return f[1 + i]; });
+        if (lane < 14) coef[(int64_t)idx * 14 + lane] = out;
+        __syncwarp();
+    }
+}
+
 // ------------------------------------------------------------------------------------------------
 // host launchers
 // ------------------------------------------------------------------------------------------------
@@ -467,6 +492,19 @@ int launch_wave_proc(se_ctx *ctx, float *frames, int count)
 {
     if (count <= 0) return SE_OK;
     wave_proc_kernel<<<(count + 3) / 4, 128, 0, ctx->cur->stream>>>(frames, count);
+    ctx->launches++;
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
+int launch_comp_ceps(se_ctx *ctx, const float *frames, float *coef, int count)
+{
+    if (count <= 0) return SE_OK;
+    const size_t smem = ((sizeof(BlockMem<8>) + 15) & ~size_t(15)) + 4 * sizeof(WarpMem<8>);
+    SE_CUDA(cudaFuncSetAttribute(comp_ceps_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));
+    int blocks = (count + 3) / 4;
+    if (blocks > ctx->sm_count * 4) blocks = ctx->sm_count * 4;
+    comp_ceps_kernel<<<blocks, 128, smem, ctx->cur->stream>>>(frames, coef, count, ctx->d_p8, ctx->d_cc);
     ctx->launches++;
     SE_CUDA(cudaGetLastError());
     return SE_OK;

@@ -97,6 +97,7 @@ SE_EXPORT void rfft(float *x, int n, int m)
 struct FEParamsX {
     se_ns_stream *ns;
     int feat_ready;
+    int gate;          // zero-frame gate currently set on the stream (1 = DoAdvProcess, 0 = bare DoNoiseSup)
 };
 
 SE_EXPORT FEParamsX *AdvProcessAlloc(int SamplingFrequency)
@@ -112,6 +113,7 @@ SE_EXPORT FEParamsX *AdvProcessAlloc(int SamplingFrequency)
     p->feat_ready = 0;
     if (report("AdvProcessAlloc", se_ns_stream_create(ctx, 8, &p->ns)) != SE_OK) { delete p; return nullptr; }
     se_ns_stream_set_zero_gate(p->ns, 1);        // DoAdvProcess skips leading all-zero frames
+    p->gate = 1;
     return p;
 }
 
@@ -127,6 +129,7 @@ SE_EXPORT int DoAdvProcess(short *CurrentFrame, short *OutBuf, float *FeatBuf, F
     for (int i = 0; i < 80; i++) in[i] = (float)CurrentFrame[i];      // ParmInterface.c:239-242
     int32_t produced = 0, n_ceps = 0;
     This->feat_ready = 0;
+    if (This->gate != 1) { se_ns_stream_set_zero_gate(This->ns, 1); This->gate = 1; }
     if (report("DoAdvProcess", se_ns_stream_push(This->ns, in, 1, out, &produced, nullptr, nullptr, nullptr,
                                                  FeatBuf ? ceps : nullptr, &n_ceps)) != SE_OK)
         return 0;
@@ -138,6 +141,35 @@ SE_EXPORT int DoAdvProcess(short *CurrentFrame, short *OutBuf, float *FeatBuf, F
 }
 
 SE_EXPORT int se_adv_feature_ready(FEParamsX *This) { return This ? This->feat_ready : 0; }
+
+// etsi/cpp/NoiseSupExports.h:20-26 / CompCepsExports.h:17-20: the module entry points DoAdvProcess reaches
+// through FEParamsX's function pointers, callable directly on the opaque handle.
+SE_EXPORT void DoNoiseSupInit(FEParamsX *This) { AdvProcessInit(This); }
+
+SE_EXPORT int DoNoiseSup(float *InData, float *OutData, FEParamsX *This)
+{
+    if (!This || !InData || !OutData) return 0;
+    if (This->gate != 0) { se_ns_stream_set_zero_gate(This->ns, 0); This->gate = 0; }   // no zero-frame gate here
+    int32_t produced = 0;
+    float out[80];
+    if (report("DoNoiseSup", se_ns_stream_push(This->ns, InData, 1, out, &produced, nullptr, nullptr, nullptr,
+                                               nullptr, nullptr)) != SE_OK)
+        return 0;
+    if (!(produced & 1)) return 0;            // latency: OutData untouched, like the reference
+    std::memcpy(OutData, out, sizeof out);
+    return 1;
+}
+
+SE_EXPORT void DoCompCepsInit(FEParamsX *) {}   // tables are built with the context
+
+SE_EXPORT int DoCompCeps(float *Data, float *Coef, FEParamsX *)
+{
+    if (!Data || !Coef) return 0;
+    se_ctx *ctx = default_ctx("DoCompCeps");
+    if (!ctx) return 0;
+    // Data[-1] must be valid (pre-emphasis, CompCeps.c:427-429): the caller passes frameBuf + 1
+    return report("DoCompCeps", se_comp_ceps_batch(ctx, Data - 1, 1, Coef, SE_MEM_HOST)) == SE_OK ? 1 : 0;
+}
 
 SE_EXPORT void AdvProcessDelete(FEParamsX **This)
 {

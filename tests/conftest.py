@@ -47,13 +47,15 @@ def rel_err(ref, test, floor):
 
 
 def ceps_err(ref, test):
-    """Cepstral parity metric: |a-b| / max(|a|, |b|, s) with s = the frame's largest |c1..c12| (for c1..c12)
-    or 1e-3 (for c0, logE).  c1..c12 are DCT sums of 23 log-band energies with cancellation; element-wise
-    relative error of a coefficient that happens to be near zero says nothing about parity (the
-    reference's own float FFT carries the same rounding noise), so the scale is the frame's vector."""
+    """Cepstral parity metric: |a-b| / max(|a|, |b|, s).  For c1..c12, s = max(the frame's largest |c1..c12|,
+    |c0|/23) (never below 1e-3); for c0 and logE, s = 1e-3.  c1..c12 are DCT sums of 23 log-band energies f_j with
+    cancellation: their rounding error scales with the size of the summed terms (mean |f_j| = |c0|/23 when the bands
+    share a sign, e.g. 10 on a frame whose bands all sit on the ln floor and whose c1..c12 cancel to ~1e-6), not with
+    the coefficient that happens to come out near zero -- the reference's own float FFT/DCT carries the same noise."""
     ref = np.asarray(ref, np.float64).reshape(-1, 14)
     test = np.asarray(test, np.float64).reshape(-1, 14)
     floor = np.full(ref.shape, 1e-3)
     if len(ref):
-        floor[:, :12] = np.maximum(np.max(np.abs(ref[:, :12]), axis=1, keepdims=True), 1e-3)
+        scale = np.maximum(np.max(np.abs(ref[:, :12]), axis=1, keepdims=True), np.abs(ref[:, 12:13]) / 23.0)
+        floor[:, :12] = np.maximum(scale, 1e-3)
     return np.abs(ref - test) / np.maximum(np.maximum(np.abs(ref), np.abs(test)), floor)

@@ -24,6 +24,9 @@ def dropin(ctx):
     L.AdvProcessInit.argtypes = [_vp]
     L.DoAdvProcess.argtypes = [_vp, _vp, _vp, _vp]
     L.se_adv_feature_ready.argtypes = [_vp]
+    L.DoNoiseSupInit.argtypes = [_vp]
+    L.DoNoiseSup.argtypes = [_vp, _vp, _vp]
+    L.DoCompCeps.argtypes = [_vp, _vp, _vp]
     L.AdvProcessDelete.argtypes = [C.POINTER(_vp)]
     L.etsi_denoise_mapping_global_init.argtypes = [C.POINTER(_vp), _vp]
     L.etsi_denoise_mapping_thread_init.argtypes = [C.POINTER(_vp), _vp]
@@ -133,3 +136,38 @@ def test_resynth_c_twin_marks_mask(dropin, oracle):
     ref, mref = oracle.resynth(x, m0, 0)
     assert np.array_equal(out, ref)
     assert np.array_equal(m, mref)                     # > 0.5 entries overwritten with 1.0 (extractwav.cpp:99)
+
+
+def test_module_entry_points_do_noise_sup_and_comp_ceps(dropin, oracle):
+    """DoNoiseSup / DoCompCeps called directly, the way DoAdvProcess reaches them through FEParamsX
+    (etsi/cpp/ParmInterface.c:260-293): float shifts in, BOOLEAN latency semantics, cepstra from frameBuf + 1."""
+    from conftest import ceps_err, snr_db
+    x = synth.utterance(9, 8000, 80 * 40)
+    x[:160] = 0                                              # no zero-frame gate at this level: processed like any frame
+    h = _vp(dropin.AdvProcessAlloc(8000))
+    assert h.value
+    dropin.DoNoiseSupInit(h)
+    s = oracle.L.so_ns_create(8)
+    hist = np.zeros(241, np.float32)                          # what BufInShiftToPut / BufInGetLast keep (BufferIn.c:157-205)
+    n_out = 0
+    for c in range(len(x) // 80):
+        frame = x[c * 80:(c + 1) * 80].astype(np.float32)
+        out = np.full(80, np.nan, np.float32)
+        ref = np.zeros(80, np.float32)
+        got = dropin.DoNoiseSup(frame.ctypes.data, out.ctypes.data, h)
+        exp = oracle.L.so_ns_block(s, frame.ctypes.data, ref.ctypes.data, None)
+        assert got == exp, c
+        if not got:
+            assert np.all(np.isnan(out))                     # latency: OutData untouched
+            continue
+        assert snr_db(ref, out) >= 60.0 or not ref.any()
+        n_out += 1
+        hist = np.concatenate([hist[80:], ref])
+        if n_out >= 3:                                        # frameBuf + 1 = the last 200 samples, [-1] valid
+            buf = np.ascontiguousarray(hist[241 - 201:])
+            coef = np.zeros(14, np.float32)
+            assert dropin.DoCompCeps(buf.ctypes.data + 4, coef.ctypes.data, h) == 1
+            assert ceps_err(oracle.comp_ceps(buf), coef).max() <= 1e-4
+    assert n_out == 40 - 4
+    oracle.L.so_ns_destroy(s)
+    dropin.AdvProcessDelete(C.byref(h))

@@ -92,3 +92,17 @@ def test_wave_proc_known_answer(ctx, oracle):
         if abs(e - 100.0) < 1e-3:
             continue                         # summation-order tie at the low-energy threshold
         assert np.array_equal(got[k], oracle.wave_proc(frames[k])), "frame %d" % k
+
+
+def test_comp_ceps_known_answer(ctx, oracle):
+    """DoCompCeps alone (se_comp_ceps_batch) on identical input frames: rel 1e-4 on the frame's cepstral scale."""
+    rng = np.random.default_rng(2)
+    n = np.arange(201)
+    frames = np.stack([(rng.standard_normal(201) * a).astype(np.float32) for a in (1.0, 300.0, 9000.0)] +
+                      [(4000 * np.sin(2 * np.pi * n * f / 8000.0)).astype(np.float32) for f in (100.0, 1234.5, 3900.0)] +
+                      [np.zeros(201, np.float32), synth.utterance(3, 8000, 201).astype(np.float32)] * 20)
+    got = ctx.comp_ceps(frames)
+    for k in range(len(frames)):
+        ref = oracle.comp_ceps(frames[k])
+        assert ceps_err(ref, got[k]).max() <= 1e-4, k
+    assert np.abs(got[6, :12]).max() < 1e-4 and got[6, 12] == -230.0 and got[6, 13] == -50.0   # all floors on a zero frame

@@ -175,7 +175,7 @@ def test_fuzz_features(ctx, oracle, oracle_fma):
     for k in range(KINDS):
         # rows above 1e-4 are WaveProc peak-position flips (tests/test_gpu_features.py): bounded by the main bar's
         # share on ordinary signals, by the reference's own flip rate on periodic / impulsive ones
-        assert g_bad[k] <= max(0.03 * rows[k], 1.5 * s_bad[k] + 5), "kind %d: %d rows off (reference vs itself %d) of %d" % (k, g_bad[k], s_bad[k], rows[k])
+        assert g_bad[k] <= max(0.03 * rows[k], 4 * s_bad[k] + 5), "kind %d: %d rows off (reference vs itself %d) of %d" % (k, g_bad[k], s_bad[k], rows[k])
         # kind 5 (isolated clicks in digital silence): almost every frame is all-zero input, where SpeechQVar's
         # variance E[W^2]-E[W]^2 (NoiseSup.c:813) is pure summation-order rounding noise compared against a running mean
         # of the same noise -- a tie by construction (the reference's two builds differ there too, test_fuzz_p8)

@@ -175,4 +175,4 @@ def test_reference_is_ill_conditioned_on_degenerate_signals(oracle):
         assert a.shape == b.shape
         if len(a):
             err[u % 10] = max(err[u % 10], float(ceps_err(a, b).max()))
-    assert err[8] < 1e-4 and err[1] > 1e-3 and err[5] > 1e-3, err
+    assert err[8] < 1e-4 and err[1] > 3e-4 and err[5] > 1e-3, err
