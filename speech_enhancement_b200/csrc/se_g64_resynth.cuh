@@ -20,7 +20,7 @@ struct GtItem {
     int32_t fs, fe, a, b;
 };
 constexpr int kGtWarm = 2560;
-constexpr int kGtChunk = 16000;
+constexpr int kGtChunk = 16000;      // smallest time chunk; the host doubles it while enough work items remain
 
 // ---- pass 1: y1[n][c] = gammatone_c(x)[n] / midEar_c, channel-minor scratch (coalesced) ---------
 template <bool EXACT>
@@ -74,7 +74,7 @@ __global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem
     };
     // run-in: samples [b, fe) only feed the filter state (default mode; empty in EXACT mode)
     int pos = it.fe - 1;
-    for (; pos >= it.b; pos--) (void)gt_step<EXACT>(g, k, y[(int64_t)(pos - it.fs) * 64]);
+    for (; pos >= it.b; pos--) (void)gt_step<EXACT>(g, k, y[(int64_t)(pos - it.a) * 64]);
 
     const int n = it.b - it.a;           // outputs to produce, from time b-1 down to a
     int h = (n > 0) ? pos / 160 : 0;
@@ -85,7 +85,7 @@ __global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem
         const int len = (n - m0 < T) ? (n - m0) : T;
         float in[T];
 #pragma unroll
-        for (int t = 0; t < T; t++) in[t] = (t < len) ? y[(int64_t)(it.b - 1 - (m0 + t) - it.fs) * 64] : 0.0f;
+        for (int t = 0; t < T; t++) in[t] = (t < len) ? y[(int64_t)(it.b - 1 - (m0 + t) - it.a) * 64] : 0.0f;
 #pragma unroll
         for (int t = 0; t < T; t++) {
             if (t < len) {
@@ -132,15 +132,19 @@ __global__ void __launch_bounds__(64) gt_fwd_fast_kernel(const int16_t *samples,
     const float scale = c_gt.gain[c] / c_gt.mid[c];
     GtStateR g; gtr_reset(g);
     const int n = it.fe - it.fs;
+    const int warm = it.a - it.fs;           // run-in: filtered for the state only, not stored (a whole number of tiles)
     int buf = 0;
     if (c < n) s_in[0][c] = (float)x[c];
     for (int t0 = 0; t0 < n; t0 += kTile, buf ^= 1) {
         const int len = (n - t0 < kTile) ? (n - t0) : kTile;
         __syncthreads();
         if (t0 + kTile + c < n) s_in[buf ^ 1][c] = (float)x[t0 + kTile + c];     // next tile, other buffer
-        float *yp = y + (int64_t)t0 * 64;
+        float *yp = y + (int64_t)(t0 - warm) * 64;                                // rows are relative to a
         gt_rot_seed(g, k, t0);
-        if (len == kTile) {
+        if (t0 < warm) {
+#pragma unroll 16
+            for (int t = 0; t < kTile; t++) (void)gt_step_rot(g, k, s_in[buf][t]);
+        } else if (len == kTile) {
 #pragma unroll 16
             for (int t = 0; t < kTile; t++) yp[t * 64] = gt_step_rot(g, k, s_in[buf][t]) * scale;
         } else {
@@ -178,7 +182,7 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
     int pos = it.fe - 1;
     while (pos >= it.b) {
         const int len = (pos - it.b + 1 < 16) ? (pos - it.b + 1) : 16;
-        const float *yp = y + (int64_t)(pos - it.fs) * 64;
+        const float *yp = y + (int64_t)(pos - it.a) * 64;
         float in[16];
 #pragma unroll
         for (int t = 0; t < 16; t++) in[t] = (t < len) ? yp[-t * 64] : 0.0f;
@@ -196,7 +200,7 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
         const int h = pos / 160, r_top = pos - h * 160;
         const float m_h = gate(h), m_h1 = gate(h + 1);
         const float wa = (m_h - m_h1) * scale, wb = m_h1 * scale;
-        const float *yp = y + (int64_t)(pos - it.fs) * 64;
+        const float *yp = y + (int64_t)(pos - it.a) * 64;
         float in[T];
         gt_rot_seed(g, k, step);
         if (len == T) {
