@@ -106,3 +106,17 @@ def test_comp_ceps_known_answer(ctx, oracle):
         ref = oracle.comp_ceps(frames[k])
         assert ceps_err(ref, got[k]).max() <= 1e-4, k
     assert np.abs(got[6, :12]).max() < 1e-4 and got[6, 12] == -230.0 and got[6, 13] == -50.0   # all floors on a zero frame
+
+
+def test_features_pipelined_chunks(ctx):
+    """SE_MEM_HOST calls are cut into H2D/kernel/D2H chunks on several streams; tiny chunks must not change the rows."""
+    samples, offsets = synth.corpus(900, 60, 8000, min_s=0.3, max_s=1.2)
+    a, den_a = ctx.etsi_features(samples, offsets, denoised=True)
+    ctx.set_pipeline(32 << 10, 4)
+    try:
+        b, den_b = ctx.etsi_features(samples, offsets, denoised=True)
+    finally:
+        ctx.set_pipeline(512 << 20, 1024)
+    assert np.array_equal(den_a, den_b)
+    for x, y in zip(a, b):
+        assert np.array_equal(x, y)
