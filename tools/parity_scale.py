@@ -1,0 +1,65 @@
+"""Parity statistics at scale (run on the GPU box): P8 and P16 on N ragged synthetic utterances against the -O2 oracle.
+Prints worst-case errors and the number of frame-dropping / VAD flag mismatches (threshold ties)."""
+import os
+import sys
+from concurrent.futures import ThreadPoolExecutor
+
+import numpy as np
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+sys.path.insert(0, ROOT)
+sys.path.insert(0, os.path.join(ROOT, "tests"))
+from conftest import ceps_err, rel_err, snr_db      # noqa: E402
+from oracle import pyoracle                         # noqa: E402
+from speech_enhancement_b200 import api, synth      # noqa: E402
+
+N = int(sys.argv[1]) if len(sys.argv) > 1 else 1000
+T = max(1, min(32, os.cpu_count() or 1))
+o = pyoracle.Oracle()
+ctx = api.Context(0)
+
+samples, offsets = synth.corpus(30000, N, 8000, min_s=2.0, max_s=6.0, threads=T)
+r = ctx.etsi_denoise(samples, offsets, ceps=True, den_f32=True, trace=True)
+
+
+def p8(u):
+    x = samples[offsets[u]:offsets[u + 1]]
+    ref = o.etsi_denoise(x, with_ceps=True, trace=True)
+    lo = int(offsets[u]); nb = len(x) // 80 * 80; nc = len(ref["ceps"]); co = int(r["ceps_offsets"][u])
+    lsb = int(np.abs(r["den_i16"][lo:lo + nb].astype(np.int32) - ref["den_i16"][:nb].astype(np.int32)).max(initial=0))
+    snr = snr_db(ref["den_f32"][:nb], r["den_f32"][lo:lo + nb])
+    ce = float(ceps_err(ref["ceps"], r["ceps"][co:co + nc]).max()) if nc else 0.0
+    tr = r["trace"][int(r["trace_offsets"][u]):int(r["trace_offsets"][u]) + ref["calls"]]
+    info = ref["info"]; on = info["stage0_ran"] > 0
+    mm = sum(int(np.sum(((tr[on] & bit) != 0) != (info[key][on] != 0)))
+             for bit, key in ((1, "flag_vad"), (2, "sp_var"), (4, "sp_spec"), (8, "sp_mel"), (16, "sp_vadns")))
+    return lsb, snr, ce, mm, int(on.sum()), nc == int(r["n_ceps"][u])
+
+
+with ThreadPoolExecutor(T) as ex:
+    res = list(ex.map(p8, range(N)))
+print("P8  %d utterances, %d frames: max |d| %d LSB, min SNR %.1f dB, max ceps err %.3g, flag mismatches %d of %d, counts ok %s"
+      % (N, sum(x[4] for x in res), max(x[0] for x in res), min(x[1] for x in res), max(x[2] for x in res),
+         sum(x[3] for x in res), 5 * sum(x[4] for x in res), all(x[5] for x in res)))
+
+samples, offsets = synth.corpus(60000, N, 16000, min_s=2.0, max_s=6.0, threads=T)
+r = ctx.p16_wiener(samples, offsets)
+bo = r["block_offsets"]
+
+
+def p16(u):
+    x = samples[offsets[u]:offsets[u + 1]]
+    s = o.p16_stream(); ref = s.func_wiener(x.astype(np.float32)); s.close()
+    lo = int(offsets[u]); nb = len(x) // 160; nr = int(r["n_rows"][u])
+    snr = snr_db(ref["out"][:nb * 160], r["out"][lo:lo + nb * 160])
+    ge = float(rel_err(ref["gains"], r["gains"][bo[u]:bo[u] + nr], 1e-3).max()) if nr and nr == len(ref["gains"]) else 0.0
+    fl = r["flags"][:, bo[u]:bo[u] + nb]
+    mm = sum(int(np.sum(fl[i] != ref[k])) for i, k in enumerate(("sp_var", "sp_spec", "sp_mel", "sp_vadns")))
+    return snr, ge, mm, nb, nr == len(ref["gains"]) and np.array_equal(fl[4], ref["frame_counter"])
+
+
+with ThreadPoolExecutor(T) as ex:
+    res = list(ex.map(p16, range(N)))
+print("P16 %d utterances, %d blocks: min SNR %.1f dB, max gains err %.3g, flag mismatches %d of %d, counts ok %s"
+      % (N, sum(x[3] for x in res), min(x[0] for x in res), max(x[1] for x in res), sum(x[2] for x in res),
+         4 * sum(x[3] for x in res), all(x[4] for x in res)))
