@@ -63,3 +63,47 @@ with ThreadPoolExecutor(T) as ex:
 print("P16 %d utterances, %d blocks: min SNR %.1f dB, max gains err %.3g, flag mismatches %d of %d, counts ok %s"
       % (N, sum(x[3] for x in res), min(x[0] for x in res), max(x[1] for x in res), sum(x[2] for x in res),
          4 * sum(x[3] for x in res), all(x[4] for x in res)))
+
+# ---- G64: default-mode resynthesis (both mask kinds), exact sub-bands and IBM bits ---------------------------
+M = max(16, N // 10)
+xs = [synth.utterance(90000 + i, 16000, synth.ragged_length(90000 + i, 16000, 1.0, 3.0), components=True) for i in range(M)]
+lens = [len(x[0]) for x in xs]
+offs = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+noisy = np.concatenate([x[0] for x in xs])
+for mode, name in ((api.RESYNTH_IBM, "IBM"), (api.RESYNTH_1DNN, "1dnn")):
+    nfs = [api.resynth_num_frames(n, mode) for n in lens]
+    fo = np.concatenate([[0], np.cumsum(nfs)]).astype(np.int64)
+    rng = np.random.default_rng(mode)
+    mask = rng.random((int(fo[-1]), 64), dtype=np.float32)
+    if mode != api.RESYNTH_IBM:
+        mask[mask < 0.2] = 0.0
+    fast = ctx.resynth(noisy, offs, mask, fo, mode, exact=False)
+    exact = ctx.resynth(noisy, offs, mask, fo, mode, exact=True)
+
+    def rs(u):
+        ref, _ = o.resynth(xs[u][0], mask[fo[u]:fo[u + 1]].copy(), mode)
+        lo, hi = int(offs[u]), int(offs[u + 1])
+        d = int(np.abs(fast[lo:hi].astype(np.int32) - ref.astype(np.int32)).max(initial=0))
+        return d, snr_db(ref, fast[lo:hi]), bool(np.array_equal(exact[lo:hi], ref))
+
+    with ThreadPoolExecutor(T) as ex:
+        res = list(ex.map(rs, range(M)))
+    print("G64 resynth %-4s %d utterances, %d samples: default mode max |d| %d LSB, min SNR %.1f dB; exact mode bit-identical: %s"
+          % (name, M, int(offs[-1]), max(x[0] for x in res), min(x[1] for x in res), all(x[2] for x in res)))
+
+pure = np.concatenate([x[1] for x in xs]); noise = np.concatenate([x[2] for x in xs])
+sub = ctx.subband(noisy, offs, exact=True)
+irm, bits, fo = ctx.ibm(pure, noise, offs)
+
+
+def g64(u):
+    lo, hi = int(offs[u]), int(offs[u + 1])
+    ok_sub = bool(np.array_equal(sub[64 * lo:64 * hi].reshape(64, hi - lo), o.subband(xs[u][0])))
+    rirm, ribm = o.single_ibm(o.subband(xs[u][1]), o.subband(xs[u][2]))
+    gb = ((bits[fo[u]:fo[u + 1], None] >> np.arange(64, dtype=np.uint64)[None, :]) & np.uint64(1)).astype(np.uint8)
+    return ok_sub, int(np.sum(gb != ribm)), ribm.size
+
+
+with ThreadPoolExecutor(T) as ex:
+    res = list(ex.map(g64, range(M)))
+print("G64 subband rows bit-identical: %s; IBM bit mismatches %d of %d" % (all(x[0] for x in res), sum(x[1] for x in res), sum(x[2] for x in res)))
