@@ -187,6 +187,8 @@ int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem);
 /* gammaToneFilter (extractwav.cpp:168-212) for `count` signals of length n with per-signal channel. */
 int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
                        int count, int flags, int mem);
+/* hairCell (extractwav.cpp:213-258, Meddis 1988) for `count` signals of length n, each from the resting state. */
+int se_haircell_batch(se_ctx *ctx, const float *in, float *out, int64_t n, int count, int mem);
 /* init-time tables as the device sees them (host copies), for table parity tests */
 int se_get_table(se_ctx *ctx, const char *name, float *out, int capacity, int *count);
 

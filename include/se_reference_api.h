@@ -96,6 +96,8 @@ int se_single_ibm(const short *pure, const short *noise, long n, float *irm /*[f
 int se_addnoise(const short *pure, short *noise, short *noisy, long n, int db);
 /* gammaToneFilter(): channel index instead of the by-value gammaTone struct (HuWang.h:50).      */
 int se_gammatone_filter(const float *input, float *output, int channel, long sigLength);
+/* hairCell(float *input, float *output, long sigLength) (HuWang.h:62, extractwav.cpp:213-258).  */
+int se_hair_cell(const float *input, float *output, long sigLength);
 
 #ifdef __cplusplus
 }

@@ -58,6 +58,7 @@ def lib():
         L.se_resynth_num_frames.argtypes = [C.c_int64, C.c_int]
         L.se_etsi_denoise_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, _vp, _vp, C.c_int]
         L.se_wave_proc_batch.argtypes = [_vp, _vp, C.c_int, C.c_int]
+        L.se_haircell_batch.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int, C.c_int]
         L.se_comp_ceps_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int]
         L.se_etsi_features_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
         L.se_p16_wiener_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
@@ -249,6 +250,13 @@ class Context:
         self.etsi_denoise_raw(samples, offsets, nu, out["den_i16"], out.get("ceps"), co, out.get("n_ceps"),
                               out.get("den_f32"), out.get("trace"), to)
         return out
+
+    def haircell(self, x):
+        x = np.ascontiguousarray(x, np.float32)
+        x2 = x.reshape(-1, x.shape[-1])
+        out = np.zeros_like(x2)
+        _check(self.L.se_haircell_batch(self.h, _ptr(x2), _ptr(out), x2.shape[1], x2.shape[0], SE_MEM_HOST), "se_haircell_batch")
+        return out.reshape(x.shape)
 
     def comp_ceps(self, frames201):
         f = np.ascontiguousarray(frames201, np.float32).reshape(-1, 201)

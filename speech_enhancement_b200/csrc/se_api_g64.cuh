@@ -192,6 +192,21 @@ int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *
     return leave(ctx, mem);
 }
 
+int se_haircell_batch(se_ctx *ctx, const float *in, float *out, int64_t n, int count, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_haircell_batch"));
+    if (count < 0 || n < 0 || (count > 0 && (!in || !out))) { set_error("se_haircell_batch: bad arguments"); return SE_EINVAL; }
+    if (count == 0 || n == 0) return SE_OK;
+    const uint64_t bytes = sizeof(float) * (uint64_t)n * (uint64_t)count;
+    const void *d_in = nullptr;
+    void *d_out = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, in, bytes, mem, &d_in));
+    SE_TRY(stage_out(ctx, kSlotOut, out, bytes, mem, false, &d_out));
+    SE_TRY(launch_haircell(ctx, (const float *)d_in, (float *)d_out, n, count));
+    SE_TRY(stage_out_copy(ctx, out, d_out, bytes, mem));
+    return leave(ctx, mem);
+}
+
 // Host copies of the init-time tables (built on the host, identical to what the kernels read).
 // ctx may be NULL: the tables are then built on the fly (no GPU needed — used by the CPU table tests).
 int se_get_table(se_ctx *ctx, const char *name, float *out, int capacity, int *count)

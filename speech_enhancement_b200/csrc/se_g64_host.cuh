@@ -144,6 +144,15 @@ int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *ch
     return SE_OK;
 }
 
+int launch_haircell(se_ctx *ctx, const float *in, float *out, int64_t n, int count)
+{
+    if (count <= 0) return SE_OK;
+    haircell_kernel<<<(count + 63) / 64, 64, 0, ctx->cur->stream>>>(in, out, n, count);
+    ctx->launches++;
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
 int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy, const int64_t *offsets, int n_utts,
                     int db)
 {

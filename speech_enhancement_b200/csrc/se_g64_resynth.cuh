@@ -242,6 +242,15 @@ __global__ void gammatone_kernel(const float *in, float *out, const int32_t *cha
     for (int64_t t = 0; t < n; t++) out[i * n + t] = gt_step<EXACT>(g, k, in[i * n + t]);
 }
 
+// ---- known-answer kernel: hairCell (extractwav.cpp:213-258) on float signals, one thread per signal ---------
+__global__ void haircell_kernel(const float *in, float *out, int64_t n, int count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    HcState h; hc_reset(h, c_gt.hc);
+    for (int64_t t = 0; t < n; t++) out[i * n + t] = hc_step(h, c_gt.hc, in[i * n + t]);
+}
+
 // ---- addnoise (enhancement_extract_subband_linux/cpp/extractwav.cpp:6-35) -----------------------
 // Energy sums accumulate in float with a double intermediate, sequentially (one thread / utterance).
 __global__ void addnoise_gain_kernel(const int16_t *pure, const int16_t *noise, const int64_t *offsets, int n_utts,

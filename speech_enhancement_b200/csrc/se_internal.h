@@ -161,6 +161,7 @@ int launch_ns_p8(se_ctx *ctx, const NsLaunch &a);
 int launch_ns_p16(se_ctx *ctx, const NsLaunch &a);
 int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count);
 int launch_wave_proc(se_ctx *ctx, float *frames, int count);
+int launch_haircell(se_ctx *ctx, const float *in, float *out, int64_t n, int count);
 int launch_comp_ceps(se_ctx *ctx, const float *frames, float *coef, int count);
 
 struct G64Launch {

@@ -306,6 +306,13 @@ SE_EXPORT int se_addnoise(const short *pure, short *noise, short *noisy, long n,
     return report("se_addnoise", se_addnoise_batch(ctx, pure, noise, noisy, off, 1, db, SE_MEM_HOST));
 }
 
+SE_EXPORT int se_hair_cell(const float *input, float *output, long sigLength)
+{
+    se_ctx *ctx = default_ctx("se_hair_cell");
+    if (!ctx) return SE_ENODEVICE;
+    return report("se_hair_cell", se_haircell_batch(ctx, input, output, sigLength, 1, SE_MEM_HOST));
+}
+
 SE_EXPORT int se_gammatone_filter(const float *input, float *output, int channel, long sigLength)
 {
     se_ctx *ctx = default_ctx("se_gammatone_filter");

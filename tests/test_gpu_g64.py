@@ -30,6 +30,16 @@ def test_gammatone_impulse_and_noise_exact(ctx, oracle):
         assert snr_db(ref, yf[c]) >= SNR_MIN_DB
 
 
+def test_haircell_known_answer(ctx, oracle):
+    """hairCell alone (Meddis model with the reference's double-promoted permeability term): bit-exact."""
+    rng = np.random.default_rng(5)
+    x = np.stack([rng.standard_normal(3000) * a for a in (0.5, 30.0, 2000.0, 60000.0)] +
+                 [np.full(3000, -3.0), np.full(3000, -2.9999998), np.zeros(3000)]).astype(np.float32)
+    y = ctx.haircell(x)
+    for i in range(len(x)):
+        assert np.array_equal(y[i], oracle.haircell(x[i])), i
+
+
 def test_tables_match_oracle(ctx, oracle):
     cf, bw, mid = oracle.channel_params()
     assert np.array_equal(api.get_table("gt.cf", ctx), cf)
