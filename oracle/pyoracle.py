@@ -96,6 +96,12 @@ class Oracle:
         L.so_wave_proc.argtypes = [_vp]
         L.so_etsi_features.restype = C.c_long
         L.so_etsi_features.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.so_etsi_features_16k.restype = C.c_long
+        L.so_etsi_features_16k.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.so_qmf_split.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.so_qmf_taps.argtypes = [_vp, _vp]
+        L.so_ns_attach_hp16k.argtypes = [_vp]
+        L.so_hp16k_tables.argtypes = [_vp, _vp, _vp, _vp]
 
     # ---- primitives
     def rfft(self, x, m, cxx=False):
@@ -139,6 +145,31 @@ class Oracle:
         den = np.zeros(len(x), np.int16)
         rows = self.L.so_etsi_features(_p(x), len(x), _p(feat), _p(den))
         return feat[:rows].copy(), den
+
+    def etsi_features_16k(self, x):
+        """16 kHz mode (QMF + HP-band coding): (feat[rows][15], low-band den_i16[(n//160)*80])."""
+        x = np.ascontiguousarray(x, np.int16)
+        feat = np.zeros((max(len(x) // 160, 1), 15), np.float32)
+        den = np.zeros((len(x) // 160) * 80, np.int16)
+        rows = self.L.so_etsi_features_16k(_p(x), len(x), _p(feat), _p(den))
+        return feat[:rows].copy(), den
+
+    def qmf_split(self, x):
+        x = np.ascontiguousarray(x, np.int16)
+        m = (len(x) // 160) * 80
+        lp = np.zeros(m, np.float32); hp = np.zeros(m, np.float32)
+        self.L.so_qmf_split(_p(x), len(x), _p(lp), _p(hp))
+        return lp, hp
+
+    def hp16k_tables(self):
+        dp = np.zeros(118, np.float32); hp = np.zeros(118, np.float32)
+        self.L.so_qmf_taps(_p(dp), _p(hp))
+        h = self.L.so_ns_create(8)
+        self.L.so_ns_attach_hp16k(h)
+        st = np.zeros(5, np.int32); ln = np.zeros(5, np.int32); fb = np.zeros((5, 65), np.float32)
+        self.L.so_hp16k_tables(h, _p(st), _p(ln), _p(fb))
+        self.L.so_ns_destroy(h)
+        return dict(dp=dp, hp=hp, start=st, len=ln, fb=fb)
 
     def cc_tables(self):
         ham = np.zeros(100, np.float32); dct = np.zeros((12, 23), np.float32)
@@ -252,11 +283,29 @@ class RefEtsi:
         L.ref_wave_proc.argtypes = [_vp]
         L.ref_etsi_features.restype = C.c_long
         L.ref_etsi_features.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.ref_etsi_features_16k.restype = C.c_long
+        L.ref_etsi_features_16k.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.ref_qmf_split.argtypes = [_vp, C.c_long, _vp, _vp]
 
     def rfft(self, x, m):
         y = np.ascontiguousarray(x, np.float32).copy()
         self.L.ref_rfft(_p(y), len(y), m)
         return y
+
+    def etsi_features_16k(self, x):
+        """16 kHz mode: (feat[rows][15], low-band den_i16[(n//160)*80])."""
+        x = np.ascontiguousarray(x, np.int16)
+        feat = np.zeros((max(len(x) // 160, 1), 15), np.float32)
+        den = np.zeros((len(x) // 160) * 80, np.int16)
+        rows = self.L.ref_etsi_features_16k(_p(x), len(x), _p(feat), _p(den))
+        return feat[:rows].copy(), den
+
+    def qmf_split(self, x):
+        x = np.ascontiguousarray(x, np.int16)
+        m = (len(x) // 160) * 80
+        lp = np.zeros(m, np.float32); hp = np.zeros(m, np.float32)
+        self.L.ref_qmf_split(_p(x), len(x), _p(lp), _p(hp))
+        return lp, hp
 
     def wave_proc(self, frame200):
         f = np.ascontiguousarray(frame200, np.float32).copy()

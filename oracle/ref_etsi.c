@@ -280,3 +280,82 @@ long ref_etsi_features(const short *in, long n, float *feat, short *den_i16)
     AdvProcessDelete(&fe);
     return rows;
 }
+
+/* ---- 16 kHz mode ----------------------------------------------------------- */
+#include "16kHzProcExports.h"
+
+/* Same loop at SamplingFrequency 16000 (AdvProcessAlloc :99-109): 160 samples per call, QMF split by
+ * Do16kProcessing (ParmInterface.c:259-260), NoiseSup on the 0-4 kHz half, HP-band coding inside DoNoiseSup
+ * and decoding/merging inside DoCompCeps (26 log bands).  den_i16: the 80 denoised LOW-BAND samples of each
+ * call, [n/160][80] (what etsi_denoise_16k's DenoiseBuffer really holds, AdvFrontEnd.c:264).
+ * feat as above.  Returns the number of rows. */
+long ref_etsi_features_16k(const short *in, long n, float *feat, short *den_i16)
+{
+    FEParamsX *fe = AdvProcessAlloc(16000);
+    X_FLOAT32 frameBuf[FRAME_BUF_SIZE + 8];
+    X_FLOAT32 fb[NUM_CEP_COEFF + 3];
+    short den_buf[80];
+    long start = 0, rows = 0, call = 0;
+    int i;
+    fe->Noc0 = 0;
+    AdvProcessInit(fe);
+    memset(den_buf, 0, sizeof den_buf);
+    memset(fb, 0, sizeof fb);
+    while (start + 160 <= n) {
+        X_FLOAT32 *pt = BufInShiftToPut(fe->denoisedBuf, fe->FrameShift);
+        float check = 0.0f;
+        int out = 0;
+        for (i = 0; i < 160; i++) {
+            fe->CurFrame[i] = (X_FLOAT32)in[start + i];
+            check += in[start + i] * in[start + i];
+        }
+        if (((int)check != 0) || (fe->NonZeroFrameOnset != 0)) {
+            fe->NonZeroFrameOnset = 1;
+            fe->Do16kProcessing(fe->CurFrame, fe->pData16k, 160);
+            if (fe->DoNoiseSup(fe->CurFrame, pt, fe)) {
+                for (i = 0; i < 80; i++) den_buf[i] = (FILE_TYPE)pt[i];
+                if (fe->offsetDenoisedFrame < 0) fe->offsetDenoisedFrame += fe->FrameShift;
+                if (fe->offsetDenoisedFrame >= 0) {
+                    BufInGetLast(fe->denoisedBuf, frameBuf, fe->FrameLength + fe->offsetDenoisedFrame + 1);
+                    fe->DoWaveProc(frameBuf + 1, fe);
+                    fe->DoCompCeps(frameBuf + 1, fb, fe);
+                    fe->DoPostProc(fb, fe);
+                    out = fe->DoVADProc(fb, fe) ? 1 : 0;
+                }
+            }
+        } else {
+            fe->ZeroFrameCounter++;
+            for (i = 0; i <= NUM_CEP_COEFF; i++) fb[i] = 0.0;
+            fe->VAD = NON_SPEECH_FRAME;
+            out = 1;
+        }
+        if (out) {
+            memcpy(feat + rows * 15, fb, sizeof(float) * 15);
+            rows++;
+        }
+        if (den_i16) memcpy(den_i16 + call * 80, den_buf, sizeof den_buf);
+        start += 160;
+        call++;
+    }
+    AdvProcessDelete(&fe);
+    return rows;
+}
+
+/* Do16kProcessing alone (16kHzProcessing.c:711): x[n] (n a multiple of 160) -> lp[n/2], hp[n/2], streaming. */
+void ref_qmf_split(const short *in, long n, float *lp, float *hp)
+{
+    FEParamsX *fe = AdvProcessAlloc(16000);
+    long start;
+    int i;
+    AdvProcessInit(fe);
+    for (start = 0; start + 160 <= n; start += 160) {
+        float buf[160];
+        for (i = 0; i < 160; i++) buf[i] = (float)in[start + i];
+        Do16kProcessing(buf, fe->pData16k, 160);
+        for (i = 0; i < 80; i++) {
+            lp[start / 2 + i] = buf[i];
+            hp[start / 2 + i] = Get16k_dataHP(fe->pData16k, i);
+        }
+    }
+    AdvProcessDelete(&fe);
+}

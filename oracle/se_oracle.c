@@ -114,7 +114,25 @@ void so_rfft_cxx(float *x, int n, int m) { so_rfft_impl(x, n, m, 1); }
 #define MAXFRAME 480
 #define MAXFFT 512
 
+/* State of the 16 kHz extension (DataFor16kProc + QMF_FIR, etsi/cpp/16kHzProcessing.c:37-84), attached to a
+ * P8 stream by so_ns_attach_hp16k(). */
+#define HP_QMF 118
+typedef struct so_hp16k {
+    float dp[HP_QMF], hp[HP_QMF], hist[HP_QMF - 1];   /* QMF_FIR: low/high-pass taps, delay line */
+    float data_hp[80];                               /* dataHP: this call's 4-8 kHz half, shifted to 0-4 kHz */
+    float buf[480];                                  /* bufferData16k */
+    float snap[256];                                 /* tmpWorkSpace16k (frame copied at stage 0, used at stage 1) */
+    float hp_bands[9], code[9], code_buf[27];        /* hpBands, CodeForBands16k, bufferCodeForBands16k */
+    float lp_log[9];                                 /* BandsForCoding16k: 3 frames x 3 log band energies */
+    float fb16k[3];                                  /* this call's spectrally-subtracted HP bands */
+    float noise[3], mean_en;
+    int nb_speech, hang_over;
+    int fb_start[5], fb_len[5];
+    float fb[5][65];                                 /* FirstWindow16k: 5 un-normalised mel triangles over 65 bins */
+} so_hp16k;
+
 struct so_ns {
+    struct so_hp16k *hp16k;
     /* profile constants: etsi/cpp/NoiseSup.h:28-79 vs aurora_etsi/NoiseSup.h:22-72 */
     int profile, S, FL, NFFT, M, SPEC, BUF, DIN, ANA, fs;
     /* BUFFERS (NoiseSup.c:92-100) */
@@ -277,7 +295,7 @@ so_ns *so_ns_create(int profile)
     return s;
 }
 
-void so_ns_destroy(so_ns *s) { free(s); }
+void so_ns_destroy(so_ns *s) { if (s) free(s->hp16k); free(s); }
 int so_ns_shift(const so_ns *s) { return s->S; }
 int so_ns_spec(const so_ns *s) { return s->SPEC; }
 
@@ -469,6 +487,204 @@ static int ns_q_mel(so_ns *s)
 
 /* One block: DoNoiseSup (etsi/cpp/NoiseSup.c:1061-1440) == body of the func_Wiener loop
  * (aurora_etsi/NoiseSup.cpp:1172-1403). */
+/* =====================================================================================
+ * 16 kHz extension of the P8 stream: etsi/cpp/16kHzProcessing.c and its hooks in
+ * DoNoiseSup (etsi/cpp/NoiseSup.c:1104-1121, 1166-1172, 1216-1235, 1307-1327, 1378-1382, 1402-1435)
+ * ===================================================================================== */
+
+/* Half-band prototype (DP_HP_filters, 16kHzProcessing.c:559-608): 118 symmetric taps, integers / 2^23; only the
+ * first 59 are listed, tap[117-i] = tap[i].  The high-pass is the time-reversed prototype with alternating signs. */
+static const int qmf_half[59] = {
+    1584, 805, -4192, -8985, -5987, 2583, 4657, -3035, -7004, 1542, 8969, 567, -10924, -3757, 12320, 7951, -12793,
+    -13048, 11923, 18793, -9331, -24802, 4694, 30570, 2233, -35439, -11526, 38680, 23114, -39474, -36701, 36999,
+    51797, -30419, -67658, 18962, 83318, -1927, -97566, -21284, 108971, 51215, -115837, -88430, 116130, 133716,
+    -107253, -188497, 85497, 255795, -44643, -342699, -28185, 468096, 167799, -696809, -519818, 1446093, 3562497};
+
+void so_qmf_taps(float *dp118, float *hp118)
+{
+    int i, sign = 1;
+    for (i = 0; i < HP_QMF; i++) dp118[i] = (float)((double)qmf_half[i < 59 ? i : HP_QMF - 1 - i] / (float)0x00800000);
+    for (i = 0; i < HP_QMF; i++) {
+        hp118[HP_QMF - 1 - i] = (float)sign * dp118[i];
+        sign = -sign;
+    }
+}
+
+/* Do16kProcAlloc/Init (16kHzProcessing.c:178-271): everything zero, 5 un-normalised mel triangles from 80 Hz over
+ * the 65-bin PSD (InitMelFBwindows(.., 80.0, 8000, 128, 5, 0)). */
+static void hp16k_init(so_hp16k *h)
+{
+    int c[5], i, j, k;
+    const float st_freq = 80.0, smpl = 8000.0;
+    const int fft_len = 128, nch = 5;
+    float start_mel = 2595.0 * log10(1.0 + (float)st_freq / 700.0);
+    float half_mel = 2595.0 * log10(1.0 + (smpl / 2) / 700.0);
+    memset(h, 0, sizeof *h);
+    so_qmf_taps(h->dp, h->hp);
+    for (i = 0; i < nch; i++) {
+        float f = 700 * (pow(10, (start_mel + (float)i / (nch - 1) * (half_mel - start_mel)) / 2595.0) - 1.0);
+        c[i] = (int)(fft_len * f / smpl + 0.5);
+    }
+    for (i = 0; i < nch; i++) {
+        float *d = h->fb[i];
+        int len;
+        if (i == 0) {
+            h->fb_start[i] = c[0];
+            len = c[1] - c[0];
+            for (j = 0; j < len; j++) d[j] = 1.0 - (float)j / (float)len;
+        } else if (i < nch - 1) {
+            const int up = c[i] - c[i - 1];
+            h->fb_start[i] = c[i - 1] + 1;
+            len = c[i + 1] - c[i - 1] - 1;
+            for (j = 0; j < up; j++) d[j] = (float)(j + 1) / (float)up;
+            for (j = up, k = 0; j < len; j++, k++) d[j] = 1.0 - (k + 1) / (float)(c[i + 1] - c[i]);
+        } else {
+            h->fb_start[i] = c[nch - 2] + 1;
+            len = c[nch - 1] - c[nch - 2];
+            for (j = 0; j < len; j++) d[j] = (float)(j + 1) / (float)len;
+        }
+        h->fb_len[i] = len;
+    }
+}
+
+int so_ns_attach_hp16k(so_ns *s)
+{
+    if (!s || s->profile != SO_PROFILE_P8 || s->hp16k) return -1;
+    s->hp16k = (so_hp16k *)malloc(sizeof(so_hp16k));
+    if (!s->hp16k) return -1;
+    hp16k_init(s->hp16k);
+    return 0;
+}
+
+void so_hp16k_tables(const so_ns *s, int *start5, int *len5, float *fb5x65)
+{
+    memcpy(start5, s->hp16k->fb_start, sizeof s->hp16k->fb_start);
+    memcpy(len5, s->hp16k->fb_len, sizeof s->hp16k->fb_len);
+    memcpy(fb5x65, s->hp16k->fb, sizeof s->hp16k->fb);
+}
+
+/* Do16kProcessing (16kHzProcessing.c:711-787) on one 160-sample call: x[160] (float 16 kHz samples) ->
+ * lp[80] (0-4 kHz half, what NoiseSup sees) and h->data_hp[80] (4-8 kHz half, spectrally flipped to 0-4 kHz). */
+static void hp16k_split(so_hp16k *h, const float *x, float *lp)
+{
+    float line[HP_QMF - 1 + 160];
+    int i, j, k, sign = 1;
+    memcpy(line, h->hist, sizeof h->hist);
+    memcpy(line + HP_QMF - 1, x, sizeof(float) * 160);
+    for (i = 0, k = 0; i < 160; i += 2, k++) {
+        float a = 0.0, b = 0.0;
+        for (j = 0; j < HP_QMF; j++) {
+            a += line[i + j] * h->dp[j];
+            b += line[i + j] * h->hp[j];
+        }
+        lp[k] = a;
+        h->data_hp[k] = (float)sign * b;
+        sign = -sign;
+    }
+    memcpy(h->hist, x + 160 - (HP_QMF - 1), sizeof h->hist);
+}
+
+/* Stage-0 hook (NoiseSup.c:1166-1172, 1216-1235): remember the HP frame that lines up with the cepstral frame,
+ * and log-energies of three low-band PSD regions (GetBandsForCoding16k, 16kHzProcessing.c:497-511) pushed into a
+ * 3-frame history. */
+static void hp16k_stage0(so_hp16k *h, const float *nsig)
+{
+    float aux[3] = {0.0, 0.0, 0.0};
+    const float floor_v = (float)exp((double)-10.0);
+    int i;
+    for (i = 0; i < 200; i++) h->snap[i] = h->buf[80 + i];             /* NS_ANALYSIS_WINDOW_16K */
+    for (i = 33; i < 39; i++) aux[0] += nsig[i];
+    for (i = 39; i < 49; i++) aux[1] += nsig[i];
+    for (i = 49; i < 65; i++) aux[2] += nsig[i];
+    for (i = 0; i < 6; i++) h->lp_log[i] = h->lp_log[i + 3];
+    for (i = 0; i < 3; i++) {
+        if (aux[i] > floor_v) h->lp_log[6 + i] = (float)log((double)aux[i]);
+        else h->lp_log[6 + i] = (float)-10.0;
+    }
+}
+
+/* DoSpecSub16k (16kHzProcessing.c:388-480): energy VAD on the 3 HP bands, noise tracking, over-subtraction 1.5
+ * with a floor at 10 %. */
+static void hp16k_spec_sub(so_hp16k *h, float *fb, long frame_no)
+{
+    const float eps = (float)exp((double)-10.0);
+    int i, flag, nbf = frame_no;
+    float lambda, diff, floor_v, frame_en, mean_en = h->mean_en;
+    if (nbf < 100) lambda = 1.0 - 1.0 / (float)nbf;
+    else lambda = 0.99;
+    frame_en = 0.0;
+    for (i = 0; i < 3; i++) frame_en += fb[i];
+    if (frame_en > 0.001) frame_en = (float)log((double)frame_en);
+    else frame_en = (float)log((double)0.001);
+    if (((frame_en - mean_en) < 1.2) || (nbf < 10)) {
+        if (nbf < 10) mean_en += (1 - lambda) * (frame_en - mean_en);
+        else if (frame_en < mean_en) mean_en += (1 - 0.98) * (frame_en - mean_en);
+        else mean_en += (1 - 0.995) * (frame_en - mean_en);
+    }
+    if ((frame_en - mean_en) > 2.2) {
+        flag = 1;
+        h->nb_speech++;
+    } else {
+        if (h->nb_speech > 4) h->hang_over = 15;
+        h->nb_speech = 0;
+        if (h->hang_over != 0) { h->hang_over--; flag = 1; }
+        else flag = 0;
+    }
+    if (flag == 0) {
+        for (i = 0; i < 3; i++) {
+            if (nbf < 10) h->noise[i] = lambda * h->noise[i] + (1 - lambda) * fb[i];
+            else if (fb[i] < h->noise[i]) h->noise[i] = lambda * h->noise[i] + (1 - lambda) * fb[i];
+            else h->noise[i] = 0.995 * h->noise[i] + (1 - 0.995) * fb[i];
+            if (h->noise[i] < eps) h->noise[i] = eps;
+        }
+    }
+    for (i = 0; i < 3; i++) {
+        floor_v = 0.1 * fb[i];
+        diff = fb[i] - 1.5 * h->noise[i];
+        fb[i] = (diff > floor_v) ? diff : floor_v;
+    }
+    h->mean_en = mean_en;
+}
+
+/* Stage-1 hook (NoiseSup.c:1307-1327): PSD of the remembered HP frame -> mel bands 1..3 of 5 -> log ->
+ * code = (oldest low-band log energies) - (HP log band) (CodeBands16k, :530-537) -> spectral subtraction. */
+static void hp16k_stage1(so_hp16k *h, const float *sig_window, long frame_no)
+{
+    float t[256], psd[65], sum[5], aux[3];
+    const float floor_v = (float)exp((double)-10.0);
+    int i, j;
+    for (i = 0; i < 200; i++) t[i] = h->snap[i] * sig_window[i];
+    for (i = 200; i < 256; i++) t[i] = 0.0;
+    so_rfft(t, 256, 8);
+    t[0] = t[0] * t[0];
+    for (i = 1, j = 255; i < 128; i++, j--) t[i] = (t[i] * t[i] + t[j] * t[j]);
+    t[i] = t[i] * t[i];
+    for (i = 0, j = 0; i < 64; i++, j += 2) psd[i] = (t[j] + t[j + 1]) / 2.0;
+    psd[i] = t[j];
+    for (j = 0; j < 5; j++) {
+        sum[j] = 0.0;
+        for (i = 0; i < h->fb_len[j]; i++) sum[j] += psd[h->fb_start[j] + i] * h->fb[j][i];
+    }
+    for (i = 0; i < 3; i++) h->fb16k[i] = sum[i + 1];
+    for (i = 0; i < 3; i++) {
+        if (h->fb16k[i] > floor_v) aux[i] = log(h->fb16k[i]);
+        else aux[i] = (float)-10.0;
+    }
+    for (i = 0; i < 3; i++)
+        for (j = 0; j < 3; j++) h->code[3 * i + j] = h->lp_log[j] - aux[i];
+    hp16k_spec_sub(h, h->fb16k, frame_no);
+}
+
+/* After a denoised shift is out (NoiseSup.c:1402-1435): 3-frame delay lines of the HP bands and their codes. */
+static void hp16k_push(so_hp16k *h)
+{
+    int i;
+    for (i = 3; i < 9; i++) h->hp_bands[i - 3] = h->hp_bands[i];
+    for (i = 0; i < 3; i++) h->hp_bands[6 + i] = h->fb16k[i];
+    for (i = 0; i < 18; i++) h->code_buf[i] = h->code_buf[i + 9];
+    for (i = 0; i < 9; i++) h->code_buf[18 + i] = h->code[i];
+}
+
 int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
 {
     float tmp[MAXFFT + SO_MAX_SPEC]; /* the reference's tmpMem aliases, kept apart here */
@@ -478,6 +694,7 @@ int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
     if (info) { memset(info, 0, sizeof *info); }
     for (i = 0; i < S; i++) s->buf1[s->DIN + i] = in[i];
     s->nb_in1++;
+    if (s->hp16k) memcpy(s->hp16k->buf + 480 - 80, s->hp16k->data_hp, sizeof(float) * 80);   /* NoiseSup.c:1119-1120 */
     for (fstage = 0; fstage < 2; fstage++) {
         float *buf, *nsig, *hist, *prv, *cur;
         short *idx;
@@ -498,6 +715,7 @@ int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
         tmp[i] = tmp[i] * tmp[i];
         for (i = 0, j = 0; i < n - 1; i++, j += 2) nsig[i] = (tmp[j] + tmp[j + 1]) / 2.0;
         nsig[i] = tmp[j];
+        if (s->hp16k && fstage == 0) hp16k_stage0(s->hp16k, nsig);
         /* PSDMean :289-303 */
         *idx = 1 - *idx;
         for (i = 0; i < n; i++) {
@@ -553,6 +771,7 @@ int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
             for (j = -NS_HALF; j <= (i <= NS_HALF ? i : NS_HALF); j++) sig_out[i] += (fir[j + NS_HALF] * cur[i - j]);
             for (j = i + 1; j <= NS_HALF; j++) sig_out[i] += (fir[j + NS_HALF] * prv[S - j + i]);
         }
+        if (s->hp16k && fstage == 1) hp16k_stage1(s->hp16k, s->sig_window, s->nb_frame[1]);
         if (fstage == 0) {
             for (i = 0; i < S; i++) s->buf2[s->DIN + i] = sig_out[i];
             s->nb_in2++;
@@ -564,6 +783,7 @@ int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
         }
     }
     if (s->nb_in1) for (i = 0; i < s->DIN; i++) s->buf1[i] = s->buf1[i + S];
+    if (s->nb_in1 && s->hp16k) memmove(s->hp16k->buf, s->hp16k->buf + 80, sizeof(float) * 400);   /* :1378-1382 */
     if (s->nb_in2) for (i = 0; i < s->DIN; i++) s->buf2[i] = s->buf2[i + S];
     if (info) {
         info->flag_vad = s->flag_vad; info->hang_over = s->hang_over; info->nb_speech = s->nb_speech;
@@ -580,6 +800,7 @@ int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
             s->dc_y = out[i];
         }
         if (info) info->produced = 1;
+        if (s->hp16k) hp16k_push(s->hp16k);
         return 1;
     }
     return 0;
@@ -589,7 +810,7 @@ int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info)
  * CompCeps (P8): etsi/cpp/CompCeps.c
  * ===================================================================================== */
 typedef struct {
-    float hamming[100], dct[12 * 23];
+    float hamming[100], dct[12 * 23], dct26[12 * 26];
     int start[23], len[23];
     float tri[23][129];
     int ready;
@@ -607,6 +828,9 @@ static void cc_init(void)
     for (i = 1; i < 13; i++)                                                                   /* :153-173 */
         for (j = 0; j < nch; j++)
             g_cc.dct[(i - 1) * nch + j] = cos(SO_PI * (float)i / (float)nch * ((float)j + 0.5));
+    for (i = 1; i < 13; i++)                                                                   /* 16 kHz: 23 + 3 bands */
+        for (j = 0; j < 26; j++)
+            g_cc.dct26[(i - 1) * 26 + j] = cos(SO_PI * (float)i / (float)26 * ((float)j + 0.5));
     /* InitFFTWindows, etsi/cpp/MelProc.c:402-463 */
     start_mel = 2595.0 * log10(1.0 + (float)st_freq / 700.0);
     half_mel = 2595.0 * log10(1.0 + (smpl / 2) / 700.0);
@@ -639,18 +863,23 @@ void so_cc_tables(float *hamming100, float *dct12x23, int *start23, int *len23, 
     memcpy(tri23x129, g_cc.tri, sizeof g_cc.tri);
 }
 
-/* WI8CompCeps, etsi/cpp/CompCeps.c:368-549 (8 kHz branch).  frame201[0] is sample -1. */
-void so_comp_ceps(const float *frame201, float *coef14)
+/* WI8CompCeps, etsi/cpp/CompCeps.c:368-549.  frame201[0] is sample -1.  hp == NULL: the 8 kHz branch (23 bands);
+ * otherwise the 16 kHz branch: 3 decoded + spectrally-subtracted HP bands are appended (26 bands, DCT over 26) and
+ * their energy is added to logE. */
+static void cc_core(const float *frame201, float *coef14, const so_hp16k *hp)
 {
     const float *cur = frame201 + 1;
-    float fb[256 + 16], sum[23], log_e;
+    float fb[256 + 16], sum[23], log_e, coded[3];
     const float floor_fb = (float)exp((double)-10.0), floor_loge = (float)exp((double)-50.0);
+    const int nb = hp ? 26 : 23;
     int i, j;
     cc_init();
     log_e = 0.0;
     for (i = 0; i < 200; i++) log_e += cur[i] * cur[i];
-    if (log_e < floor_loge) log_e = -50.0;
-    else log_e = (float)log((double)log_e);
+    if (!hp) {
+        if (log_e < floor_loge) log_e = -50.0;
+        else log_e = (float)log((double)log_e);
+    }
     for (i = 0; i < 200; i++) fb[i] = cur[i] - 0.90 * cur[i - 1];
     for (i = 0; i < 100; i++) fb[i] *= g_cc.hamming[i];
     for (i = 100; i < 200; i++) fb[i] *= g_cc.hamming[200 - 1 - i];
@@ -660,24 +889,66 @@ void so_comp_ceps(const float *frame201, float *coef14)
     for (i = 1; i < 128; i++)
         fb[i] = (float)((double)fb[i] * (double)fb[i] + (double)fb[256 - i] * (double)fb[256 - i]);
     fb[128] = (double)fb[128] * fb[128];
+    if (hp) {
+        /* GetBandsForDecoding16k + DecodeBands16k (16kHzProcessing.c:318-366) with the fixed weights of
+         * CompCeps.c:475-477 and the OLDEST of the three buffered codes */
+        float aux[3] = {0.0, 0.0, 0.0}, w[3];
+        for (i = 66; i < 77; i++) aux[0] += fb[i];
+        for (i = 78; i < 97; i++) aux[1] += fb[i];
+        for (i = 98; i < 129; i++) aux[2] += fb[i];
+        for (i = 0; i < 3; i++) {
+            aux[i] /= 2.0;
+            if (aux[i] > floor_fb) aux[i] = (float)log((double)aux[i]);
+            else aux[i] = -10.0;
+        }
+        w[0] = 0.1; w[1] = 0.2; w[2] = 0.7;
+        for (i = 0; i < 3; i++) {
+            coded[i] = 0.0;
+            for (j = 0; j < 3; j++) coded[i] += (w[j] * (aux[j] - hp->code_buf[3 * i + j]));
+        }
+    }
     for (j = 0; j < 23; j++) {      /* DoMelFB, MelProc.c:82-104 */
         sum[j] = 0.0;
         for (i = 0; i < g_cc.len[j]; i++) sum[j] += fb[g_cc.start[j] + i] * g_cc.tri[j][i];
     }
     for (j = 22; j >= 0; j--) fb[j] = sum[j];
-    for (i = 0; i < 23; i++) {
+    if (hp) {                       /* CompCeps.c:488-505: rough pre-emphasis correction of both HP estimates */
+        const float corr = log(1.0 + 0.90);
+        for (i = 0; i < 3; i++) fb[23 + i] = (1.0 + 0.90) * hp->hp_bands[i];
+        for (i = 0; i < 3; i++) coded[i] += corr;
+    }
+    for (i = 0; i < nb; i++) {
         if (fb[i] < floor_fb) fb[i] = -10.0;
         else fb[i] = (float)log((double)fb[i]);
     }
-    for (i = 1; i < 13; i++) {      /* DCT, CompCeps.c:203-227 */
-        fb[23 + (i - 1)] = 0.0;
-        for (j = 0; j < 23; j++) fb[23 + (i - 1)] += fb[j] * g_cc.dct[(i - 1) * 23 + j];
+    if (hp) {
+        /* MergeSSandCoded (16kHzProcessing.c:106-125): 70 % coded + 30 % subtracted, then bands 22|23 pulled together */
+        const float perc = 0.7;
+        float avg, e_hp = 0.0;
+        const float preem = 0.90;                 /* CorrectEnergy takes the coefficient as a float argument */
+        const float corr = log(1.0 + preem);
+        for (i = 0; i < 3; i++) fb[23 + i] = perc * coded[i] + (1.0 - perc) * fb[23 + i];
+        avg = 0.5 * fb[22] + 0.5 * fb[23];
+        fb[22] = 0.6 * fb[22] + 0.4 * avg;
+        fb[23] = 0.6 * fb[23] + 0.4 * avg;
+        /* CorrectEnergy (:145-158) */
+        for (i = 0; i < 3; i++) e_hp += exp(fb[23 + i] - corr);
+        log_e += e_hp;
+        if (log_e < floor_loge) log_e = -50.0;
+        else log_e = (float)log((double)log_e);
     }
-    fb[23 + 12] = 0.0;
-    for (i = 0; i < 23; i++) fb[23 + 12] += fb[i];
-    fb[23 + 13] = log_e;            /* Noc0 == FALSE: logE appended after c0 (:539) */
-    for (i = 0; i < 14; i++) coef14[i] = fb[23 + i];
+    for (i = 1; i < 13; i++) {      /* DCT, CompCeps.c:203-227 */
+        const float *mx = hp ? g_cc.dct26 : g_cc.dct;
+        fb[nb + (i - 1)] = 0.0;
+        for (j = 0; j < nb; j++) fb[nb + (i - 1)] += fb[j] * mx[(i - 1) * nb + j];
+    }
+    fb[nb + 12] = 0.0;
+    for (i = 0; i < nb; i++) fb[nb + 12] += fb[i];
+    fb[nb + 13] = log_e;            /* Noc0 == FALSE: logE appended after c0 (:539) */
+    for (i = 0; i < 14; i++) coef14[i] = fb[nb + i];
 }
+
+void so_comp_ceps(const float *frame201, float *coef14) { cc_core(frame201, coef14, NULL); }
 
 /* etsi_denoise (etsi/cpp/AdvFrontEnd.c:125-210) driving DoAdvProcess (etsi/cpp/ParmInterface.c:208-330),
  * with the commented CompCeps step (:274-293) when ceps != NULL. */
@@ -912,6 +1183,77 @@ long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16)
     }
     so_ns_destroy(s);
     return rows;
+}
+
+/* The same chain at SamplingFrequency 16000 (AdvProcessAlloc, ParmInterface.c:99-109): 160 samples per call, QMF
+ * split, NoiseSup on the low band, HP-band coding inside NoiseSup, decoding/merging inside CompCeps.  Driven like
+ * oracle/ref_etsi.c:ref_etsi_features_16k.  feat: [n/160][15]; den_i16: [n/160][80] (low band); returns rows. */
+long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i16)
+{
+    so_ns *s = so_ns_create(SO_PROFILE_P8);
+    so_vad vad;
+    float den_buf[241], cur[160], lp[80], fb[16], lms[12], frame[201];
+    int16_t out_buf[80];
+    long start = 0, rows = 0, call = 0;
+    int onset = 0, offset = -200, i;
+    so_ns_attach_hp16k(s);
+    memset(den_buf, 0, sizeof den_buf);
+    memset(out_buf, 0, sizeof out_buf);
+    memset(fb, 0, sizeof fb);
+    memset(lms, 0, sizeof lms);
+    so_vad_init(&vad);
+    while (start + 160 <= n) {
+        float check = 0.0, *pt = den_buf + 241 - 80;
+        so_ns_info info;
+        int out = 0;
+        memmove(den_buf, den_buf + 80, sizeof(float) * (241 - 80));
+        for (i = 0; i < 160; i++) {
+            cur[i] = (float)in[start + i];
+            check += in[start + i] * in[start + i];
+        }
+        memset(&info, 0, sizeof info);
+        if (((int)check != 0) || onset) {
+            onset = 1;
+            hp16k_split(s->hp16k, cur, lp);
+            if (so_ns_block(s, lp, pt, &info)) {
+                for (i = 0; i < 80; i++) out_buf[i] = (int16_t)pt[i];
+                if (offset < 0) offset += 80;
+                if (offset >= 0) {
+                    memcpy(frame, den_buf + 241 - (200 + offset + 1), sizeof frame);
+                    so_wave_proc(frame + 1);
+                    cc_core(frame, fb, s->hp16k);
+                    so_post_proc(fb, lms);
+                    out = so_vad_proc(&vad, fb, info.sp_spec || info.sp_mel || info.sp_var || info.sp_vadns,
+                                      info.nb_frame0);
+                }
+            }
+        } else {
+            for (i = 0; i < 14; i++) fb[i] = 0.0f;
+            out = 1;
+        }
+        if (out) { memcpy(feat + rows * 15, fb, sizeof(float) * 15); rows++; }
+        if (den_i16) memcpy(den_i16 + call * 80, out_buf, sizeof out_buf);
+        start += 160;
+        call++;
+    }
+    so_ns_destroy(s);
+    return rows;
+}
+
+/* Do16kProcessing as a stream: in[n] -> lp[n/2], hp[n/2] (n rounded down to a multiple of 160). */
+void so_qmf_split(const int16_t *in, long n, float *lp, float *hp)
+{
+    so_hp16k *h = (so_hp16k *)malloc(sizeof *h);
+    long start;
+    int i;
+    hp16k_init(h);
+    for (start = 0; start + 160 <= n; start += 160) {
+        float x[160];
+        for (i = 0; i < 160; i++) x[i] = (float)in[start + i];
+        hp16k_split(h, x, lp + start / 2);
+        memcpy(hp + start / 2, h->data_hp, sizeof h->data_hp);
+    }
+    free(h);
 }
 
 /* etsi_denoise_mapping_func_Wiener, aurora_etsi/NoiseSup.cpp:1140-1407 */

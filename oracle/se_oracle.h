@@ -64,6 +64,12 @@ void so_vad_init(so_vad *v);
 int so_vad_proc(so_vad *v, float *fb15, int speech_found, int frame_counter);   /* VAD.c:214-330    */
 /* NoiseSup -> WaveProc -> CompCeps -> PostProc -> VAD; feat[row][15] = c1..c12,c0,logE,VAD flag. */
 long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16);
+/* 16 kHz mode (etsi/cpp/16kHzProcessing.c + its hooks in NoiseSup.c / CompCeps.c) */
+int so_ns_attach_hp16k(so_ns *s);
+void so_qmf_taps(float *dp118, float *hp118);
+void so_hp16k_tables(const so_ns *s, int *start5, int *len5, float *fb5x65);
+void so_qmf_split(const int16_t *in, long n, float *lp, float *hp);
+long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i16);
 
 /* ---------- P16 plugin entry point ---------- */
 /* etsi_denoise_mapping_func_Wiener (aurora_etsi/NoiseSup.cpp:1140-1407) on an existing stream.
