@@ -114,6 +114,30 @@ int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *o
                            float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised,
                            int mem);
 
+/* ETSI 16 kHz mode: AdvProcessAlloc(16000) (etsi/cpp/ParmInterface.c:99-109) + DoAdvProcess with
+ * the feature block re-enabled.  Each call consumes 160 samples: Do16kProcessing (etsi/cpp/16kHzProcessing.c:711-787)
+ * splits them into a 0-4 kHz half (-> NoiseSup -> WaveProc -> CompCeps) and a 4-8 kHz half whose three mel-band
+ * energies are spectrally subtracted and coded against the low band inside DoNoiseSup (NoiseSup.c:1216-1235,
+ * 1307-1327, 1402-1435; DoSpecSub16k 16kHzProcessing.c:388-480) and decoded/merged inside WI8CompCeps
+ * (CompCeps.c:464-531): 26 log bands -> c1..c12, c0, logE (+ HP energy) -> PostProc -> VAD.
+ * samples  : int16 16 kHz, ragged batch as above; the tail len % 160 is ignored.
+ * features : float[feat_offsets[u] + row][15], rows as se_etsi_features_batch with calls = len/160.   [required]
+ * feat_offsets : capacity per utterance >= se_etsi16k_num_feature_rows(len).
+ * denoised_lp / den_offsets : optional int16 denoised LOW-BAND stream at 8 kHz, 80 samples per call (what
+ *            etsi_denoise_16k's DenoiseBuffer holds, AdvFrontEnd.c:264), indexed by its own host int64[n_utts+1]
+ *            offsets with capacity >= 80 * (len/160); unused capacity is zeroed.
+ * The reference's driver etsi_denoise_16k (AdvFrontEnd.c:228-313) copies 160 samples per call out of that
+ * 80-sample buffer, a heap over-read; this call returns what is defined. */
+int64_t se_etsi16k_num_feature_rows(int64_t n_samples); /* n/160: upper bound                   */
+int se_etsi16k_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                              float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised_lp,
+                              const int64_t *den_offsets, int mem);
+
+/* Module-level entry: Do16kProcessing (etsi/cpp/16kHzProcessing.c:711-787) as a stream over `count` independent
+ * signals of n int16 samples each (n a multiple of 160): lp / hp = float[count][n/2], the 0-4 kHz half and the
+ * 4-8 kHz half flipped to base band (118-tap QMF pair, decimated by 2, delay line starting from rest). */
+int se_qmf_split_batch(se_ctx *ctx, const int16_t *samples, int64_t n, int count, float *lp, float *hp, int mem);
+
 /* Module-level entry: DoCompCeps (etsi/cpp/CompCeps.c:309-318,368-549) on n independent frames of 201 floats
  * (frame[0] = the sample before the frame, needed by the 0.9 pre-emphasis) -> 14 floats c1..c12,c0,logE each. */
 int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float *coef14, int mem);

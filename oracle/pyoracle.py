@@ -67,7 +67,7 @@ class Oracle:
     def __init__(self, fast=False):
         if fast:
             so = os.path.join(HERE, "libse_oracle_fast.so")
-            if not os.path.exists(so):
+            if not os.path.exists(so) or os.path.getmtime(so) < os.path.getmtime(os.path.join(HERE, "se_oracle.c")):
                 subprocess.check_call(["make", "-s", "-C", HERE, "libse_oracle_fast.so"])
         else:
             so = build_oracle()
@@ -102,6 +102,7 @@ class Oracle:
         L.so_qmf_taps.argtypes = [_vp, _vp]
         L.so_ns_attach_hp16k.argtypes = [_vp]
         L.so_hp16k_tables.argtypes = [_vp, _vp, _vp, _vp]
+        L.so_cc_dct26.argtypes = [_vp]
 
     # ---- primitives
     def rfft(self, x, m, cxx=False):
@@ -169,7 +170,9 @@ class Oracle:
         st = np.zeros(5, np.int32); ln = np.zeros(5, np.int32); fb = np.zeros((5, 65), np.float32)
         self.L.so_hp16k_tables(h, _p(st), _p(ln), _p(fb))
         self.L.so_ns_destroy(h)
-        return dict(dp=dp, hp=hp, start=st, len=ln, fb=fb)
+        dct26 = np.zeros((12, 26), np.float32)
+        self.L.so_cc_dct26(_p(dct26))
+        return dict(dp=dp, hp=hp, start=st, len=ln, fb=fb, dct26=dct26)
 
     def cc_tables(self):
         ham = np.zeros(100, np.float32); dct = np.zeros((12, 23), np.float32)

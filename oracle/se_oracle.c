@@ -863,6 +863,12 @@ void so_cc_tables(float *hamming100, float *dct12x23, int *start23, int *len23, 
     memcpy(tri23x129, g_cc.tri, sizeof g_cc.tri);
 }
 
+void so_cc_dct26(float *dct12x26)
+{
+    cc_init();
+    memcpy(dct12x26, g_cc.dct26, sizeof g_cc.dct26);
+}
+
 /* WI8CompCeps, etsi/cpp/CompCeps.c:368-549.  frame201[0] is sample -1.  hp == NULL: the 8 kHz branch (23 bands);
  * otherwise the 16 kHz branch: 3 decoded + spectrally-subtracted HP bands are appended (26 bands, DCT over 26) and
  * their energy is added to logE. */

@@ -67,6 +67,7 @@ long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16);
 /* 16 kHz mode (etsi/cpp/16kHzProcessing.c + its hooks in NoiseSup.c / CompCeps.c) */
 int so_ns_attach_hp16k(so_ns *s);
 void so_qmf_taps(float *dp118, float *hp118);
+void so_cc_dct26(float *dct12x26);
 void so_hp16k_tables(const so_ns *s, int *start5, int *len5, float *fb5x65);
 void so_qmf_split(const int16_t *in, long n, float *lp, float *hp);
 long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i16);

@@ -51,7 +51,7 @@ def lib():
         L.se_ctx_reset_kernel_times.argtypes = [_vp]
         L.se_ctx_launch_count.restype = C.c_int64
         L.se_ctx_launch_count.argtypes = [_vp]
-        for f in ("se_etsi_num_ceps_frames", "se_etsi_num_feature_rows", "se_ibm_num_frames"):
+        for f in ("se_etsi_num_ceps_frames", "se_etsi_num_feature_rows", "se_etsi16k_num_feature_rows", "se_ibm_num_frames"):
             getattr(L, f).restype = C.c_int64
             getattr(L, f).argtypes = [C.c_int64]
         L.se_resynth_num_frames.restype = C.c_int64
@@ -61,6 +61,8 @@ def lib():
         L.se_haircell_batch.argtypes = [_vp, _vp, _vp, C.c_int64, C.c_int, C.c_int]
         L.se_comp_ceps_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int]
         L.se_etsi_features_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
+        L.se_etsi16k_features_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
+        L.se_qmf_split_batch.argtypes = [_vp, _vp, C.c_int64, C.c_int, _vp, _vp, C.c_int]
         L.se_p16_wiener_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
         L.se_ns_stream_create.argtypes = [_vp, C.c_int, C.POINTER(_vp)]
         L.se_ns_stream_destroy.argtypes = [_vp]
@@ -208,6 +210,12 @@ class Context:
                                              _ptr(feat_offsets), _ptr(n_rows), _ptr(denoised), mem),
                "se_etsi_features_batch")
 
+    def etsi16k_features_raw(self, samples, offsets, n_utts, features, feat_offsets, n_rows=None, denoised_lp=None,
+                             den_offsets=None, mem=SE_MEM_HOST):
+        _check(self.L.se_etsi16k_features_batch(self.h, _ptr(samples), _ptr(offsets), n_utts, _ptr(features),
+                                                _ptr(feat_offsets), _ptr(n_rows), _ptr(denoised_lp), _ptr(den_offsets),
+                                                mem), "se_etsi16k_features_batch")
+
     def p16_wiener_raw(self, samples, is_f32, offsets, n_utts, out_f32, flags, gains, n_rows, block_offsets,
                        mem=SE_MEM_HOST):
         _check(self.L.se_p16_wiener_batch(self.h, _ptr(samples), int(is_f32), _ptr(offsets), n_utts, _ptr(out_f32),
@@ -282,6 +290,32 @@ class Context:
         self.etsi_features_raw(samples, offsets, nu, feat, fo, rows, den)
         per_utt = [feat[fo[u]:fo[u] + rows[u]] for u in range(nu)]
         return (per_utt, den) if denoised else per_utt
+
+    def etsi16k_features(self, samples, offsets, denoised=False):
+        """ETSI 16 kHz mode: per-utterance [rows][15] arrays (+ per-utterance int16 low-band denoised streams)."""
+        samples = np.ascontiguousarray(samples, np.int16)
+        offsets = _i64(offsets)
+        nu = len(offsets) - 1
+        calls = np.diff(offsets) // 160
+        fo = np.zeros(nu + 1, np.int64)
+        fo[1:] = np.cumsum(calls)
+        do = fo * 80
+        feat = np.zeros((max(int(fo[-1]), 1), 15), np.float32)
+        rows = np.zeros(max(nu, 1), np.int32)
+        den = np.zeros(max(int(do[-1]), 1), np.int16) if denoised else None
+        self.etsi16k_features_raw(samples, offsets, nu, feat, fo, rows, den, do if denoised else None)
+        per_utt = [feat[fo[u]:fo[u] + rows[u]] for u in range(nu)]
+        return (per_utt, [den[do[u]:do[u + 1]] for u in range(nu)]) if denoised else per_utt
+
+    def qmf_split(self, x):
+        """Do16kProcessing over [count][n] int16 signals (n % 160 == 0): (lp, hp) float32 [count][n/2]."""
+        x = np.ascontiguousarray(x, np.int16)
+        x2 = x.reshape(-1, x.shape[-1])
+        lp = np.zeros((x2.shape[0], x2.shape[1] // 2), np.float32)
+        hp = np.zeros_like(lp)
+        _check(self.L.se_qmf_split_batch(self.h, _ptr(x2), x2.shape[1], x2.shape[0], _ptr(lp), _ptr(hp), SE_MEM_HOST),
+               "se_qmf_split_batch")
+        return lp, hp
 
     def p16_wiener(self, samples, offsets):
         samples = np.ascontiguousarray(samples)

@@ -101,6 +101,18 @@ static int upload_cc(se_ctx *ctx)
     for (int j = 0; j < 23; j++)
         for (int t = 0; t < 12; t++) dctT[j * 16 + t] = h.dct[t * 23 + j];
     if ((rc = upload(ctx, dctT.data(), dctT.size(), &d.dctT))) return rc;
+    // 16 kHz mode: bands 1..3 of the 5-band HP bank as dense rows (band 3 ends at bin 63), DCT over 26 bands
+    const Hp16Tables &hp = ctx->h_hp16;
+    std::vector<float> hpfb(3 * 64, 0.0f);
+    for (int b = 0; b < 3; b++) {
+        if (hp.fb_start[b + 1] + hp.fb_len[b + 1] > 64) { set_error("HP mel band %d leaves the 64-bin table", b + 1); return SE_EINVAL; }
+        for (int i = 0; i < hp.fb_len[b + 1]; i++) hpfb[b * 64 + hp.fb_start[b + 1] + i] = hp.fb[b + 1][i];
+    }
+    if ((rc = upload(ctx, hpfb.data(), hpfb.size(), &d.hpfb))) return rc;
+    std::vector<float> dct26T(26 * 16, 0.0f);
+    for (int j = 0; j < 26; j++)
+        for (int t = 0; t < 12; t++) dct26T[j * 16 + t] = hp.dct26[t * 26 + j];
+    if ((rc = upload(ctx, dct26T.data(), dct26T.size(), &d.dct26T))) return rc;
     return SE_OK;
 }
 
@@ -204,6 +216,7 @@ static int ctx_init_device(se_ctx *ctx)
     build_ns_tables_p16(ctx->h_p16);
     build_cc_tables(ctx->h_cc);
     build_gt_tables(ctx->h_gt);
+    build_hp16_tables(ctx->h_hp16);
     int rc;
     if ((rc = upload_ns(ctx, ctx->h_p8, ctx->d_p8, 16)) || (rc = upload_ns(ctx, ctx->h_p16, ctx->d_p16, 128)) ||
         (rc = upload_cc(ctx)) || (rc = upload_g64_tables(ctx)))
@@ -344,6 +357,7 @@ int se_shard_plan(const int64_t *offsets, int n_utts, int n_shards, int32_t *fir
 
 int64_t se_etsi_num_ceps_frames(int64_t n) { const int64_t c = n / 80 - 6; return c > 0 ? c : 0; }
 int64_t se_etsi_num_feature_rows(int64_t n) { return n > 0 ? n / 80 : 0; }
+int64_t se_etsi16k_num_feature_rows(int64_t n) { return n > 0 ? n / 160 : 0; }
 int64_t se_ibm_num_frames(int64_t n) { return n >= 320 ? (n - 320) / 160 + 1 : 0; }
 int64_t se_resynth_num_frames(int64_t n, int mode)
 {

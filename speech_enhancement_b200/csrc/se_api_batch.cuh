@@ -325,6 +325,43 @@ int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *o
                         offsetof(NsLaunch, n_ceps), mem);
 }
 
+int se_etsi16k_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                              float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised_lp,
+                              const int64_t *den_offsets, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_etsi16k_features_batch"));
+    if (n_utts < 0 || (n_utts > 0 && (!samples || !features || !feat_offsets)) || (denoised_lp && !den_offsets)) {
+        set_error("se_etsi16k_features_batch: bad arguments");
+        return SE_EINVAL;
+    }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_etsi16k_features_batch"));
+    SE_TRY(check_offsets(feat_offsets, n_utts, "se_etsi16k_features_batch(feat_offsets)"));
+    if (offsets[0] != 0) { set_error("se_etsi16k_features_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    if (denoised_lp) SE_TRY(check_offsets(den_offsets, n_utts, "se_etsi16k_features_batch(den_offsets)"));
+    for (int u = 0; u < n_utts; u++) {
+        const int64_t calls = se_etsi16k_num_feature_rows(offsets[u + 1] - offsets[u]);
+        if (feat_offsets[u + 1] - feat_offsets[u] < calls) {
+            set_error("se_etsi16k_features_batch: feat_offsets too small for utterance %d", u);
+            return SE_EINVAL;
+        }
+        if (denoised_lp && den_offsets[u + 1] - den_offsets[u] < calls * 80) {
+            set_error("se_etsi16k_features_batch: den_offsets too small for utterance %d", u);
+            return SE_EINVAL;
+        }
+    }
+    NsLaunch a;
+    std::memset(&a, 0, sizeof a);
+    a.zero_check = 1;
+    a.features = 2;
+    NsOut outs[] = {
+        {denoised_lp, sizeof(int16_t), kIdxAux2, false, false, kSlotOut, offsetof(NsLaunch, den_i16)},
+        {features, sizeof(float) * 15, kIdxAux1, true, false, kSlotOut2, offsetof(NsLaunch, ceps)},
+    };
+    return ns_batch_run(ctx, 8, a, samples, sizeof(int16_t), offsets, feat_offsets, denoised_lp ? den_offsets : nullptr,
+                        n_utts, outs, 2, n_rows, offsetof(NsLaunch, n_ceps), mem);
+}
+
 int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int64_t *offsets, int n_utts,
                         float *out_f32, int32_t *flags, float *gains, int32_t *n_rows,
                         const int64_t *block_offsets, int mem)

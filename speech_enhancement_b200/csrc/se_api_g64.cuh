@@ -172,6 +172,26 @@ int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float 
     return leave(ctx, mem);
 }
 
+int se_qmf_split_batch(se_ctx *ctx, const int16_t *samples, int64_t n, int count, float *lp, float *hp, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_qmf_split_batch"));
+    if (count < 0 || n < 0 || n % 160 != 0 || (count > 0 && n > 0 && (!samples || !lp || !hp))) {
+        set_error("se_qmf_split_batch: bad arguments (n must be a multiple of 160)");
+        return SE_EINVAL;
+    }
+    if (count == 0 || n == 0) return SE_OK;
+    const uint64_t total = (uint64_t)n * (uint64_t)count;
+    const void *d_in = nullptr;
+    void *d_lp = nullptr, *d_hp = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
+    SE_TRY(stage_out(ctx, kSlotOut, lp, sizeof(float) * (total / 2), mem, false, &d_lp));
+    SE_TRY(stage_out(ctx, kSlotOut2, hp, sizeof(float) * (total / 2), mem, false, &d_hp));
+    SE_TRY(launch_qmf_split(ctx, (const int16_t *)d_in, n, count, (float *)d_lp, (float *)d_hp));
+    SE_TRY(stage_out_copy(ctx, lp, d_lp, sizeof(float) * (total / 2), mem));
+    SE_TRY(stage_out_copy(ctx, hp, d_hp, sizeof(float) * (total / 2), mem));
+    return leave(ctx, mem);
+}
+
 int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
                        int count, int flags, int mem)
 {
@@ -242,6 +262,17 @@ int se_get_table(se_ctx *ctx, const char *name, float *out, int capacity, int *c
         else if (field == "start") v.assign(cc->start, cc->start + 23);
         else if (field == "len") v.assign(cc->len, cc->len + 23);
         else if (field == "tri") v.assign(&cc->tri[0][0], &cc->tri[0][0] + 23 * 129);
+        else { set_error("se_get_table: unknown table %s", name); return SE_EINVAL; }
+    } else if (key.rfind("hp16.", 0) == 0) {
+        Hp16Tables hpl;
+        const Hp16Tables *hp = &hpl;
+        if (ctx) hp = &ctx->h_hp16; else build_hp16_tables(hpl);
+        field = key.substr(5);
+        if (field == "dp") v.assign(hp->dp, hp->dp + 118);
+        else if (field == "fb") v.assign(&hp->fb[0][0], &hp->fb[0][0] + 5 * 65);
+        else if (field == "fb_start") v.assign(hp->fb_start, hp->fb_start + 5);
+        else if (field == "fb_len") v.assign(hp->fb_len, hp->fb_len + 5);
+        else if (field == "dct26") v.assign(hp->dct26, hp->dct26 + 12 * 26);
         else { set_error("se_get_table: unknown table %s", name); return SE_EINVAL; }
     } else if (key.rfind("gt.", 0) == 0) {
         const GtTables *gt = &gtl;

@@ -39,6 +39,9 @@ struct CcDevTables {
     const int *tri_start;      // [32]
     const int *tri_len;        // [32]
     const float *dctT;         // [23][16] : dctT[j*16+t] = dct[t][j], t<12
+    // 16 kHz mode (se_ns_hp16k.cuh)
+    const float *hpfb;         // [3][64]  : HP mel bands 1..3 as dense rows over PSD bins
+    const float *dct26T;       // [26][16]
 };
 
 // Per-stream NoiseSup state kept in global memory between launches (persistent streams) —
@@ -133,6 +136,7 @@ struct se_ctx {
     se::NsTables h_p8, h_p16;
     se::CcTables h_cc;
     se::GtTables h_gt;
+    se::Hp16Tables h_hp16;
     se::NsDevTables d_p8, d_p16;
     se::CcDevTables d_cc;
     std::vector<void *> table_allocs;
@@ -160,6 +164,7 @@ void prof_end(se_ctx *ctx, int k);
 int launch_ns_p8(se_ctx *ctx, const NsLaunch &a);
 int launch_ns_p16(se_ctx *ctx, const NsLaunch &a);
 int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count);
+int launch_qmf_split(se_ctx *ctx, const int16_t *x, int64_t n, int count, float *lp, float *hp);
 int launch_wave_proc(se_ctx *ctx, float *frames, int count);
 int launch_haircell(se_ctx *ctx, const float *in, float *out, int64_t n, int count);
 int launch_comp_ceps(se_ctx *ctx, const float *frames, float *coef, int count);

@@ -271,4 +271,5 @@ __device__ __forceinline__ float filter_calc_bin(const int fstage, float psd, fl
 
 #include "se_ns_stage.cuh"
 #include "se_ns_feat.cuh"
+#include "se_ns_hp16k.cuh"
 #include "se_ns_kernel.cuh"

@@ -8,7 +8,8 @@ namespace se {
 #ifndef SE_NS_WARPS
 #define SE_NS_WARPS 8
 #endif
-template <bool FEAT> struct NsWarps { static constexpr int value = FEAT ? 6 : SE_NS_WARPS; };
+// FEAT: 0 = NoiseSup (+ raw CompCeps), 1 = 8 kHz feature chain, 2 = 16 kHz feature chain (se_ns_hp16k.cuh)
+template <int FEAT> struct NsWarps { static constexpr int value = FEAT ? 6 : SE_NS_WARPS; };
 
 template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<PROF> &bm, const NsDevTables &tb,
                                                                      const CcDevTables &cc)
@@ -33,20 +34,31 @@ template <typename T> __device__ __forceinline__ float to_f32(T v) { return (flo
 
 // FEAT (P8 only): a.ceps receives 15-column feature rows (WaveProc -> CompCeps -> PostProc -> VAD,
 // se_ns_feat.cuh) instead of 14-column raw cepstra; a.n_ceps counts released rows.
-template <int PROF, typename IN_T, bool FEAT>
+template <int PROF, typename IN_T, int FEAT>
 __global__ void __launch_bounds__(NsWarps<FEAT>::value * 32, 2)
 ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 {
     using P = Prof<PROF>;
     static_assert(!FEAT || PROF == 8, "the feature chain exists for the 8 kHz profile only");
+    constexpr bool HP16 = FEAT == 2;
+    constexpr int SIN = HP16 ? 160 : P::S;      // input samples per call (16 kHz mode: two per low-band sample)
+    constexpr int NRI = HP16 ? 5 : P::NR;
     extern __shared__ __align__(16) unsigned char smem_raw[];
     BlockMem<PROF> &bm = *reinterpret_cast<BlockMem<PROF> *>(smem_raw);
     WarpMem<PROF> *wms = reinterpret_cast<WarpMem<PROF> *>(smem_raw + ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)));
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     WarpMem<PROF> &wm = wms[warp];
-    FeatMem &fm = reinterpret_cast<FeatMem *>(wms + NsWarps<FEAT>::value)[FEAT ? warp : 0];
+    FeatMem *fms = reinterpret_cast<FeatMem *>(wms + NsWarps<FEAT>::value);
+    FeatMem &fm = fms[FEAT ? warp : 0];
+    Hp16Mem *hms = reinterpret_cast<Hp16Mem *>(fms + (FEAT ? NsWarps<FEAT>::value : 0));
+    Hp16Mem &hm = hms[HP16 ? warp : 0];
+    Hp16Block &hb = *reinterpret_cast<Hp16Block *>(hms + (HP16 ? NsWarps<FEAT>::value : 0));
 
     load_block_tables<PROF>(bm, tb, cc);
+    if constexpr (HP16) {
+        for (int i = threadIdx.x; i < 3 * 64; i += blockDim.x) hb.hpfb[i] = cc.hpfb[i];
+        for (int i = threadIdx.x; i < 26 * 16; i += blockDim.x) hb.dct26T[i] = cc.dct26T[i];
+    }
     __syncthreads();
 
     FftTw tw;
@@ -70,7 +82,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 
         const int64_t off0 = a.offsets[u] - a.sample_base;
         const int64_t n = a.offsets[u + 1] - a.offsets[u];
-        const int nblk = (int)(n / P::S);
+        const int nblk = (int)(n / SIN);
         const IN_T *in = all + off0;
 
         // ---- stream state -------------------------------------------------------------------
@@ -124,6 +136,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         }
         FeatState fs;
         if constexpr (FEAT) feat_state_init(fs, fm, lane);
+        Hp16State hs;
+        if constexpr (HP16) hp16_state_init(hs, hm, lane);
         __syncwarp();
         // cepstral rows are numbered per launch: a resumed stream continues at row 0 of this push
         const int ceps_row0 = (st && a.load_state && s.nb_out2 > 2) ? s.nb_out2 - 2 : 0;
@@ -138,24 +152,24 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         // consumed (converting right after the load makes the warp wait for the load at once): -3 % on P8.
         // P16 measured 1 % slower that way, so it converts at the load.
         using NX_T = typename std::conditional<PROF == 8, IN_T, float>::type;
-        NX_T nx[P::NR];
+        NX_T nx[NRI];
 #pragma unroll
-        for (int r = 0; r < P::NR; r++) {
+        for (int r = 0; r < NRI; r++) {
             const int i = lane + 32 * r;
-            nx[r] = (nblk > 0 && i < P::S) ? NX_T(in[i]) : NX_T(0);
+            nx[r] = (nblk > 0 && i < SIN) ? NX_T(in[i]) : NX_T(0);
         }
 
         for (int b = 0; b < nblk; b++) {
-            float cur[P::NR];
+            float cur[NRI];
             float ss = 0.0f;
             bool nzl = false;
 #pragma unroll
-            for (int r = 0; r < P::NR; r++) { cur[r] = to_f32(nx[r]); ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
+            for (int r = 0; r < NRI; r++) { cur[r] = to_f32(nx[r]); ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
             if (b + 1 < nblk) {
 #pragma unroll
-                for (int r = 0; r < P::NR; r++) {
+                for (int r = 0; r < NRI; r++) {
                     const int i = lane + 32 * r;
-                    if (i < P::S) nx[r] = NX_T(in[(int64_t)(b + 1) * P::S + i]);
+                    if (i < SIN) nx[r] = NX_T(in[(int64_t)(b + 1) * SIN + i]);
                 }
             }
             // zero-frame gate: DoAdvProcess (ParmInterface.c:244-250, leading frames only) /
@@ -169,16 +183,27 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 else process = nonzero;
             }
 
-            const int64_t obase = off0 + (int64_t)b * P::S;
+            const int64_t obase = (HP16 ? tr0 : off0) + (int64_t)b * P::S;   // 16 kHz mode: low-band output, 80 per call
             float o[P::CH];
+            float hp_code = 0.0f, hp_fbss = 0.0f;
             bool produced = false, ran0 = false;
             StageFlags fl = {0, 0, 0};
             if (process) {
                 const int slot = s.nb_in1 & 3;
+                int hslot = 0;
+                if constexpr (HP16) {
+                    // Do16kProcessing (ParmInterface.c:259-260): the low band feeds NoiseSup, the high band its ring
+                    hslot = s.nb_in1 % 6;
 #pragma unroll
-                for (int r = 0; r < P::NR; r++) {
-                    const int i = lane + 32 * r;
-                    if (i < P::S) ring_store<PROF>(ring1, slot, i, cur[r]);
+                    for (int r = 0; r < NRI; r++) hm.line[117 + lane + 32 * r] = cur[r];
+                    __syncwarp();
+                    qmf_split_warp(hm, ring1, slot, hslot, lane);
+                } else {
+#pragma unroll
+                    for (int r = 0; r < P::NR; r++) {
+                        const int i = lane + 32 * r;
+                        if (i < P::S) ring_store<PROF>(ring1, slot, i, cur[r]);
+                    }
                 }
                 s.nb_in1++;
                 __syncwarp();
@@ -196,7 +221,17 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         den[r] = fstage ? den2[r] : den1[r];
                     }
                     float *grow = (PROF == 16 && fstage == 1 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
-                    ns_stage<PROF>(wm, bm, tw, ic, br, lane, s, noise, den, eps, fstage, o, fl, grow, trace);
+                    float psd_hi[2];
+                    if constexpr (HP16) {
+                        // stage-1 hook first (NoiseSup.c:1307-1327 runs it after ApplyWF; nothing it reads changes in
+                        // between, and fewer registers are live here).  nbFrame[1] is incremented by this stage's VAD.
+                        if (fstage == 1) hp16_stage1(wm, bm, hb, hm, tw, lane, hs, hslot, s.nb_frame1 + 1, hp_code, hp_fbss);
+                    }
+                    ns_stage<PROF>(wm, bm, tw, ic, br, lane, s, noise, den, eps, fstage, o, fl, grow, trace,
+                                   (HP16 && fstage == 0) ? psd_hi : nullptr);
+                    if constexpr (HP16) {
+                        if (fstage == 0) hp16_lowband_log(hs, psd_hi[0], psd_hi[1], lane);
+                    }
 #pragma unroll
                     for (int r = 0; r < P::NB; r++) {
                         if (fstage) { noise2[r] = noise[r]; den2[r] = den[r]; }
@@ -208,6 +243,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         s.n_rows++;
                         produced = true;
                         dc_offset<PROF>(o, s, lane);
+                        if constexpr (HP16) hp16_push(hs, hp_code, hp_fbss, lane);
                     }
                 }
             }
@@ -251,7 +287,11 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         for (int i = lane; i < 201; i += 32) fm.frame[i] = wm.ring3[wrap<P::RB>(base + i - 1)];
                         __syncwarp();
                         wave_proc_warp(fm, lane);
-                        c = comp_ceps_core(wm, bm, tw, br, lane, [&](int i) { return fm.frame[1 + i]; });
+                        if constexpr (HP16)
+                            c = comp_ceps_core<true>(wm, bm, tw, br, lane, [&](int i) { return fm.frame[1 + i]; }, hb.dct26T,
+                                                     hs.codeb, hs.hpb);
+                        else
+                            c = comp_ceps_core(wm, bm, tw, br, lane, [&](int i) { return fm.frame[1 + i]; });
                         c = post_proc_warp(c, fs, lane);
                         const bool speech = fl.spec || fl.mel || fl.var || (s.nb_speech > 4);
                         emit = vad_proc_warp(c, fs, fm, lane, speech, s.nb_frame0);
@@ -300,9 +340,11 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 
         // tail (len % S): the reference leaves it untouched; the batch API defines it as 0
         if (PROF == 8) {
-            for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) {
-                if (a.den_i16) a.den_i16[off0 + i] = 0;
-                if (a.den_f32) a.den_f32[off0 + i] = 0.0f;
+            const int64_t den_n = HP16 ? (a.trace_offsets ? a.trace_offsets[u + 1] - a.trace_offsets[u] : 0) : n;
+            const int64_t den0 = HP16 ? tr0 : off0;
+            for (int64_t i = (int64_t)nblk * P::S + lane; i < den_n; i += 32) {
+                if (a.den_i16) a.den_i16[den0 + i] = 0;
+                if (a.den_f32) a.den_f32[den0 + i] = 0.0f;
             }
         } else if (a.out_f32) {
             for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
@@ -400,6 +442,31 @@ __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
     }
 }
 
+// module-level kernel: Do16kProcessing over whole signals (one warp per signal, 160 samples per step)
+__global__ void qmf_split_kernel(const int16_t *x, int64_t n, int count, float *lp, float *hp)
+{
+    __shared__ Hp16Mem hms[4];
+    __shared__ float rings[4][Prof<8>::RB + 16];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 4 + warp;
+    if (idx >= count) return;
+    Hp16Mem &hm = hms[warp];
+    float *ring = rings[warp] + 8;
+    for (int i = lane; i < 280; i += 32) hm.line[i] = 0.0f;
+    __syncwarp();
+    const int16_t *in = x + (int64_t)idx * n;
+    for (int64_t b = 0; b < n / 160; b++) {
+        for (int i = lane; i < 160; i += 32) hm.line[117 + i] = (float)in[b * 160 + i];
+        __syncwarp();
+        qmf_split_warp(hm, ring, 1, 0, lane);
+        for (int i = lane; i < 80; i += 32) {
+            lp[(int64_t)idx * (n / 2) + b * 80 + i] = ring[80 + i];
+            hp[(int64_t)idx * (n / 2) + b * 80 + i] = hm.hpring[i];
+        }
+        __syncwarp();
+    }
+}
+
 // test kernel: DoWaveProc on independent frames (one warp per frame)
 __global__ void wave_proc_kernel(float *frames, int count)
 {
@@ -444,13 +511,14 @@ __global__ void __launch_bounds__(128) comp_ceps_kernel(const float *frames, flo
 // ------------------------------------------------------------------------------------------------
 // host launchers
 // ------------------------------------------------------------------------------------------------
-template <int PROF, bool FEAT> static size_t ns_smem_bytes()
+template <int PROF, int FEAT> static size_t ns_smem_bytes()
 {
     return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + NsWarps<FEAT>::value * sizeof(WarpMem<PROF>) +
-           (FEAT ? NsWarps<FEAT>::value * sizeof(FeatMem) : 0);
+           (FEAT ? NsWarps<FEAT>::value * sizeof(FeatMem) : 0) +
+           (FEAT == 2 ? NsWarps<FEAT>::value * sizeof(Hp16Mem) + sizeof(Hp16Block) : 0);
 }
 
-template <int PROF, typename IN_T, bool FEAT = false>
+template <int PROF, typename IN_T, int FEAT = 0>
 static int launch_ns(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid)
 {
     if (a.n_utts <= 0) return SE_OK;
@@ -476,7 +544,8 @@ int launch_ns_p8(se_ctx *ctx, const NsLaunch &a)
 {
     if (a.features) {
         if (a.is_f32 || a.state) { set_error("feature chain: int16 batch input only"); return SE_EUNSUPPORTED; }
-        return launch_ns<8, int16_t, true>(ctx, a, ctx->d_p8, SE_K_NS_P8);
+        if (a.features == 2) return launch_ns<8, int16_t, 2>(ctx, a, ctx->d_p8, SE_K_NS_P8);
+        return launch_ns<8, int16_t, 1>(ctx, a, ctx->d_p8, SE_K_NS_P8);
     }
     return a.is_f32 ? launch_ns<8, float>(ctx, a, ctx->d_p8, SE_K_NS_P8)
                     : launch_ns<8, int16_t>(ctx, a, ctx->d_p8, SE_K_NS_P8);
@@ -486,6 +555,15 @@ int launch_ns_p16(se_ctx *ctx, const NsLaunch &a)
 {
     return a.is_f32 ? launch_ns<16, float>(ctx, a, ctx->d_p16, SE_K_NS_P16)
                     : launch_ns<16, int16_t>(ctx, a, ctx->d_p16, SE_K_NS_P16);
+}
+
+int launch_qmf_split(se_ctx *ctx, const int16_t *x, int64_t n, int count, float *lp, float *hp)
+{
+    if (count <= 0 || n <= 0) return SE_OK;
+    qmf_split_kernel<<<(count + 3) / 4, 128, 0, ctx->cur->stream>>>(x, n, count, lp, hp);
+    ctx->launches++;
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
 }
 
 int launch_wave_proc(se_ctx *ctx, float *frames, int count)

@@ -16,7 +16,7 @@ template <int RB> __device__ __forceinline__ int wrap(int pos)
 }
 
 // Windowed frame -> PSD bins owned by this lane (psd[r] for bin lane+32r).
-template <int PROF>
+template <int PROF, int RB = Prof<PROF>::RB>
 __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, int lane,
                                           const float *ring, int wpos, float (&psd)[Prof<PROF>::NB])
 {
@@ -28,7 +28,7 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
             const int i2 = 2 * (lane + 32 * j);
             v[j] = make_float2(0.0f, 0.0f);
             if (i2 < P::FL) {
-                const int pos = wrap<P::RB>(wpos + i2);
+                const int pos = wrap<RB>(wpos + i2);
                 const float2 x = *reinterpret_cast<const float2 *>(ring + pos);
                 const float2 w = *reinterpret_cast<const float2 *>(bm.win + i2);
                 v[j] = make_float2(x.x * w.x, x.y * w.y);
@@ -63,7 +63,7 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
             va[j] = make_float2(0.0f, 0.0f);
             vw[j] = make_float2(0.0f, 0.0f);
             if (i4 < P::FL) {
-                const int pos = wrap<P::RB>(wpos + i4);
+                const int pos = wrap<RB>(wpos + i4);
                 const float4 x = *reinterpret_cast<const float4 *>(ring + pos);
                 const float4 w = *reinterpret_cast<const float4 *>(bm.win + i4);
                 va[j] = make_float2(x.x * w.x, x.z * w.z);
@@ -177,7 +177,7 @@ template <int PROF>
 __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, const IdctRegs &ic,
                                          const BankRegs &br, int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
                                          float eps, const int fstage, float (&o)[Prof<PROF>::CH], StageFlags &fl,
-                                         float *gains_row, float *spec_trace)
+                                         float *gains_row, float *spec_trace, float *psd_keep = nullptr)
 {
     using P = Prof<PROF>;
     float *ring = fstage == 0 ? wm.ring1 + 8 : wm.ring2 + 8;
@@ -187,6 +187,7 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
 
     float psd[P::NB];
     frame_psd<PROF>(wm, bm, tw, lane, ring, slot_old * P::S + P::ANA, psd);
+    if (psd_keep) { psd_keep[0] = psd[1]; psd_keep[1] = psd[2]; }      // 16 kHz mode: bins 32..64 of this frame
 
     // VAD (stage 0 only looks at the signal)
     float frame_sq = 0.0f;
@@ -369,9 +370,15 @@ template <int PROF> __device__ __forceinline__ void dc_offset(float (&o)[Prof<PR
 // position of frame sample 0); ring3 holds the float denoised stream.
 // `ld(i)` returns frame sample i, -1 <= i < 200.  Returns this lane's coefficient (lanes 0..11 = c1..c12,
 // lane 12 = c0, lane 13 = logE, 0 elsewhere).
-template <class LD>
-__device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, LD ld)
+// HP16 (16 kHz mode, CompCeps.c:464-479, 488-505, 518-531): three more log bands (70 % decoded from the low band's
+// spectrum shape + 30 % spectrally-subtracted HP energies, both delayed 3 frames) after the 23 mel bands, DCT over
+// 26 bands, HP energy added to logE.  dct_t: [bands][16] transposed DCT; code9 / hp3: lane-distributed oldest
+// entries of the code and HP-band delay lines (lanes 0..8 / 0..2).
+template <bool HP16 = false, class LD>
+__device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, LD ld,
+                                                const float *dct26T = nullptr, float code9 = 0.0f, float hp3 = 0.0f)
 {
+    constexpr int NBAND = HP16 ? 26 : 23;
     float e = 0.0f;
     float2 v[4];
 #pragma unroll
@@ -392,15 +399,23 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
     fft128_store(v, wm.Z, lane);
     __syncwarp();
     // power spectrum (:451-459), 129 bins, into wm.W
+    float d0 = 0.0f, d1 = 0.0f, d2 = 0.0f;     // HP16: GetBandsForDecoding16k, bins 66..76 | 78..96 | 98..128
 #pragma unroll
     for (int r = 0; r < 4; r++) {
         const int k = lane + 32 * r;
         const float2 xk = rsplit256(wm.Z, k, bm.twh[k]);
-        wm.W[k] = (k == 0) ? xk.x * xk.x : (xk.x * xk.x + xk.y * xk.y);
+        const float pw = (k == 0) ? xk.x * xk.x : (xk.x * xk.x + xk.y * xk.y);
+        wm.W[k] = pw;
+        if constexpr (HP16) {
+            if (k >= 66 && k < 77) d0 += pw;
+            if (k >= 78 && k < 97) d1 += pw;
+            if (k >= 98) d2 += pw;
+        }
     }
     if (lane == 0) {
         const float2 xk = rsplit256(wm.Z, 128, bm.twh[128]);
         wm.W[128] = xk.x * xk.x;
+        if constexpr (HP16) d2 += xk.x * xk.x;
     }
     __syncwarp();
     // 23 mel triangles (DoMelFB, MelProc.c:82-104), ln with floor (:509-513)
@@ -412,15 +427,45 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
         if (lane >= 14 && lane < 23) fb += hi;
     }
     const float floor_fb = 4.5399929762484854e-05f;   // (float)exp(-10.0)
-    fb = (fb < floor_fb) ? -10.0f : logf(fb);
-    if (lane >= 23) fb = 0.0f;
+    if constexpr (HP16) {
+        constexpr unsigned FULL = 0xffffffffu;
+        d0 = warp_sum(d0) * 0.5f;
+        d1 = warp_sum(d1) * 0.5f;
+        d2 = warp_sum(d2) * 0.5f;
+        d0 = (d0 > floor_fb) ? logf(d0) : -10.0f;
+        d1 = (d1 > floor_fb) ? logf(d1) : -10.0f;
+        d2 = (d2 > floor_fb) ? logf(d2) : -10.0f;
+        // lanes 23..25 = HP band i: decoded estimate (weights 0.1 / 0.2 / 0.7) and the subtracted energy x 1.9
+        const int i3 = 3 * (lane - 23);
+        const float c0_ = __shfl_sync(FULL, code9, i3 & 31), c1_ = __shfl_sync(FULL, code9, (i3 + 1) & 31),
+                    c2_ = __shfl_sync(FULL, code9, (i3 + 2) & 31);
+        const float hp_e = __shfl_sync(FULL, hp3, (lane - 23) & 31);
+        const float corr = 0.6418538689613342f;           // (float)log(1.0 + 0.90) == (float)log(1.0 + (double)0.9f)
+        float coded = __fmul_rn(0.1f, d0 - c0_);
+        coded = __fadd_rn(coded, __fmul_rn(0.2f, d1 - c1_));
+        coded = __fadd_rn(coded, __fmul_rn(0.7f, d2 - c2_));
+        coded += corr;
+        if (lane >= 23 && lane < 26) fb = 1.9f * hp_e;
+        fb = (fb < floor_fb) ? -10.0f : logf(fb);
+        if (lane >= 23 && lane < 26) fb = 0.7f * coded + 0.3f * fb;     // MergeSSandCoded
+        if (lane >= 26) fb = 0.0f;
+        const float b22 = __shfl_sync(FULL, fb, 22), b23 = __shfl_sync(FULL, fb, 23);
+        const float avg = 0.5f * b22 + 0.5f * b23;
+        if (lane == 22 || lane == 23) fb = 0.6f * fb + 0.4f * avg;
+        const float ex = expf(fb - corr);                 // CorrectEnergy
+        e += __fadd_rn(__fadd_rn(__shfl_sync(FULL, ex, 23), __shfl_sync(FULL, ex, 24)), __shfl_sync(FULL, ex, 25));
+    } else {
+        fb = (fb < floor_fb) ? -10.0f : logf(fb);
+        if (lane >= 23) fb = 0.0f;
+    }
     const float c0 = warp_sum(fb);
     wm.melw[lane] = fb;
     __syncwarp();
     float out = 0.0f;
     if (lane < 12) {
+        const float *dt = HP16 ? dct26T : bm.dctT;
 #pragma unroll
-        for (int j = 0; j < 23; j++) out += wm.melw[j] * bm.dctT[j * 16 + lane];
+        for (int j = 0; j < NBAND; j++) out += wm.melw[j] * dt[j * 16 + lane];
     } else if (lane == 12) {
         out = c0;
     } else if (lane == 13) {

@@ -174,6 +174,55 @@ void build_cc_tables(CcTables &t)
     }
 }
 
+// First half of the 118-tap QMF prototype, integers over 2^23 (DP_HP_filters, etsi/cpp/16kHzProcessing.c:559-608);
+// the prototype is symmetric.
+static const int kQmfHalf[59] = {
+    1584, 805, -4192, -8985, -5987, 2583, 4657, -3035, -7004, 1542, 8969, 567, -10924, -3757, 12320, 7951, -12793,
+    -13048, 11923, 18793, -9331, -24802, 4694, 30570, 2233, -35439, -11526, 38680, 23114, -39474, -36701, 36999,
+    51797, -30419, -67658, 18962, 83318, -1927, -97566, -21284, 108971, 51215, -115837, -88430, 116130, 133716,
+    -107253, -188497, 85497, 255795, -44643, -342699, -28185, 468096, 167799, -696809, -519818, 1446093, 3562497};
+
+void build_hp16_tables(Hp16Tables &t)
+{
+    std::memset(&t, 0, sizeof t);
+    for (int i = 0; i < 118; i++) t.dp[i] = (float)((double)kQmfHalf[i < 59 ? i : 117 - i] / 8388608.0);
+    // InitMelFBwindows(FirstWindow16k, 80.0, 8000, 128, 5, normalize=0), 16kHzProcessing.c:254-259
+    const float st_freq = 80.0f, smpl = 8000.0f;
+    const int fft_len = 128, nch = 5;
+    int c[5];
+    const float start_mel = (float)(2595.0 * std::log10(1.0 + (double)st_freq / 700.0));
+    const float half_mel = (float)(2595.0 * std::log10(1.0 + (double)(smpl / 2) / 700.0));
+    for (int i = 0; i < nch; i++) {
+        const float arg = start_mel + (float)i / (float)(nch - 1) * (half_mel - start_mel);
+        const float f = (float)(700.0 * (std::pow(10.0, (double)arg / 2595.0) - 1.0));
+        c[i] = (int)((double)((float)fft_len * f / smpl) + 0.5);
+    }
+    for (int i = 0; i < nch; i++) {
+        float *d = t.fb[i];
+        int len;
+        if (i == 0) {
+            t.fb_start[i] = c[0];
+            len = c[1] - c[0];
+            for (int j = 0; j < len; j++) d[j] = (float)(1.0 - (double)((float)j / (float)len));
+        } else if (i < nch - 1) {
+            const int up = c[i] - c[i - 1];
+            t.fb_start[i] = c[i - 1] + 1;
+            len = c[i + 1] - c[i - 1] - 1;
+            for (int j = 0; j < up; j++) d[j] = (float)(j + 1) / (float)up;
+            for (int j = up, k = 0; j < len; j++, k++) d[j] = (float)(1.0 - (double)((float)(k + 1) / (float)(c[i + 1] - c[i])));
+        } else {
+            t.fb_start[i] = c[nch - 2] + 1;
+            len = c[nch - 1] - c[nch - 2];
+            for (int j = 0; j < len; j++) d[j] = (float)(j + 1) / (float)len;
+        }
+        t.fb_len[i] = len;
+    }
+    // InitDCTMatrix(13, 23 + 3), etsi/cpp/CompCeps.c:279-280
+    for (int i = 1; i < 13; i++)
+        for (int j = 0; j < 26; j++)
+            t.dct26[(i - 1) * 26 + j] = (float)std::cos(kPI * (double)(float)i / (double)(float)26 * ((double)(float)j + 0.5));
+}
+
 // BS3383 table 1 as entered in initMiddleEar(), resyth_64sub_IBM/cpp/extractwav.cpp:134-167
 static const float kEarF[29] = {20.0f, 25.0f, 31.5f, 40.0f, 50.0f, 63.0f, 80.0f, 100.0f, 125.0f, 160.0f, 200.0f,
     250.0f, 315.0f, 400.0f, 500.0f, 630.0f, 800.0f, 1000.0f, 1250.0f, 1600.0f, 2000.0f, 2500.0f, 3150.0f, 4000.0f,

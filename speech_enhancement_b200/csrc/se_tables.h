@@ -28,6 +28,13 @@ struct CcTables {                 // CompCeps, 8 kHz
     float tri[23][129];
 };
 
+struct Hp16Tables {               // ETSI 16 kHz mode (etsi/cpp/16kHzProcessing.c)
+    float dp[118];                            // half-band low-pass prototype; high-pass = reversed, alternating signs
+    int fb_start[5], fb_len[5];
+    float fb[5][65];                          // 5 un-normalised mel triangles from 80 Hz over the 65-bin PSD
+    float dct26[12 * 26];                     // DCT over 23 + 3 log bands
+};
+
 struct GtTables {                 // 64-channel gammatone
     float cf[kGtChannels], bw[kGtChannels], mid[kGtChannels];
     float f1[kGtChannels], f2[kGtChannels], gain[kGtChannels];
@@ -39,5 +46,6 @@ void build_ns_tables_p8(NsTables &t);
 void build_ns_tables_p16(NsTables &t);
 void build_cc_tables(CcTables &t);
 void build_gt_tables(GtTables &t);
+void build_hp16_tables(Hp16Tables &t);
 
 }  // namespace se

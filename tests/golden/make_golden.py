@@ -38,11 +38,28 @@ def features():
                         frames=frames, wp=np.stack([r.wave_proc(v) for v in frames]))
 
 
+def etsi16k():
+    """ETSI 16 kHz mode (16kHzProcessing.c + hooks): feature rows, low-band stream and the bare QMF split."""
+    assert po.build_ref(), "needs /root/reference"
+    r = po.RefEtsi()
+    x = synth.utterance(5, 16000, 16000 + 71)
+    xz = synth.utterance(7, 16000, 8000)                     # 5 leading all-zero calls -> 5 null vectors
+    f, d = r.etsi_features_16k(x)
+    fz, dz = r.etsi_features_16k(xz)
+    q = synth.utterance(9, 16000, 160 * 12)
+    lp, hp = r.qmf_split(q)
+    np.savez_compressed(os.path.join(HERE, "etsi16k_features.npz"), x=x, xz=xz, feat=f, z_feat=fz, den=d, z_den=dz,
+                        q=q, lp=lp, hp=hp)
+
+
 def main():
     assert po.build_ref(), "needs /root/reference"
     if "--only-features" in sys.argv:
         return features()
+    if "--only-16k" in sys.argv:
+        return etsi16k()
     features()
+    etsi16k()
     rng = np.random.default_rng(20141106)
 
     # ---- P8: etsi_denoise + re-enabled CompCeps step, with the per-call VAD trace ------------------

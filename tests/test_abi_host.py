@@ -86,6 +86,13 @@ def test_tables_bit_identical_to_oracle(oracle):
     tri = api.get_table("cc.tri").reshape(23, 129)
     for j in range(23):
         assert np.array_equal(tri[j, :ln[j]], c["tri"][j, :ln[j]])
+    h = oracle.hp16k_tables()                                     # ETSI 16 kHz mode
+    assert np.array_equal(api.get_table("hp16.dp"), h["dp"])
+    assert np.array_equal(api.get_table("hp16.fb").reshape(5, 65), h["fb"])
+    assert np.array_equal(api.get_table("hp16.fb_start").astype(int), h["start"])
+    assert np.array_equal(api.get_table("hp16.fb_len").astype(int), h["len"])
+    assert np.array_equal(api.get_table("hp16.dct26").reshape(12, 26), h["dct26"])
+    assert np.array_equal(h["hp"], -h["dp"] * (-1.0) ** np.arange(118))       # the high-pass is the sign-alternated prototype
     cf, bw, mid = oracle.channel_params()
     assert np.array_equal(api.get_table("gt.cf"), cf)
     assert np.array_equal(api.get_table("gt.bw"), bw)

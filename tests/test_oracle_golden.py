@@ -58,6 +58,22 @@ def test_p8_features_golden(oracle):
     assert np.array_equal(g["wp"][2], g["frames"][2])                    # low-energy frames pass untouched
 
 
+def test_etsi16k_golden(oracle):
+    """ETSI 16 kHz mode: QMF split, HP-band coding/decoding, 26-band CompCeps -- bit-exact against the reference build."""
+    g = load("etsi16k_features.npz")
+    for xk, fk, dk in (("x", "feat", "den"), ("xz", "z_feat", "z_den")):
+        f, d = oracle.etsi_features_16k(g[xk])
+        assert f.shape == g[fk].shape and np.array_equal(f, g[fk])
+        assert np.array_equal(d, g[dk])
+    assert len(g["feat"]) == 100 - 12 and len(g["z_feat"]) == 5 + (50 - 5 - 12)
+    assert not g["z_feat"][:5].any() and g["feat"][0, :14].all()
+    lp, hp = oracle.qmf_split(g["q"])
+    assert np.array_equal(lp, g["lp"]) and np.array_equal(hp, g["hp"])
+    # the 16 kHz rows are not the 8 kHz rows of the decimated signal: the HP bands enter c0 / logE / the DCT
+    f8, _ = oracle.etsi_features(np.ascontiguousarray(g["x"][::2]))
+    assert f8.shape == g["feat"].shape and np.abs(f8[:, 12] - g["feat"][:, 12]).min() > 1.0
+
+
 def test_rfft_golden(oracle):
     g = load("rfft.npz")
     for x, y in zip(g["x256"], g["y256"]):
@@ -142,6 +158,9 @@ def test_oracle_vs_reference_build_live():
     assert np.array_equal(a["den_i16"][:n], b["den_i16"][:n]) and np.array_equal(a["ceps"], b["ceps"])
     fa, fb = o.etsi_features(x), po.RefEtsi().etsi_features(x)
     assert np.array_equal(fa[0], fb[0]) and np.array_equal(fa[1], fb[1]) and fa[0][:, 14].any()
+    xw = synth.utterance(24, 16000, synth.ragged_length(24, 16000, 1.0, 2.0))
+    ga, gb = o.etsi_features_16k(xw), po.RefEtsi().etsi_features_16k(xw)
+    assert np.array_equal(ga[0], gb[0]) and np.array_equal(ga[1], gb[1]) and ga[0][:, 14].any()
     x16 = synth.utterance(22, 16000, 16000 + 77).astype(np.float32)
     s, R = o.p16_stream(), po.RefP16()
     A, B = s.func_wiener(x16), R.func_wiener(x16)
