@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
     ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
-    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "resynth", "ibm", "subband"],
+    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "etsi16k", "resynth", "ibm", "subband"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
 
@@ -339,6 +339,40 @@ def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features
             "ms_per_step": ms / args.steps, "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
+def bench_etsi16k(args, torch, api, ctx, dist, stream, first_u, n_utts=3000):
+    """ETSI 16 kHz mode (QMF split -> low-band NoiseSup/WaveProc/CompCeps + HP-band spectral subtraction and coding
+    -> 26-band cepstra -> PostProc -> VAD) on 10 s 16 kHz utterances; 15-column feature rows + low-band int16 out."""
+    samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
+    total = int(offsets[-1])
+    fo = np.zeros(n_utts + 1, np.int64)
+    fo[1:] = np.cumsum(np.diff(offsets) // 160)
+    do = fo * 80
+    d_in = dev(torch, samples)
+    d_feat = torch.empty(int(fo[-1]) * 15, dtype=torch.float32, device="cuda")
+    d_den = torch.empty(int(do[-1]), dtype=torch.int16, device="cuda")
+    d_nr = torch.empty(n_utts, dtype=torch.int32, device="cuda")
+
+    def step():
+        ctx.etsi16k_features_raw(d_in.data_ptr(), offsets, n_utts, d_feat.data_ptr(), fo, d_nr.data_ptr(),
+                                 d_den.data_ptr(), do, mem=api.SE_MEM_DEVICE)
+
+    for _ in range(args.warmup):
+        step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    ms = timed_steps(torch, dist, stream, step, 0, args.steps)
+    k_ms, k_n = ctx.kernel_time(api.K_NS_P8)
+    ctx.profiling(False)
+    audio_s = total / 16000.0
+    calls = total // 160
+    hbm, _ = peaks()
+    gbs = calls * (320 + 160 + 60) / (k_ms / max(k_n, 1) * 1e-3) / 1e9      # 160 int16 in, 80 int16 + 15 f32 out
+    return {"workload": "ETSI 16 kHz mode feature chain, %d x 10 s 16 kHz" % n_utts,
+            "xrt": audio_s * args.steps / (ms * 1e-3), "ms_per_step": ms / args.steps,
+            "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
+
+
 def bench_ibm(args, torch, api, ctx, dist, stream, first_u, n_utts=2000, seconds=5.0):
     """G64: fused subbband(pure) + subbband(noise) + make_single_IBM -> IRM + packed IBM bits (exact mode)."""
     from speech_enhancement_b200 import synth
@@ -553,7 +587,7 @@ def run_ours(args):
     if args.profile_only:
         with torch.cuda.stream(stream):
             fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm, "subband": lambda *a: bench_subband(*a, n_utts=int(os.environ.get("SE_SUB_UTTS", "1000")), seconds=float(os.environ.get("SE_SUB_SEC", "5"))),
-                  "p8feat": lambda *a: bench_p8(*a, features=True)}[args.profile_only]
+                  "p8feat": lambda *a: bench_p8(*a, features=True), "etsi16k": bench_etsi16k}[args.profile_only]
             print(json.dumps(fn(args, torch, api, ctx, dist, stream, first_u + 500000)), flush=True)
         ctx.close()
         dist.close()
@@ -564,6 +598,7 @@ def run_ours(args):
         if not args.no_extra and args.gpus == 1:
             extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000),
                      bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000, features=True),
+                     bench_etsi16k(args, torch, api, ctx, dist, stream, first_u + 600000),
                      bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000),
                      bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000),
                      bench_subband(args, torch, api, ctx, dist, stream, first_u + 900000)]

@@ -176,6 +176,25 @@ def test_oracle_vs_reference_build_live():
         assert np.array_equal(o.resynth(w, m, mode)[0], po.RefG64(v).resynth(w, m)[0]), v
 
 
+@pytest.mark.skipif(not po.have_ref(), reason="oracle/_ref not built (needs /root/reference)")
+def test_oracle_long_utterance_q2_wrap():
+    """Past 32 767 frames FilterCalc's int16 copy of the frame counter goes negative (SURVEY Q2,
+    etsi/cpp/NoiseSup.c:451-475): the restatement follows the reference's code across the wrap, bit for bit."""
+    o = po.Oracle()
+    n = 33000 * 80 + 5
+    x = np.concatenate([synth.utterance(100 + u, 8000, 80000) for u in range(n // 80000 + 1)])[:n]
+    a, b = o.etsi_denoise(x, with_ceps=True), po.RefEtsi().trace(x)
+    assert np.array_equal(a["den_i16"][:33000 * 80], b["den_i16"][:33000 * 80]) and np.array_equal(a["ceps"], b["ceps"])
+    n = 33000 * 160 + 77
+    x16 = np.concatenate([synth.utterance(100 + u, 16000, 160000) for u in range(n // 160000 + 1)])[:n].astype(np.float32)
+    s, R = o.p16_stream(), po.RefP16()
+    A, B = s.func_wiener(x16), R.func_wiener(x16)
+    for k in ("out", "sp_var", "sp_spec", "sp_mel", "sp_vadns", "frame_counter"):
+        assert np.array_equal(A[k], B[k]), k
+    s.close()
+    R.close()
+
+
 def test_reference_is_ill_conditioned_on_degenerate_signals(oracle):
     """Evidence for the self-calibrated bars of tests/test_gpu_fuzz.py: on DC and isolated-click inputs the
     reference algorithm, compiled -O3 with FMA contraction, disagrees with its own -O2/no-contraction build by far
