@@ -28,10 +28,27 @@ int etsi_denoise(short *p_data, short *p_denoised, long i_frame);
  * returned TRUE (i.e. on FAILURE), and it copies i_frame-320 BYTES.  On success p_denoised is left
  * untouched, exactly as the reference does.                                                      */
 int etsi_denoise_synchronization(short *p_data, short *p_denoised, long i_frame);
-/* The 16 kHz ETSI mode (etsi/cpp/16kHzProcessing.c) is outside the hot path: these
- * return TRUE(1) = failure and print "unsupported" on stderr.                                    */
+/* etsi_denoise_16k (AdvFrontEnd.c:228-313) copies 160 samples per call out of the 80-sample DenoiseBuffer
+ * (:264,290-293): half of what it returns is a heap over-read, so there is no defined output to match.  These
+ * return TRUE(1) = failure and print why on stderr; the 16 kHz mode itself (features + the defined low-band
+ * denoised stream) is se_etsi16k_features_batch in se_b200.h.                                      */
 int etsi_denoise_16k(short *p_data, short *p_denoised, long i_frame);
 int etsi_denoise_16k_synchronization(short *p_data, short *p_denoised, long i_frame);
+
+/* ---- function/20141106_speech_enhancement/aurora_speech_enhancement/aurora_speech_enhancement.cpp -----------
+ * BufferDenoise (:25-79): denoise a long 8 kHz recording in windows of batch_length samples (the tool uses
+ * 3 min = 1 440 000), each window after the first started etsi_offset_points = 320 samples early so that
+ * etsi_denoise's 320-sample latency is absorbed, outputs shifted back by 320, last 320 samples zeroed.  Same
+ * arithmetic and the same `work` buffer semantics as the reference (each etsi_denoise call overwrites
+ * work[0 .. len - len%80) and leaves the rest, so the < 80 stale samples the last window's copy picks up are
+ * reproduced); `work` needs batch_length + 320 shorts.  Here ALL windows of the recording go to the GPU as one
+ * ragged batch (they are independent), instead of one after the other.  samples < 320 is rejected (the
+ * tool's caller skips such files, :167-170).  Returns 0 / negative SE_E* (BufferDenoise itself: void).      */
+void BufferDenoise(short *src_wave, short *des_wave, int samples, int batch_length, short *work);
+int se_buffer_denoise(const short *src_wave, short *des_wave, int samples, int batch_length /* 0 = 1440000 */);
+/* The RMS normalisation the same tool applies before BufferDenoise (:172-184): scales p_data in place to an
+ * RMS of `target` (the tool: 3000) with its double/float promotions and (short) cast; returns the factor.  */
+double se_rms_normalise(short *p_data, int samples, float target);
 
 /* ---- etsi/cpp/rfft.h:19 — in place, output Re0..Re(n/2), Im(n/2-1)..Im1.  (n,m) must be (256,8) or
  * the plugin's (512,8); anything else prints an error and leaves x untouched.     */

@@ -4,6 +4,7 @@
 // text formatting the reference does around its kernels.
 #include "se_b200.h"
 #include "se_reference_api.h"
+#include <cmath>
 #include <cstdio>
 #include <cstdlib>
 #include <cstring>
@@ -74,14 +75,88 @@ SE_EXPORT int etsi_denoise_synchronization(short *p_data, short *p_denoised, lon
 
 SE_EXPORT int etsi_denoise_16k(short *, short *, long)
 {
-    std::fprintf(stderr, "etsi_denoise_16k: unsupported (16 kHz ETSI mode is outside the accelerated path)\n");
+    std::fprintf(stderr, "etsi_denoise_16k: unsupported (the reference reads 160 samples per call out of an 80-sample "
+                         "buffer, AdvFrontEnd.c:264,290-293; use se_etsi16k_features_batch)\n");
     return 1;
 }
 
 SE_EXPORT int etsi_denoise_16k_synchronization(short *, short *, long)
 {
-    std::fprintf(stderr, "etsi_denoise_16k_synchronization: unsupported (16 kHz ETSI mode is outside the accelerated path)\n");
+    std::fprintf(stderr, "etsi_denoise_16k_synchronization: unsupported (see etsi_denoise_16k)\n");
     return 1;
+}
+
+// ---------------------------------------------------------------------------------------------
+// aurora_speech_enhancement.cpp:25-79 (BufferDenoise) and :172-184 (RMS normalisation)
+// ---------------------------------------------------------------------------------------------
+namespace {
+int buffer_denoise(const short *src, short *des, int samples, int bl, short *work)
+{
+    const int kOff = 320;                                    // etsi_offset_points, :23
+    if (!src || !des || !work || bl <= 0 || samples < kOff) return SE_EINVAL;
+    se_ctx *ctx = default_ctx("BufferDenoise");
+    if (!ctx) return SE_ENODEVICE;
+    const int times = samples / bl, left = samples % bl;
+    // the windows the reference hands to etsi_denoise one after the other: (start, length)
+    std::vector<int64_t> start, off(1, 0);
+    auto add = [&](int64_t s, int64_t n) { start.push_back(s); off.push_back(off.back() + n); };
+    if (times == 0) add(0, samples);
+    else {
+        add(0, bl);
+        for (int i = 1; i < times; i++) add((int64_t)i * bl - kOff, bl + kOff);
+        add((int64_t)times * bl - kOff, left + kOff);
+    }
+    const int nw = (int)start.size();
+    std::vector<short> in((size_t)off.back()), out((size_t)off.back());
+    for (int w = 0; w < nw; w++) std::memcpy(&in[off[w]], src + start[w], (size_t)(off[w + 1] - off[w]) * sizeof(short));
+    int rc = se_etsi_denoise_batch(ctx, in.data(), off.data(), nw, out.data(), nullptr, nullptr, nullptr, nullptr, nullptr,
+                                   nullptr, SE_MEM_HOST);
+    if (report("BufferDenoise", rc) != SE_OK) return rc;
+    // replay the reference's sequence of writes into `work` and copies out of it
+    for (int w = 0; w < nw; w++) {
+        const int64_t len = off[w + 1] - off[w];
+        std::memcpy(work, &out[off[w]], (size_t)(len - len % 80) * sizeof(short));     // etsi_denoise leaves the tail
+        if (times == 0) {
+            std::memcpy(des, work + kOff, (size_t)(samples - kOff) * sizeof(short));
+        } else if (w == 0) {
+            std::memcpy(des, work + kOff, (size_t)(bl - kOff) * sizeof(short));
+        } else if (w < times) {
+            std::memcpy(des + (int64_t)w * bl - kOff, work + kOff, (size_t)bl * sizeof(short));
+        } else {
+            std::memcpy(des + (int64_t)times * bl - kOff, work + kOff, (size_t)left * sizeof(short));
+        }
+    }
+    std::memset(des + samples - kOff, 0, kOff * sizeof(short));
+    return SE_OK;
+}
+}  // namespace
+
+SE_EXPORT void BufferDenoise(short *src_wave, short *des_wave, int samples, int batch_length, short *work)
+{
+    buffer_denoise(src_wave, des_wave, samples, batch_length, work);
+}
+
+SE_EXPORT int se_buffer_denoise(const short *src_wave, short *des_wave, int samples, int batch_length)
+{
+    if (batch_length == 0) batch_length = 8000 * 60 * 3;     // :22
+    if (batch_length < 0) return SE_EINVAL;
+    std::vector<short> work((size_t)batch_length + 320, 0);
+    return buffer_denoise(src_wave, des_wave, samples, batch_length, work.data());
+}
+
+SE_EXPORT double se_rms_normalise(short *p_data, int samples, float target)
+{
+    double energy = 0.0;
+    for (int t = 0; t < samples; t++) energy += p_data[t] * p_data[t];      // int product, double sum (:175-178)
+    energy /= samples;
+    energy = std::sqrt(energy);
+    const double factor = target / energy;
+    for (int t = 0; t < samples; t++) {
+        const double v = (float)p_data[t] * factor;
+        // (short) of a double on x86-64: cvttsd2si to int32 (0x80000000 when out of range or NaN), low 16 bits
+        p_data[t] = (v > -2147483649.0 && v < 2147483648.0) ? (short)(int)v : (short)0;
+    }
+    return factor;
 }
 
 SE_EXPORT void rfft(float *x, int n, int m)

@@ -122,3 +122,23 @@ def test_shard_plan_properties():
         assert loads.max() - loads.min() <= 2 * 160000          # balanced to within one utterance each side
     assert list(api.shard_plan([0, 10], 4)) == [0, 0, 1, 1, 1]  # fewer utterances than shards: empty shards
     assert list(api.shard_plan([0], 3)) == [0, 0, 0, 0]
+
+
+def test_rms_normalise_matches_the_tools_arithmetic():
+    """se_rms_normalise = aurora_speech_enhancement.cpp:172-184 (host-side caller code, no GPU needed)."""
+    D = C.CDLL(api.DROPIN_PATH)
+    D.se_rms_normalise.restype = C.c_double
+    D.se_rms_normalise.argtypes = [C.c_void_p, C.c_int, C.c_float]
+    rng = np.random.default_rng(5)
+    for scale in (30.0, 900.0, 9000.0):
+        p = np.clip(rng.standard_normal(5000) * scale, -32768, 32767).astype(np.int16)
+        q = p.copy()
+        f = D.se_rms_normalise(q.ctypes.data, len(q), 3000.0)
+        energy = np.sqrt(np.sum(p.astype(np.int64) ** 2).astype(np.float64) / len(p))
+        assert abs(f - 3000.0 / energy) <= 1e-12 * f
+        want = np.trunc(p.astype(np.float32).astype(np.float64) * f).astype(np.int64)
+        want = ((want + 32768) % 65536 - 32768).astype(np.int16)       # (short) wraps like the reference's cast
+        assert np.array_equal(q, want)
+    z = np.zeros(16, np.int16)
+    D.se_rms_normalise(z.ctypes.data, 16, 3000.0)                      # 0 * inf = NaN -> cvttsd2si -> low 16 bits 0
+    assert np.all(z == 0)

@@ -171,3 +171,61 @@ def test_module_entry_points_do_noise_sup_and_comp_ceps(dropin, oracle):
     assert n_out == 40 - 4
     oracle.L.so_ns_destroy(s)
     dropin.AdvProcessDelete(C.byref(h))
+
+
+def _buffer_denoise_restated(etsi_denoise, src, bl, work):
+    """aurora_speech_enhancement.cpp:25-79 line by line over any etsi_denoise(x) -> int16[len - len%80]."""
+    n = len(src)
+    des = np.full(n, 777, np.int16)
+    times, left = n // bl, n % bl
+
+    def run(lo, ln):
+        y = etsi_denoise(src[lo:lo + ln])
+        work[:len(y)] = y                                # the tail ln % 80 of `work` keeps what it held
+
+    if times == 0:
+        run(0, n)
+        des[:n - 320] = work[320:n]
+    else:
+        run(0, bl)
+        des[:bl - 320] = work[320:bl]
+        for i in range(1, times):
+            run(i * bl - 320, bl + 320)
+            des[i * bl - 320:(i + 1) * bl - 320] = work[320:bl + 320]
+        run(times * bl - 320, left + 320)
+        des[times * bl - 320:times * bl - 320 + left] = work[320:320 + left]
+    des[n - 320:] = 0
+    return des
+
+
+@pytest.mark.parametrize("n,bl", [(8000 * 7 + 3333, 16000), (8000 * 7 + 3333, 80000), (16000 * 3, 16000), (4321, 8000)])
+def test_buffer_denoise_windows_as_one_batch(dropin, oracle, n, bl):
+    """BufferDenoise (the Win32 tool's 3-minute windows with 320 samples of overlap) with small windows: all
+    windows run as ONE ragged GPU batch; result = the reference's sequential loop, stale `work` tail included."""
+    dropin.BufferDenoise.argtypes = [_vp, _vp, C.c_int, C.c_int, _vp]
+    dropin.BufferDenoise.restype = None
+    dropin.se_buffer_denoise.argtypes = [_vp, _vp, C.c_int, C.c_int]
+    x = synth.utterance(9, 8000, n)
+    des = np.full(n, 777, np.int16)
+    work = np.full(bl + 320, -5, np.int16)
+    dropin.BufferDenoise(x.ctypes.data, des.ctypes.data, n, bl, work.ctypes.data)
+
+    def ours(seg):                                      # the drop-in's own per-call etsi_denoise (GPU)
+        y = np.zeros(len(seg), np.int16)
+        seg = np.ascontiguousarray(seg)
+        assert dropin.etsi_denoise(seg.ctypes.data, y.ctypes.data, len(seg)) == 0
+        return y[:len(seg) - len(seg) % 80]
+
+    seq = _buffer_denoise_restated(ours, x, bl, np.full(bl + 320, -5, np.int16))
+    assert np.array_equal(des, seq)                     # batched windows == sequential windows, bit for bit
+    ref = _buffer_denoise_restated(lambda s: oracle.etsi_denoise(s)["den_i16"][:len(s) - len(s) % 80], x, bl,
+                                   np.full(bl + 320, -5, np.int16))
+    assert np.abs(des.astype(np.int32) - ref.astype(np.int32)).max() <= 1
+    assert np.all(des[n - 320:] == 0)
+    des2 = np.zeros(n, np.int16)
+    assert dropin.se_buffer_denoise(x.ctypes.data, des2.ctypes.data, n, bl) == 0
+    stale = (n % bl + 320) % 80 if n >= bl else n % 80   # only the < 80 stale samples depend on `work`'s history
+    keep = np.ones(n, bool)
+    keep[n - 320 - stale:n - 320] = False
+    assert np.array_equal(des2[keep], des[keep])
+    assert dropin.se_buffer_denoise(x.ctypes.data, des2.ctypes.data, 100, bl) != 0      # < 320 samples: rejected
