@@ -17,7 +17,7 @@ pytestmark = pytest.mark.gpu
 
 CEPS_TOL = 1e-4
 OUTLIER_SHARE = 0.02      # frames allowed to exceed CEPS_TOL (peak-position flips)
-OUTLIER_TOL = 0.25       # measured on 97 600 frames: 0.5 % above 1e-4, 0.04 % above 1e-3, max 0.125 (tools/feature_outliers.py)
+OUTLIER_TOL = 0.25       # measured on 97 600 frames: 0.5 % above 1e-4, 0.04 % above 1e-3, max 0.125 (tests/tools/feature_outliers.py)
 
 
 def _batch(lens, zeros):
