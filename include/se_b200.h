@@ -50,6 +50,14 @@ int  se_ctx_sync(se_ctx *ctx);
  * enough to keep the persistent warps busy); H2D, kernels and D2H of successive chunks overlap.
  * Results do not depend on the chunking (utterances are independent). */
 int  se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts);
+/* FlushAdvProcess (etsi/cpp/ParmInterface.c:347-355 -> DoVADFlush, VAD.c:342-431): with enable != 0,
+ * se_etsi_features_batch and se_etsi16k_features_batch end every utterance the way the ETSI driver loop
+ * `while (FlushAdvProcess(FeatureBuffer, fe)) write` does: SE_FEATURE_FLUSH_ROWS more rows leave the VAD's 7-frame
+ * delay line (for utterances too short to have started it, the reference's loop writes its stale FeatureBuffer six
+ * times; so does this).  feat_offsets capacity per utterance grows by SE_FEATURE_FLUSH_ROWS.  Default off: none of
+ * the reference's drivers flushes. */
+#define SE_FEATURE_FLUSH_ROWS 6
+int  se_ctx_set_feature_flush(se_ctx *ctx, int enable);
 /* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 48 GiB. */
 int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
 

@@ -44,6 +44,16 @@ def have_ref(name="libref_etsi.so"):
     return os.path.exists(os.path.join(REF_DIR, name))
 
 
+def _features_ex(fn, x, mode16k):
+    x = np.ascontiguousarray(x, np.int16)
+    hop = 160 if mode16k else 80
+    feat = np.zeros((len(x) // hop + 6, 15), np.float32)
+    fn.restype = C.c_long
+    fn.argtypes = [_vp, C.c_long, _vp, _vp, C.c_int]
+    rows = fn(_p(x), len(x), _p(feat), None, (1 if mode16k else 0) | 2)
+    return feat[:rows].copy()
+
+
 class InfoStruct(C.Structure):
     _fields_ = [("produced", C.c_int), ("stage0_ran", C.c_int), ("stage1_ran", C.c_int),
                 ("flag_vad", C.c_int), ("hang_over", C.c_int), ("nb_speech", C.c_int),
@@ -98,6 +108,8 @@ class Oracle:
         L.so_etsi_features.argtypes = [_vp, C.c_long, _vp, _vp]
         L.so_etsi_features_16k.restype = C.c_long
         L.so_etsi_features_16k.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.so_etsi_features_ex.restype = C.c_long
+        L.so_etsi_features_ex.argtypes = [_vp, C.c_long, _vp, _vp, C.c_int]
         L.so_qmf_split.argtypes = [_vp, C.c_long, _vp, _vp]
         L.so_qmf_taps.argtypes = [_vp, _vp]
         L.so_ns_attach_hp16k.argtypes = [_vp]
@@ -146,6 +158,9 @@ class Oracle:
         den = np.zeros(len(x), np.int16)
         rows = self.L.so_etsi_features(_p(x), len(x), _p(feat), _p(den))
         return feat[:rows].copy(), den
+
+    def etsi_features_flush(self, x, mode16k=False):
+        return _features_ex(self.L.so_etsi_features_ex, x, mode16k)
 
     def etsi_features_16k(self, x):
         """16 kHz mode (QMF + HP-band coding): (feat[rows][15], low-band den_i16[(n//160)*80])."""
@@ -302,6 +317,10 @@ class RefEtsi:
         den = np.zeros((len(x) // 160) * 80, np.int16)
         rows = self.L.ref_etsi_features_16k(_p(x), len(x), _p(feat), _p(den))
         return feat[:rows].copy(), den
+
+    def etsi_features_flush(self, x, mode16k=False):
+        """The feature chain + the ETSI driver's flush loop (while FlushAdvProcess(...) write): feat[rows][15]."""
+        return _features_ex(self.L.ref_etsi_features_ex, x, mode16k)
 
     def qmf_split(self, x):
         x = np.ascontiguousarray(x, np.int16)

@@ -231,6 +231,7 @@ void ref_wave_proc(float *frame200)
  * like etsi_denoise's loop (AdvFrontEnd.c:173-191).  FEParamsX.FrameCounter, which gates DoVADProc
  * (VAD.c:256), is maintained by DoNoiseSup itself (NoiseSup.c:1366: stage-1 VAD frame count).
  * feat: [n/80][15] = c1..c12, c0, logE (post-processed), VAD flag.  Returns the number of rows written. */
+static int g_flush = 0;      /* ref_etsi_features_ex sets it: run FlushAdvProcess after the last call */
 long ref_etsi_features(const short *in, long n, float *feat, short *den_i16)
 {
     FEParamsX *fe = AdvProcessAlloc(8000);
@@ -277,6 +278,7 @@ long ref_etsi_features(const short *in, long n, float *feat, short *den_i16)
         if (den_i16) memcpy(den_i16 + start, den_buf, sizeof den_buf);
         start += 80;
     }
+    while (g_flush && FlushAdvProcess(fb, fe)) { memcpy(feat + rows * 15, fb, sizeof(float) * 15); rows++; }
     AdvProcessDelete(&fe);
     return rows;
 }
@@ -337,7 +339,18 @@ long ref_etsi_features_16k(const short *in, long n, float *feat, short *den_i16)
         start += 160;
         call++;
     }
+    while (g_flush && FlushAdvProcess(fb, fe)) { memcpy(feat + rows * 15, fb, sizeof(float) * 15); rows++; }
     AdvProcessDelete(&fe);
+    return rows;
+}
+
+/* flags: bit 0 = 16 kHz mode, bit 1 = flush (the ETSI driver loop: while (FlushAdvProcess(FeatureBuffer, fe)) write) */
+long ref_etsi_features_ex(const short *in, long n, float *feat, short *den_i16, int flags)
+{
+    long rows;
+    g_flush = (flags >> 1) & 1;
+    rows = (flags & 1) ? ref_etsi_features_16k(in, n, feat, den_i16) : ref_etsi_features(in, n, feat, den_i16);
+    g_flush = 0;
     return rows;
 }
 

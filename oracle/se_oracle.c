@@ -1114,6 +1114,7 @@ void so_post_proc(float *coef14, float *lms12)
 void so_vad_init(so_vad *v)
 {
     memset(v, 0, sizeof *v);
+    v->flush_focus = -1;                                                /* :142 */
     v->hang_over = 23;                                                  /* HANGOVERV, :113 */
 }
 
@@ -1140,10 +1141,40 @@ int so_vad_proc(so_vad *v, float *fb15, int speech_found, int frame_counter)
     return 1;
 }
 
+/* DoVADFlush, etsi/cpp/VAD.c:342-431: one flushing step.  The delay line is not written, only the focus moves, so
+ * the scan order of the 7 speech flags rotates.  Returns 1 while rows are due (6 times); fb15 is rewritten only when
+ * the incremented frame counter is past 10 -- otherwise the caller's FeatureBuffer keeps what it held and the
+ * reference's driver loop (while (FlushAdvProcess(...)) write) emits that stale row. */
+int so_vad_flush(so_vad *v, float *fb15, int *frame_counter)
+{
+    int i, run = 0, longest = 0;
+    if (v->flush_focus < 0) v->flush_focus = v->focus;
+    v->focus = (v->focus + 1) % 7;
+    if (v->focus == v->flush_focus) return 0;
+    (*frame_counter)++;
+    if (*frame_counter > 10) {
+        for (i = 1; i <= 7; i++) {
+            if (v->buf[(v->focus + i) % 7][14] != 0.0f) { if (++run > longest) longest = run; }
+            else run = 0;
+        }
+        if (longest >= 4) {
+            v->h_count = v->hang_over;
+            if (*frame_counter <= 35) v->hang_over = 50;
+        }
+        if (v->h_count && longest < 3) v->h_count--;
+        if (longest >= 3) v->v_count = 5;
+        if (v->v_count && longest < 3) v->v_count--;
+        memcpy(fb15, v->buf[(v->focus + 1) % 7], sizeof(float) * 14);
+        fb15[14] = (v->v_count || v->h_count || longest >= 3) ? 1.0f : 0.0f;
+    }
+    return 1;
+}
+
 /* The full per-frame chain, driven like oracle/ref_etsi.c:ref_etsi_features.  The VAD's FrameCounter
  * is the stage-1 frame count DoNoiseSup publishes (NoiseSup.c:1366).  feat: [n/80][15]; returns rows. */
-long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16)
+static long features_impl(const int16_t *in, long n, float *feat, int16_t *den_i16, int flush)
 {
+    int frame_counter = 0;
     so_ns *s = so_ns_create(SO_PROFILE_P8);
     so_vad vad;
     float den_buf[241], cur[80], fb[16], lms[12], frame[201];
@@ -1167,7 +1198,9 @@ long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16)
         memset(&info, 0, sizeof info);
         if (((int)check != 0) || onset) {
             onset = 1;
-            if (so_ns_block(s, cur, pt, &info)) {
+            const int produced = so_ns_block(s, cur, pt, &info);
+            if (info.stage0_ran || info.stage1_ran) frame_counter = info.nb_frame0;     /* NoiseSup.c:1366 */
+            if (produced) {
                 for (i = 0; i < 80; i++) out_buf[i] = (int16_t)pt[i];
                 if (offset < 0) offset += 80;
                 if (offset >= 0) {
@@ -1187,6 +1220,8 @@ long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16)
         if (den_i16) memcpy(den_i16 + start, out_buf, sizeof out_buf);
         start += 80;
     }
+    /* FlushAdvProcess (ParmInterface.c:347-355) the way the ETSI driver loop uses it: while it returns TRUE, write */
+    while (flush && so_vad_flush(&vad, fb, &frame_counter)) { memcpy(feat + rows * 15, fb, sizeof(float) * 15); rows++; }
     so_ns_destroy(s);
     return rows;
 }
@@ -1194,8 +1229,9 @@ long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16)
 /* The same chain at SamplingFrequency 16000 (AdvProcessAlloc, ParmInterface.c:99-109): 160 samples per call, QMF
  * split, NoiseSup on the low band, HP-band coding inside NoiseSup, decoding/merging inside CompCeps.  Driven like
  * oracle/ref_etsi.c:ref_etsi_features_16k.  feat: [n/160][15]; den_i16: [n/160][80] (low band); returns rows. */
-long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i16)
+static long features16_impl(const int16_t *in, long n, float *feat, int16_t *den_i16, int flush)
 {
+    int frame_counter = 0;
     so_ns *s = so_ns_create(SO_PROFILE_P8);
     so_vad vad;
     float den_buf[241], cur[160], lp[80], fb[16], lms[12], frame[201];
@@ -1221,7 +1257,9 @@ long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i
         if (((int)check != 0) || onset) {
             onset = 1;
             hp16k_split(s->hp16k, cur, lp);
-            if (so_ns_block(s, lp, pt, &info)) {
+            const int produced = so_ns_block(s, lp, pt, &info);
+            if (info.stage0_ran || info.stage1_ran) frame_counter = info.nb_frame0;
+            if (produced) {
                 for (i = 0; i < 80; i++) out_buf[i] = (int16_t)pt[i];
                 if (offset < 0) offset += 80;
                 if (offset >= 0) {
@@ -1242,8 +1280,18 @@ long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i
         start += 160;
         call++;
     }
+    /* FlushAdvProcess (ParmInterface.c:347-355) the way the ETSI driver loop uses it: while it returns TRUE, write */
+    while (flush && so_vad_flush(&vad, fb, &frame_counter)) { memcpy(feat + rows * 15, fb, sizeof(float) * 15); rows++; }
     so_ns_destroy(s);
     return rows;
+}
+
+long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16) { return features_impl(in, n, feat, den_i16, 0); }
+long so_etsi_features_16k(const int16_t *in, long n, float *feat, int16_t *den_i16) { return features16_impl(in, n, feat, den_i16, 0); }
+/* flags: bit 0 = 16 kHz mode, bit 1 = flush the VAD delay line at the end; feat needs calls + 6 rows */
+long so_etsi_features_ex(const int16_t *in, long n, float *feat, int16_t *den_i16, int flags)
+{
+    return (flags & 1) ? features16_impl(in, n, feat, den_i16, (flags >> 1) & 1) : features_impl(in, n, feat, den_i16, (flags >> 1) & 1);
 }
 
 /* Do16kProcessing as a stream: in[n] -> lp[n/2], hp[n/2] (n rounded down to a multiple of 160). */

@@ -57,13 +57,16 @@ void so_comp_ceps(const float *frame201, float *coef14);   /* etsi/cpp/CompCeps.
 void so_cc_tables(float *hamming100, float *dct12x23, int *start23, int *len23, float *tri23x129);
 
 /* ---------- P8 back half: WaveProc / PostProc / VAD (etsi/cpp/ParmInterface.c:274-311) ---------- */
-typedef struct { float buf[7][16]; int focus, hang_over, h_count, v_count; } so_vad;
+typedef struct { float buf[7][16]; int focus, hang_over, h_count, v_count, flush_focus; } so_vad;
 void so_wave_proc(float *frame200);                          /* etsi/cpp/WaveProc.c:386-453          */
 void so_post_proc(float *coef14, float *lms12);              /* etsi/cpp/PostProc.c:117-150          */
 void so_vad_init(so_vad *v);
 int so_vad_proc(so_vad *v, float *fb15, int speech_found, int frame_counter);   /* VAD.c:214-330    */
 /* NoiseSup -> WaveProc -> CompCeps -> PostProc -> VAD; feat[row][15] = c1..c12,c0,logE,VAD flag. */
 long so_etsi_features(const int16_t *in, long n, float *feat, int16_t *den_i16);
+int so_vad_flush(so_vad *v, float *fb15, int *frame_counter);                   /* VAD.c:342-431    */
+/* flags: bit 0 = 16 kHz mode, bit 1 = FlushAdvProcess at the end (up to 6 more rows) */
+long so_etsi_features_ex(const int16_t *in, long n, float *feat, int16_t *den_i16, int flags);
 /* 16 kHz mode (etsi/cpp/16kHzProcessing.c + its hooks in NoiseSup.c / CompCeps.c) */
 int so_ns_attach_hp16k(so_ns *s);
 void so_qmf_taps(float *dp118, float *hp118);

@@ -47,6 +47,7 @@ def lib():
         L.se_ctx_set_scratch_limit.argtypes = [_vp, C.c_uint64]
         L.se_ctx_profiling.argtypes = [_vp, C.c_int]
         L.se_ctx_set_pipeline.argtypes = [_vp, C.c_uint64, C.c_int]
+        L.se_ctx_set_feature_flush.argtypes = [_vp, C.c_int]
         L.se_ctx_kernel_time.argtypes = [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
         L.se_ctx_reset_kernel_times.argtypes = [_vp]
         L.se_ctx_launch_count.restype = C.c_int64
@@ -283,13 +284,18 @@ class Context:
         offsets = _i64(offsets)
         nu = len(offsets) - 1
         fo = np.zeros(nu + 1, np.int64)
-        fo[1:] = np.cumsum(np.diff(offsets) // 80)
+        fo[1:] = np.cumsum(np.diff(offsets) // 80 + getattr(self, "_flush_rows", 0))
         feat = np.zeros((max(int(fo[-1]), 1), 15), np.float32)
         rows = np.zeros(max(nu, 1), np.int32)
         den = np.zeros(len(samples), np.int16) if denoised else None
         self.etsi_features_raw(samples, offsets, nu, feat, fo, rows, den)
         per_utt = [feat[fo[u]:fo[u] + rows[u]] for u in range(nu)]
         return (per_utt, den) if denoised else per_utt
+
+    def set_feature_flush(self, enable):
+        """FlushAdvProcess at the end of every utterance of the feature-chain calls (6 more rows)."""
+        _check(self.L.se_ctx_set_feature_flush(self.h, int(bool(enable))), "se_ctx_set_feature_flush")
+        self._flush_rows = 6 if enable else 0
 
     def etsi16k_features(self, samples, offsets, denoised=False):
         """ETSI 16 kHz mode: per-utterance [rows][15] arrays (+ per-utterance int16 low-band denoised streams)."""
@@ -298,8 +304,9 @@ class Context:
         nu = len(offsets) - 1
         calls = np.diff(offsets) // 160
         fo = np.zeros(nu + 1, np.int64)
-        fo[1:] = np.cumsum(calls)
-        do = fo * 80
+        fo[1:] = np.cumsum(calls + getattr(self, "_flush_rows", 0))
+        do = np.zeros(nu + 1, np.int64)
+        do[1:] = np.cumsum(calls) * 80
         feat = np.zeros((max(int(fo[-1]), 1), 15), np.float32)
         rows = np.zeros(max(nu, 1), np.int32)
         den = np.zeros(max(int(do[-1]), 1), np.int16) if denoised else None

@@ -247,6 +247,7 @@ int se_ctx_create(int device, se_ctx **out)
     ctx->scratch_limit = 48ull << 30;
     ctx->chunk_bytes = 512ull << 20;
     ctx->chunk_min_utts = 1024;
+    ctx->feature_flush = 0;
     ctx->profiling = 0;
     std::memset(ctx->k_ms, 0, sizeof ctx->k_ms);
     std::memset(ctx->k_launches, 0, sizeof ctx->k_launches);
@@ -307,6 +308,13 @@ int se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts)
     if (!ctx || chunk_bytes == 0 || min_utts < 1) return SE_EINVAL;
     ctx->chunk_bytes = chunk_bytes;
     ctx->chunk_min_utts = min_utts;
+    return SE_OK;
+}
+
+int se_ctx_set_feature_flush(se_ctx *ctx, int enable)
+{
+    if (!ctx) return SE_EINVAL;
+    ctx->feature_flush = enable ? 1 : 0;
     return SE_OK;
 }
 

@@ -309,7 +309,8 @@ int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *o
     SE_TRY(check_offsets(feat_offsets, n_utts, "se_etsi_features_batch(feat_offsets)"));
     if (offsets[0] != 0) { set_error("se_etsi_features_batch: offsets[0] must be 0"); return SE_EINVAL; }
     for (int u = 0; u < n_utts; u++)
-        if (feat_offsets[u + 1] - feat_offsets[u] < se_etsi_num_feature_rows(offsets[u + 1] - offsets[u])) {
+        if (feat_offsets[u + 1] - feat_offsets[u] <
+            se_etsi_num_feature_rows(offsets[u + 1] - offsets[u]) + (ctx->feature_flush ? SE_FEATURE_FLUSH_ROWS : 0)) {
             set_error("se_etsi_features_batch: feat_offsets too small for utterance %d", u);
             return SE_EINVAL;
         }
@@ -317,6 +318,7 @@ int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *o
     std::memset(&a, 0, sizeof a);
     a.zero_check = 1;
     a.features = 1;
+    a.flush = ctx->feature_flush;
     NsOut outs[] = {
         {denoised, sizeof(int16_t), kIdxSample, false, false, kSlotOut, offsetof(NsLaunch, den_i16)},
         {features, sizeof(float) * 15, kIdxAux1, true, false, kSlotOut2, offsetof(NsLaunch, ceps)},
@@ -341,7 +343,7 @@ int se_etsi16k_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t
     if (denoised_lp) SE_TRY(check_offsets(den_offsets, n_utts, "se_etsi16k_features_batch(den_offsets)"));
     for (int u = 0; u < n_utts; u++) {
         const int64_t calls = se_etsi16k_num_feature_rows(offsets[u + 1] - offsets[u]);
-        if (feat_offsets[u + 1] - feat_offsets[u] < calls) {
+        if (feat_offsets[u + 1] - feat_offsets[u] < calls + (ctx->feature_flush ? SE_FEATURE_FLUSH_ROWS : 0)) {
             set_error("se_etsi16k_features_batch: feat_offsets too small for utterance %d", u);
             return SE_EINVAL;
         }
@@ -354,6 +356,7 @@ int se_etsi16k_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t
     std::memset(&a, 0, sizeof a);
     a.zero_check = 1;
     a.features = 2;
+    a.flush = ctx->feature_flush;
     NsOut outs[] = {
         {denoised_lp, sizeof(int16_t), kIdxAux2, false, false, kSlotOut, offsetof(NsLaunch, den_i16)},
         {features, sizeof(float) * 15, kIdxAux1, true, false, kSlotOut2, offsetof(NsLaunch, ceps)},

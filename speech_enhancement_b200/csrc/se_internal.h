@@ -80,6 +80,7 @@ struct NsLaunch {
     float *den_f32;
     float *ceps;                 // [row][14] raw cepstra, or [row][15] feature rows when `features`
     int features;                // P8: run WaveProc -> CompCeps -> PostProc -> VAD behind NoiseSup
+    int flush;                   // ... and FlushAdvProcess after the last call (6 more rows)
     const int64_t *ceps_offsets; // device
     int32_t *n_ceps;
     uint8_t *vad_trace;
@@ -132,6 +133,7 @@ struct se_ctx {
     se_lane *cur;               // lane the launch helpers currently target
     uint64_t chunk_bytes;       // SE_MEM_HOST pipelining: target I/O bytes per chunk
     int chunk_min_utts;         // ... and the fewest utterances worth a launch of their own
+    int feature_flush;          // se_ctx_set_feature_flush: the feature-chain calls append FlushAdvProcess's 6 rows
     // tables
     se::NsTables h_p8, h_p16;
     se::CcTables h_cc;

@@ -166,15 +166,10 @@ __device__ __forceinline__ float post_proc_warp(float c, FeatState &f, int lane)
     return c;
 }
 
-// DoVADProc.  c = this lane's coefficient (lanes 0..13).  Returns true when a frame is released; then
-// `c` holds this lane's column of the released row (lane 14 = VAD flag).
-__device__ __forceinline__ bool vad_proc_warp(float &c, FeatState &f, FeatMem &fm, int lane, bool speech_found, int frame_counter)
+// The release half of DoVADProc / DoVADFlush (VAD.c:256-303, :377-419): trigger logic over the 7 speech flags
+// (bit 0 = the slot at Focus, scanned last), then the row one past Focus leaves the delay line.
+__device__ __forceinline__ void vad_release_warp(float &c, FeatState &f, const FeatMem &fm, int lane, int frame_counter)
 {
-    f.focus = f.focus == 6 ? 0 : f.focus + 1;
-    if (lane < 14) fm.vad[f.focus * 16 + lane] = c;
-    f.speech_bits = ((f.speech_bits << 1) | (speech_found ? 1 : 0)) & 0x7f;
-    __syncwarp();
-    if (frame_counter <= 10) return false;                              // BUFFER_SIZE + 3, VAD.c:256
     const int x = f.speech_bits;
     const bool run3 = (x & (x >> 1) & (x >> 2)) != 0;                   // longest run of speech flags >= V_TRIGGER
     const bool run4 = (x & (x >> 1) & (x >> 2) & (x >> 3)) != 0;        // ... >= H_TRIGGER
@@ -188,8 +183,33 @@ __device__ __forceinline__ bool vad_proc_warp(float &c, FeatState &f, FeatMem &f
     const int oldest = f.focus == 6 ? 0 : f.focus + 1;
     c = (lane < 14) ? fm.vad[oldest * 16 + lane] : 0.0f;
     if (lane == 14) c = (f.v_count || f.h_count || run3) ? 1.0f : 0.0f;
+}
+
+// DoVADProc.  c = this lane's coefficient (lanes 0..13).  Returns true when a frame is released; then
+// `c` holds this lane's column of the released row (lane 14 = VAD flag).
+__device__ __forceinline__ bool vad_proc_warp(float &c, FeatState &f, FeatMem &fm, int lane, bool speech_found, int frame_counter)
+{
+    f.focus = f.focus == 6 ? 0 : f.focus + 1;
+    if (lane < 14) fm.vad[f.focus * 16 + lane] = c;
+    f.speech_bits = ((f.speech_bits << 1) | (speech_found ? 1 : 0)) & 0x7f;
+    __syncwarp();
+    if (frame_counter <= 10) return false;                              // BUFFER_SIZE + 3, VAD.c:256
+    vad_release_warp(c, f, fm, lane, frame_counter);
     __syncwarp();
     return true;
+}
+
+// DoVADFlush (VAD.c:342-431), one step: Focus moves on without a write, so the scan order of the flags rotates.
+// The row is rewritten only when the incremented FrameCounter is past 10; otherwise FeatureBuffer (fb) keeps what
+// it held and the driver loop `while (FlushAdvProcess(...)) write` emits that stale row.
+__device__ __forceinline__ void vad_flush_warp(float &fb, FeatState &f, const FeatMem &fm, int lane, int &frame_counter)
+{
+    f.focus = f.focus == 6 ? 0 : f.focus + 1;
+    frame_counter++;
+    if (frame_counter > 10) {
+        f.speech_bits = ((f.speech_bits << 1) | (f.speech_bits >> 6)) & 0x7f;
+        vad_release_warp(fb, f, fm, lane, frame_counter);
+    }
 }
 
 }  // namespace se

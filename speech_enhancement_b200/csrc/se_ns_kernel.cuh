@@ -135,6 +135,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 for (int i = lane; i < P::RB; i += 32) wm.ring3[i] = 0.0f;
         }
         FeatState fs;
+        float fb_last = 0.0f;                             // lane i < 15: FeatureBuffer[i] as the last call left it
         if constexpr (FEAT) feat_state_init(fs, fm, lane);
         Hp16State hs;
         if constexpr (HP16) hp16_state_init(hs, hm, lane);
@@ -282,6 +283,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     float c = 0.0f;
                     if (!process) {
                         emit = true;                     // null feature vector, ParmInterface.c:314-327
+                        if (lane < 14) fb_last = 0.0f;
                     } else if (produced && s.nb_out2 >= 3) {
                         const int base = ((s.nb_out2 - 3) & 3) * P::S;
                         for (int i = lane; i < 201; i += 32) fm.frame[i] = wm.ring3[wrap<P::RB>(base + i - 1)];
@@ -295,6 +297,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         c = post_proc_warp(c, fs, lane);
                         const bool speech = fl.spec || fl.mel || fl.var || (s.nb_speech > 4);
                         emit = vad_proc_warp(c, fs, fm, lane, speech, s.nb_frame0);
+                        if (emit || lane < 14) fb_last = c;       // what the caller's FeatureBuffer holds after this call
                     }
                     if (emit) {
                         if (a.ceps && fs.rows < ceps_cap && lane < kFeatCols) a.ceps[(ceps0 + fs.rows) * kFeatCols + lane] = c;
@@ -336,6 +339,17 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             if (a.produced && lane == 0)
                 a.produced[blk0 + b] = (produced ? 1 : 0) | (ran0 ? 2 : 0) | (process ? 0 : 4);
             __syncwarp();
+        }
+
+        if constexpr (FEAT) {
+            if (a.flush) {                                // FlushAdvProcess, ParmInterface.c:347-355: 6 more rows
+                int fc = s.nb_frame0;                     // FEParamsX.FrameCounter as DoNoiseSup last published it
+                for (int k = 0; k < 6; k++) {
+                    vad_flush_warp(fb_last, fs, fm, lane, fc);
+                    if (a.ceps && fs.rows < ceps_cap && lane < kFeatCols) a.ceps[(ceps0 + fs.rows) * kFeatCols + lane] = fb_last;
+                    fs.rows++;
+                }
+            }
         }
 
         // tail (len % S): the reference leaves it untouched; the batch API defines it as 0

@@ -34,8 +34,12 @@ def features():
                        (3000 * np.sin(2 * np.pi * n / 61.0) * (1 + 0.5 * np.sin(2 * np.pi * n / 57))).astype(np.float32),
                        np.round(rng.standard_normal(200) * 0.5).astype(np.float32),     # below the energy gate
                        rng.integers(-32768, 32768, 200).astype(np.float32)])           # int32 wrap-around case
+    xs = synth.utterance(11, 8000, 80 * 9)                   # too short to start the VAD: the flush emits stale rows
     np.savez_compressed(os.path.join(HERE, "p8_features.npz"), x=x, xz=xz, feat=f, z_feat=fz, den=d, z_den=dz,
-                        frames=frames, wp=np.stack([r.wave_proc(v) for v in frames]))
+                        frames=frames, wp=np.stack([r.wave_proc(v) for v in frames]),
+                        # + FlushAdvProcess: the last 6 rows of each
+                        flush=r.etsi_features_flush(x)[-6:], z_flush=r.etsi_features_flush(xz)[-6:],
+                        xs=xs, s_flush=r.etsi_features_flush(xs))
 
 
 def etsi16k():
@@ -49,7 +53,7 @@ def etsi16k():
     q = synth.utterance(9, 16000, 160 * 12)
     lp, hp = r.qmf_split(q)
     np.savez_compressed(os.path.join(HERE, "etsi16k_features.npz"), x=x, xz=xz, feat=f, z_feat=fz, den=d, z_den=dz,
-                        q=q, lp=lp, hp=hp)
+                        q=q, lp=lp, hp=hp, flush=r.etsi_features_flush(x, True)[-6:])
 
 
 def main():

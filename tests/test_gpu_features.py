@@ -120,3 +120,33 @@ def test_features_pipelined_chunks(ctx):
     assert np.array_equal(den_a, den_b)
     for x, y in zip(a, b):
         assert np.array_equal(x, y)
+
+
+def test_flush_rows(ctx, oracle):
+    """FlushAdvProcess / DoVADFlush (ParmInterface.c:347-355, VAD.c:342-431) behind se_ctx_set_feature_flush: six more
+    rows per utterance -- the frames still in the VAD's delay line with the flush's own trigger logic, or, for
+    utterances too short to have started the VAD, six copies of the stale FeatureBuffer, like the reference's driver
+    loop.  Row counts and flags identical, coefficients of the flushed rows = rows already checked (delay line)."""
+    lens = [16000, 24000, 8000, 80 * 9, 80 * 3, 0, 79, 80 * 16, 80 * 17, 12345]
+    zeros = [0, 3, 7, 0, 0, 0, 0, 0, 2, 1]
+    xs, offsets = _batch(lens, zeros)
+    samples = np.concatenate(xs)
+    plain = ctx.etsi_features(samples, offsets)
+    ctx.set_feature_flush(True)
+    try:
+        got = ctx.etsi_features(samples, offsets)
+        got16 = ctx.etsi16k_features(synth.utterance(31, 16000, 20000), [0, 20000])[0]
+    finally:
+        ctx.set_feature_flush(False)
+    for u, x in enumerate(xs):
+        ref = oracle.etsi_features_flush(x)
+        g = got[u]
+        assert g.shape == ref.shape == (len(plain[u]) + 6, 15), (u, g.shape, ref.shape)
+        assert np.array_equal(g[:-6], plain[u])                       # the flush only appends
+        assert np.array_equal(g[:, 14], ref[:, 14]), "utterance %d: VAD flags differ" % u
+        err = ceps_err(ref[-6:, :14], g[-6:, :14]).max(axis=1)
+        assert err.max() <= OUTLIER_TOL and (err > CEPS_TOL).sum() <= 1, (u, err)
+    ref16 = oracle.etsi_features_flush(synth.utterance(31, 16000, 20000), True)
+    assert got16.shape == ref16.shape and np.array_equal(got16[:, 14], ref16[:, 14])
+    assert ceps_err(ref16[-6:, :14], got16[-6:, :14]).max() <= OUTLIER_TOL
+    assert np.array_equal(ctx.etsi_features(samples, offsets)[0], plain[0])          # and it is off again

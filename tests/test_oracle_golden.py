@@ -53,6 +53,11 @@ def test_p8_features_golden(oracle):
         assert np.array_equal(d, g[dk])
     assert len(g["feat"]) == 100 - 12 and len(g["z_feat"]) == 5 + (50 - 5 - 12)
     assert not g["z_feat"][:5].any() and g["feat"][0, :14].all()        # null vectors, then real frames
+    # FlushAdvProcess (DoVADFlush): 6 more rows; on an utterance too short to start the VAD, six stale FeatureBuffers
+    assert np.array_equal(oracle.etsi_features_flush(g["x"])[-6:], g["flush"])
+    assert np.array_equal(oracle.etsi_features_flush(g["x"])[:-6], g["feat"])
+    assert np.array_equal(oracle.etsi_features_flush(g["xz"])[-6:], g["z_flush"])
+    assert np.array_equal(oracle.etsi_features_flush(g["xs"]), g["s_flush"]) and g["s_flush"].shape == (6, 15)
     for v, w in zip(g["frames"], g["wp"]):
         assert np.array_equal(oracle.wave_proc(v), w)
     assert np.array_equal(g["wp"][2], g["frames"][2])                    # low-energy frames pass untouched
@@ -67,6 +72,7 @@ def test_etsi16k_golden(oracle):
         assert np.array_equal(d, g[dk])
     assert len(g["feat"]) == 100 - 12 and len(g["z_feat"]) == 5 + (50 - 5 - 12)
     assert not g["z_feat"][:5].any() and g["feat"][0, :14].all()
+    assert np.array_equal(oracle.etsi_features_flush(g["x"], True)[-6:], g["flush"])
     lp, hp = oracle.qmf_split(g["q"])
     assert np.array_equal(lp, g["lp"]) and np.array_equal(hp, g["hp"])
     # the 16 kHz rows are not the 8 kHz rows of the decimated signal: the HP bands enter c0 / logE / the DCT
@@ -158,6 +164,8 @@ def test_oracle_vs_reference_build_live():
     assert np.array_equal(a["den_i16"][:n], b["den_i16"][:n]) and np.array_equal(a["ceps"], b["ceps"])
     fa, fb = o.etsi_features(x), po.RefEtsi().etsi_features(x)
     assert np.array_equal(fa[0], fb[0]) and np.array_equal(fa[1], fb[1]) and fa[0][:, 14].any()
+    for xx, m16 in ((x, False), (x[:80 * 8], False), (x[:0], False), (synth.utterance(24, 16000, 20000), True)):
+        assert np.array_equal(o.etsi_features_flush(xx, m16), po.RefEtsi().etsi_features_flush(xx, m16))
     xw = synth.utterance(24, 16000, synth.ragged_length(24, 16000, 1.0, 2.0))
     ga, gb = o.etsi_features_16k(xw), po.RefEtsi().etsi_features_16k(xw)
     assert np.array_equal(ga[0], gb[0]) and np.array_equal(ga[1], gb[1]) and ga[0][:, 14].any()
