@@ -30,3 +30,23 @@ print("rows", rows, "vad flag mismatches", vad_diff)
 for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
     print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
 print("max err %.4g, median %.3g" % (e.max(), np.median(e)))
+
+# ---- the same statistics for the ETSI 16 kHz mode, with the flush rows on ---------------------------------------
+ctx.set_feature_flush(True)
+xs = [synth.utterance(7000 + i, 16000, 16000 * 5) for i in range(n_utts)]
+offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
+got, den = ctx.etsi16k_features(np.concatenate(xs), offsets, denoised=True)
+errs, vad_diff, rows, lsb = [], 0, 0, 0
+for u, x in enumerate(xs):
+    ref = o.etsi_features_flush(x, True)
+    _, rden = o.etsi_features_16k(x)
+    assert ref.shape == got[u].shape, (u, ref.shape, got[u].shape)
+    errs.append(ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1))
+    vad_diff += int((ref[:, 14] != got[u][:, 14]).sum())
+    lsb = max(lsb, int(np.abs(den[u].astype(np.int32) - rden.astype(np.int32)).max()))
+    rows += len(ref)
+e = np.concatenate(errs)
+print("16 kHz mode (+flush): rows", rows, "vad flag mismatches", vad_diff, "low-band int16 max |d|", lsb)
+for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
+    print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
+print("max err %.4g, median %.3g" % (e.max(), np.median(e)))

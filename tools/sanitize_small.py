@@ -20,6 +20,13 @@ with api.Context(0) as ctx:
     st.push(s16[:1600].astype(np.float32)); st.push(s16[1600:3200].astype(np.float32)); st.close()
     st = ctx.ns_stream(8)
     st.push(s8[:800].astype(np.float32)); st.push(s8[800:1600].astype(np.float32)); st.close()
+    ctx.etsi_features(s8, o8, denoised=True)
+    ctx.etsi16k_features(s16, o16, denoised=True)
+    ctx.set_feature_flush(True)
+    ctx.etsi_features(s8, o8)
+    ctx.etsi16k_features(s16, o16)
+    ctx.set_feature_flush(False)
+    ctx.qmf_split(s16[:1600].reshape(2, 800)[:, :640])
     ctx.rfft(np.random.default_rng(0).standard_normal((3, 256)).astype(np.float32))
     ctx.rfft(np.random.default_rng(0).standard_normal((3, 512)).astype(np.float32))
     n = 20000
