@@ -9,7 +9,13 @@ namespace se {
 #define SE_NS_WARPS 8
 #endif
 // FEAT: 0 = NoiseSup (+ raw CompCeps), 1 = 8 kHz feature chain, 2 = 16 kHz feature chain (se_ns_hp16k.cuh)
-template <int FEAT> struct NsWarps { static constexpr int value = FEAT ? 6 : SE_NS_WARPS; };
+#ifndef SE_NS_WARPS_F1
+#define SE_NS_WARPS_F1 6
+#endif
+#ifndef SE_NS_WARPS_F2
+#define SE_NS_WARPS_F2 6
+#endif
+template <int FEAT> struct NsWarps { static constexpr int value = FEAT == 2 ? SE_NS_WARPS_F2 : (FEAT ? SE_NS_WARPS_F1 : SE_NS_WARPS); };
 
 template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<PROF> &bm, const NsDevTables &tb,
                                                                      const CcDevTables &cc)
