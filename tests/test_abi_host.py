@@ -142,3 +142,21 @@ def test_rms_normalise_matches_the_tools_arithmetic():
     z = np.zeros(16, np.int16)
     D.se_rms_normalise(z.ctypes.data, 16, 3000.0)                      # 0 * inf = NaN -> cvttsd2si -> low 16 bits 0
     assert np.all(z == 0)
+
+
+def build_cxx_driver(out_dir):
+    """tests/cxx/dropin_driver.cpp: a stand-in for the reference's C++ drivers over include/se_reference_api.hpp."""
+    import subprocess
+    exe = os.path.join(str(out_dir), "dropin_driver")
+    lib = os.path.dirname(api.DROPIN_PATH)
+    subprocess.check_call(["g++", "-O2", "-std=c++17", "-Wall", "-Werror", "-I" + os.path.join(ROOT, "include"),
+                           os.path.join(ROOT, "tests", "cxx", "dropin_driver.cpp"), "-L" + lib, "-lse_b200_dropin",
+                           "-lse_b200", "-Wl,-rpath," + lib, "-o", exe])
+    return exe
+
+
+def test_cxx_adapters_compile_and_link(tmp_path):
+    """subbband / resynth / addnoise with the reference's C++ signatures (CWave*, FILESNAME, vector<vector<float>>&)
+    compile against a stand-in wave class and resolve against libse_b200_dropin.so."""
+    exe = build_cxx_driver(tmp_path)
+    assert os.path.exists(exe)

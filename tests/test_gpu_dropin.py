@@ -229,3 +229,33 @@ def test_buffer_denoise_windows_as_one_batch(dropin, oracle, n, bl):
     keep[n - 320 - stale:n - 320] = False
     assert np.array_equal(des2[keep], des[keep])
     assert dropin.se_buffer_denoise(x.ctypes.data, des2.ctypes.data, 100, bl) != 0      # < 320 samples: rejected
+
+
+@pytest.mark.parametrize("mode", [0, 2])
+def test_cxx_signatures_drive_the_gpu(ctx, tmp_path, mode):
+    """include/se_reference_api.hpp: subbband(CWave*, path, tail, id), resynth(CWave*, FILESNAME, vector<vector<float>>&, id)
+    and addnoise(CWave*, CWave*, CWave*, id, FILESNAME) compiled into a C++ driver; the files it writes (the reference's
+    names: <id><tail>_<chan>.wav, <id>_e_resynth.wav, <id>_noisy.wav) hold exactly what the batch API returns."""
+    import subprocess
+    from test_abi_host import build_cxx_driver
+    exe = build_cxx_driver(tmp_path)
+    n = 6000
+    x, clean, noise = synth.utterance(41, 16000, n, components=True)
+    nf = api.resynth_num_frames(n, mode)
+    mask = np.random.default_rng(3).random((nf, 64)).astype(np.float32)
+    for d in ("sub", "res", "mix"):
+        (tmp_path / d).mkdir()
+    x.tofile(tmp_path / "x.i16"); noise.tofile(tmp_path / "n.i16"); mask.tofile(tmp_path / "m.f32")
+    subprocess.check_call([exe, str(tmp_path / "x.i16"), str(tmp_path / "n.i16"), str(tmp_path / "m.f32"), str(nf), str(mode),
+                           str(tmp_path) + "/"])
+    sub = ctx.subband(x, [0, n], exact=True).reshape(64, n)
+    for chan in (0, 17, 63):
+        got = np.fromfile(tmp_path / "sub" / ("utt1_t_%d.wav" % chan), np.int16)
+        assert np.array_equal(got, sub[chan])
+    want = ctx.resynth(x, [0, n], mask, [0, nf], mode)
+    assert np.array_equal(np.fromfile(tmp_path / "res" / "utt1_e_resynth.wav", np.int16), want)
+    after = np.fromfile(tmp_path / "res" / "mask_after.f32", np.float32).reshape(nf, 64)
+    assert np.array_equal(after, np.where(mask > 0.5, np.float32(1.0), mask) if mode == 0 else mask)
+    an, ay = ctx.addnoise(x, noise, [0, n], 5)
+    assert np.array_equal(np.fromfile(tmp_path / "mix" / "utt1_noisy.wav", np.int16), ay)
+    assert np.array_equal(np.fromfile(tmp_path / "mix" / "noise_scaled.i16", np.int16), an)
