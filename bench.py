@@ -138,6 +138,8 @@ class Dist:
             import torch.distributed as dist
             self.dist = dist
             os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+            # stdout carries exactly one JSON line: NCCL's version banner / debug log goes to stderr
+            os.environ.setdefault("NCCL_DEBUG_FILE", "/dev/stderr")
             dist.init_process_group("nccl", device_id=torch.device("cuda", self.local))
 
     def barrier(self):

@@ -39,7 +39,9 @@ int  se_device_count(void);
 /* One context per GPU (reference analogue: one "thread instance" per worker,
  * function/.../aurora_etsi/NoiseSupExports.h:36).  Owns a stream, constant tables and scratch.
  * Threading: a context (and the streams created from it) is NOT thread-safe -- one host thread at a time
- * per context, like the plugin's thread instance; different contexts may be used concurrently. */
+ * per context, like the plugin's thread instance; different contexts may be used concurrently, and their calls
+ * overlap on the GPU (results reach pageable caller arrays through a pinned arena so that no call holds the driver
+ * while its kernel runs).  The reference-named adapters of se_reference_api.h use one context per calling thread. */
 int  se_ctx_create(int device, se_ctx **out);
 void se_ctx_destroy(se_ctx *ctx);
 /* Launch on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL restores the own stream. */

@@ -64,8 +64,7 @@ static int stage_out(se_ctx *ctx, int slot, void *p, uint64_t bytes, int mem, bo
 static int stage_out_copy(se_ctx *ctx, void *host, const void *dev, uint64_t bytes, int mem)
 {
     if (!host || mem == SE_MEM_DEVICE || bytes == 0) return SE_OK;
-    SE_CUDA(cudaMemcpyAsync(host, dev, bytes, cudaMemcpyDeviceToHost, ctx->cur->stream));
-    return SE_OK;
+    return d2h_async(ctx, host, dev, bytes);
 }
 
 static int enter(se_ctx *ctx, int mem, const char *what)
@@ -78,7 +77,12 @@ static int enter(se_ctx *ctx, int mem, const char *what)
 
 static int leave(se_ctx *ctx, int mem)
 {
-    if (mem == SE_MEM_HOST) SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
+    if (mem == SE_MEM_HOST) {
+        const cudaError_t e = cudaStreamSynchronize(ctx->cur->stream);
+        if (e != cudaSuccess) { ctx->bounces.clear(); ctx->bounce_used = 0; }
+        SE_CUDA(e);
+        finish_host_copies(ctx);
+    }
     return SE_OK;
 }
 
@@ -202,13 +206,17 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
                 if (!o.host) continue;
                 const uint64_t cnt = (uint64_t)(hi[o.index] - lo[o.index]);
                 if (cnt == 0) continue;
-                if (o.planes5) {
+                if (o.planes5 && n_chunks > 1) {
                     const uint64_t T = (uint64_t)idx[o.index][n_utts];
                     SE_CUDA(cudaMemcpy2DAsync((char *)o.host + o.elem * (uint64_t)lo[o.index], o.elem * T, d_out[k],
                                               o.elem * cnt, o.elem * cnt, 5, cudaMemcpyDeviceToHost, ctx->cur->stream));
-                } else {
+                } else if (o.planes5) {      // one chunk: the 5 planes are contiguous on both sides
+                    SE_TRY(d2h_async(ctx, o.host, d_out[k], o.elem * cnt * 5));
+                } else if (n_chunks > 1) {   // pipelined big batches: straight to the caller's (pinned) array
                     SE_CUDA(cudaMemcpyAsync((char *)o.host + o.elem * (uint64_t)lo[o.index], d_out[k], o.elem * cnt,
                                             cudaMemcpyDeviceToHost, ctx->cur->stream));
+                } else {
+                    SE_TRY(d2h_async(ctx, (char *)o.host + o.elem * (uint64_t)lo[o.index], d_out[k], o.elem * cnt));
                 }
             }
             mark(c, "d2h");
@@ -225,11 +233,12 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
     }
     if (rc) {
         cudaStreamSynchronize(lane0->stream);
+        ctx->bounces.clear();
+        ctx->bounce_used = 0;
         for (auto &t : trace) cudaEventDestroy(t.e);
         return rc;
     }
-    if (counts && mem == SE_MEM_HOST)
-        SE_CUDA(cudaMemcpyAsync(counts, d_counts, sizeof(int32_t) * (size_t)n_utts, cudaMemcpyDeviceToHost, lane0->stream));
+    if (counts && mem == SE_MEM_HOST) SE_TRY(d2h_async(ctx, counts, d_counts, sizeof(int32_t) * (size_t)n_utts));
     const int rc_leave = leave(ctx, mem);
     if (tracing && !trace.empty()) {
         std::fprintf(stderr, "[se_b200 trace] %d chunks\n", n_chunks);

@@ -131,22 +131,23 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
         SE_TRY(launch_ns_p16(ctx, a));
     }
     s->fresh = 0;
-    if (out) SE_CUDA(cudaMemcpyAsync(out, s->d_out, sizeof(float) * (size_t)n, cudaMemcpyDeviceToHost, ctx->cur->stream));
-    if (produced)
-        SE_CUDA(cudaMemcpyAsync(produced, s->d_produced, sizeof(int32_t) * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
+    SE_TRY(d2h_async(ctx, out, s->d_out, sizeof(float) * (size_t)n));
+    SE_TRY(d2h_async(ctx, produced, s->d_produced, sizeof(int32_t) * (size_t)n_blocks));
     if (s->profile == 8 && ceps) {
-        SE_CUDA(cudaMemcpyAsync(ceps, s->d_ceps, sizeof(float) * 14 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
-        if (n_ceps) SE_CUDA(cudaMemcpyAsync(n_ceps, s->d_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->cur->stream));
+        SE_TRY(d2h_async(ctx, ceps, s->d_ceps, sizeof(float) * 14 * (size_t)n_blocks));
+        SE_TRY(d2h_async(ctx, n_ceps, s->d_rows, sizeof(int32_t)));
     }
     if (s->profile == 16) {
-        if (flags)
-            SE_CUDA(cudaMemcpyAsync(flags, s->d_flags, sizeof(int32_t) * 5 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
-        if (gains)
-            SE_CUDA(cudaMemcpyAsync(gains, s->d_gains, sizeof(float) * 25 * (size_t)n_blocks, cudaMemcpyDeviceToHost, ctx->cur->stream));
-        if (n_rows)
-            SE_CUDA(cudaMemcpyAsync(n_rows, s->d_rows, sizeof(int32_t), cudaMemcpyDeviceToHost, ctx->cur->stream));
+        SE_TRY(d2h_async(ctx, flags, s->d_flags, sizeof(int32_t) * 5 * (size_t)n_blocks));
+        SE_TRY(d2h_async(ctx, gains, s->d_gains, sizeof(float) * 25 * (size_t)n_blocks));
+        SE_TRY(d2h_async(ctx, n_rows, s->d_rows, sizeof(int32_t)));
     }
-    SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
+    {
+        const cudaError_t e = cudaStreamSynchronize(ctx->cur->stream);
+        if (e != cudaSuccess) { ctx->bounces.clear(); ctx->bounce_used = 0; }
+        SE_CUDA(e);
+        finish_host_copies(ctx);
+    }
     return SE_OK;
 }
 

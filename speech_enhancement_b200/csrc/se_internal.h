@@ -145,6 +145,12 @@ struct se_ctx {
     // scratch
     void *d_scratch;
     uint64_t scratch_bytes, scratch_limit;
+    // D2H copies into PAGEABLE caller memory go through this pinned arena and reach their destination after the
+    // stream synchronisation that ends the call (se::d2h_async / se::finish_host_copies)
+    void *bounce;
+    uint64_t bounce_cap, bounce_used;
+    struct Bounce { void *dst; const void *src; uint64_t bytes; };
+    std::vector<Bounce> bounces;
     // profiling
     int profiling;
     struct Ev { cudaEvent_t a, b; int k; };
@@ -159,6 +165,8 @@ namespace se {
 // host helpers (se_api.cu)
 int ensure_stage(se_ctx *ctx, int slot, uint64_t bytes, void **out);
 int ensure_scratch(se_ctx *ctx, uint64_t bytes);
+int d2h_async(se_ctx *ctx, void *host, const void *dev, uint64_t bytes);
+void finish_host_copies(se_ctx *ctx);
 void prof_begin(se_ctx *ctx, int k);
 void prof_end(se_ctx *ctx, int k);
 

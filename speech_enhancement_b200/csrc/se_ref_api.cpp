@@ -16,22 +16,30 @@
 namespace {
 
 std::mutex g_mu;
-se_ctx *g_ctx = nullptr;
+std::vector<se_ctx *> g_ctxs;                 // every context ever handed out (kept until the process ends)
+thread_local se_ctx *t_ctx = nullptr;
 
-// One process-wide context (the reference's entry points carry no handle).  Fails loudly without a GPU.
+// The reference's entry points carry no handle, and its batch tool calls them from N worker threads at once
+// (aurora_speech_enhancement.cpp:110-120, 312-328).  A se_ctx serves one host thread at a time, so every calling
+// thread gets its own (own stream, own staging buffers): calls from different threads run concurrently on the GPU.
+// Contexts are not torn down at thread exit -- handles created from them (FEParamsX, plugin thread instances) may
+// outlive the thread.  Fails loudly without a GPU.
 se_ctx *default_ctx(const char *who)
 {
-    std::lock_guard<std::mutex> lk(g_mu);
-    if (!g_ctx) {
+    if (!t_ctx) {
         int dev = 0;
         if (const char *e = std::getenv("SE_B200_DEVICE")) dev = std::atoi(e);
-        int rc = se_ctx_create(dev, &g_ctx);
+        se_ctx *c = nullptr;
+        int rc = se_ctx_create(dev, &c);
         if (rc != SE_OK) {
             std::fprintf(stderr, "%s: libse_b200 cannot run (%d): %s\n", who, rc, se_last_error());
-            g_ctx = nullptr;
+            return nullptr;
         }
+        std::lock_guard<std::mutex> lk(g_mu);
+        g_ctxs.push_back(c);
+        t_ctx = c;
     }
-    return g_ctx;
+    return t_ctx;
 }
 
 int report(const char *who, int rc)
@@ -54,7 +62,8 @@ SE_EXPORT int etsi_denoise(short *p_data, short *p_denoised, long i_frame)
     const int64_t off[2] = {0, body};
     int rc = se_etsi_denoise_batch(ctx, p_data, off, 1, p_denoised, nullptr, nullptr, nullptr, nullptr, nullptr,
                                    nullptr, SE_MEM_HOST);
-    return report("etsi_denoise", rc) == SE_OK ? 0 : 1;
+    if (report("etsi_denoise", rc) != SE_OK) return 1;
+    return 0;
 }
 
 SE_EXPORT int etsi_denoise_synchronization(short *p_data, short *p_denoised, long i_frame)
