@@ -556,7 +556,7 @@ def run_reference(args):
             "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
                              "sample": "first %d utterances of the workload per step, %d steps" % (n, args.steps)},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
-    print(json.dumps(line), flush=True)
+    emit(line)
 
 
 def run_ours(args):
@@ -590,7 +590,7 @@ def run_ours(args):
         with torch.cuda.stream(stream):
             fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm, "subband": lambda *a: bench_subband(*a, n_utts=int(os.environ.get("SE_SUB_UTTS", "1000")), seconds=float(os.environ.get("SE_SUB_SEC", "5"))),
                   "p8feat": lambda *a: bench_p8(*a, features=True), "etsi16k": bench_etsi16k}[args.profile_only]
-            print(json.dumps(fn(args, torch, api, ctx, dist, stream, first_u + 500000)), flush=True)
+            emit(fn(args, torch, api, ctx, dist, stream, first_u + 500000))
         ctx.close()
         dist.close()
         return
@@ -632,12 +632,26 @@ def run_ours(args):
     if extra:
         line["other_workloads"] = extra
     if rank == 0:
-        print(json.dumps(line), flush=True)
+        emit(line)
     ctx.close()
     dist.close()
 
 
+_JSON_OUT = None
+
+
+def emit(obj):
+    """The one JSON line goes to the process's real stdout; everything else printed to fd 1 by libraries (NCCL's
+    version banner ignores NCCL_DEBUG_FILE) was redirected to stderr in __main__."""
+    out = _JSON_OUT or sys.stdout
+    out.write(json.dumps(obj) + "\n")
+    out.flush()
+
+
 if __name__ == "__main__":
+    sys.stdout.flush()
+    _JSON_OUT = os.fdopen(os.dup(1), "w")
+    os.dup2(2, 1)
     a = parse()
     if a.impl == "reference":
         run_reference(a)
