@@ -104,7 +104,8 @@ void etsi_denoise_mapping_global_release(PINSTANCE sm_glb_pins);
 int se_subband(const short *wav, long n, short *out64xn);
 /* resynth(): mode 0 = resyth_64sub_IBM, 1 = resyth_64sub_ori, 2 = 1dnn_resynth.  mask is
  * [num_frame][64]; in IBM mode entries > 0.5 are overwritten with 1.0 like the reference does
- * (resyth_64sub_IBM/cpp/extractwav.cpp:99).                                                      */
+ * (resyth_64sub_IBM/cpp/extractwav.cpp:99).  Bit-exact kernels by default; with SE_B200_FAST=1 in the
+ * environment the time-chunked default-mode kernels run instead (within 1 LSB, far lower latency).  */
 int se_resynth(const short *wav, long n, float *mask, int num_frame, int mode, short *out);
 /* make_single_IBM arithmetic fused with the two subbband() calls feeding it.                     */
 int se_single_ibm(const short *pure, const short *noise, long n, float *irm /*[frames][64]*/,

@@ -313,3 +313,28 @@ def test_concurrent_callers_get_their_own_context(dropin, oracle):
         assert rs(i) == 0 and np.array_equal(outs[i], par[i])
     print("8 x 10 s utterances: sequential %.1f ms, 8 threads %.1f ms" % (t_seq * 1e3, t_par * 1e3))
     assert t_par < 0.6 * t_seq
+
+
+def test_resynth_adapter_fast_mode_env(dropin, tmp_path):
+    """SE_B200_FAST=1 (read once per process) switches se_resynth to the time-chunked default-mode kernels: within
+    1 LSB of the bit-exact adapter output."""
+    import os
+    import subprocess
+    import sys
+    n = 64000
+    x = synth.utterance(81, 16000, n)
+    nf = api.resynth_num_frames(n, 1)
+    mask = np.random.default_rng(8).random((nf, 64)).astype(np.float32)
+    exact = np.zeros(n, np.int16)
+    assert dropin.se_resynth(x.ctypes.data, n, mask.copy().ctypes.data, nf, 1, exact.ctypes.data) == 0
+    x.tofile(tmp_path / "x.i16"); mask.tofile(tmp_path / "m.f32")
+    code = ("import ctypes as C, numpy as np, sys\n"
+            "D = C.CDLL(sys.argv[1]); D.se_resynth.argtypes = [C.c_void_p, C.c_long, C.c_void_p, C.c_int, C.c_int, C.c_void_p]\n"
+            "x = np.fromfile(sys.argv[2] + '/x.i16', np.int16); m = np.fromfile(sys.argv[2] + '/m.f32', np.float32)\n"
+            "o = np.zeros(len(x), np.int16)\n"
+            "assert D.se_resynth(x.ctypes.data, len(x), m.ctypes.data, len(m) // 64, 1, o.ctypes.data) == 0\n"
+            "o.tofile(sys.argv[2] + '/o.i16')\n")
+    subprocess.check_call([sys.executable, "-c", code, api.DROPIN_PATH, str(tmp_path)], env=dict(os.environ, SE_B200_FAST="1"))
+    fast = np.fromfile(tmp_path / "o.i16", np.int16)
+    d = np.abs(fast.astype(np.int32) - exact.astype(np.int32))
+    assert d.max() <= 1
