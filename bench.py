@@ -44,7 +44,7 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
     ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
-    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "etsi16k", "resynth", "ibm", "subband"],
+    ap.add_argument("--profile-only", default="", choices=["", "p8", "p8feat", "etsi16k", "resynth", "ibm", "subband", "wiener"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
 
@@ -440,6 +440,42 @@ def bench_subband(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, sec
             "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
+def bench_extract_wiener(args, torch, api, ctx, dist, stream, first_u, n_utts=2368, seconds=5.0):
+    """extract_Wiener, the literal enhancement_extract_subband flow behind configs[1]: subbband() -> 64 channel signals
+    -> func_Wiener over all 64 with one carried state (aurora_etsi_test.cpp:16-141), device-resident.  One utterance =
+    one 64 x 5 s stream on one warp, so 2368 = 148 SMs x 16 warps utterances make exactly one wave."""
+    samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=seconds)
+    total = int(offsets[-1])
+    bo = np.zeros(n_utts + 1, np.int64)
+    bo[1:] = np.cumsum(64 * (np.diff(offsets) // 160))
+    d_in = dev(torch, samples)
+    d_gains = torch.empty(int(bo[-1]) * 25, dtype=torch.float32, device="cuda")
+    d_flags = torch.empty(int(bo[-1]) * 5, dtype=torch.int32, device="cuda")
+    d_rows = torch.empty(n_utts, dtype=torch.int32, device="cuda")
+
+    def step():
+        api._check(ctx.L.se_extract_wiener_batch(ctx.h, d_in.data_ptr(), offsets.ctypes.data, n_utts, d_gains.data_ptr(),
+                                                 d_flags.data_ptr(), d_rows.data_ptr(), bo.ctypes.data, api.SE_MEM_DEVICE),
+                   "se_extract_wiener_batch")
+
+    step()
+    ctx.sync()
+    ctx.reset_kernel_times()
+    ctx.profiling(True)
+    steps = min(args.steps, 2)
+    ms = timed_steps(torch, dist, stream, step, 0, steps)
+    ks_ms, ks_n = ctx.kernel_time(api.K_SUBBAND)
+    kn_ms, kn_n = ctx.kernel_time(api.K_NS_P16)
+    ctx.profiling(False)
+    hbm, _ = peaks()
+    # compulsory bytes: int16 in, 25 gains + 5 flags per 160-sample block of each of the 64 channels out
+    gbs = (2 * total + 120 * int(bo[-1])) / (ms / steps * 1e-3) / 1e9
+    return {"workload": "extract_Wiener chain (subbband -> 64 x func_Wiener, carried state), %d x %.0f s 16 kHz" % (n_utts, seconds),
+            "xrt": total / 16000.0 * steps / (ms * 1e-3), "ms_per_step": ms / steps,
+            "kernel_ms": {"subband": ks_ms / max(ks_n, 1), "ns_p16": kn_ms / max(kn_n, 1)},
+            "sub_band_audio_xrt": 64 * total / 16000.0 * steps / (ms * 1e-3), "achieved_gbs": gbs, "frac": gbs / hbm}
+
+
 def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
     """G64: resyth_64sub_IBM on 10 s 16 kHz utterances (BASELINE configs[2] shape)."""
     samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
@@ -589,7 +625,7 @@ def run_ours(args):
     if args.profile_only:
         with torch.cuda.stream(stream):
             fn = {"p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm, "subband": lambda *a: bench_subband(*a, n_utts=int(os.environ.get("SE_SUB_UTTS", "1000")), seconds=float(os.environ.get("SE_SUB_SEC", "5"))),
-                  "p8feat": lambda *a: bench_p8(*a, features=True), "etsi16k": bench_etsi16k}[args.profile_only]
+                  "p8feat": lambda *a: bench_p8(*a, features=True), "etsi16k": bench_etsi16k, "wiener": bench_extract_wiener}[args.profile_only]
             emit(fn(args, torch, api, ctx, dist, stream, first_u + 500000))
         ctx.close()
         dist.close()
@@ -603,7 +639,8 @@ def run_ours(args):
                      bench_etsi16k(args, torch, api, ctx, dist, stream, first_u + 600000),
                      bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000),
                      bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000),
-                     bench_subband(args, torch, api, ctx, dist, stream, first_u + 900000)]
+                     bench_subband(args, torch, api, ctx, dist, stream, first_u + 900000),
+                     bench_extract_wiener(args, torch, api, ctx, dist, stream, first_u + 950000)]
     audio_all = dist.sum(r["audio_s"])
     value = audio_all * args.steps / (r["ms"] * 1e-3)
     e2e = audio_all * args.steps / (r["e2e_ms"] * 1e-3)

@@ -201,6 +201,21 @@ int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
 int64_t se_ibm_num_frames(int64_t n_samples);
 int se_ibm_batch(se_ctx *ctx, const int16_t *pure, const int16_t *noise, const int64_t *offsets, int n_utts,
                  float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem);
+
+/* extract_Wiener (function/20141106_speech_enhancement/aurora_etsi_test/aurora_etsi_test.cpp:16-141) for a batch of
+ * noisy utterances, device-resident from end to end: subbband() -> the 64 hair-cell channel signals of each utterance
+ * (what the driver reads back as <id>_noisy_<chan>.wav), each cut to a multiple of 160 samples (:100-101), all 64 run
+ * through etsi_denoise_mapping_func_Wiener on ONE thread instance without re-init (:21-22, 90-141) -- the NoiseSup state
+ * carries over from channel to channel, so an utterance is one 64 * (len - len % 160)-sample stream for one warp.
+ * The 64 x L sub-band signals never leave the GPU and outData is not produced (the driver frees it unused, :133).
+ * gains : float[block_offsets[u] + row][25], the rows of the 64 ".wiener" files of utterance u back to back (file c
+ *         holds the rows whose stage-2 frame falls into channel c; n_rows[u] rows in total; the rest stay 0).
+ * flags : int32[5][block_offsets[n_utts]] as se_p16_wiener_batch, block b of channel c at block_offsets[u] + c*(len/160) + b.
+ * block_offsets : host int64[n_utts+1], EXACTLY the running sum of se_extract_wiener_num_blocks(len) = 64 * (len/160).
+ * Intermediates (130 B per sample) live in the context scratch; batches beyond se_ctx_set_scratch_limit run in groups. */
+int64_t se_extract_wiener_num_blocks(int64_t n_samples);
+int se_extract_wiener_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                            float *gains, int32_t *flags, int32_t *n_rows, const int64_t *block_offsets, int mem);
 /* resynth (resyth_64sub_IBM/cpp/extractwav.cpp:9-132 and its _ori / 1dnn variants).
  * mask: float[frame_offsets[u]+f][64]; frames_u = se_resynth_num_frames(len_u, mode). */
 #define SE_RESYNTH_IBM   0

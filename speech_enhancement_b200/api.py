@@ -48,6 +48,7 @@ def lib():
         L.se_ctx_profiling.argtypes = [_vp, C.c_int]
         L.se_ctx_set_pipeline.argtypes = [_vp, C.c_uint64, C.c_int]
         L.se_ctx_set_feature_flush.argtypes = [_vp, C.c_int]
+        L.se_extract_wiener_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
         L.se_ctx_kernel_time.argtypes = [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
         L.se_ctx_reset_kernel_times.argtypes = [_vp]
         L.se_ctx_launch_count.restype = C.c_int64
@@ -361,6 +362,21 @@ class Context:
         bits = np.zeros(nf, np.uint64)
         self.ibm_raw(pure, noise, offsets, nu, irm, bits, fo)
         return irm[:int(fo[-1])], bits[:int(fo[-1])], fo
+
+    def extract_wiener(self, samples, offsets):
+        """extract_Wiener over a batch: per-utterance (gains[64*(len//160)][25], flags[5][64*(len//160)], n_rows)."""
+        samples = np.ascontiguousarray(samples, np.int16)
+        offsets = _i64(offsets)
+        nu = len(offsets) - 1
+        bo = np.zeros(nu + 1, np.int64)
+        bo[1:] = np.cumsum(64 * (np.diff(offsets) // 160))
+        tb = max(int(bo[-1]), 1)
+        gains = np.zeros((tb, 25), np.float32)
+        flags = np.zeros((5, tb), np.int32)
+        rows = np.zeros(max(nu, 1), np.int32)
+        _check(self.L.se_extract_wiener_batch(self.h, _ptr(samples), _ptr(offsets), nu, _ptr(gains), _ptr(flags),
+                                              _ptr(rows), _ptr(bo), SE_MEM_HOST), "se_extract_wiener_batch")
+        return [(gains[bo[u]:bo[u + 1]], flags[:, bo[u]:bo[u + 1]], int(rows[u])) for u in range(nu)]
 
     def resynth(self, samples, offsets, mask, frame_offsets, mode, exact=True):
         samples = np.ascontiguousarray(samples, np.int16)

@@ -296,4 +296,105 @@ int se_get_table(se_ctx *ctx, const char *name, float *out, int capacity, int *c
     return SE_OK;
 }
 
+
+}  // extern "C"
+
+// ---- extract_Wiener as one device-resident chain --------------------------------------------------------------
+namespace se {
+// dst[d_off[u] + i] = src[s_off[u] + i] for i < d_off[u+1] - d_off[u]: drops each utterance's len % 160 tail
+__global__ void __launch_bounds__(256) compact_kernel(const int16_t *src, const int64_t *s_off, const int64_t *d_off, int16_t *dst)
+{
+    const int u = blockIdx.x;
+    const int64_t n = d_off[u + 1] - d_off[u];
+    const int16_t *s = src + s_off[u];
+    int16_t *d = dst + d_off[u];
+    for (int64_t i = (int64_t)blockIdx.y * blockDim.x + threadIdx.x; i < n; i += (int64_t)gridDim.y * blockDim.x) d[i] = s[i];
+}
+}  // namespace se
+
+extern "C" {
+
+int64_t se_extract_wiener_num_blocks(int64_t n_samples) { return n_samples > 0 ? 64 * (n_samples / 160) : 0; }
+
+int se_extract_wiener_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
+                            float *gains, int32_t *flags, int32_t *n_rows, const int64_t *block_offsets, int mem)
+{
+    SE_TRY(enter(ctx, mem, "se_extract_wiener_batch"));
+    if (n_utts < 0 || (n_utts > 0 && (!samples || !block_offsets || (!gains && !flags)))) {
+        set_error("se_extract_wiener_batch: bad arguments");
+        return SE_EINVAL;
+    }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_extract_wiener_batch"));
+    if (offsets[0] != 0 || block_offsets[0] != 0) { set_error("se_extract_wiener_batch: offsets[0] / block_offsets[0] must be 0"); return SE_EINVAL; }
+    for (int u = 0; u < n_utts; u++)
+        if (block_offsets[u + 1] - block_offsets[u] != se_extract_wiener_num_blocks(offsets[u + 1] - offsets[u])) {
+            set_error("se_extract_wiener_batch: block_offsets[%d+1] - block_offsets[%d] must be 64 * (len / 160)", u, u);
+            return SE_EINVAL;
+        }
+    const int64_t T = block_offsets[n_utts];        // rows of the whole batch: the pitch of the caller's flags planes
+    // per truncated sample: 2 B compact + 128 B sub-band rows + (100 B gains + 20 B flags) * 64 / 160
+    const uint64_t kPerSample = 2 + 128 + 48 + 1;
+    int u0 = 0;
+    while (u0 < n_utts) {
+        // group of utterances whose intermediates fit the scratch limit (at least one utterance)
+        int u1 = u0;
+        uint64_t tot = 0;
+        while (u1 < n_utts) {
+            const uint64_t l = (uint64_t)((offsets[u1 + 1] - offsets[u1]) / 160 * 160);
+            if (u1 > u0 && (tot + l) * kPerSample + 4096 > ctx->scratch_limit) break;
+            tot += l;
+            u1++;
+        }
+        const int cnt = u1 - u0;
+        std::vector<int64_t> s_off(cnt + 1), t_off(cnt + 1), w_off(cnt + 1), b_off(cnt + 1);
+        t_off[0] = 0;
+        for (int k = 0; k <= cnt; k++) s_off[k] = offsets[u0 + k] - offsets[u0];
+        for (int k = 0; k < cnt; k++) t_off[k + 1] = t_off[k] + (offsets[u0 + k + 1] - offsets[u0 + k]) / 160 * 160;
+        for (int k = 0; k <= cnt; k++) { w_off[k] = 64 * t_off[k]; b_off[k] = w_off[k] / 160; }
+        const uint64_t ts = (uint64_t)t_off[cnt], B = (uint64_t)b_off[cnt];
+        if (ts > 0) {
+            auto up256 = [](uint64_t x) { return (x + 255) & ~255ull; };
+            const uint64_t o_rows = up256(2 * ts), o_gains = o_rows + up256(128 * ts), o_flags = o_gains + up256(100 * B),
+                           o_cnt = o_flags + up256(20 * B), need = o_cnt + up256(4 * (uint64_t)cnt);
+            SE_TRY(ensure_scratch(ctx, need));
+            char *sc = (char *)ctx->d_scratch;
+            int16_t *d_compact = (int16_t *)sc, *d_rows = (int16_t *)(sc + o_rows);
+            float *d_gains = (float *)(sc + o_gains);
+            int32_t *d_flags = (int32_t *)(sc + o_flags), *d_cnt = (int32_t *)(sc + o_cnt);
+            const void *d_in = nullptr;
+            SE_TRY(stage_in(ctx, kSlotIn, samples + offsets[u0], sizeof(int16_t) * (uint64_t)(offsets[u1] - offsets[u0]), mem, &d_in));
+            const int64_t *d_soff = nullptr, *d_toff = nullptr;
+            SE_TRY(upload_offsets(ctx, 13, s_off.data(), cnt + 1, &d_soff));
+            SE_TRY(upload_offsets(ctx, 14, t_off.data(), cnt + 1, &d_toff));
+            se::compact_kernel<<<dim3((unsigned)cnt, 8), 256, 0, ctx->cur->stream>>>((const int16_t *)d_in, d_soff, d_toff, d_compact);
+            SE_CUDA(cudaGetLastError());
+            ctx->launches++;
+            // subbband() of every utterance: 64 hair-cell rows of len - len % 160 samples, back to back = the 64
+            // channel files extract_Wiener walks (aurora_etsi_test.cpp:90-107, tail wiped at :100-101)
+            SE_TRY(se_subband_batch(ctx, d_compact, t_off.data(), cnt, d_rows, SE_FLAG_EXACT, SE_MEM_DEVICE));
+            // ... through func_Wiener on ONE thread instance without re-init (:21-22): state carries over from channel to
+            // channel, i.e. the 64 rows are one stream of 64 * len samples
+            SE_CUDA(cudaMemsetAsync(d_gains, 0, 100 * B, ctx->cur->stream));
+            SE_CUDA(cudaMemsetAsync(d_flags, 0, 20 * B, ctx->cur->stream));
+            SE_TRY(se_p16_wiener_batch(ctx, d_rows, 0, w_off.data(), cnt, nullptr, d_flags, d_gains, d_cnt, b_off.data(), SE_MEM_DEVICE));
+            const int64_t r0 = block_offsets[u0];
+            const cudaMemcpyKind kind = mem == SE_MEM_HOST ? cudaMemcpyDeviceToHost : cudaMemcpyDeviceToDevice;
+            if (gains && mem == SE_MEM_HOST) SE_TRY(d2h_async(ctx, gains + 25 * r0, d_gains, 100 * B));
+            else if (gains) SE_CUDA(cudaMemcpyAsync(gains + 25 * r0, d_gains, 100 * B, kind, ctx->cur->stream));
+            if (flags) SE_CUDA(cudaMemcpy2DAsync(flags + r0, sizeof(int32_t) * (size_t)T, d_flags, sizeof(int32_t) * B, sizeof(int32_t) * B, 5, kind, ctx->cur->stream));
+            if (n_rows) SE_CUDA(cudaMemcpyAsync(n_rows + u0, d_cnt, sizeof(int32_t) * (size_t)cnt, kind, ctx->cur->stream));
+            if (u1 < n_utts) {                                                    // the next group reuses the scratch
+                SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
+                finish_host_copies(ctx);
+            }
+        } else if (n_rows) {
+            if (mem == SE_MEM_HOST) std::memset(n_rows + u0, 0, sizeof(int32_t) * (size_t)cnt);
+            else SE_CUDA(cudaMemsetAsync(n_rows + u0, 0, sizeof(int32_t) * (size_t)cnt, ctx->cur->stream));
+        }
+        u0 = u1;
+    }
+    return leave(ctx, mem);
+}
+
 }  // extern "C"

@@ -55,3 +55,52 @@ def test_mix_mask_resynth_chain_device_resident(ctx, oracle):
             continue          # 0/0 frames (digital silence in both signals) make the mask undefined in the reference too
         ref_out, _ = oracle.resynth(mix, m.copy(), api.RESYNTH_IBM)
         assert np.array_equal(out[lo:hi], ref_out), u
+
+
+def test_extract_wiener_chain(ctx, oracle):
+    """extract_Wiener (aurora_etsi_test.cpp:16-141) as one device-resident chain: subbband() -> 64 channel signals, each
+    cut to a multiple of 160 samples, all 64 through func_Wiener on ONE thread instance (state carries over from channel
+    to channel).  Against the oracle driven exactly that way: FrameCounter and row counts exact, flags equal except
+    ties, 25-band gains rel 1e-4.  Includes a scratch limit that forces the batch into several groups."""
+    from conftest import rel_err
+    lens = [160 * 12 + 77, 160 * 7, 100, 160 * 20 + 159, 0, 160 * 9 + 1]
+    xs = [synth.utterance(500 + i, 16000, n) for i, n in enumerate(lens)]
+    offsets = np.concatenate([[0], np.cumsum(lens)]).astype(np.int64)
+    samples = np.concatenate(xs)
+    got = ctx.extract_wiener(samples, offsets)
+    ctx.set_scratch_limit(1 << 20)                          # ~8 000 samples per group: one or two utterances each
+    try:
+        grouped = ctx.extract_wiener(samples, offsets)
+    finally:
+        ctx.set_scratch_limit(48 << 30)
+    mism = blocks = 0
+    for u, x in enumerate(xs):
+        n = len(x) - len(x) % 160
+        nb = n // 160
+        g, fl, rows = got[u]
+        assert g.shape == (64 * nb, 25) and fl.shape == (5, 64 * nb)
+        assert np.array_equal(g, grouped[u][0]) and np.array_equal(fl, grouped[u][1]) and rows == grouped[u][2]
+        if nb == 0:
+            assert rows == 0
+            continue
+        sub = oracle.subband(x[:n]).reshape(64, n)
+        s = oracle.p16_stream()
+        ref_rows = 0
+        r0 = 0
+        for chan in range(64):
+            ref = s.func_wiener(sub[chan].astype(np.float32))
+            k = len(ref["gains"])
+            if k:
+                e = rel_err(ref["gains"], g[r0:r0 + k], 1e-3)
+                assert e.max() <= 1e-4, (u, chan, e.max())
+            r0 += k
+            ref_rows += k
+            f = fl[:, chan * nb:(chan + 1) * nb]
+            assert np.array_equal(f[4], ref["frame_counter"]), (u, chan)
+            for i, key in enumerate(("sp_var", "sp_spec", "sp_mel", "sp_vadns")):
+                mism += int(np.sum(f[i] != ref[key]))
+            blocks += nb
+        s.close()
+        assert rows == ref_rows
+        assert not g[ref_rows:].any()
+    assert mism <= max(1, int(1e-3 * blocks * 4))
