@@ -6,6 +6,10 @@ in utterance chunks, host buffers in and out (pinned), corpus generated on the h
 previous chunk is NOT attempted: generation and GPU time are reported separately.  Prints one JSON line.
 
 Usage: python tools/c5_pipeline.py [hours=100] [chunk_utts=3000]
+   or: python -m torch.distributed.run --nnodes=1 --nproc-per-node N --master-addr 127.0.0.1 tools/c5_pipeline.py ...
+       (one rank per GPU, contiguous utterance shards, no collective on the data path; a gloo all_gather collects the
+       per-rank wall times and checksums at the end).  The checksum is a plain sum over per-utterance strided samples, so
+       it is the same number for any sharding / chunking iff every utterance's outputs are bit-identical.
 """
 import json
 import os
@@ -22,9 +26,13 @@ from speech_enhancement_b200 import api, synth          # noqa: E402
 
 HOURS = float(sys.argv[1]) if len(sys.argv) > 1 else 100.0
 CHUNK = int(sys.argv[2]) if len(sys.argv) > 2 else 3000
-N = int(round(HOURS * 3600 / 10.0))
-T = max(1, min(32, os.cpu_count() or 1))
-ctx = api.Context(0)
+N_ALL = int(round(HOURS * 3600 / 10.0))
+RANK, WORLD, LOCAL = (int(os.environ.get(k, d)) for k, d in (("RANK", "0"), ("WORLD_SIZE", "1"), ("LOCAL_RANK", "0")))
+U0, U1 = N_ALL * RANK // WORLD, N_ALL * (RANK + 1) // WORLD     # this rank's contiguous shard of the corpus
+N = U1 - U0
+T = max(1, min(32, (os.cpu_count() or 1) // WORLD))
+torch.cuda.set_device(LOCAL)
+ctx = api.Context(LOCAL)
 L = synth._load()
 gen_s = gpu_a = gpu_b = 0.0
 rows_a = frames_b = 0
@@ -43,8 +51,8 @@ def corpus16(first, count, n):
     return pure, noise
 
 
-for c0 in range(0, N, CHUNK):
-    cnt = min(CHUNK, N - c0)
+for c0 in range(U0, U1, CHUNK):
+    cnt = min(CHUNK, U1 - c0)
     # ---- (A) 8 kHz ETSI front end, host buffers through the C ABI
     t0 = time.perf_counter()
     s8, o8 = synth.corpus(200000 + c0, cnt, 8000, seconds=10.0, threads=T)
@@ -53,7 +61,7 @@ for c0 in range(0, N, CHUNK):
     r = ctx.etsi_denoise(s8, o8, ceps=True)
     gpu_a += time.perf_counter() - t0
     rows_a += int(r["n_ceps"].sum())
-    checksum ^= int(r["den_i16"][::997].astype(np.int64).sum()) & 0xffffffff
+    checksum = (checksum + int(r["den_i16"].reshape(cnt, 80000)[:, ::997].astype(np.int64).sum())) & 0xffffffff
     del s8, r
     # ---- (B) 16 kHz: mixture -> masks -> resynthesis, chained on the device
     n = 160000
@@ -82,17 +90,31 @@ for c0 in range(0, N, CHUNK):
     ctx.set_stream(None)
     gpu_b += time.perf_counter() - t0
     frames_b += cnt * nf
-    checksum ^= (int(out[::997].astype(np.int64).sum()) ^ int(bits[::101].sum())) & 0xffffffff
+    checksum = (checksum + int(out.reshape(cnt, n)[:, ::997].astype(np.int64).sum())
+                + int((bits.reshape(cnt, nf)[:, ::101] & 0xffff).sum())) & 0xffffffff
     del pure, noise, d_pure, d_noise, d_noisy, d_irm, d_bits, d_out, out, bits
     torch.cuda.empty_cache()
 
-audio_s = N * 10.0
-print(json.dumps({
-    "workload": "configs[4]: %.0f h synthetic corpus (%d x 10 s), 8 kHz ETSI NoiseSup+CompCeps and 16 kHz mix -> IBM/IRM -> "
-                "IBM-masked resynthesis, 1 B200, chunks of %d utterances" % (HOURS, N, CHUNK),
-    "etsi_wall_s": gpu_a, "etsi_xrt": audio_s / gpu_a, "cepstral_frames": rows_a,
-    "g64_wall_s": gpu_b, "g64_xrt": audio_s / gpu_b, "mask_frames": frames_b,
-    "both_halves_xrt": audio_s / (gpu_a + gpu_b), "host_corpus_generation_s": gen_s, "host_threads": T,
-    "checksum": checksum,
-    "note": "wall times include every H2D/D2H copy (host arrays in, host arrays out); corpus generation is host work "
-            "outside the measured path"}))
+if WORLD > 1:
+    import torch.distributed as dist
+    os.environ.setdefault("MASTER_ADDR", "127.0.0.1")
+    dist.init_process_group("gloo")
+    mine = torch.tensor([gpu_a, gpu_b, gen_s, float(rows_a), float(frames_b), float(checksum)], dtype=torch.float64)
+    allr = [torch.zeros_like(mine) for _ in range(WORLD)]
+    dist.all_gather(allr, mine)
+    dist.destroy_process_group()
+    allr = torch.stack(allr).numpy()
+    gpu_a, gpu_b, gen_s = float(allr[:, 0].max()), float(allr[:, 1].max()), float(allr[:, 2].max())
+    rows_a, frames_b = int(allr[:, 3].sum()), int(allr[:, 4].sum())
+    checksum = int(sum(int(v) for v in allr[:, 5])) & 0xffffffff
+if RANK == 0:
+    audio_s = N_ALL * 10.0
+    print(json.dumps({
+        "workload": "configs[4]: %.0f h synthetic corpus (%d x 10 s), 8 kHz ETSI NoiseSup+CompCeps and 16 kHz mix -> IBM/IRM -> "
+                    "IBM-masked resynthesis, %d B200, chunks of %d utterances" % (HOURS, N_ALL, WORLD, CHUNK),
+        "n_gpus": WORLD, "etsi_wall_s": gpu_a, "etsi_xrt": audio_s / gpu_a, "cepstral_frames": rows_a,
+        "g64_wall_s": gpu_b, "g64_xrt": audio_s / gpu_b, "mask_frames": frames_b,
+        "both_halves_xrt": audio_s / (gpu_a + gpu_b), "host_corpus_generation_s": gen_s, "host_threads_per_rank": T,
+        "checksum": checksum,
+        "note": "wall times (max over ranks) include every H2D/D2H copy (host arrays in, host arrays out); corpus "
+                "generation is host work outside the measured path; the checksum does not depend on the sharding"}))
