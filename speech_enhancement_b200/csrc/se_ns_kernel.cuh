@@ -41,7 +41,10 @@ template <typename T> __device__ __forceinline__ float to_f32(T v) { return (flo
 // FEAT (P8 only): a.ceps receives 15-column feature rows (WaveProc -> CompCeps -> PostProc -> VAD,
 // se_ns_feat.cuh) instead of 14-column raw cepstra; a.n_ceps counts released rows.
 template <int PROF, typename IN_T, int FEAT>
-__global__ void __launch_bounds__(NsWarps<FEAT>::value * 32, 2)
+#ifndef SE_NS_MINBLOCKS
+#define SE_NS_MINBLOCKS 2
+#endif
+__global__ void __launch_bounds__(NsWarps<FEAT>::value * 32, (FEAT ? 2 : SE_NS_MINBLOCKS))
 ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 {
     using P = Prof<PROF>;
