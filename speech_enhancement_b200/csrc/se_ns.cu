@@ -13,6 +13,12 @@
 // memory rings, filter banks / IDCT / windows are CTA-shared tables in shared memory.  HBM traffic is
 // exactly the algorithmic minimum: each input sample is read once, each output written once.
 #include <type_traits>
+// Per-lane loop-invariant constants (FFT twiddles, IDCT taps, mel / CompCeps triangle taps) live in shared memory
+// ([field][lane], conflict-free) and are reloaded at their use sites instead of holding ~25-45 registers through the
+// frame loop.  -DSE_NS_CONST_REGS restores the register version.
+#ifndef SE_NS_CONST_REGS
+#define SE_NS_CONST_SMEM 1
+#endif
 #include "se_internal.h"
 #include "se_warp_fft.cuh"
 
@@ -68,6 +74,11 @@ template <int PROF> struct __align__(16) BlockMem {
     float triT[P::CEPS ? kTriRows * 32 : 4];
     int tri_start[32], tri_len[32];
     float dctT[P::CEPS ? 23 * 16 : 4];
+#ifdef SE_NS_CONST_SMEM
+    float lane_tw[15 * 32];      // FftTw of every lane, [field][lane]
+    float lane_ic[10 * 32];      // IdctRegs of every lane
+    float lane_br[PROF == 8 ? 22 * 32 : 4];   // BankRegs taps of every lane: 10 mel + 12 CompCeps triangle taps
+#endif
 };
 
 // Scalar (warp-uniform) part of the stream state: the GPU image of VAD_DATA_NS, VAD_DATA_FD,

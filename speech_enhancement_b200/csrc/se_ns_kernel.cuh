@@ -10,7 +10,7 @@ namespace se {
 #endif
 // FEAT: 0 = NoiseSup (+ raw CompCeps), 1 = 8 kHz feature chain, 2 = 16 kHz feature chain (se_ns_hp16k.cuh)
 #ifndef SE_NS_WARPS_F1
-#define SE_NS_WARPS_F1 6
+#define SE_NS_WARPS_F1 8
 #endif
 #ifndef SE_NS_WARPS_F2
 #define SE_NS_WARPS_F2 6
@@ -77,6 +77,13 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     BankRegs br;
     if constexpr (PROF == 8) bank_regs_init(br, bm, lane);
     else { br.mel_st = br.tri_st = 0; }
+#ifdef SE_NS_CONST_SMEM
+    if (warp == 0) {
+        lane_consts_store(bm.lane_tw, bm.lane_ic, tw, ic, lane);
+        if constexpr (PROF == 8) bank_regs_store(bm.lane_br, br, lane);
+    }
+    __syncthreads();
+#endif
     for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;       // zero-weight taps may read past the spectrum
     const float eps = tb.eps;
     const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
@@ -521,6 +528,13 @@ __global__ void __launch_bounds__(128) comp_ceps_kernel(const float *frames, flo
     fft_tw_init(tw, lane);
     BankRegs br;
     bank_regs_init(br, bm, lane);
+#ifdef SE_NS_CONST_SMEM
+    {
+        IdctRegs ic0 = {};
+        if (warp == 0) { lane_consts_store(bm.lane_tw, bm.lane_ic, tw, ic0, lane); bank_regs_store(bm.lane_br, br, lane); }
+        __syncthreads();
+    }
+#endif
     for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;
     __syncwarp();
     for (int idx = blockIdx.x * 4 + warp; idx < count; idx += gridDim.x * 4) {

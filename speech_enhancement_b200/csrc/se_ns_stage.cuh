@@ -8,6 +8,36 @@
 
 namespace se {
 
+struct IdctRegs { float c[9]; float firwin; };
+
+#ifdef SE_NS_CONST_SMEM
+__device__ __forceinline__ void lane_consts_store(float *tw_tab, float *ic_tab, const FftTw &t, const IdctRegs &ic, int lane)
+{
+    const float v[15] = {t.q1.x, t.q1.y, t.q2.x, t.q2.y, t.q3.x, t.q3.y, t.s16.x, t.s16.y, t.s8.x, t.s8.y,
+                         t.s4.x, t.s4.y, t.s2.x, t.s2.y, __uint_as_float(t.sign)};
+#pragma unroll
+    for (int i = 0; i < 15; i++) tw_tab[i * 32 + lane] = v[i];
+#pragma unroll
+    for (int i = 0; i < 9; i++) ic_tab[i * 32 + lane] = ic.c[i];
+    ic_tab[9 * 32 + lane] = ic.firwin;
+}
+__device__ __forceinline__ FftTw lane_tw_load(const float *tab, int lane)
+{
+    FftTw t;
+    const float *p = tab + lane;
+    t.q1 = make_float2(p[0], p[32]);     t.q2 = make_float2(p[64], p[96]);    t.q3 = make_float2(p[128], p[160]);
+    t.s16 = make_float2(p[192], p[224]); t.s8 = make_float2(p[256], p[288]);  t.s4 = make_float2(p[320], p[352]);
+    t.s2 = make_float2(p[384], p[416]);  t.sign = __float_as_uint(p[448]);
+    return t;
+}
+#define SE_TW_LOCAL(bm, tw, lane) const FftTw tw##_l = lane_tw_load((bm).lane_tw, lane)
+#define SE_TW(tw) tw##_l
+#else
+#define SE_TW_LOCAL(bm, tw, lane)
+#define SE_TW(tw) tw
+#endif
+
+
 template <int RB> __device__ __forceinline__ int wrap(int pos)
 {
     if (pos >= RB) pos -= RB;
@@ -34,7 +64,10 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
                 v[j] = make_float2(x.x * w.x, x.y * w.y);
             }
         }
-        fft128_warp(v, tw, lane);
+        {
+            SE_TW_LOCAL(bm, tw, lane);
+            fft128_warp(v, SE_TW(tw), lane);
+        }
         fft128_store(v, wm.Z, lane);
         __syncwarp();
         // FFTtoPSD, etsi/cpp/NoiseSup.c:249-270: |X|^2 on 129 bins, pair-averaged to 65
@@ -70,8 +103,11 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
                 vw[j] = make_float2(x.y * w.y, x.w * w.w);
             }
         }
-        fft128_warp(va, tw, lane);
-        fft128_warp(vw, tw, lane);
+        {
+            SE_TW_LOCAL(bm, tw, lane);
+            fft128_warp(va, SE_TW(tw), lane);
+            fft128_warp(vw, SE_TW(tw), lane);
+        }
         fft128_store(va, wm.Z, lane);
         fft128_store(vw, wm.Z2, lane);
         __syncwarp();
@@ -135,7 +171,6 @@ template <int PROF> __device__ __forceinline__ void ring_store(float *ring, int 
 
 // Per-lane registers of the 25x9 IDCT (DoMelIDCT restricted to the 9 taps DoFilterWindowing keeps):
 // lane L = t + 9 g (t < 9 taps, g < 3 groups) owns bands f = 9 g + i, i < 9.
-struct IdctRegs { float c[9]; float firwin; };
 
 __device__ __forceinline__ void idct_regs_init(IdctRegs &ic, const float *idctT /*[25][16]*/, const float *firwin9, int lane)
 {
@@ -170,6 +205,20 @@ __device__ __forceinline__ void bank_regs_init(BankRegs &br, const BlockMem<8> &
 #pragma unroll
     for (int i = 0; i < kTriTaps; i++) br.tri[i] = (t0 + i < tl) ? bm.triT[(t0 + i) * 32 + band] : 0.0f;
 }
+#ifdef SE_NS_CONST_SMEM
+__device__ __forceinline__ void bank_regs_store(float *tab /*[22][32]*/, const BankRegs &br, int lane)
+{
+#pragma unroll
+    for (int i = 0; i < kMelTaps; i++) tab[i * 32 + lane] = br.mel[i];
+#pragma unroll
+    for (int i = 0; i < kTriTaps; i++) tab[(kMelTaps + i) * 32 + lane] = br.tri[i];
+}
+#define SE_BR_MEL(bm, br, i, lane) (bm).lane_br[(i) * 32 + (lane)]
+#define SE_BR_TRI(bm, br, i, lane) (bm).lane_br[(kMelTaps + (i)) * 32 + (lane)]
+#else
+#define SE_BR_MEL(bm, br, i, lane) (br).mel[i]
+#define SE_BR_TRI(bm, br, i, lane) (br).tri[i]
+#endif
 
 // One Wiener-filter stage (fstage is warp-uniform at run time: both stages share one copy of the code,
 // which halves the kernel's instruction footprint).
@@ -236,7 +285,7 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
     if constexpr (PROF == 8) {
         __syncwarp();
 #pragma unroll
-        for (int i = 0; i < kMelTaps; i++) mw = fmaf(wm.W[br.mel_st + i], br.mel[i], mw);
+        for (int i = 0; i < kMelTaps; i++) mw = fmaf(wm.W[br.mel_st + i], SE_BR_MEL(bm, br, i, lane), mw);
     } else {
         // dense 25 x 128: every lane multiplies its own 4 bins (registers) into 25 partial sums, then a
         // butterfly reduce-scatter leaves band j's total on lane j (31 shuffles instead of 25 x 5)
@@ -289,9 +338,15 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
         const int g9 = (lane / 9) * 9;
         float acc = 0.0f;
 #pragma unroll
+#ifdef SE_NS_CONST_SMEM
+        for (int i = 0; i < 9; i++) acc += __shfl_sync(0xffffffffu, mw, (g9 + i) & 31) * bm.lane_ic[i * 32 + lane];
+        acc += __shfl_down_sync(0xffffffffu, acc, 9) + __shfl_down_sync(0xffffffffu, acc, 18);
+        acc *= bm.lane_ic[9 * 32 + lane];
+#else
         for (int i = 0; i < 9; i++) acc += __shfl_sync(0xffffffffu, mw, (g9 + i) & 31) * ic.c[i];
         acc += __shfl_down_sync(0xffffffffu, acc, 9) + __shfl_down_sync(0xffffffffu, acc, 18);
         acc *= ic.firwin;
+#endif
 #pragma unroll
         for (int t = 0; t < 9; t++) h[t] = __shfl_sync(0xffffffffu, acc, t);
     }
@@ -395,7 +450,10 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
         }
     }
     e = warp_sum(e);
-    fft128_warp(v, tw, lane);
+    {
+        SE_TW_LOCAL(bm, tw, lane);
+        fft128_warp(v, SE_TW(tw), lane);
+    }
     fft128_store(v, wm.Z, lane);
     __syncwarp();
     // power spectrum (:451-459), 129 bins, into wm.W
@@ -421,7 +479,7 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
     // 23 mel triangles (DoMelFB, MelProc.c:82-104), ln with floor (:509-513)
     float fb = 0.0f;
 #pragma unroll
-    for (int i = 0; i < kTriTaps; i++) fb = fmaf(wm.W[br.tri_st + i], br.tri[i], fb);
+    for (int i = 0; i < kTriTaps; i++) fb = fmaf(wm.W[br.tri_st + i], SE_BR_TRI(bm, br, i, lane), fb);
     {
         const float hi = __shfl_down_sync(0xffffffffu, fb, 9);      // taps 12.. of bands 14..22 live on lanes 23..31
         if (lane >= 14 && lane < 23) fb += hi;

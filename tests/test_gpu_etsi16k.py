@@ -16,7 +16,9 @@ from speech_enhancement_b200 import synth
 pytestmark = pytest.mark.gpu
 
 CEPS_TOL = 1e-4
-OUTLIER_SHARE = 0.02
+FLIP_TOL = 1e-3           # bars as tests/test_gpu_features.py
+FLIP_SHARE = 0.005
+TAIL_SHARE = 0.10
 OUTLIER_TOL = 0.25
 
 
@@ -57,7 +59,7 @@ def test_features16k_vs_oracle(ctx, oracle):
     zeros = [0, 3, 7, 0, 0, 1, 0, 0, 0, 0, 2]
     xs, offsets = _batch(lens, zeros)
     got, den = ctx.etsi16k_features(np.concatenate(xs), offsets, denoised=True)
-    n_bad = n_all = 0
+    n_bad = n_all = n_flip = 0
     for u, x in enumerate(xs):
         ref, ref_den = oracle.etsi_features_16k(x)
         g = got[u]
@@ -71,10 +73,12 @@ def test_features16k_vs_oracle(ctx, oracle):
         assert not g[:zeros[u]].any()
         err = ceps_err(ref[:, :14], g[:, :14]).max(axis=1)
         n_bad += int((err > CEPS_TOL).sum())
+        n_flip += int((err > FLIP_TOL).sum())
         n_all += len(err)
         assert err.max() <= OUTLIER_TOL, "utterance %d frame %d: %g" % (u, int(err.argmax()), err.max())
     assert n_all > 1000
-    assert n_bad <= OUTLIER_SHARE * n_all, "%d of %d frames above %g" % (n_bad, n_all, CEPS_TOL)
+    assert n_bad <= TAIL_SHARE * n_all, "%d of %d frames above %g" % (n_bad, n_all, CEPS_TOL)
+    assert n_flip <= max(2, FLIP_SHARE * n_all), "%d of %d frames above %g" % (n_flip, n_all, FLIP_TOL)
 
 
 def test_features16k_use_the_high_band(ctx):
@@ -124,4 +128,4 @@ def test_features16k_full_size(ctx, oracle):
         assert got[u].shape == ref.shape
         assert np.array_equal(got[u][:, 14], ref[:, 14])
         err = ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1)
-        assert (err > CEPS_TOL).mean() <= OUTLIER_SHARE and err.max() <= OUTLIER_TOL
+        assert (err > CEPS_TOL).mean() <= TAIL_SHARE and (err > FLIP_TOL).sum() <= max(2, FLIP_SHARE * len(err)) and err.max() <= OUTLIER_TOL
