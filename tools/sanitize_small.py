@@ -1,4 +1,6 @@
-"""Smallest run of every kernel, for compute-sanitizer (one tool per gpurun call):
+"""Smallest run of every kernel, for compute-sanitizer (one tool per gpurun call; the tool is closed on the shared pool
+this round was built on, so the last clean memcheck / racecheck runs predate the 16 kHz-mode, flush and extract_Wiener
+entry points -- those are covered by the parity tests only):
     compute-sanitizer --tool memcheck  python tools/sanitize_small.py
     compute-sanitizer --tool racecheck python tools/sanitize_small.py
 """
@@ -26,6 +28,7 @@ with api.Context(0) as ctx:
     ctx.etsi_features(s8, o8)
     ctx.etsi16k_features(s16, o16)
     ctx.set_feature_flush(False)
+    ctx.extract_wiener(s16, o16)
     ctx.qmf_split(s16[:1600].reshape(2, 800)[:, :640])
     ctx.rfft(np.random.default_rng(0).standard_normal((3, 256)).astype(np.float32))
     ctx.rfft(np.random.default_rng(0).standard_normal((3, 512)).astype(np.float32))
