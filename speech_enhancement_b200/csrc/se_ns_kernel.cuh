@@ -150,6 +150,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             if (P::CEPS)
                 for (int i = lane; i < P::RB; i += 32) wm.ring3[i] = 0.0f;
         }
+        SE_COLD(cold_fd_store(wm.cold, s));            // after scal_init / the state load above
+        SE_COLD(cold_gf_store(wm.cold, s));
         FeatState fs;
         float fb_last = 0.0f;                             // lane i < 15: FeatureBuffer[i] as the last call left it
         if constexpr (FEAT) feat_state_init(fs, fm, lane);
@@ -388,6 +390,8 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         }
 
         if (st) {
+            SE_COLD(cold_fd_load(s, wm.cold));
+            SE_COLD(cold_gf_load(s, wm.cold));
             if (lane == 0) {
                 st->nb_in1 = s.nb_in1; st->nb_in2 = s.nb_in2; st->nb_out2 = s.nb_out2;
                 st->nb_frame0 = s.nb_frame0; st->nb_frame1 = s.nb_frame1;

@@ -277,7 +277,9 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
     if (fstage == 0) {
         wsum = warp_sum(wsum);
         wsq = warp_sum(wsq);
+        SE_COLD(cold_fd_load(s, wm.cold));
         fl.var = q_var(s, wsum, wsq, P::QVAR);
+        SE_COLD(cold_fd_store(wm.cold, s));
     }
 
     // DoMelFB (etsi/cpp/MelProc.c:82-104) / DoGamma (aurora_etsi/MelProc.cpp:119-141, ignores StartingPoint)
@@ -315,6 +317,8 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
     if (fstage == 0) {
         // frame-dropping VAD statistics, NoiseSup.c:1268-1281
         const float te = warp_sum(mw);
+        SE_COLD(cold_fd_load(s, wm.cold));
+        SE_COLD(cold_gf_load(s, wm.cold));
         s.fd_spec_val = (float)((double)(te * te) - 3.0);
         fl.spec = q_spec(s);
         const float w1 = __shfl_sync(0xffffffffu, mw, 1), w2 = __shfl_sync(0xffffffffu, mw, 2),
@@ -325,9 +329,13 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
         s.den_en0 = s.den_en1;
         s.den_en1 = s.den_en2;
         s.den_en2 = warp_sum(den_sum);
+        SE_COLD(cold_fd_store(wm.cold, s));
+        SE_COLD(cold_gf_store(wm.cold, s));
     } else {
+        SE_COLD(cold_gf_load(s, wm.cold));
         gain_fact_stage2<PROF>(s, warp_sum(noise_sum));
         mw = (float)((double)__fmul_rn(s.alfa_gf, mw) + (1.0 - (double)s.alfa_gf) * 1.0);
+        SE_COLD(cold_gf_store(wm.cold, s));
         if (gains_row && lane < kMel) gains_row[lane] = mw;
     }
 
