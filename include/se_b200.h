@@ -13,7 +13,10 @@
  * (n_utts+1 entries, in samples) delimits utterance u.  `mem` says where ALL data pointers of the call
  * live: SE_MEM_HOST (the library stages H2D/D2H itself) or SE_MEM_DEVICE (pointers are device
  * pointers on the context's GPU; nothing is copied, the call is asynchronous on the context stream
- * until se_ctx_sync()).  offsets / frame-offset arrays are always HOST arrays.
+ * until se_ctx_sync()).  offsets / frame-offset arrays are always HOST arrays and start at 0.
+ * Output rows the path does not produce (capacity beyond n_rows / n_ceps, latency blocks of gains / flags) are zeroed
+ * in SE_MEM_HOST mode; in SE_MEM_DEVICE mode the caller's device arrays are written in place and such rows are left
+ * as they were (nothing is cleared behind the caller's back on the device-resident path).
  */
 #ifndef SE_B200_H
 #define SE_B200_H
@@ -38,10 +41,12 @@ const char *se_last_error(void);
 int  se_device_count(void);
 /* One context per GPU (reference analogue: one "thread instance" per worker,
  * function/.../aurora_etsi/NoiseSupExports.h:36).  Owns a stream, constant tables and scratch.
- * Threading: a context (and the streams created from it) is NOT thread-safe -- one host thread at a time
- * per context, like the plugin's thread instance; different contexts may be used concurrently, and their calls
- * overlap on the GPU (results reach pageable caller arrays through a pinned arena so that no call holds the driver
- * while its kernel runs).  The reference-named adapters of se_reference_api.h use one context per calling thread. */
+ * Threading: every call on a context (or on a stream created from it) holds the context's internal lock, so a
+ * context or stream handle may be created on one host thread and used on others -- calls on ONE context serialise,
+ * like the plugin's thread instance; different contexts run concurrently, and their calls overlap on the GPU
+ * (results reach pageable caller arrays through a pinned arena so that no call holds the driver while its kernel
+ * runs).  The reference-named adapters of se_reference_api.h use one context per calling thread; a handle they
+ * return (FEParamsX, plugin thread instance) stays bound to the context of the thread that created it. */
 int  se_ctx_create(int device, se_ctx **out);
 void se_ctx_destroy(se_ctx *ctx);
 /* Launch on a caller-owned CUDA stream (cudaStream_t passed as void*); NULL restores the own stream. */
@@ -167,6 +172,20 @@ int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int6
                         float *out_f32, int32_t *flags, float *gains, int32_t *n_rows,
                         const int64_t *block_offsets, int mem);
 
+/* ---- spectral state per block, for parity checks at the spectrum level -------------
+ * Runs the same fused NoiseSup kernel as the two calls above (profile 8: se_etsi_denoise_batch, int16 input;
+ * profile 16: se_p16_wiener_batch) and writes, for block b of utterance u,
+ * spectra[block_offsets[u] + b][8][spec] (spec = 65 | 129) = the SPECTRUM state of NoiseSupStructX after the call
+ * (etsi/cpp/NoiseSup.c:102-115, as FilterCalc :449-563 leaves it):
+ *   [0] nSigSE1  [1] noiseSE1  [2] denSigSE1  [3] nSigSE2  [4] noiseSE2  [5] denSigSE2
+ *   [6] / [7] sqrt(PSDMeaned) of stage 1 / 2 (FFTtoPSD :249-270 -> PSDMean :289-303 -> sqrt :522-526).
+ * Planes of a stage are only written in blocks where that stage ran (produced[] bit 1 = stage 1 of the two-stage
+ * filter ran, bit 0 = stage 2 ran and a shift was output, bit 2 = block skipped by the zero gate); others stay 0.
+ * spectra is required, produced (int32 per block, same indexing) optional.  A test / diagnostic entry: 8 spectra per
+ * block are 13-26x the path's normal output bytes. */
+int se_ns_spectra_batch(se_ctx *ctx, int profile, const void *samples, int is_f32, const int64_t *offsets, int n_utts,
+                        float *spectra, int32_t *produced, const int64_t *block_offsets, int mem);
+
 /* ---- persistent NoiseSup streams (state carried across calls, like the plugin's thread instance
  *      reused over 64 channel files, function/.../aurora_etsi_test/aurora_etsi_test.cpp:21-141) --- */
 typedef struct se_ns_stream se_ns_stream;
@@ -190,6 +209,8 @@ int  se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *ou
 #define SE_FLAG_EXACT   1   /* evaluate the IIR recurrences with separately rounded mul/add, in the
                                reference's order (bit-identical to its float arithmetic); default is
                                FMA-contracted (faster, ~-120 dB relative difference)               */
+#define SE_FLAG_OUT_F32 2   /* se_resynth_batch: `out` is a float array that receives resynth_e[] before the
+                               (short) cast (resyth_64sub_IBM/cpp/extractwav.cpp:109-122), for waveform-SNR checks */
 /* subbband (enhancement_extract_subband_linux/cpp/extractwav.cpp:36-97): int16 hair-cell output per
  * channel; out holds, for utterance u, 64 rows of len_u samples starting at 64*offsets[u]. */
 int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
@@ -201,6 +222,13 @@ int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
 int64_t se_ibm_num_frames(int64_t n_samples);
 int se_ibm_batch(se_ctx *ctx, const int16_t *pure, const int16_t *noise, const int64_t *offsets, int n_utts,
                  float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem);
+
+/* make_single_IBM exactly as the reference drives it (show_IBM.cpp:118-170): from the MATERIALISED sub-band rows
+ * that subbband() wrote for the clean and the noise signal (pure64 / noise64 laid out like se_subband_batch's
+ * output: 64 rows of len_u int16 starting at 64*offsets[u]).  Same outputs as se_ibm_batch; identical values when
+ * the rows are what se_subband_batch produces for the same waveforms. */
+int se_ibm_rows_batch(se_ctx *ctx, const int16_t *pure64, const int16_t *noise64, const int64_t *offsets, int n_utts,
+                      float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem);
 
 /* extract_Wiener (function/20141106_speech_enhancement/aurora_etsi_test/aurora_etsi_test.cpp:16-141) for a batch of
  * noisy utterances, device-resident from end to end: subbband() -> the 64 hair-cell channel signals of each utterance
@@ -236,6 +264,11 @@ int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem);
 /* gammaToneFilter (extractwav.cpp:168-212) for `count` signals of length n with per-signal channel. */
 int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
                        int count, int flags, int mem);
+/* The same filter with caller-supplied coefficients (gammaToneFilter takes its gammaTone channel BY VALUE, HuWang.h:49,
+ * so any cf / bw / midEarCoeff is legal): coef is a HOST array [count][3] = f1, f2, gain as extractwav.cpp:176-183
+ * derives them (the drop-in adapter gammaToneFilter() of se_reference_api.hpp does that). */
+int se_gammatone_coef_batch(se_ctx *ctx, const float *in, float *out, const float *coef, int64_t n, int count, int flags,
+                            int mem);
 /* hairCell (extractwav.cpp:213-258, Meddis 1988) for `count` signals of length n, each from the resting state. */
 int se_haircell_batch(se_ctx *ctx, const float *in, float *out, int64_t n, int count, int mem);
 /* init-time tables as the device sees them (host copies), for table parity tests */

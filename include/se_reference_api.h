@@ -59,7 +59,10 @@ void rfft(float *x, int n, int m);
  * of the four calls are the reference's: DoAdvProcess consumes FrameShift=80 int16 samples, returns
  * TRUE(1) when a denoised shift was written to OutBuf (2+2 frames latency, NoiseSup.c:1436-1439) and
  * writes 14 cepstral coefficients c1..c12,c0,logE to FeatBuf when a cepstral frame is due (the
- * CompCeps step of ParmInterface.c:274-293; *feat_ready set to 1).                               */
+ * CompCeps step of ParmInterface.c:274-293; *feat_ready set to 1).  A leading all-zero frame returns TRUE(1) with
+ * FeatBuf[0..13] = 0 and OutBuf untouched (ParmInterface.c:314-327).
+ * Threading: a handle stays bound to the GPU context of the host thread that allocated it; it may be USED from any
+ * thread (calls on one context serialise on its internal lock, se_b200.h).                       */
 typedef struct FEParamsX FEParamsX;
 FEParamsX *AdvProcessAlloc(int SamplingFrequency);            /* only 8000 is on the hot path      */
 void AdvProcessInit(FEParamsX *This);
@@ -69,10 +72,19 @@ int se_adv_feature_ready(FEParamsX *This);                    /* additive: 1 if 
  * their Alloc/Delete halves are part of AdvProcessAlloc/AdvProcessDelete here.
  * DoNoiseSup: 80 floats in; TRUE(1) when 80 denoised floats were written to OutData (NoiseSup.c:1436-1439),
  * no zero-frame gate.  DoCompCeps: Data = 200-sample frame with Data[-1] valid; Coef = c1..c12,c0,logE. */
+typedef struct NoiseSupStructX NoiseSupStructX;
+NoiseSupStructX *DoNoiseSupAlloc(void);                       /* NoiseSupExports.h:20: one NoiseSup state (GPU) */
+void DoNoiseSupDelete(NoiseSupStructX *NSX);                  /* NoiseSupExports.h:26                           */
 void DoNoiseSupInit(FEParamsX *This);
 int DoNoiseSup(float *InData, float *OutData, FEParamsX *This);
 void DoCompCepsInit(FEParamsX *This);
 int DoCompCeps(float *Data, float *Coef, FEParamsX *This);
+/* FlushAdvProcess (etsi/cpp/ParmInterface.h:217, ParmInterface.c:347-355 -> DoVADFlush, VAD.c:342-431).  As shipped,
+ * DoAdvProcess never feeds the VAD delay line (ParmInterface.c:274-311 is commented out), so the flush walks the
+ * freshly initialised 7-slot ring: TRUE six times, then FALSE; FrameCounter advances, and once it exceeds 10 an
+ * all-zero row with VAD flag 0 is copied to FeatureBuffer[0..14].  Reproduced exactly.  (The flush of the
+ * RE-ENABLED feature chain is se_ctx_set_feature_flush + se_etsi_features_batch in se_b200.h.)              */
+int FlushAdvProcess(float *FeatBuf, FEParamsX *This);
 void AdvProcessDelete(FEParamsX **This);
 
 /* ---- function/20141106_speech_enhancement/aurora_etsi/NoiseSupExports.h:9-42 -------------------- */
@@ -116,6 +128,14 @@ int se_addnoise(const short *pure, short *noise, short *noisy, long n, int db);
 int se_gammatone_filter(const float *input, float *output, int channel, long sigLength);
 /* hairCell(float *input, float *output, long sigLength) (HuWang.h:62, extractwav.cpp:213-258).  */
 int se_hair_cell(const float *input, float *output, long sigLength);
+/* gammaToneFilter() with the by-value channel parameters of HuWang.h:49 (any cf / bw / midEarCoeff); the C++
+ * signature gammaToneFilter(float*, float*, gammaTone, long) is a header-only adapter in se_reference_api.hpp. */
+int se_gammatone_filter_params(const float *input, float *output, float cf, float bw, float midEarCoeff,
+                               long sigLength);
+/* make_single_IBM() arithmetic on the 2 x 64 sub-band signals it reads back from the wavs subbband() wrote
+ * (show_IBM.cpp:118-170): pure64xn / noise64xn are 64 channel-major rows of n int16; irm is [frames][64].
+ * The C++ signature make_single_IBM(char*, FILE*, FILESNAME) is a header-only adapter in se_reference_api.hpp. */
+int se_single_ibm_rows(const short *pure64xn, const short *noise64xn, long n, float *irm);
 
 #ifdef __cplusplus
 }

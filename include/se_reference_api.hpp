@@ -9,6 +9,8 @@
  *   addnoise   enhancement_extract_subband_linux/cpp/extractwav.cpp:6-35     (extractwav.h:5)
  *   subbband   enhancement_extract_subband_linux/cpp/extractwav.cpp:36-97    (extractwav.h:6)
  *   resynth    resyth_64sub_IBM/cpp/extractwav.cpp:9-132                     (extractwav.h:4)
+ *   make_single_IBM  enhancement_extract_subband_linux/cpp/show_IBM.cpp:92-213 (make_IBM.h:9)
+ *   gammaToneFilter / hairCell  <tool>/cpp/extractwav.cpp:168-258            (HuWang.h:49,62)
  *              resyth_64sub_ori/cpp/extractwav.cpp, 1dnn_resynth/extractwav.cpp: same signature, other `mode`
  *
  * The templates live in namespace se_dropin.  Define SE_DROPIN_WAVE (e.g. asdk::CWave) and, for resynth/addnoise,
@@ -79,6 +81,53 @@ inline void resynth(Wave *wav, Opts opts, std::vector<std::vector<float> > &v_er
     resynth_wav_e.Write(temp);
 }
 
+/* gammaToneFilter(): the channel is passed BY VALUE (cf, bw, midEarCoeff; its p / q state is zeroed on entry,
+ * extractwav.cpp:168-189), so any parameters are legal, not only the 64 presets.  GammaTone is the driver's own
+ * `struct gammaTone` (HuWang.h:20-26). */
+template <class GammaTone>
+inline void gammaToneFilter(float *input, float *output, GammaTone fChan, long sigLength)
+{
+    se_gammatone_filter_params(input, output, fChan.cf, fChan.bw, fChan.midEarCoeff, sigLength);
+}
+
+/* make_single_IBM(): reads the clean wav for its length and the 2 x 64 sub-band wavs subbband() wrote
+ * (<out><save_subband_pure_wav_dir><id>_<c>.wav, <out><save_subband_noise_wav_dir><id>_noise_<c>.wav), computes
+ * IRM = Sp / (Sp + Sn) per (frame, channel) on the GPU and appends the "<id>_noisy [ ... ]" text matrix to fp_IRM_W
+ * (show_IBM.cpp:92-213).  Wave needs a default constructor and asdk::CWave's Read(path, channel, bHead, type, nFs,
+ * nChannel, nMaxSample) with its LEFT_CHANNEL / PCM enumerators (:95-107).  Frame powers sit on OUR restatement of
+ * the un-vendored asdk::SpecInfo (parity unpinned at that boundary). */
+template <class Wave, class Opts>
+inline void make_single_IBM(char *name_id, FILE *fp_IRM_W, Opts opts)
+{
+    char temp[1024];
+    Wave speech;
+    std::snprintf(temp, sizeof temp, "%s%s.wav", opts.purewavDictionary, name_id);
+    speech.Read(temp, Wave::LEFT_CHANNEL, true, Wave::PCM, 16000, 1, -1);
+    const long n = speech.GetSampleNum();
+    const long frames = n >= 320 ? (n - 320) / 160 + 1 : 0;                 /* buffNum, :110 */
+    if (frames <= 0 || !fp_IRM_W) return;
+    std::vector<short> pure((size_t)64 * (size_t)n, 0), noise((size_t)64 * (size_t)n, 0);
+    for (int c = 0; c < 64; c++) {
+        Wave p, z;
+        std::snprintf(temp, sizeof temp, "%s%s%s_%d.wav", opts.outputDictionary, opts.save_subband_pure_wav_dir, name_id, c);
+        p.Read(temp, Wave::LEFT_CHANNEL, true, Wave::PCM, 16000, 1, -1);
+        std::snprintf(temp, sizeof temp, "%s%s%s_noise_%d.wav", opts.outputDictionary, opts.save_subband_noise_wav_dir, name_id, c);
+        z.Read(temp, Wave::LEFT_CHANNEL, true, Wave::PCM, 16000, 1, -1);
+        const long np = p.GetSampleNum() < n ? p.GetSampleNum() : n, nz = z.GetSampleNum() < n ? z.GetSampleNum() : n;
+        for (long i = 0; i < np; i++) pure[(size_t)c * (size_t)n + (size_t)i] = p.GetDataPtr()[i];
+        for (long i = 0; i < nz; i++) noise[(size_t)c * (size_t)n + (size_t)i] = z.GetDataPtr()[i];
+    }
+    std::vector<float> irm((size_t)frames * 64);
+    if (se_single_ibm_rows(pure.data(), noise.data(), n, irm.data()) != 0) return;
+    std::fprintf(fp_IRM_W, "%s_noisy [\n", name_id);                         /* :194-209 */
+    for (long f = 0; f < frames - 1; f++) {
+        for (int c = 0; c < 64; c++) std::fprintf(fp_IRM_W, "%.7f ", irm[(size_t)f * 64 + c]);
+        std::fprintf(fp_IRM_W, "\n ");
+    }
+    for (int c = 0; c < 64; c++) std::fprintf(fp_IRM_W, "%.7f ", irm[(size_t)(frames - 1) * 64 + c]);
+    std::fprintf(fp_IRM_W, "]\n");
+}
+
 }  // namespace se_dropin
 
 #ifdef SE_DROPIN_WAVE
@@ -103,6 +152,20 @@ inline void addnoise(SE_DROPIN_WAVE *purewav, SE_DROPIN_WAVE *temp_noisewav, SE_
     se_dropin::addnoise(purewav, temp_noisewav, noisywav, name_id, opts);
 }
 #endif
+#ifdef SE_DROPIN_HAVE_IBM_OPTS           /* FILESNAME of enhancement_extract_subband_linux/cpp/struct.h (make_IBM.h:9) */
+inline void make_single_IBM(char *name_id, FILE *fp_IRM_W, FILESNAME opts)
+{
+    se_dropin::make_single_IBM<SE_DROPIN_WAVE>(name_id, fp_IRM_W, opts);
+}
+#endif
 #endif /* SE_DROPIN_WAVE */
+
+#ifdef SE_DROPIN_HAVE_GAMMATONE          /* `struct gammaTone` of HuWang.h:20-26 is declared: HuWang.h:49,62 by name */
+inline void gammaToneFilter(float *input, float *output, gammaTone fChan, long sigLength)
+{
+    se_dropin::gammaToneFilter(input, output, fChan, sigLength);
+}
+inline void hairCell(float *input, float *output, long sigLength) { se_hair_cell(input, output, sigLength); }
+#endif
 
 #endif

@@ -140,6 +140,40 @@ class Oracle:
             out["info"] = info[:calls]
         return out
 
+    def ns_spectra(self, profile, x):
+        """Block-by-block SPECTRUM state (so_ns_spectrum planes 0..7) behind the caller's zero-frame gate:
+        profile 8 = DoAdvProcess (leading all-zero frames only, ParmInterface.c:244-250), 16 = func_Wiener (anywhere,
+        NoiseSup.cpp:1159-1170).  Returns spectra[block][8][spec], ran[block] (bit 1 = stage 1 ran, bit 0 = stage 2
+        ran, bit 2 = skipped by the gate) -- the layout of se_ns_spectra_batch."""
+        shift, spec = (80, 65) if profile == 8 else (160, 129)
+        xf = np.ascontiguousarray(x, np.float32)
+        nb = len(xf) // shift
+        h = self.L.so_ns_create(profile)
+        sp = np.zeros((nb, 8, spec), np.float32)
+        ran = np.zeros(nb, np.int32)
+        out = np.zeros(shift, np.float32)
+        info = np.zeros(1, INFO_DTYPE)
+        onset = False
+        for b in range(nb):
+            blk = np.ascontiguousarray(xf[b * shift:(b + 1) * shift])
+            nonzero = int(np.float32(np.sum(blk.astype(np.float64) ** 2))) != 0
+            if profile == 8:
+                if not (nonzero or onset):
+                    ran[b] = 4
+                    continue
+                onset = True
+            elif not nonzero:
+                ran[b] = 4
+                continue
+            self.L.so_ns_block(h, _p(blk), _p(out), _p(info))
+            ran[b] = (1 if info[0]["stage1_ran"] else 0) | (2 if info[0]["stage0_ran"] else 0)
+            for st, bit in ((0, 2), (1, 1)):
+                if ran[b] & bit:
+                    for w in (3 * st, 3 * st + 1, 3 * st + 2, 6 + st):
+                        sp[b, w] = np.ctypeslib.as_array(self.L.so_ns_spectrum(h, w), (spec,))
+        self.L.so_ns_destroy(h)
+        return sp, ran
+
     def comp_ceps(self, frame201):
         f = np.ascontiguousarray(frame201, np.float32)
         o = np.zeros(14, np.float32)
@@ -304,11 +338,26 @@ class RefEtsi:
         L.ref_etsi_features_16k.restype = C.c_long
         L.ref_etsi_features_16k.argtypes = [_vp, C.c_long, _vp, _vp]
         L.ref_qmf_split.argtypes = [_vp, C.c_long, _vp, _vp]
+        L.ref_adv_process_as_shipped.argtypes = [_vp, C.c_long, _vp, _vp, _vp, _vp, _vp]
 
     def rfft(self, x, m):
         y = np.ascontiguousarray(x, np.float32).copy()
         self.L.ref_rfft(_p(y), len(y), m)
         return y
+
+    def adv_process_as_shipped(self, x):
+        """DoAdvProcess frame by frame + the FlushAdvProcess loop, as shipped (feature block commented out):
+        out int16[calls*80] (0x7a7a where DenoiseBuffer was not written), feat[calls][15] (7.0 where FeatureBuffer
+        was not written), wrote[calls], flush_rets, flush_feat[k][15]."""
+        x = np.ascontiguousarray(x, np.int16)
+        calls = len(x) // 80
+        out = np.zeros(max(calls, 1) * 80, np.int16)
+        feat = np.zeros((max(calls, 1), 15), np.float32)
+        wrote = np.zeros(max(calls, 1), np.int32)
+        fr = np.zeros(8, np.int32)
+        ff = np.zeros((8, 15), np.float32)
+        k = self.L.ref_adv_process_as_shipped(_p(x), len(x), _p(out), _p(feat), _p(wrote), _p(fr), _p(ff))
+        return dict(out=out[:calls * 80], feat=feat[:calls], wrote=wrote[:calls], flush_rets=fr[:k], flush_feat=ff[:k])
 
     def etsi_features_16k(self, x):
         """16 kHz mode: (feat[rows][15], low-band den_i16[(n//160)*80])."""

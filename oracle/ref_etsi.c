@@ -372,3 +372,39 @@ void ref_qmf_split(const short *in, long n, float *lp, float *hp)
     }
     AdvProcessDelete(&fe);
 }
+
+/* ---- DoAdvProcess / FlushAdvProcess exactly as shipped (the feature block of ParmInterface.c:274-311 stays commented
+ * out): one call per 80-sample frame, then the ETSI driver's flush loop.  rets[n_calls]: DoAdvProcess's return value
+ * per call (the success path falls off the end of the function without a return, ParmInterface.c:262-313, so -- like
+ * the reference's own callers -- only "did it write DenoiseBuffer" is recorded: out80 is pre-filled with a sentinel);
+ * out[n_calls*80] / feat[n_calls*15] hold what the call left in DenoiseBuffer / FeatureBuffer (feat pre-filled with
+ * the sentinel 7.0f).  flush_rets[8] / flush_feat[8*15]: return value and FeatureBuffer of up to 8 FlushAdvProcess
+ * calls.  Returns the number of flush calls made (the first FALSE included). */
+int ref_adv_process_as_shipped(const short *in, long n, short *out, float *feat, int *wrote, int *flush_rets,
+                               float *flush_feat)
+{
+    FEParamsX *fe = AdvProcessAlloc(8000);
+    long calls = n / 80, c;
+    int k, i;
+    short frame[80], den[80];
+    float fb[15];
+    AdvProcessInit(fe);
+    for (c = 0; c < calls; c++) {
+        memcpy(frame, in + c * 80, sizeof frame);
+        for (i = 0; i < 80; i++) den[i] = (short)0x7a7a;
+        for (i = 0; i < 15; i++) fb[i] = 7.0f;
+        (void)DoAdvProcess(frame, den, fb, fe);
+        wrote[c] = 0;
+        for (i = 0; i < 80; i++) if (den[i] != (short)0x7a7a) wrote[c] = 1;
+        memcpy(out + c * 80, den, sizeof den);
+        memcpy(feat + c * 15, fb, sizeof fb);
+    }
+    for (k = 0; k < 8; k++) {
+        for (i = 0; i < 15; i++) fb[i] = 7.0f;
+        flush_rets[k] = FlushAdvProcess(fb, fe) ? 1 : 0;
+        memcpy(flush_feat + k * 15, fb, sizeof fb);
+        if (!flush_rets[k]) { k++; break; }
+    }
+    AdvProcessDelete(&fe);
+    return k;
+}

@@ -147,6 +147,7 @@ struct so_ns {
     float fd_mel_mean, fd_var_mean, fd_acc_test, fd_spec_mean, fd_mel_val[2], fd_spec_val, fd_in_vadq;
     /* SPECTRUM (NoiseSup.c:102-115) */
     float nsig[2][SO_MAX_SPEC], noise[2][SO_MAX_SPEC], den[2][SO_MAX_SPEC];
+    float psdm[2][SO_MAX_SPEC];     /* trace only: sqrt(PSDMeaned) as FilterCalc leaves it (NoiseSup.c:522-526) */
     short idx[2];
     float psd_hist[2][SO_MAX_SPEC * 2];
     /* NS_TMP tables (NoiseSup.c:130-137) */
@@ -307,7 +308,9 @@ const float *so_ns_spectrum(const so_ns *s, int which)
     case 2: return s->den[0];
     case 3: return s->nsig[1];
     case 4: return s->noise[1];
-    default: return s->den[1];
+    case 5: return s->den[1];
+    case 6: return s->psdm[0];
+    default: return s->psdm[1];
     }
 }
 
@@ -387,6 +390,7 @@ static void ns_filter_calc(so_ns *s, int fstage, float *psd_mean, float *W)
     for (i = 0; i < n; i++) {
         nsig[i] = (float)sqrt(nsig[i]);
         psd_mean[i] = (float)sqrt(psd_mean[i]);
+        s->psdm[fstage][i] = psd_mean[i];
     }
     if (fstage == 0) {
         if (nbf < 100) lambda = 1 - 1 / (float)nbf;

@@ -41,7 +41,8 @@ int so_ns_spec(const so_ns *s);                       /* 65 or 129              
 /* One DoNoiseSup call (etsi/cpp/NoiseSup.c:1061) / one loop iteration of func_Wiener
  * (aurora_etsi/NoiseSup.cpp:1156-1405, after the zero-block test). */
 int so_ns_block(so_ns *s, const float *in, float *out, so_ns_info *info);
-/* state views for traces: which = 0 nSigSE1, 1 noiseSE1, 2 denSigSE1, 3 nSigSE2, 4 noiseSE2, 5 denSigSE2 */
+/* state views for traces: which = 0 nSigSE1, 1 noiseSE1, 2 denSigSE1, 3 nSigSE2, 4 noiseSE2, 5 denSigSE2,
+ * 6 / 7 sqrt(PSDMeaned) of stage 1 / 2 as FilterCalc leaves it (NoiseSup.c:522-526) */
 const float *so_ns_spectrum(const so_ns *s, int which);
 /* init-time tables */
 void so_ns_tables(const so_ns *s, float *sig_window, float *ir_window, float *bank /*25*spec-or-128*/,

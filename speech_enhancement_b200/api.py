@@ -15,6 +15,7 @@ DROPIN_PATH = os.path.join(_HERE, "lib", "libse_b200_dropin.so")
 
 SE_MEM_HOST, SE_MEM_DEVICE = 0, 1
 SE_FLAG_EXACT = 1
+SE_FLAG_OUT_F32 = 2
 RESYNTH_IBM, RESYNTH_ORI, RESYNTH_1DNN = 0, 1, 2
 K_NS_P8, K_NS_P16, K_GT_FWD, K_GT_BWD, K_SUBBAND, K_IBM, K_ADDNOISE = range(7)
 KERNEL_NAMES = {K_NS_P8: "ns_p8", K_NS_P16: "ns_p16", K_GT_FWD: "gt_fwd", K_GT_BWD: "gt_bwd",
@@ -66,6 +67,7 @@ def lib():
         L.se_etsi16k_features_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
         L.se_qmf_split_batch.argtypes = [_vp, _vp, C.c_int64, C.c_int, _vp, _vp, C.c_int]
         L.se_p16_wiener_batch.argtypes = [_vp, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, _vp, _vp, C.c_int]
+        L.se_ns_spectra_batch.argtypes = [_vp, C.c_int, _vp, C.c_int, _vp, C.c_int, _vp, _vp, _vp, C.c_int]
         L.se_ns_stream_create.argtypes = [_vp, C.c_int, C.POINTER(_vp)]
         L.se_ns_stream_destroy.argtypes = [_vp]
         L.se_ns_stream_reset.argtypes = [_vp]
@@ -343,6 +345,24 @@ class Context:
                             out["gains"] if bo[-1] else None, out["n_rows"], bo)
         return out
 
+    def ns_spectra(self, profile, samples, offsets):
+        """Per-block spectral state (se_ns_spectra_batch): spectra[block][8][spec], produced[block], block_offsets."""
+        samples = np.ascontiguousarray(samples)
+        is_f32 = samples.dtype == np.float32
+        if not is_f32:
+            samples = np.ascontiguousarray(samples, np.int16)
+        offsets = _i64(offsets)
+        nu = len(offsets) - 1
+        shift, spec = (80, 65) if profile == 8 else (160, 129)
+        bo = np.zeros(nu + 1, np.int64)
+        bo[1:] = np.cumsum(np.diff(offsets) // shift)
+        tb = max(int(bo[-1]), 1)
+        sp = np.zeros((tb, 8, spec), np.float32)
+        produced = np.zeros(tb, np.int32)
+        _check(self.L.se_ns_spectra_batch(self.h, profile, _ptr(samples), int(is_f32), _ptr(offsets), nu, _ptr(sp),
+                                          _ptr(produced), _ptr(bo), SE_MEM_HOST), "se_ns_spectra_batch")
+        return sp[:int(bo[-1])], produced[:int(bo[-1])], bo
+
     def subband(self, samples, offsets, exact=True):
         samples = np.ascontiguousarray(samples, np.int16)
         offsets = _i64(offsets)
@@ -378,12 +398,12 @@ class Context:
                                               _ptr(rows), _ptr(bo), SE_MEM_HOST), "se_extract_wiener_batch")
         return [(gains[bo[u]:bo[u + 1]], flags[:, bo[u]:bo[u + 1]], int(rows[u])) for u in range(nu)]
 
-    def resynth(self, samples, offsets, mask, frame_offsets, mode, exact=True):
+    def resynth(self, samples, offsets, mask, frame_offsets, mode, exact=True, f32=False):
         samples = np.ascontiguousarray(samples, np.int16)
         mask = np.ascontiguousarray(mask, np.float32)
-        out = np.zeros(len(samples), np.int16)
+        out = np.zeros(len(samples), np.float32 if f32 else np.int16)
         self.resynth_raw(samples, _i64(offsets), len(offsets) - 1, mask, _i64(frame_offsets), mode,
-                         SE_FLAG_EXACT if exact else 0, out)
+                         (SE_FLAG_EXACT if exact else 0) | (SE_FLAG_OUT_F32 if f32 else 0), out)
         return out
 
     def addnoise(self, pure, noise, offsets, db):

@@ -289,6 +289,7 @@ int se_ctx_create(int device, se_ctx **out)
     SE_CUDA(cudaSetDevice(device));
     se_ctx *ctx = new se_ctx();
     ctx->device = device;
+    ctx->exact = 0;
     ctx->own_stream = nullptr;
     std::memset(ctx->lanes, 0, sizeof ctx->lanes);
     ctx->cur = &ctx->lanes[0];
@@ -344,6 +345,7 @@ int se_ctx_set_stream(se_ctx *ctx, void *cuda_stream)
 int se_ctx_sync(se_ctx *ctx)
 {
     if (!ctx) return SE_EINVAL;
+    std::lock_guard<std::recursive_mutex> guard(ctx->mu);
     SE_CUDA(cudaSetDevice(ctx->device));
     SE_CUDA(cudaStreamSynchronize(ctx->cur->stream));
     return SE_OK;
@@ -364,6 +366,13 @@ int se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts)
     return SE_OK;
 }
 
+int se_ctx_set_exact(se_ctx *ctx, int enable)
+{
+    if (!ctx) return SE_EINVAL;
+    ctx->exact = enable ? 1 : 0;
+    return SE_OK;
+}
+
 int se_ctx_set_feature_flush(se_ctx *ctx, int enable)
 {
     if (!ctx) return SE_EINVAL;
@@ -381,6 +390,7 @@ int se_ctx_profiling(se_ctx *ctx, int enable)
 int se_ctx_kernel_time(se_ctx *ctx, int kernel_id, double *total_ms, int64_t *launches)
 {
     if (!ctx || kernel_id < 0 || kernel_id >= SE_K_COUNT) return SE_EINVAL;
+    std::lock_guard<std::recursive_mutex> guard(ctx->mu);
     int rc = drain_events(ctx);
     if (rc) return rc;
     if (total_ms) *total_ms = ctx->k_ms[kernel_id];
@@ -391,6 +401,7 @@ int se_ctx_kernel_time(se_ctx *ctx, int kernel_id, double *total_ms, int64_t *la
 int se_ctx_reset_kernel_times(se_ctx *ctx)
 {
     if (!ctx) return SE_EINVAL;
+    std::lock_guard<std::recursive_mutex> guard(ctx->mu);
     int rc = drain_events(ctx);
     if (rc) return rc;
     std::memset(ctx->k_ms, 0, sizeof ctx->k_ms);

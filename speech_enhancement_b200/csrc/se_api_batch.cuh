@@ -87,6 +87,10 @@ static int leave(se_ctx *ctx, int mem)
 }
 
 #define SE_TRY(expr) do { int rc__ = (expr); if (rc__) return rc__; } while (0)
+// argument checks + cudaSetDevice, then the context lock for the rest of the call (se_ctx::mu)
+#define SE_ENTER(ctx, mem, what)                                   \
+    SE_TRY(enter(ctx, mem, what));                                 \
+    std::lock_guard<std::recursive_mutex> se_ctx_guard__((ctx)->mu)
 
 
 // ------------------------------------------------------------------------------------------------
@@ -276,7 +280,7 @@ int se_etsi_denoise_batch(se_ctx *ctx, const int16_t *samples, const int64_t *of
                           int16_t *denoised, float *ceps, const int64_t *ceps_offsets, int32_t *n_ceps,
                           float *den_f32, uint8_t *vad_trace, const int64_t *trace_offsets, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_etsi_denoise_batch"));
+    SE_ENTER(ctx, mem, "se_etsi_denoise_batch");
     if (n_utts < 0 || (n_utts > 0 && !samples)) { set_error("se_etsi_denoise_batch: bad arguments"); return SE_EINVAL; }
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_etsi_denoise_batch"));
@@ -284,6 +288,10 @@ int se_etsi_denoise_batch(se_ctx *ctx, const int16_t *samples, const int64_t *of
     if (vad_trace && !trace_offsets) { set_error("se_etsi_denoise_batch: vad_trace needs trace_offsets"); return SE_EINVAL; }
     if (offsets[0] != 0) { set_error("se_etsi_denoise_batch: offsets[0] must be 0"); return SE_EINVAL; }
     if (ceps) SE_TRY(check_offsets(ceps_offsets, n_utts, "se_etsi_denoise_batch(ceps_offsets)"));
+    if ((ceps && ceps_offsets[0] != 0) || (vad_trace && trace_offsets[0] != 0)) {
+        set_error("se_etsi_denoise_batch: ceps_offsets[0] / trace_offsets[0] must be 0");
+        return SE_EINVAL;
+    }
     if (vad_trace) {
         SE_TRY(check_offsets(trace_offsets, n_utts, "se_etsi_denoise_batch(trace_offsets)"));
         for (int u = 0; u < n_utts; u++)
@@ -308,7 +316,7 @@ int se_etsi_denoise_batch(se_ctx *ctx, const int16_t *samples, const int64_t *of
 int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
                            float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_etsi_features_batch"));
+    SE_ENTER(ctx, mem, "se_etsi_features_batch");
     if (n_utts < 0 || (n_utts > 0 && (!samples || !features || !feat_offsets))) {
         set_error("se_etsi_features_batch: bad arguments");
         return SE_EINVAL;
@@ -316,7 +324,7 @@ int se_etsi_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t *o
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_etsi_features_batch"));
     SE_TRY(check_offsets(feat_offsets, n_utts, "se_etsi_features_batch(feat_offsets)"));
-    if (offsets[0] != 0) { set_error("se_etsi_features_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    if (offsets[0] != 0 || feat_offsets[0] != 0) { set_error("se_etsi_features_batch: offsets[0] / feat_offsets[0] must be 0"); return SE_EINVAL; }
     for (int u = 0; u < n_utts; u++)
         if (feat_offsets[u + 1] - feat_offsets[u] <
             se_etsi_num_feature_rows(offsets[u + 1] - offsets[u]) + (ctx->feature_flush ? SE_FEATURE_FLUSH_ROWS : 0)) {
@@ -340,7 +348,7 @@ int se_etsi16k_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t
                               float *features, const int64_t *feat_offsets, int32_t *n_rows, int16_t *denoised_lp,
                               const int64_t *den_offsets, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_etsi16k_features_batch"));
+    SE_ENTER(ctx, mem, "se_etsi16k_features_batch");
     if (n_utts < 0 || (n_utts > 0 && (!samples || !features || !feat_offsets)) || (denoised_lp && !den_offsets)) {
         set_error("se_etsi16k_features_batch: bad arguments");
         return SE_EINVAL;
@@ -348,8 +356,9 @@ int se_etsi16k_features_batch(se_ctx *ctx, const int16_t *samples, const int64_t
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_etsi16k_features_batch"));
     SE_TRY(check_offsets(feat_offsets, n_utts, "se_etsi16k_features_batch(feat_offsets)"));
-    if (offsets[0] != 0) { set_error("se_etsi16k_features_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    if (offsets[0] != 0 || feat_offsets[0] != 0) { set_error("se_etsi16k_features_batch: offsets[0] / feat_offsets[0] must be 0"); return SE_EINVAL; }
     if (denoised_lp) SE_TRY(check_offsets(den_offsets, n_utts, "se_etsi16k_features_batch(den_offsets)"));
+    if (denoised_lp && den_offsets[0] != 0) { set_error("se_etsi16k_features_batch: den_offsets[0] must be 0"); return SE_EINVAL; }
     for (int u = 0; u < n_utts; u++) {
         const int64_t calls = se_etsi16k_num_feature_rows(offsets[u + 1] - offsets[u]);
         if (feat_offsets[u + 1] - feat_offsets[u] < calls + (ctx->feature_flush ? SE_FEATURE_FLUSH_ROWS : 0)) {
@@ -378,7 +387,7 @@ int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int6
                         float *out_f32, int32_t *flags, float *gains, int32_t *n_rows,
                         const int64_t *block_offsets, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_p16_wiener_batch"));
+    SE_ENTER(ctx, mem, "se_p16_wiener_batch");
     if (n_utts < 0 || (n_utts > 0 && !samples)) { set_error("se_p16_wiener_batch: bad arguments"); return SE_EINVAL; }
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_p16_wiener_batch"));
@@ -386,6 +395,7 @@ int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int6
     if (offsets[0] != 0) { set_error("se_p16_wiener_batch: offsets[0] must be 0"); return SE_EINVAL; }
     if (block_offsets) {
         SE_TRY(check_offsets(block_offsets, n_utts, "se_p16_wiener_batch(block_offsets)"));
+        if (block_offsets[0] != 0) { set_error("se_p16_wiener_batch: block_offsets[0] must be 0"); return SE_EINVAL; }
         for (int u = 0; u < n_utts; u++)
             if (block_offsets[u + 1] - block_offsets[u] < (offsets[u + 1] - offsets[u]) / 160) {
                 set_error("se_p16_wiener_batch: block_offsets too small for utterance %d", u);
@@ -404,6 +414,41 @@ int se_p16_wiener_batch(se_ctx *ctx, const void *samples, int is_f32, const int6
     };
     return ns_batch_run(ctx, 16, a, samples, is_f32 ? sizeof(float) : sizeof(int16_t), offsets, block_offsets, nullptr,
                         n_utts, outs, 3, n_rows, offsetof(NsLaunch, n_rows), mem);
+}
+
+int se_ns_spectra_batch(se_ctx *ctx, int profile, const void *samples, int is_f32, const int64_t *offsets, int n_utts,
+                        float *spectra, int32_t *produced, const int64_t *block_offsets, int mem)
+{
+    SE_ENTER(ctx, mem, "se_ns_spectra_batch");
+    if ((profile != 8 && profile != 16) || n_utts < 0 || (n_utts > 0 && (!samples || !spectra || !block_offsets)) ||
+        (profile == 8 && is_f32)) {
+        set_error("se_ns_spectra_batch: bad arguments");
+        return SE_EINVAL;
+    }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_ns_spectra_batch"));
+    SE_TRY(check_offsets(block_offsets, n_utts, "se_ns_spectra_batch(block_offsets)"));
+    if (offsets[0] != 0 || block_offsets[0] != 0) { set_error("se_ns_spectra_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    const int shift = profile == 8 ? 80 : 160, spec = profile == 8 ? 65 : 129;
+    for (int u = 0; u < n_utts; u++)
+        if (block_offsets[u + 1] - block_offsets[u] < (offsets[u + 1] - offsets[u]) / shift) {
+            set_error("se_ns_spectra_batch: block_offsets too small for utterance %d", u);
+            return SE_EINVAL;
+        }
+    NsLaunch a;
+    std::memset(&a, 0, sizeof a);
+    a.is_f32 = is_f32 ? 1 : 0;
+    a.zero_check = profile == 8 ? 1 : 2;
+    a.total_blocks = block_offsets[n_utts];
+    // P8 indexes per-call outputs through its trace offsets (aux 2), P16 through block_offsets (aux 1)
+    const int idx = profile == 8 ? kIdxAux2 : kIdxAux1;
+    NsOut outs[] = {
+        {spectra, sizeof(float) * 8 * (uint64_t)spec, idx, true, false, kSlotOut, offsetof(NsLaunch, spec_trace)},
+        {produced, sizeof(int32_t), idx, true, false, kSlotOut2, offsetof(NsLaunch, produced)},
+    };
+    return ns_batch_run(ctx, profile, a, samples, is_f32 ? sizeof(float) : sizeof(int16_t), offsets,
+                        profile == 8 ? nullptr : block_offsets, profile == 8 ? block_offsets : nullptr, n_utts, outs, 2,
+                        nullptr, 0, mem);
 }
 
 }  // extern "C"

@@ -6,7 +6,7 @@ extern "C" {
 int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
                      int16_t *out, int flags, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_subband_batch"));
+    SE_ENTER(ctx, mem, "se_subband_batch");
     if (n_utts < 0 || (n_utts > 0 && (!samples || !out))) { set_error("se_subband_batch: bad arguments"); return SE_EINVAL; }
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_subband_batch"));
@@ -31,7 +31,7 @@ int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
 int se_ibm_batch(se_ctx *ctx, const int16_t *pure, const int16_t *noise, const int64_t *offsets, int n_utts,
                  float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_ibm_batch"));
+    SE_ENTER(ctx, mem, "se_ibm_batch");
     if (n_utts < 0 || (n_utts > 0 && (!pure || !noise || !frame_offsets))) { set_error("se_ibm_batch: bad arguments"); return SE_EINVAL; }
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_ibm_batch"));
@@ -68,7 +68,7 @@ int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
                      const float *mask, const int64_t *frame_offsets, int mode, int flags,
                      int16_t *out, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_resynth_batch"));
+    SE_ENTER(ctx, mem, "se_resynth_batch");
     if (n_utts < 0 || (n_utts > 0 && (!samples || !mask || !frame_offsets || !out)) || mode < 0 || mode > 2) {
         set_error("se_resynth_batch: bad arguments");
         return SE_EINVAL;
@@ -93,20 +93,21 @@ int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
     SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
     SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
     SE_TRY(stage_in(ctx, kSlotIn2, mask, sizeof(float) * 64 * frames, mem, &d_mask));
-    SE_TRY(stage_out(ctx, kSlotOut, out, sizeof(int16_t) * total, mem, false, &d_out));
+    const uint64_t out_elem = (flags & SE_FLAG_OUT_F32) ? sizeof(float) : sizeof(int16_t);
+    SE_TRY(stage_out(ctx, kSlotOut, out, out_elem * total, mem, false, &d_out));
     a.samples = (const int16_t *)d_in;
     a.utt_begin = 0;
     a.utt_count = n_utts;
     a.flags = flags;
     SE_TRY(launch_resynth(ctx, a, offsets, (const float *)d_mask, frame_offsets, mode, (int16_t *)d_out));
-    SE_TRY(stage_out_copy(ctx, out, d_out, sizeof(int16_t) * total, mem));
+    SE_TRY(stage_out_copy(ctx, out, d_out, out_elem * total, mem));
     return leave(ctx, mem);
 }
 
 int se_addnoise_batch(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy,
                       const int64_t *offsets, int n_utts, int db, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_addnoise_batch"));
+    SE_ENTER(ctx, mem, "se_addnoise_batch");
     if (n_utts < 0 || (n_utts > 0 && (!pure || !noise || !noisy))) { set_error("se_addnoise_batch: bad arguments"); return SE_EINVAL; }
     if (n_utts == 0) return SE_OK;
     SE_TRY(check_offsets(offsets, n_utts, "se_addnoise_batch"));
@@ -128,7 +129,7 @@ int se_addnoise_batch(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t 
 
 int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_rfft_batch"));
+    SE_ENTER(ctx, mem, "se_rfft_batch");
     if (count < 0 || (count > 0 && !x)) { set_error("se_rfft_batch: bad arguments"); return SE_EINVAL; }
     if (!((n == 256 && m == 8) || (n == 512 && m == 8))) {
         set_error("se_rfft_batch: only (256,8) and (512,8) are on the hot path");
@@ -146,7 +147,7 @@ int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem)
 
 int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_wave_proc_batch"));
+    SE_ENTER(ctx, mem, "se_wave_proc_batch");
     if (n_frames < 0 || (n_frames > 0 && !frames)) { set_error("se_wave_proc_batch: bad arguments"); return SE_EINVAL; }
     if (n_frames == 0) return SE_OK;
     const uint64_t bytes = sizeof(float) * 200u * (uint64_t)n_frames;
@@ -160,7 +161,7 @@ int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem)
 
 int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float *coef14, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_comp_ceps_batch"));
+    SE_ENTER(ctx, mem, "se_comp_ceps_batch");
     if (n_frames < 0 || (n_frames > 0 && (!frames201 || !coef14))) { set_error("se_comp_ceps_batch: bad arguments"); return SE_EINVAL; }
     if (n_frames == 0) return SE_OK;
     const void *d_in = nullptr;
@@ -174,7 +175,7 @@ int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float 
 
 int se_qmf_split_batch(se_ctx *ctx, const int16_t *samples, int64_t n, int count, float *lp, float *hp, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_qmf_split_batch"));
+    SE_ENTER(ctx, mem, "se_qmf_split_batch");
     if (count < 0 || n < 0 || n % 160 != 0 || (count > 0 && n > 0 && (!samples || !lp || !hp))) {
         set_error("se_qmf_split_batch: bad arguments (n must be a multiple of 160)");
         return SE_EINVAL;
@@ -195,7 +196,7 @@ int se_qmf_split_batch(se_ctx *ctx, const int16_t *samples, int64_t n, int count
 int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n,
                        int count, int flags, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_gammatone_batch"));
+    SE_ENTER(ctx, mem, "se_gammatone_batch");
     if (count < 0 || n < 0 || (count > 0 && (!in || !out || !channel))) { set_error("se_gammatone_batch: bad arguments"); return SE_EINVAL; }
     if (count == 0 || n == 0) return SE_OK;
     if (mem == SE_MEM_HOST)
@@ -212,9 +213,57 @@ int se_gammatone_batch(se_ctx *ctx, const float *in, float *out, const int32_t *
     return leave(ctx, mem);
 }
 
+int se_gammatone_coef_batch(se_ctx *ctx, const float *in, float *out, const float *coef, int64_t n, int count, int flags,
+                            int mem)
+{
+    SE_ENTER(ctx, mem, "se_gammatone_coef_batch");
+    if (count < 0 || n < 0 || (count > 0 && (!in || !out || !coef))) { set_error("se_gammatone_coef_batch: bad arguments"); return SE_EINVAL; }
+    if (count == 0 || n == 0) return SE_OK;
+    const uint64_t bytes = sizeof(float) * (uint64_t)n * (uint64_t)count;
+    const void *d_in = nullptr, *d_coef = nullptr;
+    void *d_out = nullptr;
+    SE_TRY(stage_in(ctx, kSlotIn, in, bytes, mem, &d_in));
+    SE_TRY(stage_in(ctx, kSlotIn2, coef, sizeof(float) * 3 * (uint64_t)count, SE_MEM_HOST, &d_coef));   // coef: host array
+    SE_TRY(stage_out(ctx, kSlotOut, out, bytes, mem, false, &d_out));
+    SE_TRY(launch_gammatone_coef(ctx, (const float *)d_in, (float *)d_out, (const float *)d_coef, n, count, flags));
+    SE_TRY(stage_out_copy(ctx, out, d_out, bytes, mem));
+    return leave(ctx, mem);
+}
+
+int se_ibm_rows_batch(se_ctx *ctx, const int16_t *pure64, const int16_t *noise64, const int64_t *offsets, int n_utts,
+                      float *irm, uint64_t *ibm_bits, const int64_t *frame_offsets, int mem)
+{
+    SE_ENTER(ctx, mem, "se_ibm_rows_batch");
+    if (n_utts < 0 || (n_utts > 0 && (!pure64 || !noise64 || !frame_offsets))) { set_error("se_ibm_rows_batch: bad arguments"); return SE_EINVAL; }
+    if (n_utts == 0) return SE_OK;
+    SE_TRY(check_offsets(offsets, n_utts, "se_ibm_rows_batch"));
+    SE_TRY(check_offsets(frame_offsets, n_utts, "se_ibm_rows_batch(frame_offsets)"));
+    if (offsets[0] != 0 || frame_offsets[0] != 0) { set_error("se_ibm_rows_batch: offsets[0] must be 0"); return SE_EINVAL; }
+    for (int u = 0; u < n_utts; u++)
+        if (frame_offsets[u + 1] - frame_offsets[u] < se_ibm_num_frames(offsets[u + 1] - offsets[u])) {
+            set_error("se_ibm_rows_batch: frame_offsets too small for utterance %d", u);
+            return SE_EINVAL;
+        }
+    const uint64_t total = (uint64_t)offsets[n_utts], frames = (uint64_t)frame_offsets[n_utts];
+    const int64_t *d_off = nullptr, *d_fo = nullptr;
+    const void *d_p = nullptr, *d_n = nullptr;
+    void *d_irm = nullptr, *d_bits = nullptr;
+    SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &d_off));
+    SE_TRY(upload_offsets(ctx, kSlotOffsets2, frame_offsets, n_utts + 1, &d_fo));
+    SE_TRY(stage_in(ctx, kSlotIn, pure64, sizeof(int16_t) * 64 * total, mem, &d_p));
+    SE_TRY(stage_in(ctx, kSlotIn2, noise64, sizeof(int16_t) * 64 * total, mem, &d_n));
+    SE_TRY(stage_out(ctx, kSlotOut, irm, sizeof(float) * 64 * frames, mem, true, &d_irm));
+    SE_TRY(stage_out(ctx, kSlotOut2, ibm_bits, sizeof(uint64_t) * frames, mem, true, &d_bits));
+    SE_TRY(launch_ibm_rows(ctx, (const int16_t *)d_p, (const int16_t *)d_n, d_off, n_utts, (float *)d_irm, (uint64_t *)d_bits,
+                           d_fo, (int64_t)frames));
+    SE_TRY(stage_out_copy(ctx, irm, d_irm, sizeof(float) * 64 * frames, mem));
+    SE_TRY(stage_out_copy(ctx, ibm_bits, d_bits, sizeof(uint64_t) * frames, mem));
+    return leave(ctx, mem);
+}
+
 int se_haircell_batch(se_ctx *ctx, const float *in, float *out, int64_t n, int count, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_haircell_batch"));
+    SE_ENTER(ctx, mem, "se_haircell_batch");
     if (count < 0 || n < 0 || (count > 0 && (!in || !out))) { set_error("se_haircell_batch: bad arguments"); return SE_EINVAL; }
     if (count == 0 || n == 0) return SE_OK;
     const uint64_t bytes = sizeof(float) * (uint64_t)n * (uint64_t)count;
@@ -319,7 +368,7 @@ int64_t se_extract_wiener_num_blocks(int64_t n_samples) { return n_samples > 0 ?
 int se_extract_wiener_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
                             float *gains, int32_t *flags, int32_t *n_rows, const int64_t *block_offsets, int mem)
 {
-    SE_TRY(enter(ctx, mem, "se_extract_wiener_batch"));
+    SE_ENTER(ctx, mem, "se_extract_wiener_batch");
     if (n_utts < 0 || (n_utts > 0 && (!samples || !block_offsets || (!gains && !flags)))) {
         set_error("se_extract_wiener_batch: bad arguments");
         return SE_EINVAL;

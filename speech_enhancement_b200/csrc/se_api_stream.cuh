@@ -63,6 +63,7 @@ int se_ns_stream_create(se_ctx *ctx, int profile, se_ns_stream **out)
 void se_ns_stream_destroy(se_ns_stream *s)
 {
     if (!s) return;
+    std::lock_guard<std::recursive_mutex> guard(s->ctx->mu);
     cudaSetDevice(s->ctx->device);
     cudaStreamSynchronize(s->ctx->cur->stream);
     void *bufs[] = {s->d_state, s->d_in, s->d_out, s->d_produced, s->d_flags, s->d_gains, s->d_rows, s->d_offsets, s->d_ceps};
@@ -93,6 +94,7 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
     if (n_ceps) *n_ceps = 0;
     if (n_blocks == 0) return SE_OK;
     se_ctx *ctx = s->ctx;
+    std::lock_guard<std::recursive_mutex> guard(ctx->mu);    // the handle may be used on any host thread
     SE_CUDA(cudaSetDevice(ctx->device));
     SE_TRY(stream_reserve(s, (uint64_t)n_blocks));
     const int shift = s->profile == 8 ? 80 : 160;

@@ -141,6 +141,38 @@ __global__ void __launch_bounds__(128) ibm_kernel(const int16_t *pure, const int
     }
 }
 
+// make_single_IBM on MATERIALISED sub-band rows (what the reference reads back from the 2 x 64 wav files that
+// subbband() wrote, show_IBM.cpp:118-144): rows are laid out like se_subband_batch's output.  One CTA per frame of
+// the batch, thread = (signal, channel); the three Parseval sums run over the frame's 320 samples in the same order
+// as in ibm_kernel, so both entry points give identical values on identical sub-band samples.
+__global__ void __launch_bounds__(128) ibm_rows_kernel(const int16_t *pure64, const int16_t *noise64, const int64_t *offsets,
+                                                       int n_utts, float *irm, uint32_t *bits, const int64_t *frame_offsets)
+{
+    __shared__ float s_pow[2][64];
+    const int64_t F = blockIdx.x;
+    int lo = 0, hi = n_utts;                       // utterance u with frame_offsets[u] <= F < frame_offsets[u + 1]
+    while (hi - lo > 1) {
+        const int mid = (lo + hi) >> 1;
+        if (frame_offsets[mid] <= F) lo = mid; else hi = mid;
+    }
+    const int u = lo, sig = threadIdx.x >> 6, c = threadIdx.x & 63, warp = c >> 5;
+    const int64_t off = offsets[u], n = offsets[u + 1] - off, f = F - frame_offsets[u];
+    const int64_t frames = (n >= 320) ? (n - 320) / 160 + 1 : 0;
+    if (f >= frames) return;                       // spare capacity rows of this utterance (uniform over the CTA)
+    const int16_t *x = (sig ? noise64 : pure64) + 64 * off + (int64_t)c * n + 160 * f;
+    FrameAcc a;
+    acc_reset(a);
+    for (int k = 0; k < 320; k++) acc_add(a, __fmul_rn((float)x[k], c_ibm_win[k]), k);
+    s_pow[sig][c] = acc_power(a);
+    __syncthreads();
+    if (sig == 0) {
+        const float sp = s_pow[0][c], sn = s_pow[1][c];
+        if (irm) irm[F * 64 + c] = sp / __fadd_rn(sp, sn);
+        const unsigned b = __ballot_sync(0xffffffffu, sn < sp);
+        if (bits && (c & 31) == 0) bits[F * 2 + warp] = b;
+    }
+}
+
 }  // namespace se
 
 #include "se_g64_resynth.cuh"

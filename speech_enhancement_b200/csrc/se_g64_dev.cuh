@@ -142,6 +142,12 @@ __device__ __forceinline__ float hc_step(HcState &s, const float *hc, float in)
 }
 
 // (short) of a float as x86 does it: cvttss2si to int32, keep the low 16 bits.
-__device__ __forceinline__ short cast_i16(float v) { return (short)__float2int_rz(v); }
+// Out of int32 range (or NaN) cvttss2si returns the "integer indefinite" 0x80000000, whose low 16 bits are 0;
+// __float2int_rz would saturate positive overflow to 0x7fffffff (low 16 bits -1) instead.
+__device__ __forceinline__ short cast_i16(float v)
+{
+    if (!(v > -2147483904.0f && v < 2147483648.0f)) return (short)0;
+    return (short)__float2int_rz(v);
+}
 
 }  // namespace se

@@ -61,12 +61,13 @@ int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, cons
 }
 
 template <bool EXACT>
-static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const GtItem *items, const float *mask, int16_t *out)
+static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const GtItem *items, const float *mask, int16_t *out,
+                       float *out_f)
 {
     if (mode == SE_RESYNTH_IBM)
-        gt_bwd_kernel<EXACT, SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, items, mask, out);
+        gt_bwd_kernel<EXACT, SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, items, mask, out, out_f);
     else
-        gt_bwd_kernel<EXACT, SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, items, mask, out);
+        gt_bwd_kernel<EXACT, SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, items, mask, out, out_f);
 }
 
 // h_offsets / h_frame_offsets: host copies (work items are planned on the host and grouped against the
@@ -74,6 +75,7 @@ static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const G
 int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, const float *mask,
                    const int64_t *h_frame_offsets, int mode, int16_t *out)
 {
+    float *out_f = (a.flags & SE_FLAG_OUT_F32) ? reinterpret_cast<float *>(out) : nullptr;
     const bool exact = (a.flags & SE_FLAG_EXACT) != 0;
     const int end = a.utt_begin + a.utt_count;
     const int64_t max_rows = (int64_t)(ctx->scratch_limit / (64 * sizeof(float)));
@@ -96,9 +98,9 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
         else gt_fwd_fast_kernel<<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
         prof_end(ctx, SE_K_GT_FWD);
         prof_begin(ctx, SE_K_GT_BWD);
-        if (exact) launch_bwd<true>(ctx, mode, count, Y, it, mask, out);
-        else if (mode == SE_RESYNTH_IBM) gt_bwd_fast_kernel<SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out);
-        else gt_bwd_fast_kernel<SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out);
+        if (exact) launch_bwd<true>(ctx, mode, count, Y, it, mask, out, out_f);
+        else if (mode == SE_RESYNTH_IBM) gt_bwd_fast_kernel<SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out, out_f);
+        else gt_bwd_fast_kernel<SE_RESYNTH_ORI><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out, out_f);
         prof_end(ctx, SE_K_GT_BWD);
         SE_CUDA(cudaGetLastError());
         items.clear();
@@ -144,6 +146,29 @@ int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *ch
     return SE_OK;
 }
 
+int launch_gammatone_coef(se_ctx *ctx, const float *in, float *out, const float *coef, int64_t n, int count, int flags)
+{
+    if (count <= 0) return SE_OK;
+    if (flags & SE_FLAG_EXACT) gammatone_coef_kernel<true><<<(count + 63) / 64, 64, 0, ctx->cur->stream>>>(in, out, coef, n, count);
+    else gammatone_coef_kernel<false><<<(count + 63) / 64, 64, 0, ctx->cur->stream>>>(in, out, coef, n, count);
+    ctx->launches++;
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
+int launch_ibm_rows(se_ctx *ctx, const int16_t *pure64, const int16_t *noise64, const int64_t *offsets, int n_utts,
+                    float *irm, uint64_t *bits, const int64_t *frame_offsets, int64_t total_frames)
+{
+    if (n_utts <= 0 || total_frames <= 0) return SE_OK;
+    if (total_frames > 0x7fffffff) { set_error("se_ibm_rows_batch: more than 2^31 frames in one call"); return SE_EINVAL; }
+    prof_begin(ctx, SE_K_IBM);
+    ibm_rows_kernel<<<(unsigned)total_frames, 128, 0, ctx->cur->stream>>>(pure64, noise64, offsets, n_utts, irm,
+                                                                        reinterpret_cast<uint32_t *>(bits), frame_offsets);
+    prof_end(ctx, SE_K_IBM);
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
 int launch_haircell(se_ctx *ctx, const float *in, float *out, int64_t n, int count)
 {
     if (count <= 0) return SE_OK;
@@ -163,7 +188,8 @@ int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *n
     const float db_lin = (float)std::pow(10.0, db / 10.0);
     prof_begin(ctx, SE_K_ADDNOISE);
     addnoise_gain_kernel<<<(n_utts + 63) / 64, 64, 0, ctx->cur->stream>>>(pure, noise, offsets, n_utts, db_lin, (float *)g);
-    addnoise_mix_kernel<<<dim3(64, n_utts), 256, 0, ctx->cur->stream>>>(pure, noise, noisy, offsets, (const float *)g);
+    if (n_utts > (0x7fffffff >> 6)) { set_error("se_addnoise_batch: more than 2^25 utterances in one call"); return SE_EINVAL; }
+    addnoise_mix_kernel<<<(unsigned)n_utts * 64u, 256, 0, ctx->cur->stream>>>(pure, noise, noisy, offsets, (const float *)g);
     prof_end(ctx, SE_K_ADDNOISE);
     SE_CUDA(cudaGetLastError());
     return SE_OK;

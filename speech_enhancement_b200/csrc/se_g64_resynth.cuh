@@ -52,7 +52,7 @@ __global__ void __launch_bounds__(64) gt_fwd_kernel(const int16_t *samples, cons
 // weight of sample n (hop h=n/160, r=n%160): fall[r]*m[h] (frame h's falling half, added first)
 //                                          + rise[r]*m[h+1] (frame h+1's rising half), gated per mode.
 template <bool EXACT, int MODE>
-__global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem *items, const float *mask, int16_t *out)
+__global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem *items, const float *mask, int16_t *out, float *out_f)
 {
     constexpr int T = 32;
     __shared__ float tile[2][T][65];
@@ -115,7 +115,9 @@ __global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem
             float acc = 0.0f;
 #pragma unroll 8
             for (int ch = 0; ch < 64; ch++) acc = __fadd_rn(acc, tile[buf][c][ch]);
-            o[it.b - 1 - (m0 + c)] = cast_i16(acc);
+            // resynth_e[] (float) and its (short) cast, extractwav.cpp:119-122; SE_FLAG_OUT_F32 returns the float
+            if (out_f) out_f[it.sample_off + it.b - 1 - (m0 + c)] = acc;
+            else o[it.b - 1 - (m0 + c)] = cast_i16(acc);
         }
     }
 }
@@ -157,7 +159,7 @@ __global__ void __launch_bounds__(64) gt_fwd_fast_kernel(const int16_t *samples,
 // (160 = 5 x 32): the two mask values that weight a hop are fetched once per tile, and the raised-cosine
 // weight is  w = m[h+1] + (m[h] - m[h+1]) * fall[r]   (fall[r] + rise[r] = 1).
 template <int MODE>
-__global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const GtItem *items, const float *mask, int16_t *out)
+__global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const GtItem *items, const float *mask, int16_t *out, float *out_f)
 {
     constexpr int T = 32;
     __shared__ float tile[2][T][65];
@@ -222,7 +224,8 @@ __global__ void __launch_bounds__(64) gt_bwd_fast_kernel(const float *Y, const G
             float acc = 0.0f;
 #pragma unroll 16
             for (int ch = 0; ch < 64; ch++) acc += tile[buf][c][ch];
-            o[pos - c] = cast_i16(acc);
+            if (out_f) out_f[it.sample_off + pos - c] = acc;
+            else o[pos - c] = cast_i16(acc);
         }
         pos -= len;
         step += len;
@@ -238,6 +241,18 @@ __global__ void gammatone_kernel(const float *in, float *out, const int32_t *cha
     const int i = blockIdx.x * blockDim.x + threadIdx.x;
     if (i >= count) return;
     const GtCoef k = load_coef(channel[i]);
+    GtState g; gt_reset(g);
+    for (int64_t t = 0; t < n; t++) out[i * n + t] = gt_step<EXACT>(g, k, in[i * n + t]);
+}
+
+// gammaToneFilter with caller-supplied coefficients (any cf / bw / midEarCoeff, HuWang.h:49): coef[i] = {f1, f2, gain}
+template <bool EXACT>
+__global__ void gammatone_coef_kernel(const float *in, float *out, const float *coef, int64_t n, int count)
+{
+    const int i = blockIdx.x * blockDim.x + threadIdx.x;
+    if (i >= count) return;
+    GtCoef k;
+    k.f1 = coef[3 * i]; k.f2 = coef[3 * i + 1]; k.gain = coef[3 * i + 2]; k.mid = 1.0f;
     GtState g; gt_reset(g);
     for (int64_t t = 0; t < n; t++) out[i * n + t] = gt_step<EXACT>(g, k, in[i * n + t]);
 }
@@ -269,10 +284,10 @@ __global__ void addnoise_gain_kernel(const int16_t *pure, const int16_t *noise, 
 __global__ void addnoise_mix_kernel(const int16_t *pure, int16_t *noise, int16_t *noisy, const int64_t *offsets,
                                     const float *gain)
 {
-    const int u = blockIdx.y;
+    // 64 CTAs per utterance, utterance index on grid.x (grid.y is capped at 65 535, a corpus of short files is not)
+    const int u = blockIdx.x >> 6, part = blockIdx.x & 63;
     const float g = gain[u];
-    for (int64_t i = offsets[u] + blockIdx.x * blockDim.x + threadIdx.x; i < offsets[u + 1];
-         i += (int64_t)gridDim.x * blockDim.x) {
+    for (int64_t i = offsets[u] + part * blockDim.x + threadIdx.x; i < offsets[u + 1]; i += (int64_t)64 * blockDim.x) {
         const short z = cast_i16(__fmul_rn((float)noise[i], g));   // Q4: cast before the multiply
         noise[i] = z;
         noisy[i] = (short)((int)pure[i] + (int)z);

@@ -2,6 +2,7 @@
 #pragma once
 #include <cuda_runtime.h>
 #include <stdint.h>
+#include <mutex>
 #include <string>
 #include <vector>
 #include "../../include/se_b200.h"
@@ -97,7 +98,7 @@ struct NsLaunch {
     int load_state;
     int32_t *produced;           // optional per-block bitmask: 1 = shift output, 2 = stage 0 ran, 4 = skipped
     int zero_check;              // 0 none (DoNoiseSup), 1 leading frames only (DoAdvProcess), 2 anywhere (func_Wiener)
-    float *spec_trace;           // optional debug [total_blocks][6][spec]
+    float *spec_trace;           // optional [block][8][spec] spectral state per block (se_ns_spectra_batch)
     // work queue
     int *work_counter;           // device int, zeroed before launch
 };
@@ -126,6 +127,11 @@ struct se_lane {
 };
 
 struct se_ctx {
+    // Every public entry point that works on a context (or on a stream created from it) holds this lock for the call:
+    // handles may be created on one host thread and used on another (the reference's handles are plain heap structs);
+    // calls on ONE context serialise, calls on different contexts overlap.
+    std::recursive_mutex mu;
+    int exact;                  // se_ctx_set_exact: NoiseSup / CompCeps / feature chains in the reference's arithmetic
     int device;
     int sm_count;
     cudaStream_t own_stream;
@@ -191,6 +197,9 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
                    const int64_t *h_frame_offsets, int mode, int16_t *out);
 int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n, int count,
                      int flags);
+int launch_gammatone_coef(se_ctx *ctx, const float *in, float *out, const float *coef, int64_t n, int count, int flags);
+int launch_ibm_rows(se_ctx *ctx, const int16_t *pure64, const int16_t *noise64, const int64_t *offsets, int n_utts,
+                    float *irm, uint64_t *bits, const int64_t *frame_offsets, int64_t total_frames);
 int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy, const int64_t *offsets,
                     int n_utts, int db);
 int upload_g64_tables(se_ctx *ctx);

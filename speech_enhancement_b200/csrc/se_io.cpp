@@ -46,9 +46,14 @@ SE_EXPORT int se_wav_read(const char *path, int channel, short **data, long *n_s
                 return -4;      // only PCM16 is what the drivers read (CWave::PCM)
             }
             // tolerate a wrong/streamed size field: read what is there
+            // (a streamed 0xFFFFFFFF size must not allocate 4 GB: clamp to what is left in the file)
+            const long here = ftell(fp);
+            long left = -1;
+            if (here >= 0 && fseek(fp, 0, SEEK_END) == 0) { left = ftell(fp) - here; fseek(fp, here, SEEK_SET); }
+            const size_t want = (left >= 0 && (unsigned long)left < (unsigned long)sz) ? (size_t)left : (size_t)sz;
             std::vector<unsigned char> raw;
-            raw.resize(sz);
-            const size_t got = fread(raw.data(), 1, sz, fp);
+            raw.resize(want);
+            const size_t got = fread(raw.data(), 1, want, fp);
             fclose(fp);
             const long frames = (long)(got / (2u * (unsigned)n_chan));
             short *out = (short *)malloc(sizeof(short) * (size_t)(frames > 0 ? frames : 1));

@@ -226,7 +226,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 }
                 s.nb_in1++;
                 __syncwarp();
-                float *trace = a.spec_trace ? a.spec_trace + (blk0 + b) * 6 * P::SPEC : nullptr;
+                float *trace = a.spec_trace ? a.spec_trace + ((PROF == 8 ? tr0 : blk0) + b) * 8 * P::SPEC : nullptr;
 #pragma unroll 1
                 for (int fstage = 0; fstage < 2; fstage++) {
                     // stage 0 runs from the 3rd block on, stage 1 from the 3rd stage-0 output on
@@ -355,7 +355,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 }
             }
             if (a.produced && lane == 0)
-                a.produced[blk0 + b] = (produced ? 1 : 0) | (ran0 ? 2 : 0) | (process ? 0 : 4);
+                a.produced[(PROF == 8 ? tr0 : blk0) + b] = (produced ? 1 : 0) | (ran0 ? 2 : 0) | (process ? 0 : 4);
             __syncwarp();
         }
 

@@ -268,9 +268,12 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
             den_sum += den[r];
             noise_sum += noise[r];
             if (spec_trace) {
-                spec_trace[(3 * fstage + 0) * P::SPEC + b] = sqrtf(psd[r]);
+                // the SPECTRUM state as FilterCalc leaves it (NoiseSup.c:519-560): nSigSE, noiseSE, denSigSE, and
+                // sqrt(PSDMeaned) (a local of DoNoiseSup in the reference) -- se_ns_spectra_batch
+                spec_trace[(3 * fstage + 0) * P::SPEC + b] = fsqrt(psd[r]);
                 spec_trace[(3 * fstage + 1) * P::SPEC + b] = noise[r];
                 spec_trace[(3 * fstage + 2) * P::SPEC + b] = den[r];
+                spec_trace[(6 + fstage) * P::SPEC + b] = fsqrt(pm);
             }
         }
     }

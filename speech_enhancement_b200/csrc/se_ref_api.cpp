@@ -187,11 +187,36 @@ SE_EXPORT void rfft(float *x, int n, int m)
 // ---------------------------------------------------------------------------------------------
 // etsi/cpp/ParmInterface.h: AdvProcessAlloc / Init / DoAdvProcess / Delete on an opaque handle
 // ---------------------------------------------------------------------------------------------
+struct NoiseSupStructX { se_ns_stream *ns; };     // what DoNoiseSupAlloc hands out: one NoiseSup state on the GPU
+
 struct FEParamsX {
-    se_ns_stream *ns;
+    NoiseSupStructX *NSX;     // the member AdvProcessAlloc fills with DoNoiseSupAlloc() (ParmInterface.c:83)
+    se_ns_stream *ns;         // == NSX->ns
     int feat_ready;
     int gate;          // zero-frame gate currently set on the stream (1 = DoAdvProcess, 0 = bare DoNoiseSup)
+    // as-shipped DoAdvProcess never reaches DoVADProc (ParmInterface.c:274-311 is commented out), so all
+    // FlushAdvProcess / DoVADFlush (VAD.c:342-431) ever see is the freshly initialised VAD structure:
+    int ns_frames;            // vadNS.nbFrame[0]
+    int frame_counter;        // FEParamsX.FrameCounter as DoNoiseSup last published it (NoiseSup.c:1366)
+    int vad_focus, vad_flush_focus;
 };
+
+SE_EXPORT NoiseSupStructX *DoNoiseSupAlloc(void)
+{
+    se_ctx *ctx = default_ctx("DoNoiseSupAlloc");
+    if (!ctx) return nullptr;
+    NoiseSupStructX *n = new NoiseSupStructX();
+    n->ns = nullptr;
+    if (report("DoNoiseSupAlloc", se_ns_stream_create(ctx, 8, &n->ns)) != SE_OK) { delete n; return nullptr; }
+    return n;
+}
+
+SE_EXPORT void DoNoiseSupDelete(NoiseSupStructX *NSX)
+{
+    if (!NSX) return;
+    se_ns_stream_destroy(NSX->ns);
+    delete NSX;
+}
 
 SE_EXPORT FEParamsX *AdvProcessAlloc(int SamplingFrequency)
 {
@@ -202,17 +227,26 @@ SE_EXPORT FEParamsX *AdvProcessAlloc(int SamplingFrequency)
     se_ctx *ctx = default_ctx("AdvProcessAlloc");
     if (!ctx) return nullptr;
     FEParamsX *p = new FEParamsX();
-    p->ns = nullptr;
+    p->NSX = DoNoiseSupAlloc();                  // ParmInterface.c:83
+    if (!p->NSX) { delete p; return nullptr; }
+    p->ns = p->NSX->ns;
     p->feat_ready = 0;
-    if (report("AdvProcessAlloc", se_ns_stream_create(ctx, 8, &p->ns)) != SE_OK) { delete p; return nullptr; }
     se_ns_stream_set_zero_gate(p->ns, 1);        // DoAdvProcess skips leading all-zero frames
     p->gate = 1;
+    p->ns_frames = p->frame_counter = 0;
+    p->vad_focus = 0;
+    p->vad_flush_focus = -1;
     return p;
 }
 
 SE_EXPORT void AdvProcessInit(FEParamsX *This)
 {
-    if (This) { se_ns_stream_reset(This->ns); This->feat_ready = 0; }
+    if (!This) return;
+    se_ns_stream_reset(This->ns);
+    This->feat_ready = 0;
+    This->ns_frames = This->frame_counter = 0;   // ParmInterface.c:184
+    This->vad_focus = 0;                         // DoVADInit, VAD.c:137-142
+    This->vad_flush_focus = -1;
 }
 
 SE_EXPORT int DoAdvProcess(short *CurrentFrame, short *OutBuf, float *FeatBuf, FEParamsX *This)
@@ -226,10 +260,35 @@ SE_EXPORT int DoAdvProcess(short *CurrentFrame, short *OutBuf, float *FeatBuf, F
     if (report("DoAdvProcess", se_ns_stream_push(This->ns, in, 1, out, &produced, nullptr, nullptr, nullptr,
                                                  FeatBuf ? ceps : nullptr, &n_ceps)) != SE_OK)
         return 0;
+    if (produced & 4) {
+        // leading all-zero frame (ParmInterface.c:314-327): null MFCC vector FeatureBuffer[0..NUM_CEP_COEFF],
+        // VAD = NON_SPEECH_FRAME, return TRUE; DenoiseBuffer is not touched
+        if (FeatBuf) std::memset(FeatBuf, 0, 14 * sizeof(float));
+        return 1;
+    }
+    if (produced & 2) This->ns_frames++;                          // vadNS.nbFrame[0]: stage-1 frames so far
+    if (produced & 3) This->frame_counter = This->ns_frames;      // published by every stage that ran (NoiseSup.c:1366)
     if (!(produced & 1)) return 0;
     if (OutBuf)
         for (int i = 0; i < 80; i++) OutBuf[i] = (short)(int)out[i];   // ParmInterface.c:264-268: C cast
     if (FeatBuf && n_ceps > 0) { std::memcpy(FeatBuf, ceps, sizeof ceps); This->feat_ready = 1; }
+    return 1;
+}
+
+// FlushAdvProcess (ParmInterface.c:347-355) -> DoVADFlush (VAD.c:342-431) on the VAD structure as DoVADInit left it
+// (the as-shipped DoAdvProcess never feeds it): the 7-slot delay line is all zeros and every counter is 0, so the
+// flush walks Focus once around the ring -- TRUE six times, then FALSE -- incrementing FrameCounter, and from
+// FrameCounter > BUFFER_SIZE + 3 = 10 on it copies an all-zero row with VAD flag 0 into FeatureBuffer[0..14].
+SE_EXPORT int FlushAdvProcess(float *FeatBuf, FEParamsX *This)
+{
+    if (!This) return 0;
+    if (This->vad_flush_focus == -1) This->vad_flush_focus = This->vad_focus;
+    int focus = This->vad_focus + 1;
+    if (focus == 7) focus = 0;
+    if (focus == This->vad_flush_focus) return 0;
+    This->frame_counter++;
+    if (This->frame_counter > 7 + 3 && FeatBuf) std::memset(FeatBuf, 0, 15 * sizeof(float));
+    This->vad_focus = focus;
     return 1;
 }
 
@@ -267,7 +326,7 @@ SE_EXPORT int DoCompCeps(float *Data, float *Coef, FEParamsX *)
 SE_EXPORT void AdvProcessDelete(FEParamsX **This)
 {
     if (!This || !*This) return;
-    se_ns_stream_destroy((*This)->ns);
+    DoNoiseSupDelete((*This)->NSX);              // ParmInterface.c:376
     delete *This;
     *This = nullptr;
 }
@@ -412,4 +471,34 @@ SE_EXPORT int se_gammatone_filter(const float *input, float *output, int channel
     if (!ctx) return SE_ENODEVICE;
     const int32_t ch = channel;
     return report("se_gammatone_filter", se_gammatone_batch(ctx, input, output, &ch, sigLength, 1, SE_FLAG_EXACT, SE_MEM_HOST));
+}
+
+// gammaToneFilter with the channel passed by value (HuWang.h:49): any cf / bw / midEarCoeff.  The three derived
+// coefficients follow extractwav.cpp:176-183 (C++: exp / cos / sin / pow of float arguments as the reference compiles
+// them -- float overloads for exp/cos/sin, double pow).
+SE_EXPORT int se_gammatone_filter_params(const float *input, float *output, float cf, float bw, float midEarCoeff,
+                                         long sigLength)
+{
+    se_ctx *ctx = default_ctx("se_gammatone_filter_params");
+    if (!ctx) return SE_ENODEVICE;
+    const float dt = 1 / (float)16000;
+    const float two_pi_t = (float)(2 * 3.1415926535897932384626433832795 * (double)dt);
+    float coef[3];
+    const float z = expf(-two_pi_t * bw);
+    coef[0] = cosf(cf * two_pi_t) * z;
+    coef[1] = sinf(cf * two_pi_t) * z;
+    coef[2] = (float)((double)midEarCoeff * std::pow((double)(two_pi_t * bw), 4.0) / 3.0);
+    return report("se_gammatone_filter_params",
+                  se_gammatone_coef_batch(ctx, input, output, coef, sigLength, 1, SE_FLAG_EXACT, SE_MEM_HOST));
+}
+
+// make_single_IBM's arithmetic on the sub-band rows it reads back from disk (show_IBM.cpp:118-170)
+SE_EXPORT int se_single_ibm_rows(const short *pure64xn, const short *noise64xn, long n, float *irm)
+{
+    se_ctx *ctx = default_ctx("se_single_ibm_rows");
+    if (!ctx) return SE_ENODEVICE;
+    const int64_t frames = se_ibm_num_frames(n);
+    if (frames <= 0) return SE_OK;
+    const int64_t off[2] = {0, n}, fo[2] = {0, frames};
+    return report("se_single_ibm_rows", se_ibm_rows_batch(ctx, pure64xn, noise64xn, off, 1, irm, nullptr, fo, SE_MEM_HOST));
 }

@@ -1,6 +1,6 @@
 // Host-side constant tables of the hot path (built once per context, uploaded to the GPU).
 // Each builder restates the reference's init code with the same float/double promotions so the
-// tables are bit-identical to the reference's (checked by tests/test_tables.py against the oracle).
+// tables are bit-identical to the reference's (checked by tests/test_abi_host.py::test_tables_bit_identical_to_oracle against the oracle).
 #pragma once
 #include <vector>
 

@@ -59,3 +59,11 @@ def ceps_err(ref, test):
         scale = np.maximum(np.max(np.abs(ref[:, :12]), axis=1, keepdims=True), np.abs(ref[:, 12:13]) / 23.0)
         floor[:, :12] = np.maximum(scale, 1e-3)
     return np.abs(ref - test) / np.maximum(np.maximum(np.abs(ref), np.abs(test)), floor)
+
+
+def ceps_err_survey(ref, test):
+    """SURVEY.md 8(c)'s own cepstral metric, element-wise: |a-b| / max(|a|, |b|, 1e-3).  Reported (and bounded) beside
+    ceps_err: a DCT coefficient that cancels to ~0 makes this ratio large on rounding noise alone."""
+    ref = np.asarray(ref, np.float64).reshape(-1, 14)
+    test = np.asarray(test, np.float64).reshape(-1, 14)
+    return np.abs(ref - test) / np.maximum(np.maximum(np.abs(ref), np.abs(test)), 1e-3)

@@ -56,14 +56,62 @@ def etsi16k():
                         q=q, lp=lp, hp=hp, flush=r.etsi_features_flush(x, True)[-6:])
 
 
+def spectra():
+    """Per-call SPECTRUM state of the reference itself (NoiseSupStructX.nsVar.spectrum after each call): the P8 utterance
+    of p8_etsi.npz through ref_etsi_trace, the P16 signal `a` of p16_wiener.npz through func_Wiener one 160-sample block
+    at a time on one thread instance.  Calls 0..15 and every 4th after that are kept (planes nSigSE1, noiseSE1,
+    denSigSE1, nSigSE2, noiseSE2, denSigSE2)."""
+    assert po.build_ref(), "needs /root/reference"
+    keys = ("nsig1", "noise1", "den1", "nsig2", "noise2", "den2")
+    r = po.RefEtsi()
+    x = synth.utterance(3, 8000, 8000 + 33)
+    t = r.trace(x, with_ceps=False)
+    n8 = len(x) // 80
+    keep8 = np.array([c for c in range(n8) if c < 16 or c % 4 == 3 or c == n8 - 1])
+    p8 = np.stack([t[k][keep8] for k in keys], axis=1)
+    p = po.RefP16()
+    a = synth.utterance(5, 16000, 16000).astype(np.float32)
+    a[160 * 20:160 * 22] = 0.0
+    n16 = len(a) // 160
+    rows = []
+    for b in range(n16):
+        p.func_wiener(a[160 * b:160 * (b + 1)])
+        rows.append(np.stack(p.state()[0]))
+    p.close()
+    keep16 = np.array([c for c in range(n16) if c < 16 or c % 4 == 3 or c == n16 - 1])
+    np.savez_compressed(os.path.join(HERE, "spectra.npz"), x8=x, calls8=keep8, sp8=p8, ret8=t["ret"], a16=a,
+                        calls16=keep16, sp16=np.stack(rows)[keep16])
+
+
+def adv_shipped():
+    """DoAdvProcess / FlushAdvProcess exactly as the reference ships them (ParmInterface.c:208-355), frame by frame:
+    leading all-zero frames (null vector, TRUE), latency calls, and the flush of a never-fed VAD delay line."""
+    assert po.build_ref(), "needs /root/reference"
+    r = po.RefEtsi()
+    d = {}
+    for tag, seed, n in (("z", 7, 4000), ("s", 3, 80 * 9), ("m", 3, 80 * 20)):
+        x = synth.utterance(seed, 8000, n)
+        t = r.adv_process_as_shipped(x)
+        d[tag + "_x"] = x
+        for k, v in t.items():
+            d[tag + "_" + k] = v
+    np.savez_compressed(os.path.join(HERE, "adv_shipped.npz"), **d)
+
+
 def main():
     assert po.build_ref(), "needs /root/reference"
+    if "--only-adv" in sys.argv:
+        return adv_shipped()
+    if "--only-spectra" in sys.argv:
+        return spectra()
     if "--only-features" in sys.argv:
         return features()
     if "--only-16k" in sys.argv:
         return etsi16k()
     features()
     etsi16k()
+    spectra()
+    adv_shipped()
     rng = np.random.default_rng(20141106)
 
     # ---- P8: etsi_denoise + re-enabled CompCeps step, with the per-call VAD trace ------------------

@@ -28,6 +28,9 @@ def dropin(ctx):
     L.DoNoiseSup.argtypes = [_vp, _vp, _vp]
     L.DoCompCeps.argtypes = [_vp, _vp, _vp]
     L.AdvProcessDelete.argtypes = [C.POINTER(_vp)]
+    L.FlushAdvProcess.argtypes = [_vp, _vp]
+    L.DoNoiseSupAlloc.restype = _vp
+    L.DoNoiseSupDelete.argtypes = [_vp]
     L.etsi_denoise_mapping_global_init.argtypes = [C.POINTER(_vp), _vp]
     L.etsi_denoise_mapping_thread_init.argtypes = [C.POINTER(_vp), _vp]
     L.etsi_denoise_mapping_func_Wiener.argtypes = [_vp] * 5
@@ -82,6 +85,100 @@ def test_do_adv_process_frame_by_frame(dropin, oracle):
     assert np.abs(got.astype(np.int32) - ref["den_i16"]).max() <= 1
     assert len(feats) == len(ref["ceps"]) == 34
     assert ceps_err(ref["ceps"], np.array(feats)).max() <= 1e-4
+
+
+@pytest.mark.parametrize("tag", ["z", "s", "m"])
+def test_do_adv_process_and_flush_as_shipped(dropin, tag):
+    """DoAdvProcess frame by frame and the FlushAdvProcess loop against the reference ITSELF driven the same way
+    (tests/golden/adv_shipped.npz from oracle/_ref): which calls write DenoiseBuffer / FeatureBuffer and what they
+    leave there.  z = 5 leading all-zero frames (TRUE, FeatureBuffer[0..13] = 0, DenoiseBuffer untouched,
+    ParmInterface.c:314-327); s / m = 9 / 20 calls (FrameCounter below / above the flush's write threshold of 10)."""
+    import os
+    g = np.load(os.path.join(os.path.dirname(os.path.abspath(__file__)), "golden", "adv_shipped.npz"))
+    x = g[tag + "_x"]
+    calls = len(x) // 80
+    h = _vp(dropin.AdvProcessAlloc(8000))
+    dropin.AdvProcessInit(h)
+    rets = []
+    for b in range(calls):
+        frame = np.ascontiguousarray(x[b * 80:(b + 1) * 80])
+        out = np.full(80, 0x7a7a, np.int16)
+        feat = np.full(15, 7.0, np.float32)
+        rets.append(dropin.DoAdvProcess(frame.ctypes.data, out.ctypes.data, feat.ctypes.data, h))
+        wrote = bool(np.any(out != 0x7a7a))
+        assert wrote == bool(g[tag + "_wrote"][b]), "call %d" % b
+        ref_out = g[tag + "_out"][b * 80:(b + 1) * 80]
+        if wrote:
+            assert np.abs(out.astype(np.int32) - ref_out).max() <= 1
+        ref_feat = g[tag + "_feat"][b]
+        zero_frame = not np.any(frame) and not wrote and ref_feat[0] == 0.0
+        if zero_frame:                       # null MFCC vector: [0..13] zeroed, [14] untouched; returns TRUE
+            assert rets[-1] == 1 and not feat[:14].any() and feat[14] == 7.0
+            assert np.array_equal(feat, ref_feat)
+        elif not wrote:
+            assert rets[-1] == 0 and np.array_equal(feat, ref_feat)      # latency: nothing touched
+        else:
+            assert rets[-1] == 1
+    fr, ff = [], []
+    for k in range(8):
+        feat = np.full(15, 7.0, np.float32)
+        fr.append(dropin.FlushAdvProcess(feat.ctypes.data, h))
+        ff.append(feat)
+        if not fr[-1]:
+            break
+    dropin.AdvProcessDelete(C.byref(h))
+    assert fr == list(g[tag + "_flush_rets"])
+    assert np.array_equal(np.array(ff), g[tag + "_flush_feat"])
+
+
+def test_noise_sup_alloc_delete_by_name(dropin):
+    """NoiseSupExports.h:20,26 by name: a NoiseSup state can be allocated and released on its own."""
+    n = dropin.DoNoiseSupAlloc()
+    assert n
+    dropin.DoNoiseSupDelete(n)
+    dropin.DoNoiseSupDelete(None)
+
+
+def test_handles_used_from_other_threads(dropin, oracle):
+    """Handles are created on one host thread and driven from others (the reference's handles are plain heap
+    structs): every call holds its context's lock, so pushes from 4 threads on 4 handles of ONE context -- while the
+    creating thread keeps calling etsi_denoise on the same context -- give the single-threaded results."""
+    import threading
+    xs = [synth.utterance(70 + i, 8000, 80 * 30) for i in range(4)]
+    hs = [_vp(dropin.AdvProcessAlloc(8000)) for _ in xs]
+    for h in hs:
+        dropin.AdvProcessInit(h)
+    got = [None] * 4
+    err = []
+
+    def work(i):
+        try:
+            outs = []
+            for b in range(30):
+                frame = np.ascontiguousarray(xs[i][b * 80:(b + 1) * 80])
+                out = np.zeros(80, np.int16)
+                dropin.DoAdvProcess(frame.ctypes.data, out.ctypes.data, None, hs[i])
+                outs.append(out)
+            got[i] = np.concatenate(outs)
+        except Exception as e:      # pragma: no cover
+            err.append(e)
+
+    ths = [threading.Thread(target=work, args=(i,)) for i in range(4)]
+    for t in ths:
+        t.start()
+    big = synth.utterance(80, 8000, 80000)
+    big_out = np.zeros_like(big)
+    for _ in range(3):                                   # the creating thread's own context stays busy meanwhile
+        assert dropin.etsi_denoise(big.ctypes.data, big_out.ctypes.data, len(big)) == 0
+    for t in ths:
+        t.join()
+    assert not err
+    for i, x in enumerate(xs):
+        ref = oracle.etsi_denoise(x)["den_i16"]
+        assert np.abs(got[i].astype(np.int32) - ref).max() <= 1
+    assert np.abs(big_out.astype(np.int32) - oracle.etsi_denoise(big)["den_i16"]).max() <= 1
+    for h in hs:
+        dropin.AdvProcessDelete(C.byref(h))
 
 
 def test_plugin_api_like_extract_wiener(dropin, oracle, tmp_path):
@@ -243,11 +340,28 @@ def test_cxx_signatures_drive_the_gpu(ctx, tmp_path, mode):
     x, clean, noise = synth.utterance(41, 16000, n, components=True)
     nf = api.resynth_num_frames(n, mode)
     mask = np.random.default_rng(3).random((nf, 64)).astype(np.float32)
-    for d in ("sub", "res", "mix"):
+    for d in ("sub", "res", "mix", "pure", "subp", "subn"):
         (tmp_path / d).mkdir()
     x.tofile(tmp_path / "x.i16"); noise.tofile(tmp_path / "n.i16"); mask.tofile(tmp_path / "m.f32")
+    clean.tofile(tmp_path / "c.i16")
     subprocess.check_call([exe, str(tmp_path / "x.i16"), str(tmp_path / "n.i16"), str(tmp_path / "m.f32"), str(nf), str(mode),
-                           str(tmp_path) + "/"])
+                           str(tmp_path) + "/"] + ([str(tmp_path / "c.i16")] if mode == 0 else []))
+    if mode == 0:
+        # make_single_IBM(char*, FILE*, FILESNAME) (make_IBM.h:9): the text matrix it appends holds the IRM of the fused
+        # batch call, digit for digit; gammaToneFilter / hairCell (HuWang.h:49,62) with a by-value, non-preset channel
+        irm, _, _ = ctx.ibm(clean, noise, [0, n])
+        txt = open(tmp_path / "irm.txt").read()
+        assert txt.startswith("utt1_noisy [\n") and txt.endswith("]\n")
+        rows = txt[len("utt1_noisy [\n"):-2].split("\n ")
+        assert len(rows) == len(irm)
+        want_rows = ["".join("%.7f " % v for v in r) for r in irm]
+        assert rows == want_rows
+        from oracle import pyoracle
+        o = pyoracle.Oracle()
+        gt = np.fromfile(tmp_path / "gt.f32", np.float32)
+        ref_gt = o.gammatone(x.astype(np.float32), 1234.5, 150.0, 0.7)
+        assert np.array_equal(gt, ref_gt)
+        assert np.array_equal(np.fromfile(tmp_path / "hc.f32", np.float32), o.haircell(ref_gt))
     sub = ctx.subband(x, [0, n], exact=True).reshape(64, n)
     for chan in (0, 17, 63):
         got = np.fromfile(tmp_path / "sub" / ("utt1_t_%d.wav" % chan), np.int16)

@@ -39,6 +39,34 @@ def test_p8_against_reference_vectors(ctx, prefix, xkey):
     assert mism == 0                                                           # no tie on these fixtures
 
 
+SPEC_FLOOR = float(np.exp(-10.0))          # floor e^-10 for PSD-domain quantities
+
+
+def spec_rel(ref, got):
+    ref = np.asarray(ref, np.float64)
+    got = np.asarray(got, np.float64)
+    return np.abs(ref - got) / np.maximum(np.maximum(np.abs(ref), np.abs(got)), SPEC_FLOOR)
+
+
+def test_spectra_against_reference_vectors(ctx):
+    """a6/a7/a9 at the spectrum level: sqrt(PSD) (FFTtoPSD), noise estimate and denoised spectrum (PSDMean -> FilterCalc)
+    of BOTH stages after every kept call, against the reference's own per-call state; rel 1e-4, floor e^-10."""
+    g = load("spectra.npz")
+    for prof, xk, ck, sk in ((8, "x8", "calls8", "sp8"), (16, "a16", "calls16", "sp16")):
+        x = g[xk]
+        sp, produced, _ = ctx.ns_spectra(prof, x, [0, len(x)])
+        calls = g[ck]
+        for st, bit in ((0, 2), (1, 1)):
+            m = (produced[calls] & bit) != 0
+            assert m.sum() >= len(calls) - 6
+            err = spec_rel(g[sk][m][:, 3 * st:3 * st + 3], sp[calls][m][:, 3 * st:3 * st + 3])
+            assert err.max() <= 1e-4, (prof, st, err.max())
+    gp = load("p8_etsi.npz")                 # the fixture's last-call noise / denoised spectra
+    sp, produced, _ = ctx.ns_spectra(8, gp["x"], [0, len(gp["x"])])
+    assert spec_rel(gp["noise1_last"], sp[-1, 1]).max() <= 1e-4 and spec_rel(gp["den2_last"], sp[-1, 5]).max() <= 1e-4
+    assert np.array_equal((produced & 1) != 0, gp["ret"] > 0)
+
+
 def test_rfft_against_reference_vectors(ctx):
     g = load("rfft.npz")
     y = ctx.rfft(g["x256"], 8)

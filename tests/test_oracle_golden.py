@@ -44,6 +44,20 @@ def test_p8_etsi_golden(oracle, prefix, xkey):
     assert len(r["ceps"]) == n_ceps
 
 
+def test_spectra_golden(oracle):
+    """Per-call SPECTRUM state (nSigSE / noiseSE / denSigSE of both Wiener stages, NoiseSup.c:102-115 as FFTtoPSD ->
+    PSDMean -> FilterCalc leave them) bit-for-bit against the reference build, both profiles."""
+    g = load("spectra.npz")
+    for prof, xk, ck, sk in ((8, "x8", "calls8", "sp8"), (16, "a16", "calls16", "sp16")):
+        sp, ran = oracle.ns_spectra(prof, g[xk])
+        calls = g[ck]
+        for st, bit in ((0, 2), (1, 1)):
+            m = (ran[calls] & bit) != 0                       # the planes of a stage move only when it runs
+            assert m.sum() >= len(calls) - 6
+            assert np.array_equal(sp[calls][m][:, 3 * st:3 * st + 3], g[sk][m][:, 3 * st:3 * st + 3]), (prof, st)
+    assert np.array_equal((oracle.ns_spectra(8, g["x8"])[1] & 1) != 0, g["ret8"] > 0)
+
+
 def test_p8_features_golden(oracle):
     """WaveProc -> CompCeps -> PostProc -> VAD behind NoiseSup: bit-exact rows against the reference build."""
     g = load("p8_features.npz")

@@ -8,7 +8,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-from conftest import ceps_err                      # noqa: E402
+from conftest import ceps_err, ceps_err_survey     # noqa: E402
 from oracle import pyoracle                        # noqa: E402
 from speech_enhancement_b200 import api, synth     # noqa: E402
 
@@ -18,11 +18,12 @@ ctx = api.Context(0)
 xs = [synth.utterance(5000 + i, 8000, 8000 * 5) for i in range(n_utts)]
 offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
 got = ctx.etsi_features(np.concatenate(xs), offsets)
-errs, vad_diff, rows = [], 0, 0
+errs, vad_diff, rows, sv = [], 0, 0, []
 for u, x in enumerate(xs):
     ref, _ = o.etsi_features(x)
     assert ref.shape == got[u].shape
     errs.append(ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1))
+    sv.append(ceps_err_survey(ref[:, :14], got[u][:, :14]).ravel())
     vad_diff += int((ref[:, 14] != got[u][:, 14]).sum())
     rows += len(ref)
 e = np.concatenate(errs)
@@ -30,18 +31,21 @@ print("rows", rows, "vad flag mismatches", vad_diff)
 for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
     print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
 print("max err %.4g, median %.3g" % (e.max(), np.median(e)))
+sv = np.concatenate(sv)
+print("SURVEY 8(c) element-wise metric: %d of %d values above 1e-4 (share %.5f), max %.3g" % ((sv > 1e-4).sum(), sv.size, (sv > 1e-4).mean(), sv.max()))
 
 # ---- the same statistics for the ETSI 16 kHz mode, with the flush rows on ---------------------------------------
 ctx.set_feature_flush(True)
 xs = [synth.utterance(7000 + i, 16000, 16000 * 5) for i in range(n_utts)]
 offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
 got, den = ctx.etsi16k_features(np.concatenate(xs), offsets, denoised=True)
-errs, vad_diff, rows, lsb = [], 0, 0, 0
+errs, vad_diff, rows, lsb, sv = [], 0, 0, 0, []
 for u, x in enumerate(xs):
     ref = o.etsi_features_flush(x, True)
     _, rden = o.etsi_features_16k(x)
     assert ref.shape == got[u].shape, (u, ref.shape, got[u].shape)
     errs.append(ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1))
+    sv.append(ceps_err_survey(ref[:, :14], got[u][:, :14]).ravel())
     vad_diff += int((ref[:, 14] != got[u][:, 14]).sum())
     lsb = max(lsb, int(np.abs(den[u].astype(np.int32) - rden.astype(np.int32)).max()))
     rows += len(ref)
@@ -50,3 +54,5 @@ print("16 kHz mode (+flush): rows", rows, "vad flag mismatches", vad_diff, "low-
 for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
     print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
 print("max err %.4g, median %.3g" % (e.max(), np.median(e)))
+sv = np.concatenate(sv)
+print("SURVEY 8(c) element-wise metric: %d of %d values above 1e-4 (share %.5f), max %.3g" % ((sv > 1e-4).sum(), sv.size, (sv > 1e-4).mean(), sv.max()))

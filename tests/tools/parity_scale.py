@@ -9,7 +9,7 @@ import numpy as np
 ROOT = os.path.dirname(os.path.dirname(os.path.dirname(os.path.abspath(__file__))))
 sys.path.insert(0, ROOT)
 sys.path.insert(0, os.path.join(ROOT, "tests"))
-from conftest import ceps_err, rel_err, snr_db      # noqa: E402
+from conftest import ceps_err, ceps_err_survey, rel_err, snr_db      # noqa: E402
 from oracle import pyoracle                         # noqa: E402
 from speech_enhancement_b200 import api, synth      # noqa: E402
 
@@ -29,11 +29,12 @@ def p8(u):
     lsb = int(np.abs(r["den_i16"][lo:lo + nb].astype(np.int32) - ref["den_i16"][:nb].astype(np.int32)).max(initial=0))
     snr = snr_db(ref["den_f32"][:nb], r["den_f32"][lo:lo + nb])
     ce = float(ceps_err(ref["ceps"], r["ceps"][co:co + nc]).max()) if nc else 0.0
+    sv = ceps_err_survey(ref["ceps"], r["ceps"][co:co + nc]) if nc else np.zeros((0, 14))
     tr = r["trace"][int(r["trace_offsets"][u]):int(r["trace_offsets"][u]) + ref["calls"]]
     info = ref["info"]; on = info["stage0_ran"] > 0
     mm = sum(int(np.sum(((tr[on] & bit) != 0) != (info[key][on] != 0)))
              for bit, key in ((1, "flag_vad"), (2, "sp_var"), (4, "sp_spec"), (8, "sp_mel"), (16, "sp_vadns")))
-    return lsb, snr, ce, mm, int(on.sum()), nc == int(r["n_ceps"][u])
+    return lsb, snr, ce, mm, int(on.sum()), nc == int(r["n_ceps"][u]), int((sv > 1e-4).sum()), sv.size, float(sv.max(initial=0))
 
 
 with ThreadPoolExecutor(T) as ex:
@@ -41,6 +42,9 @@ with ThreadPoolExecutor(T) as ex:
 print("P8  %d utterances, %d frames: max |d| %d LSB, min SNR %.1f dB, max ceps err %.3g, flag mismatches %d of %d, counts ok %s"
       % (N, sum(x[4] for x in res), max(x[0] for x in res), min(x[1] for x in res), max(x[2] for x in res),
          sum(x[3] for x in res), 5 * sum(x[4] for x in res), all(x[5] for x in res)))
+print("P8  SURVEY 8(c) element-wise metric (floor 1e-3): %d of %d cepstral values above 1e-4 (share %.5f), max %.3g"
+      % (sum(x[6] for x in res), sum(x[7] for x in res), sum(x[6] for x in res) / max(1, sum(x[7] for x in res)),
+         max(x[8] for x in res)))
 
 samples, offsets = synth.corpus(60000, N, 16000, min_s=2.0, max_s=6.0, threads=T)
 r = ctx.p16_wiener(samples, offsets)
