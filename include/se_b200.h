@@ -65,6 +65,18 @@ int  se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts);
  * the reference's drivers flushes. */
 #define SE_FEATURE_FLUSH_ROWS 6
 int  se_ctx_set_feature_flush(se_ctx *ctx, int enable);
+/* Arithmetic mode of the NoiseSup family (se_etsi_denoise_batch, se_etsi_features_batch, se_etsi16k_features_batch,
+ * se_p16_wiener_batch, se_ns_spectra_batch, se_ns_stream_*, se_rfft_batch, se_comp_ceps_batch, se_wave_proc_batch,
+ * se_qmf_split_batch) -- the counterpart of SE_FLAG_EXACT of the G64 calls.
+ *   0 (default): fast arithmetic -- in-register shuffle FFT, FMA contraction, MUFU reciprocal / square root, float
+ *      logarithms, tree-shaped sums.  Within the parity bars (waveform >= 60 dB, spectra / gains / cepstra rel 1e-4 of
+ *      their scale) but not bit-identical, and a 1-ulp difference can move one of WaveProc's integer peak positions.
+ *   1: the SAME kernels compiled a second time in the reference's own arithmetic: its split-radix rfft butterfly
+ *      schedule (etsi/cpp/rfft.c:45-180; for the plugin the truncated rfft(x,512,8)), every sum in the reference's order,
+ *      IEEE division and square root, the double-promoted sub-expressions of the C sources, no FMA contraction.  The
+ *      only freedom left is libm's log / log10 / exp in double (<= 1 ulp in both libraries before rounding to float).
+ *      Used by the parity tests to show that every frame of the feature chains meets rel 1e-4; ~3-5x slower. */
+int  se_ctx_set_exact(se_ctx *ctx, int enable);
 /* Upper bound for internal device scratch (gammatone intermediate), bytes.  Default 48 GiB. */
 int  se_ctx_set_scratch_limit(se_ctx *ctx, uint64_t bytes);
 

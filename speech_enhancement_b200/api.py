@@ -49,6 +49,7 @@ def lib():
         L.se_ctx_profiling.argtypes = [_vp, C.c_int]
         L.se_ctx_set_pipeline.argtypes = [_vp, C.c_uint64, C.c_int]
         L.se_ctx_set_feature_flush.argtypes = [_vp, C.c_int]
+        L.se_ctx_set_exact.argtypes = [_vp, C.c_int]
         L.se_extract_wiener_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
         L.se_ctx_kernel_time.argtypes = [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
         L.se_ctx_reset_kernel_times.argtypes = [_vp]
@@ -185,6 +186,10 @@ class Context:
 
     def set_pipeline(self, chunk_bytes, min_utts):
         _check(self.L.se_ctx_set_pipeline(self.h, int(chunk_bytes), int(min_utts)), "se_ctx_set_pipeline")
+
+    def set_exact(self, enable):
+        """NoiseSup family in the reference's own arithmetic (se_ctx_set_exact)."""
+        _check(self.L.se_ctx_set_exact(self.h, int(bool(enable))), "se_ctx_set_exact")
 
     def profiling(self, on):
         _check(self.L.se_ctx_profiling(self.h, 1 if on else 0), "se_ctx_profiling")

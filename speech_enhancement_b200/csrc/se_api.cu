@@ -72,6 +72,16 @@ static int upload_ns(se_ctx *ctx, const NsTables &h, NsDevTables &d, int bank_ro
     }
     if ((rc = upload(ctx, tw.data(), tw.size(), &d.tw_half))) return rc;
     d.eps = h.eps;
+    // exact mode: the reference's rfft schedule (P8: rfft(x, 256, 8) of the C file; P16: the plugin's rfft(x, 512, 8))
+    const RfftPlan &pl = (bank_rows == 128) ? ctx->h_rf16 : ctx->h_rf8;
+    int lvl[32];
+    for (int k = 0; k < 16; k++) { lvl[k] = k <= pl.m ? pl.level_begin[k] : 0; lvl[16 + k] = k <= pl.m ? pl.tw_begin[k] : 0; }
+    const int *d_lvl = nullptr;
+    if ((rc = upload(ctx, pl.ops.data(), pl.ops.size(), &d.rf_ops))) return rc;
+    if ((rc = upload(ctx, lvl, 32, &d_lvl))) return rc;
+    if ((rc = upload(ctx, pl.tw.data(), pl.tw.size(), &d.rf_tw))) return rc;
+    d.rf_lvl = d_lvl;
+    d.rf_m = pl.m;
     return SE_OK;
 }
 
@@ -262,6 +272,8 @@ static int ctx_init_device(se_ctx *ctx)
         SE_CUDA(cudaMalloc((void **)&ctx->lanes[l].d_work_counter, sizeof(int)));
         SE_CUDA(cudaEventCreateWithFlags(&ctx->lanes[l].done, cudaEventDisableTiming));
     }
+    build_rfft_plan(ctx->h_rf8, 256, 8, false);
+    build_rfft_plan(ctx->h_rf16, 512, 8, true);
     build_ns_tables_p8(ctx->h_p8);
     build_ns_tables_p16(ctx->h_p16);
     build_cc_tables(ctx->h_cc);

@@ -202,7 +202,8 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
                 set_field(b, o.field, d_out[k]);
             }
             mark(c, "h2d");
-            SE_TRY(profile == 8 ? launch_ns_p8(ctx, b) : launch_ns_p16(ctx, b));
+            SE_TRY(ctx->exact ? (profile == 8 ? se_exact::launch_ns_p8(ctx, b) : se_exact::launch_ns_p16(ctx, b))
+                               : (profile == 8 ? launch_ns_p8(ctx, b) : launch_ns_p16(ctx, b)));
             mark(c, "kernel");
             if (mem != SE_MEM_HOST) return SE_OK;
             for (int k = 0; k < n_outs; k++) {

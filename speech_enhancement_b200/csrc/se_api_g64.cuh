@@ -140,7 +140,7 @@ int se_rfft_batch(se_ctx *ctx, float *x, int n, int m, int count, int mem)
     const void *d_in = nullptr;
     SE_TRY(stage_in(ctx, kSlotIn, x, bytes, mem, &d_in));
     float *d = const_cast<float *>((const float *)d_in);
-    SE_TRY(launch_rfft(ctx, d, n, m, count));
+    SE_TRY(ctx->exact ? se_exact::launch_rfft(ctx, d, n, m, count) : launch_rfft(ctx, d, n, m, count));
     SE_TRY(stage_out_copy(ctx, x, d, bytes, mem));
     return leave(ctx, mem);
 }
@@ -154,7 +154,7 @@ int se_wave_proc_batch(se_ctx *ctx, float *frames, int n_frames, int mem)
     const void *d_in = nullptr;
     SE_TRY(stage_in(ctx, kSlotIn, frames, bytes, mem, &d_in));
     float *d = const_cast<float *>((const float *)d_in);
-    SE_TRY(launch_wave_proc(ctx, d, n_frames));
+    SE_TRY(ctx->exact ? se_exact::launch_wave_proc(ctx, d, n_frames) : launch_wave_proc(ctx, d, n_frames));
     SE_TRY(stage_out_copy(ctx, frames, d, bytes, mem));
     return leave(ctx, mem);
 }
@@ -168,7 +168,8 @@ int se_comp_ceps_batch(se_ctx *ctx, const float *frames201, int n_frames, float 
     void *d_out = nullptr;
     SE_TRY(stage_in(ctx, kSlotIn, frames201, sizeof(float) * 201u * (uint64_t)n_frames, mem, &d_in));
     SE_TRY(stage_out(ctx, kSlotOut, coef14, sizeof(float) * 14u * (uint64_t)n_frames, mem, false, &d_out));
-    SE_TRY(launch_comp_ceps(ctx, (const float *)d_in, (float *)d_out, n_frames));
+    SE_TRY(ctx->exact ? se_exact::launch_comp_ceps(ctx, (const float *)d_in, (float *)d_out, n_frames)
+                      : launch_comp_ceps(ctx, (const float *)d_in, (float *)d_out, n_frames));
     SE_TRY(stage_out_copy(ctx, coef14, d_out, sizeof(float) * 14u * (uint64_t)n_frames, mem));
     return leave(ctx, mem);
 }
@@ -187,7 +188,8 @@ int se_qmf_split_batch(se_ctx *ctx, const int16_t *samples, int64_t n, int count
     SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
     SE_TRY(stage_out(ctx, kSlotOut, lp, sizeof(float) * (total / 2), mem, false, &d_lp));
     SE_TRY(stage_out(ctx, kSlotOut2, hp, sizeof(float) * (total / 2), mem, false, &d_hp));
-    SE_TRY(launch_qmf_split(ctx, (const int16_t *)d_in, n, count, (float *)d_lp, (float *)d_hp));
+    SE_TRY(ctx->exact ? se_exact::launch_qmf_split(ctx, (const int16_t *)d_in, n, count, (float *)d_lp, (float *)d_hp)
+                      : launch_qmf_split(ctx, (const int16_t *)d_in, n, count, (float *)d_lp, (float *)d_hp));
     SE_TRY(stage_out_copy(ctx, lp, d_lp, sizeof(float) * (total / 2), mem));
     SE_TRY(stage_out_copy(ctx, hp, d_hp, sizeof(float) * (total / 2), mem));
     return leave(ctx, mem);

@@ -120,7 +120,7 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
             a.ceps_offsets = (const int64_t *)s->d_offsets;   // {0, n}: row 0, capacity n >= n_blocks
             a.n_ceps = (int32_t *)s->d_rows;
         }
-        SE_TRY(launch_ns_p8(ctx, a));
+        SE_TRY(ctx->exact ? se_exact::launch_ns_p8(ctx, a) : launch_ns_p8(ctx, a));
     } else {
         a.out_f32 = (float *)s->d_out;
         a.flags = (int32_t *)s->d_flags;
@@ -130,7 +130,7 @@ int se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *out
         a.block_offsets = (const int64_t *)s->d_offsets;   // {0, ...}: rows and flags start at 0
         a.zero_check = s->zero_gate;
         SE_CUDA(cudaMemsetAsync(s->d_gains, 0, sizeof(float) * 25 * (size_t)n_blocks, ctx->cur->stream));
-        SE_TRY(launch_ns_p16(ctx, a));
+        SE_TRY(ctx->exact ? se_exact::launch_ns_p16(ctx, a) : launch_ns_p16(ctx, a));
     }
     s->fresh = 0;
     SE_TRY(d2h_async(ctx, out, s->d_out, sizeof(float) * (size_t)n));

@@ -100,7 +100,9 @@ __global__ void __launch_bounds__(64) gt_bwd_kernel(const float *Y, const GtItem
                     w = 0.0f;
                     if (EXACT) {
                         if (m_h != 0.0f) w = (float)(c_w_fall_d[r] * (double)m_h);
-                        if (m_h1 != 0.0f) w = (float)((double)w + c_w_rise_d[r] * (double)m_h1);
+                        // separately rounded double product and sum (no FMA contraction: the float output must match
+                        // the reference bit for bit, SE_FLAG_OUT_F32)
+                        if (m_h1 != 0.0f) w = (float)__dadd_rn((double)w, __dmul_rn(c_w_rise_d[r], (double)m_h1));
                     } else {
                         if (m_h != 0.0f) w = c_w_fall[r] * m_h;
                         if (m_h1 != 0.0f) w += c_w_rise[r] * m_h1;

@@ -32,6 +32,11 @@ struct NsDevTables {
     const float *idctT;        // [25][16] : idctT[f*16+t] = idct[t][f], t<9
     const float *tw_half;      // [129] float2 : exp(-2 pi i k / 256), k=0..128 (real-FFT split twiddles)
     float eps;
+    // exact arithmetic mode (se_ctx_set_exact): the reference's rfft schedule for this profile (RfftPlan, se_tables.h)
+    const unsigned *rf_ops;
+    const int *rf_lvl;         // [32]: level_begin[0..15], tw_begin[0..15]
+    const float *rf_tw;        // float4 per twiddle set
+    int rf_m;
 };
 
 struct CcDevTables {
@@ -142,6 +147,7 @@ struct se_ctx {
     int feature_flush;          // se_ctx_set_feature_flush: the feature-chain calls append FlushAdvProcess's 6 rows
     // tables
     se::NsTables h_p8, h_p16;
+    se::RfftPlan h_rf8, h_rf16;
     se::CcTables h_cc;
     se::GtTables h_gt;
     se::Hp16Tables h_hp16;
@@ -205,3 +211,15 @@ int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *n
 int upload_g64_tables(se_ctx *ctx);
 
 }  // namespace se
+
+// The same fused NoiseSup kernels compiled a second time (se_ns.cu with -DSE_NS_EXACT -fmad=false) in the reference's
+// own arithmetic: its rfft butterfly schedule, its summation orders, IEEE division / square root, double-promoted
+// sub-expressions.  Selected per context by se_ctx_set_exact().
+namespace se_exact {
+int launch_ns_p8(se_ctx *ctx, const se::NsLaunch &a);
+int launch_ns_p16(se_ctx *ctx, const se::NsLaunch &a);
+int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count);
+int launch_qmf_split(se_ctx *ctx, const int16_t *x, int64_t n, int count, float *lp, float *hp);
+int launch_wave_proc(se_ctx *ctx, float *frames, int count);
+int launch_comp_ceps(se_ctx *ctx, const float *frames, float *coef, int count);
+}  // namespace se_exact

@@ -20,9 +20,19 @@
 #define SE_NS_CONST_SMEM 1
 #endif
 #include "se_internal.h"
+// This file is compiled twice: as is (namespace se, the default fast arithmetic) and with -DSE_NS_EXACT=1
+// -DSE_NSPACE=se_exact -fmad=false (the reference's arithmetic, se_ns_exact.cuh); the two sets of kernels live in
+// different namespaces so both can be linked into libse_b200.so.
+#ifndef SE_NSPACE
+#define SE_NSPACE se
+#endif
+#ifdef SE_NS_EXACT
+#define SE_NS_FAST_MATH 0
+namespace se_exact { using namespace se; }
+#endif
 #include "se_warp_fft.cuh"
 
-namespace se {
+namespace SE_NSPACE {
 
 // ------------------------------------------------------------------------------------------------
 // profiles
@@ -60,7 +70,15 @@ template <int PROF> struct __align__(16) WarpMem {
     float melw[32];
     float fir[16];
     float cold[PROF == 8 ? 16 : 4];   // P8: Scal fields touched once per block, parked here between their uses
+#ifdef SE_NS_EXACT
+    float xf[PROF == 8 ? 256 : 512];  // the reference's in-place rfft array
+    float sden[132], snoise[132];     // denSigSE / noiseSE of the current stage, for the in-order energy sums
+#endif
 };
+
+#ifdef SE_NS_EXACT
+struct RfPlanDev { const unsigned *ops; const int *lvl; const float *tw; int m; };
+#endif
 
 template <int PROF> struct __align__(16) BlockMem {
     using P = Prof<PROF>;
@@ -79,6 +97,9 @@ template <int PROF> struct __align__(16) BlockMem {
     float lane_tw[15 * 32];      // FftTw of every lane, [field][lane]
     float lane_ic[10 * 32];      // IdctRegs of every lane
     float lane_br[PROF == 8 ? 22 * 32 : 4];   // BankRegs taps of every lane: 10 mel + 12 CompCeps triangle taps
+#endif
+#ifdef SE_NS_EXACT
+    RfPlanDev rf;
 #endif
 };
 
@@ -139,10 +160,15 @@ __device__ __forceinline__ void vad_ns(Scal &s, int fstage, float frame_sq)
     if (fstage) { s.nb_frame1 = nbf; return; }
     s.nb_frame0 = nbf;
     float lambda = (nbf < 10) ? (1.0f - 1.0f / (float)nbf) : 0.97f;
+#ifdef SE_NS_EXACT
+    // exact mode: frame_sq already is 64 + the in-order sum; NoiseSup.c:391 in double, log(2.0) as gcc folds it
+    float frame_en = (float)(0.5 + (log((double)frame_sq / 64.0) / 0.69314718055994530942) * 16.0);
+#else
     float frame_en = 64.0f + frame_sq;
     // NoiseSup.c:391: 0.5 + log(frame_en/64)/log(2) * 16 (double in the reference; float log2 is within
     // an ulp of the float result, the same order as the float sum of squares feeding it)
     frame_en = 0.5f + log2f(frame_en * (1.0f / 64.0f)) * 16.0f;
+#endif
     float mean_en = s.mean_en;
     if (((frame_en - mean_en) < 20.0f) || (nbf < 10)) {
         // separately rounded mul/add (no FMA contraction): this recursion feeds the VAD decision
@@ -216,7 +242,14 @@ template <int PROF> __device__ __forceinline__ void gain_fact_stage2(Scal &s, fl
 {
     float aver = (s.den_en0 * s.den_en1 * s.den_en2) / (noise_en * noise_en * noise_en);
     if ((double)aver > 0.00001) {
+#ifdef SE_NS_EXACT
+        // the ETSI file is C: (20 * log10((double)aver)) / 3.0; the plugin is C++: log10 of a float is the float overload
+        // (evaluated here as the correctly rounded float of the double log10), times 20 in float, / 3.0 in double
+        if (PROF == 8) aver = (float)((20 * log10((double)aver)) / 3.0);
+        else aver = (float)((double)(20 * (float)log10((double)aver)) / 3.0);
+#else
         aver = (20.0f * log10f(aver)) / 3.0f;
+#endif
     } else {
         aver = (float)(-100.0 / 3.0);
     }
@@ -267,6 +300,43 @@ __device__ __forceinline__ float fsqrt(float a)
 
 // Decision-directed Wiener gain of one bin, etsi/cpp/NoiseSup.c:449-563 (FilterCalc).
 // psd: this frame's PSD bin, psd_mean: 2-frame mean.  Returns W; updates noise/den.
+#ifdef SE_NS_EXACT
+__device__ __forceinline__ float filter_calc_bin(const int fstage, float psd, float psd_mean, float &noise, float &den,
+                                                 int nbf, int flag_vad, float eps)
+{
+    const float beta = 0.98f, rsb_min = 0.079432823f;
+    if (fstage == 1) {
+        float n2 = noise * noise;                                    // noise estimation in energy, NoiseSup.c:486-517
+        if (nbf < 11) {
+            const float lambda = 1 - 1 / (float)nbf;
+            n2 = lambda * n2 + (1 - lambda) * psd_mean;
+        } else {
+            const float up = (float)(0.9 + 0.1 * (double)(psd_mean / (psd_mean + n2)) *
+                                               (1.0 + 1.0 / (1.0 + 0.1 * (double)(psd_mean / n2))));
+            n2 = n2 * up;
+        }
+        noise = (float)sqrt((double)n2);
+        if (noise < eps) noise = eps;
+    }
+    const float nsig = (float)sqrt((double)psd);                     // :522-526
+    const float pm = (float)sqrt((double)psd_mean);
+    if (fstage == 0) {
+        const float lambda = (nbf < 100) ? (1 - 1 / (float)nbf) : 0.99f;
+        if (flag_vad == 0) {
+            noise = lambda * noise + (1 - lambda) * pm;
+            if (noise < eps) noise = eps;
+        }
+    }
+    const float post = (pm / noise) - 1;                             // :551-560
+    float prio = beta * (den / noise) + (1 - beta) * ((0 > post) ? 0 : post);
+    float W = prio / (1 + prio);
+    prio = W * pm / noise;
+    prio = (prio > rsb_min) ? prio : rsb_min;
+    W = prio / (1 + prio);
+    den = W * nsig;
+    return W;
+}
+#else
 __device__ __forceinline__ float filter_calc_bin(const int fstage, float psd, float psd_mean, float &noise, float &den,
                                                  int nbf, int flag_vad, float eps)
 {
@@ -302,8 +372,9 @@ __device__ __forceinline__ float filter_calc_bin(const int fstage, float psd, fl
     den = W * nsig;
     return W;
 }
+#endif
 
-}  // namespace se
+}  // namespace SE_NSPACE
 
 #include "se_ns_stage.cuh"
 #include "se_ns_feat.cuh"

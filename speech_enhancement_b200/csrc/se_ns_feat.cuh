@@ -7,7 +7,7 @@
 // One warp per utterance, as everywhere in this kernel; included by se_ns.cu.
 #pragma once
 
-namespace se {
+namespace SE_NSPACE {
 
 constexpr int kFeatCols = 15;    // c1..c12, c0, logE, VAD flag (FeatureBuffer[0..NUM_CEP_COEFF+1])
 
@@ -48,10 +48,14 @@ __device__ __forceinline__ void wave_proc_warp(FeatMem &fm, int lane)
     // low-energy check (:400-404).  The reference sums sequentially; a frame whose energy sits within
     // float rounding of 100.0 may take the other branch here.
     float e = 0.0f;
+#ifdef SE_NS_EXACT
+    for (int i = 0; i < L; i++) e += d[i] * d[i];        // exact mode: the reference's in-order sum (every lane)
+#else
 #pragma unroll
     for (int t = 0; t < T; t++)
         if (s0 + t < L) e = fmaf(x[t + 1], x[t + 1], e);
     e = warp_sum(e);
+#endif
     if (!(e >= 100.0f)) return;
 
     // Teager energy, scaled by 0.25 and rounded to int (:173-184, :222-227)
@@ -212,4 +216,4 @@ __device__ __forceinline__ void vad_flush_warp(float &fb, FeatState &f, const Fe
     }
 }
 
-}  // namespace se
+}  // namespace SE_NSPACE

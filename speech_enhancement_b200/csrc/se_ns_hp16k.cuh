@@ -10,7 +10,7 @@
 #pragma once
 #include "se_qmf_taps.h"
 
-namespace se {
+namespace SE_NSPACE {
 
 __constant__ float c_qmfz[126] = SE_QMF_PADDED;
 #undef Q
@@ -50,6 +50,22 @@ __device__ __forceinline__ void hp16_state_init(Hp16State &h, Hp16Mem &hm, int l
 // The reference accumulates j = 0..117 in one float chain; this order differs by float rounding only.
 __device__ __forceinline__ void qmf_split_warp(Hp16Mem &hm, float *ring1, int slot, int hslot, int lane)
 {
+#ifdef SE_NS_EXACT
+    // exact mode: both 118-tap sums of every output in the reference's order j = 0..117 (16kHzProcessing.c:735-760);
+    // the high-pass taps are the low-pass prototype with alternating signs (+ for odd j), the output sign alternates
+#pragma unroll 1
+    for (int k = lane; k < 80; k += 32) {
+        float a = 0.0f, b = 0.0f;
+        const float *x = hm.line + 2 * k;
+        for (int j = 0; j < 118; j++) {
+            const float tap = c_qmfz[4 + j];
+            a += x[j] * tap;
+            b += x[j] * ((j & 1) ? tap : -tap);
+        }
+        ring_store<8>(ring1, slot, k, a);
+        hm.hpring[hslot * 80 + k] = (k & 1) ? -b : b;
+    }
+#else
     if (lane < 27) {
         float e0 = 0.0f, o0 = 0.0f, e1 = 0.0f, o1 = 0.0f, e2 = 0.0f, o2 = 0.0f;
         const float2 *xp = reinterpret_cast<const float2 *>(hm.line + 6 * lane);
@@ -74,6 +90,7 @@ __device__ __forceinline__ void qmf_split_warp(Hp16Mem &hm, float *ring1, int sl
             }
         }
     }
+#endif
     __syncwarp();
     // keep the last 117 samples as the next call's delay line
     float keep[4];
@@ -90,15 +107,26 @@ __device__ __forceinline__ void qmf_split_warp(Hp16Mem &hm, float *ring1, int sl
 // psd1 / psd2 = this lane's bins lane+32 and lane+64.
 __device__ __forceinline__ void hp16_lowband_log(Hp16State &h, float psd1, float psd2, int lane)
 {
+    const float floor_v = 4.5399929762484854e-05f;   // NS_SPEC_FLOOR = (float)exp(-10.0)
+#ifdef SE_NS_EXACT
+    // exact mode: GetBandsForCoding16k's three sums bin after bin (16kHzProcessing.c:497-511), double log
+    float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f;
+    for (int i = 33; i < 39; i++) a0 += __shfl_sync(0xffffffffu, psd1, i - 32);
+    for (int i = 39; i < 49; i++) a1 += __shfl_sync(0xffffffffu, psd1, i - 32);
+    for (int i = 49; i < 64; i++) a2 += __shfl_sync(0xffffffffu, psd1, i - 32);
+    a2 += __shfl_sync(0xffffffffu, psd2, 0);
+    const float sel = (lane == 6) ? a0 : ((lane == 7) ? a1 : a2);
+    const float lg = (sel > floor_v) ? (float)log((double)sel) : -10.0f;
+#else
     float a0 = (lane >= 1 && lane <= 6) ? psd1 : 0.0f;
     float a1 = (lane >= 7 && lane <= 16) ? psd1 : 0.0f;
     float a2 = (lane >= 17) ? psd1 : ((lane == 0) ? psd2 : 0.0f);
     a0 = warp_sum(a0);
     a1 = warp_sum(a1);
     a2 = warp_sum(a2);
-    const float floor_v = 4.5399929762484854e-05f;   // NS_SPEC_FLOOR = (float)exp(-10.0)
     const float sel = (lane == 6) ? a0 : ((lane == 7) ? a1 : a2);
     const float lg = (sel > floor_v) ? logf(sel) : -10.0f;
+#endif
     const float down = __shfl_down_sync(0xffffffffu, h.lpl, 3);
     h.lpl = (lane < 6) ? down : ((lane < 9) ? lg : 0.0f);
 }
@@ -116,25 +144,43 @@ __device__ __forceinline__ void hp16_stage1(WarpMem<8> &wm, const BlockMem<8> &b
     int wslot = hslot + 2;
     if (wslot >= 6) wslot -= 6;
     frame_psd<8, kHpRing>(wm, bm, tw, lane, hm.hpring, wslot * 80, psd);
+#ifdef SE_NS_EXACT
+    // exact mode: DoMelFB over the HP bank bin after bin (MelProc.c:82-104; zero weights outside a triangle add
+    // exact zeros), double logs below
+#define SE_HP_LOG(v) ((float)log((double)(v)))
+    wm.W[lane] = psd[0];
+    wm.W[32 + lane] = psd[1];
+    __syncwarp();
+    float f0 = 0.0f, f1 = 0.0f, f2 = 0.0f;
+    for (int i = 0; i < 64; i++) {
+        const float pv = wm.W[i];
+        f0 += pv * hb.hpfb[i];
+        f1 += pv * hb.hpfb[64 + i];
+        f2 += pv * hb.hpfb[128 + i];
+    }
+    __syncwarp();
+#else
+#define SE_HP_LOG(v) logf(v)
     float f0 = psd[0] * hb.hpfb[lane] + psd[1] * hb.hpfb[32 + lane];
     float f1 = psd[0] * hb.hpfb[64 + lane] + psd[1] * hb.hpfb[96 + lane];
     float f2 = psd[0] * hb.hpfb[128 + lane] + psd[1] * hb.hpfb[160 + lane];
     f0 = warp_sum(f0);
     f1 = warp_sum(f1);
     f2 = warp_sum(f2);
+#endif
     const float floor_v = 4.5399929762484854e-05f;
     // CodeBands16k: code[3 i + j] = lp_log[j] - aux[i]
     {
         const int i = lane / 3, j = lane - 3 * i;
         const float fi = (i == 0) ? f0 : ((i == 1) ? f1 : f2);
-        const float aux = (fi > floor_v) ? logf(fi) : -10.0f;
+        const float aux = (fi > floor_v) ? SE_HP_LOG(fi) : -10.0f;
         code = __shfl_sync(FULL, h.lpl, j) - aux;
     }
     // DoSpecSub16k (warp-uniform scalars; lane i < 3 owns band i's noise estimate)
     const int nbf = frame_no;
     const float lambda = (nbf < 100) ? (float)(1.0 - 1.0 / (double)(float)nbf) : 0.99f;
     float frame_en = __fadd_rn(__fadd_rn(f0, f1), f2);
-    frame_en = ((double)frame_en > 0.001) ? logf(frame_en) : -6.9077552789821368f;      // (float)log(0.001)
+    frame_en = ((double)frame_en > 0.001) ? SE_HP_LOG(frame_en) : -6.9077552789821368f;      // (float)log(0.001)
     float mean_en = h.mean_en;
     if (((double)__fsub_rn(frame_en, mean_en) < 1.2) || (nbf < 10)) {
         const float d = __fsub_rn(frame_en, mean_en);
@@ -166,6 +212,8 @@ __device__ __forceinline__ void hp16_stage1(WarpMem<8> &wm, const BlockMem<8> &b
     fbss = (diff > fl) ? diff : fl;
 }
 
+#undef SE_HP_LOG
+
 // After a denoised shift is out: advance the three delay lines.
 __device__ __forceinline__ void hp16_push(Hp16State &h, float code, float fbss, int lane)
 {
@@ -178,4 +226,4 @@ __device__ __forceinline__ void hp16_push(Hp16State &h, float code, float fbss, 
     h.codeb = (lane < 18) ? cb_down : ((lane < 27) ? cb_new : 0.0f);
 }
 
-}  // namespace se
+}  // namespace SE_NSPACE

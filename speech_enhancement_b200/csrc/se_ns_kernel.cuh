@@ -1,7 +1,7 @@
 // Persistent fused NoiseSup kernel + host launchers.  Included by se_ns.cu.
 #pragma once
 
-namespace se {
+namespace SE_NSPACE {
 
 // warps (= concurrent utterances) per CTA; 2 CTAs per SM.  The feature-chain variant keeps more state live
 // per warp, so it trades occupancy (12 instead of 16 warps/SM) for 168 registers per thread.
@@ -28,6 +28,9 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
     for (int i = tid; i < 32; i += nt) { bm.bank_start[i] = tb.bank_start[i]; bm.bank_len[i] = tb.bank_len[i]; }
     for (int i = tid; i < 25 * 16; i += nt) bm.idctT[i] = tb.idctT[i];
     for (int i = tid; i < 9; i += nt) bm.firwin[i] = tb.fir_window[i];
+#ifdef SE_NS_EXACT
+    if (tid == 0) { bm.rf.ops = tb.rf_ops; bm.rf.lvl = tb.rf_lvl; bm.rf.tw = tb.rf_tw; bm.rf.m = tb.rf_m; }
+#endif
     if constexpr (P::CEPS) {
         for (int i = tid; i < 200; i += nt) bm.ham[i] = cc.hamming[i];
         for (int i = tid; i < kTriRows * 32; i += nt) bm.triT[i] = cc.triT[i];
@@ -261,7 +264,11 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     } else {
                         s.n_rows++;
                         produced = true;
+#ifdef SE_NS_EXACT
+                        dc_offset<PROF>(o, s, lane, wm.xf);
+#else
                         dc_offset<PROF>(o, s, lane);
+#endif
                         if constexpr (HP16) hp16_push(hs, hp_code, hp_fbss, lane);
                     }
                 }
@@ -425,6 +432,22 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 // ------------------------------------------------------------------------------------------------
 // test kernel: batched rfft in the reference's output layout (one warp per transform)
 // ------------------------------------------------------------------------------------------------
+#ifdef SE_NS_EXACT
+// exact mode: the reference's own butterfly schedule (rfft_exact), one warp per transform
+__global__ void rfft_kernel(float *x, int n, int count, const RfPlanDev pl)
+{
+    __shared__ float xs[4][512];
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    const int idx = blockIdx.x * 4 + warp;
+    if (idx >= count) return;
+    float *p = x + (int64_t)idx * n;
+    const int bits = (n == 256) ? 8 : 9;
+    for (int i = lane; i < n; i += 32) xs[warp][__brev((unsigned)i) >> (32 - bits)] = p[i];
+    __syncwarp();
+    rfft_exact(xs[warp], pl, lane);
+    for (int i = lane; i < n; i += 32) p[i] = xs[warp][i];
+}
+#else
 __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
 {
     __shared__ float2 Zs[4][132], Z2s[4][132];
@@ -475,6 +498,8 @@ __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
         }
     }
 }
+
+#endif
 
 // module-level kernel: Do16kProcessing over whole signals (one warp per signal, 160 samples per step)
 __global__ void qmf_split_kernel(const int16_t *x, int64_t n, int count, float *lp, float *hp)
@@ -636,10 +661,17 @@ int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count)
         return SE_EUNSUPPORTED;
     }
     if (count <= 0) return SE_OK;
+#ifdef SE_NS_EXACT
+    const NsDevTables &t = (n == 256) ? ctx->d_p8 : ctx->d_p16;
+    RfPlanDev pl;
+    pl.ops = t.rf_ops; pl.lvl = t.rf_lvl; pl.tw = t.rf_tw; pl.m = t.rf_m;
+    rfft_kernel<<<(count + 3) / 4, 128, 0, ctx->cur->stream>>>(x, n, count, pl);
+#else
     rfft_kernel<<<(count + 3) / 4, 128, 0, ctx->cur->stream>>>(x, n, count, ctx->d_p8.tw_half);
+#endif
     ctx->launches++;
     SE_CUDA(cudaGetLastError());
     return SE_OK;
 }
 
-}  // namespace se
+}  // namespace SE_NSPACE

@@ -6,7 +6,7 @@
 // DoFilterWindowing -> ApplyWF.
 #pragma once
 
-namespace se {
+namespace SE_NSPACE {
 
 struct IdctRegs { float c[9]; float firwin; };
 
@@ -45,6 +45,7 @@ template <int RB> __device__ __forceinline__ int wrap(int pos)
     return pos;
 }
 
+#ifndef SE_NS_EXACT
 // Windowed frame -> PSD bins owned by this lane (psd[r] for bin lane+32r).
 template <int PROF, int RB = Prof<PROF>::RB>
 __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, int lane,
@@ -156,6 +157,8 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
     }
 }
 
+#endif  // !SE_NS_EXACT
+
 struct StageFlags { int var, spec, mel; };
 
 // Sample rings: 4 shifts of history per stage, stored with 8 guard samples on either side (a copy of the
@@ -220,6 +223,7 @@ __device__ __forceinline__ void bank_regs_store(float *tab /*[22][32]*/, const B
 #define SE_BR_TRI(bm, br, i, lane) (br).tri[i]
 #endif
 
+#ifndef SE_NS_EXACT
 // One Wiener-filter stage (fstage is warp-uniform at run time: both stages share one copy of the code,
 // which halves the kernel's instruction footprint).
 template <int PROF>
@@ -554,4 +558,10 @@ __device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm,
     if (lane < 14) row[lane] = out;
 }
 
-}  // namespace se
+#endif  // !SE_NS_EXACT
+
+}  // namespace SE_NSPACE
+
+#ifdef SE_NS_EXACT
+#include "se_ns_exact.cuh"
+#endif

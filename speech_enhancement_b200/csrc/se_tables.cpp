@@ -248,6 +248,41 @@ static float loudness_phons(float freq)
     return (float)(4.2 + (double)afy * (60.0 - (double)tfy) / (1.0 + (double)bfy * (60.0 - (double)tfy)));
 }
 
+void build_rfft_plan(RfftPlan &p, int n, int m, bool float_trig)
+{
+    p.n = n;
+    p.m = m;
+    p.ops.clear();
+    p.tw.clear();
+    // length-two butterflies, rfft.c:77-92
+    p.level_begin[0] = 0;
+    p.tw_begin[0] = 0;
+    for (int is = 0, id = 4; is < n - 1; is = 2 * id - 2, id *= 4)
+        for (int i = is; i < n; i += id) p.ops.push_back((unsigned)i);
+    // L-shaped butterflies, rfft.c:94-179: the blocks a level visits, once for the twiddle-free part and once per j
+    for (int level = 1; level < m; level++) {
+        const int n2 = 2 << level, n8 = n2 >> 3;
+        p.level_begin[level] = (int)p.ops.size();
+        p.tw_begin[level] = (int)(p.tw.size() / 4);
+        const float e = (float)((3.14159265358979323846 * 2) / n2);
+        for (int j = 0; j < (n8 > 1 ? n8 : 1); j++) {
+            if (j >= 1) {
+                const float a = (float)j * e, a3 = 3 * a;
+                if (float_trig) {
+                    p.tw.push_back(cosf(a)); p.tw.push_back(sinf(a)); p.tw.push_back(cosf(a3)); p.tw.push_back(sinf(a3));
+                } else {
+                    p.tw.push_back((float)std::cos((double)a)); p.tw.push_back((float)std::sin((double)a));
+                    p.tw.push_back((float)std::cos((double)a3)); p.tw.push_back((float)std::sin((double)a3));
+                }
+            }
+            for (int is = 0, id = 2 * n2; is < n; is = 2 * id - n2, id *= 4)
+                for (int i = is; i < n; i += id) p.ops.push_back((unsigned)i | ((unsigned)j << 16));
+        }
+    }
+    p.level_begin[m] = (int)p.ops.size();
+    p.tw_begin[m] = (int)(p.tw.size() / 4);
+}
+
 void build_gt_tables(GtTables &t)
 {
     // channel set-up inline in resynth()/subbband(), extractwav.cpp:41-54

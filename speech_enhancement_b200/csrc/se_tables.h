@@ -42,6 +42,22 @@ struct GtTables {                 // 64-channel gammatone
     double fall_d[160], rise_d[160];          // raised-cosine halves, double as in the reference
 };
 
+// SE_FLAG-less "exact" arithmetic mode (se_ctx_set_exact): the butterfly schedule of rfft(x, n, m)
+// (etsi/cpp/rfft.c:45-180, split-radix after Sorensen et al. 1987) flattened into per-level lists of INDEPENDENT
+// butterflies, so a warp can run one level in parallel and still produce every value with the reference's operations
+// in the reference's order.  Level 0 = the length-two butterflies (op = first index); level k >= 1 = the L-shaped
+// butterflies of size n2 = 2 << k (op = block base i | j << 16; j = 0 is the twiddle-free butterfly incl. its n2/8
+// part, j >= 1 uses twiddle set j - 1 of that level: cc1, ss1, cc3, ss3 exactly as rfft.c:133-139 evaluates them --
+// double cos/sin of a FLOAT angle in the C file, the float overloads in the plugin's C++ copy).
+struct RfftPlan {
+    int n, m;
+    std::vector<unsigned> ops;
+    int level_begin[16];          // first op of level k (k = 0..m-1), level_begin[m] = ops.size()
+    int tw_begin[16];             // first twiddle set (4 floats each) of level k
+    std::vector<float> tw;
+};
+void build_rfft_plan(RfftPlan &p, int n, int m, bool float_trig);
+
 void build_ns_tables_p8(NsTables &t);
 void build_ns_tables_p16(NsTables &t);
 void build_cc_tables(CcTables &t);

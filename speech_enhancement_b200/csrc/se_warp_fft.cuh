@@ -7,7 +7,7 @@
 #pragma once
 #include <cuda_runtime.h>
 
-namespace se {
+namespace SE_NSPACE {
 
 __device__ __forceinline__ float2 cadd(float2 a, float2 b) { return make_float2(a.x + b.x, a.y + b.y); }
 __device__ __forceinline__ float2 csub(float2 a, float2 b) { return make_float2(a.x - b.x, a.y - b.y); }
@@ -123,4 +123,4 @@ __device__ __forceinline__ void rsplit_pair(const float2 *W, int k, float2 &B, f
     C = make_float2(di, -dr);
 }
 
-}  // namespace se
+}  // namespace SE_NSPACE

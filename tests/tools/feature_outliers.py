@@ -15,6 +15,9 @@ from speech_enhancement_b200 import api, synth     # noqa: E402
 n_utts = int(sys.argv[1]) if len(sys.argv) > 1 else 200
 o = pyoracle.Oracle(fast=False)
 ctx = api.Context(0)
+if "--exact" in sys.argv:                           # se_ctx_set_exact: the reference's own arithmetic
+    ctx.set_exact(True)
+    print("exact arithmetic mode")
 xs = [synth.utterance(5000 + i, 8000, 8000 * 5) for i in range(n_utts)]
 offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
 got = ctx.etsi_features(np.concatenate(xs), offsets)
@@ -27,7 +30,8 @@ for u, x in enumerate(xs):
     vad_diff += int((ref[:, 14] != got[u][:, 14]).sum())
     rows += len(ref)
 e = np.concatenate(errs)
-print("rows", rows, "vad flag mismatches", vad_diff)
+print("rows", rows, "vad flag mismatches", vad_diff, "values not bit-identical",
+      sum(int(np.sum(o.etsi_features(x)[0].view(np.uint32) != got[u].view(np.uint32))) for u, x in enumerate(xs)))
 for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
     print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
 print("max err %.4g, median %.3g" % (e.max(), np.median(e)))
@@ -50,7 +54,9 @@ for u, x in enumerate(xs):
     lsb = max(lsb, int(np.abs(den[u].astype(np.int32) - rden.astype(np.int32)).max()))
     rows += len(ref)
 e = np.concatenate(errs)
-print("16 kHz mode (+flush): rows", rows, "vad flag mismatches", vad_diff, "low-band int16 max |d|", lsb)
+print("16 kHz mode (+flush): rows", rows, "vad flag mismatches", vad_diff, "low-band int16 max |d|", lsb,
+      "values not bit-identical",
+      sum(int(np.sum(o.etsi_features_flush(x, True).view(np.uint32) != got[u].view(np.uint32))) for u, x in enumerate(xs)))
 for t in (1e-5, 1e-4, 1e-3, 1e-2, 5e-2):
     print("share of frames with err > %g: %.5f" % (t, float((e > t).mean())))
 print("max err %.4g, median %.3g" % (e.max(), np.median(e)))
