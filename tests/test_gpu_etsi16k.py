@@ -4,22 +4,18 @@ QMF split -> NoiseSup on the low band + spectral subtraction / coding of three 4
 tests/test_oracle_golden.py::test_etsi16k_*).
 
 Bars as for the 8 kHz chain (tests/test_gpu_features.py): row counts and VAD flags identical, low-band int16
-stream within 1 LSB, cepstra within 1e-4 of the frame's scale on all but a small share of frames (WaveProc's
-integer peak picking), those bounded separately.
+stream within 1 LSB, cepstra within 1e-4 of the frame's scale except WaveProc peak flips, bounded by
+conftest.check_feature_envelope; the exact arithmetic mode is bit-identical on every row (tests/test_gpu_exact.py).
 """
 import numpy as np
 import pytest
 
-from conftest import ceps_err
+from conftest import FEAT_OUTLIER_TOL, ceps_err, check_feature_envelope
 from speech_enhancement_b200 import synth
 
 pytestmark = pytest.mark.gpu
 
-CEPS_TOL = 1e-4
-FLIP_TOL = 1e-3           # bars as tests/test_gpu_features.py
-FLIP_SHARE = 0.005
-TAIL_SHARE = 0.10
-OUTLIER_TOL = 0.25
+OUTLIER_TOL = FEAT_OUTLIER_TOL
 
 
 def _batch(lens, zeros, seed=700):
@@ -59,7 +55,7 @@ def test_features16k_vs_oracle(ctx, oracle):
     zeros = [0, 3, 7, 0, 0, 1, 0, 0, 0, 0, 2]
     xs, offsets = _batch(lens, zeros)
     got, den = ctx.etsi16k_features(np.concatenate(xs), offsets, denoised=True)
-    n_bad = n_all = n_flip = 0
+    n_all = 0
     for u, x in enumerate(xs):
         ref, ref_den = oracle.etsi_features_16k(x)
         g = got[u]
@@ -72,13 +68,23 @@ def test_features16k_vs_oracle(ctx, oracle):
         assert np.array_equal(g[:, 14], ref[:, 14]), "utterance %d: VAD flags differ" % u
         assert not g[:zeros[u]].any()
         err = ceps_err(ref[:, :14], g[:, :14]).max(axis=1)
-        n_bad += int((err > CEPS_TOL).sum())
-        n_flip += int((err > FLIP_TOL).sum())
         n_all += len(err)
         assert err.max() <= OUTLIER_TOL, "utterance %d frame %d: %g" % (u, int(err.argmax()), err.max())
     assert n_all > 1000
-    assert n_bad <= TAIL_SHARE * n_all, "%d of %d frames above %g" % (n_bad, n_all, CEPS_TOL)
-    assert n_flip <= max(2, FLIP_SHARE * n_all), "%d of %d frames above %g" % (n_flip, n_all, FLIP_TOL)
+
+
+def test_features16k_within_the_reference_own_envelope(ctx, oracle):
+    """40 x 5 s of 16 kHz audio (19 520 rows) against the envelope of conftest.check_feature_envelope."""
+    xs = [synth.utterance(7000 + i, 16000, 16000 * 5) for i in range(40)]
+    offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
+    got = ctx.etsi16k_features(np.concatenate(xs), offsets)
+    errs = []
+    for u, x in enumerate(xs):
+        ref, _ = oracle.etsi_features_16k(x)
+        assert got[u].shape == ref.shape and np.array_equal(got[u][:, 14], ref[:, 14])
+        errs.append(ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1))
+    n_tail, n_flip = check_feature_envelope(np.concatenate(errs))
+    print("16 kHz mode, fast mode: %d frames above 1e-4, %d above 1e-3 of %d" % (n_tail, n_flip, sum(map(len, errs))))
 
 
 def test_features16k_use_the_high_band(ctx):
@@ -128,4 +134,4 @@ def test_features16k_full_size(ctx, oracle):
         assert got[u].shape == ref.shape
         assert np.array_equal(got[u][:, 14], ref[:, 14])
         err = ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1)
-        assert (err > CEPS_TOL).mean() <= TAIL_SHARE and (err > FLIP_TOL).sum() <= max(2, FLIP_SHARE * len(err)) and err.max() <= OUTLIER_TOL
+        assert err.max() <= OUTLIER_TOL

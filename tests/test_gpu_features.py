@@ -2,26 +2,21 @@
 etsi/cpp/ParmInterface.c:274-311, against the oracle (pinned bit-for-bit on the reference build by
 tests/test_oracle_golden.py).
 
-Bars: row counts and VAD flags identical; cepstra within 1e-4 of the frame's scale (conftest.ceps_err) on all
-but a small share of frames -- WaveProc picks integer peak positions from a rounded Teager energy, so a
-1-ulp difference in the denoised stream can move a window edge by a sample on a few frames (the reference
-itself would differ there between -O2 and -O3 builds); those frames are bounded separately.
+Bars (default = fast arithmetic mode): row counts and VAD flags identical; denoised int16 within 1 LSB; cepstra within
+1e-4 of the frame's scale (conftest.ceps_err) except where a 1-ulp difference in the denoised stream moved one of
+WaveProc's integer peak positions -- bounded by the envelope the reference shows against ITSELF between two compiler
+settings (conftest.check_feature_envelope, profiles/r02_ref_vs_ref_envelope.json).  In the exact arithmetic mode every
+row is bit-identical (tests/test_gpu_exact.py::test_feature_chains_every_frame).
 """
 import numpy as np
 import pytest
 
-from conftest import ceps_err
+from conftest import FEAT_OUTLIER_TOL, ceps_err, check_feature_envelope
 from speech_enhancement_b200 import synth
 
 pytestmark = pytest.mark.gpu
 
-CEPS_TOL = 1e-4
-FLIP_TOL = 1e-3           # a frame whose WaveProc window edge moved (a flip) lands above this
-FLIP_SHARE = 0.005        # ... measured 0.006 % of 97 600 frames; the bar leaves room for small samples
-TAIL_SHARE = 0.10         # frames above CEPS_TOL: a flip also perturbs PostProc's LMS equaliser (step 0.0088), so the
-                          # ~100 frames after it sit between 1e-4 and 1e-3 until the weights have re-converged; measured
-                          # 0.4 % at scale, up to 4.7 % on a 1 195-frame sample that contains one flip
-OUTLIER_TOL = 0.25       # measured on 97 600 frames: 0.5 % above 1e-4, 0.04 % above 1e-3, max 0.125 (tests/tools/feature_outliers.py)
+OUTLIER_TOL = FEAT_OUTLIER_TOL
 
 
 def _batch(lens, zeros):
@@ -39,7 +34,6 @@ def test_features_vs_oracle(ctx, oracle):
     zeros = [0, 3, 7, 0, 0, 1, 0, 0, 0, 0, 2]
     xs, offsets = _batch(lens, zeros)
     got, den = ctx.etsi_features(np.concatenate(xs) if sum(lens) else np.zeros(0, np.int16), offsets, denoised=True)
-    n_bad = n_all = n_flip = 0
     for u, x in enumerate(xs):
         ref, ref_den = oracle.etsi_features(x)
         g = got[u]
@@ -54,12 +48,22 @@ def test_features_vs_oracle(ctx, oracle):
         z = zeros[u]
         assert not g[:z].any()
         err = ceps_err(ref[:, :14], g[:, :14]).max(axis=1)
-        n_bad += int((err > CEPS_TOL).sum())
-        n_flip += int((err > FLIP_TOL).sum())
-        n_all += len(err)
         assert err.max() <= OUTLIER_TOL, "utterance %d frame %d: %g" % (u, int(err.argmax()), err.max())
-    assert n_bad <= TAIL_SHARE * n_all, "%d of %d frames above %g" % (n_bad, n_all, CEPS_TOL)
-    assert n_flip <= max(2, FLIP_SHARE * n_all), "%d of %d frames above %g" % (n_flip, n_all, FLIP_TOL)
+
+
+def test_features_within_the_reference_own_envelope(ctx, oracle):
+    """40 x 5 s (19 520 rows): shares of frames beyond 1e-4 / 1e-3 of the frame scale and the largest error stay inside
+    what two builds of the reference show against each other."""
+    xs = [synth.utterance(5000 + i, 8000, 8000 * 5) for i in range(40)]
+    offsets = np.concatenate([[0], np.cumsum([len(x) for x in xs])]).astype(np.int64)
+    got = ctx.etsi_features(np.concatenate(xs), offsets)
+    errs = []
+    for u, x in enumerate(xs):
+        ref, _ = oracle.etsi_features(x)
+        assert got[u].shape == ref.shape and np.array_equal(got[u][:, 14], ref[:, 14])
+        errs.append(ceps_err(ref[:, :14], got[u][:, :14]).max(axis=1))
+    n_tail, n_flip = check_feature_envelope(np.concatenate(errs))
+    print("8 kHz feature chain, fast mode: %d frames above 1e-4, %d above 1e-3 of %d" % (n_tail, n_flip, sum(map(len, errs))))
 
 
 def test_features_device_memory_and_shards(ctx, oracle):
