@@ -536,3 +536,49 @@ class RefG64:
         rc = self.L.ref_resynth(_p(wav), len(wav), _p(m), m.shape[0], _p(out))
         assert rc == 0
         return out, m
+
+
+# ------------------------------------------------------------------------------------------
+# oracle/ref_bench.c : the reference arm's timing loop (bench.py --impl reference / cpu_baseline)
+# ------------------------------------------------------------------------------------------
+class RefBench:
+    """Times the reference's own CPU code (oracle/_ref/*_fast.so; the plain-C port where that is absent) over a batch
+    of in-memory utterances on N forked worker processes -- no Python inside the timed region (oracle/ref_bench.c).
+    workload: 'p8' (etsi_denoise + CompCeps step), 'p16' (func_Wiener), 'resynth' (resyth_64sub_IBM)."""
+    LIBS = {"p8": "libref_etsi_fast.so", "p16": "libref_p16_fast.so", "resynth": "libref_resynth_ibm_fast.so"}
+    IDS = {"p8": 0, "p16": 1, "resynth": 2}
+
+    def __init__(self, workload):
+        so = os.path.join(HERE, "libse_refbench.so")
+        src = os.path.join(HERE, "ref_bench.c")
+        if not os.path.exists(so) or (os.path.exists(src) and os.path.getmtime(so) < os.path.getmtime(src)):
+            subprocess.check_call(["make", "-s", "-C", HERE, "libse_refbench.so"])
+        self.L = C.CDLL(so)
+        self.L.ref_bench_open.argtypes = [C.c_char_p]
+        self.L.ref_bench_run.argtypes = [C.c_int, C.c_int, _vp, _vp, C.c_int, _vp, _vp, C.c_int,
+                                         C.POINTER(C.c_double), C.POINTER(C.c_double)]
+        self.workload = workload
+        if have_ref(self.LIBS[workload]):
+            self.kind, path = "reference", os.path.join(REF_DIR, self.LIBS[workload])
+        else:
+            self.kind = "port"
+            path = os.path.join(HERE, "libse_oracle_fast.so")
+            if not os.path.exists(path):
+                subprocess.check_call(["make", "-s", "-C", HERE, "libse_oracle_fast.so"])
+        self.lib_path = path
+        if self.L.ref_bench_open(path.encode()) != 0:
+            raise RuntimeError("cannot load " + path)
+
+    def run(self, samples, offsets, workers, mask=None, frame_offsets=None):
+        """-> (seconds, checksum) for utterances 0..len(offsets)-2."""
+        samples = np.ascontiguousarray(samples, np.int16)
+        offsets = np.ascontiguousarray(offsets, np.int64)
+        if mask is not None:
+            mask = np.ascontiguousarray(mask, np.float32)
+            frame_offsets = np.ascontiguousarray(frame_offsets, np.int64)
+        sec, cs = C.c_double(0), C.c_double(0)
+        rc = self.L.ref_bench_run(self.IDS[self.workload], 1 if self.kind == "port" else 0, _p(samples), _p(offsets),
+                                  len(offsets) - 1, _p(mask), _p(frame_offsets), int(workers), C.byref(sec), C.byref(cs))
+        if rc != 0:
+            raise RuntimeError("ref_bench_run failed (%d)" % rc)
+        return sec.value, cs.value

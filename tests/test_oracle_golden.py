@@ -236,3 +236,40 @@ def test_reference_is_ill_conditioned_on_degenerate_signals(oracle):
         if len(a):
             err[u % 10] = max(err[u % 10], float(ceps_err(a, b).max()))
     assert err[8] < 1e-4 and err[1] > 3e-4 and err[5] > 1e-3, err
+
+
+def test_ref_bench_loop_is_the_reference(oracle):
+    """oracle/ref_bench.c (the timing loop of bench.py's reference arm): the outputs it computes on forked workers are
+    those of the direct calls, for any worker count."""
+    from speech_enhancement_b200 import api  # noqa: F401  (only for the frame-count formula below)
+    xs8 = [synth.utterance(400 + i, 8000, 8000 + 37 * i) for i in range(5)]
+    off8 = np.concatenate([[0], np.cumsum([len(x) for x in xs8])]).astype(np.int64)
+    rb = po.RefBench("p8")
+    t1, c1 = rb.run(np.concatenate(xs8), off8, 1)
+    t3, c3 = rb.run(np.concatenate(xs8), off8, 3)
+    want = 0.0
+    for x in xs8:
+        r = oracle.etsi_denoise(x, with_ceps=True)
+        want += float(r["den_i16"].astype(np.float64).sum()) + float(r["ceps"].astype(np.float64).sum())
+    # (the timed libraries are the -O3 / FMA builds: single LSBs may differ from the -O2 parity build)
+    assert abs(c1 - c3) <= 1e-9 * max(1.0, abs(c1))                     # any worker count, same outputs
+    assert abs(c1 - want) <= 50 + 1e-4 * abs(want)
+    assert t1 > 0 and t3 > 0
+    xs16 = [synth.utterance(410 + i, 16000, 16000 + 41 * i) for i in range(3)]
+    off16 = np.concatenate([[0], np.cumsum([len(x) for x in xs16])]).astype(np.int64)
+    rb = po.RefBench("p16")
+    _, c = rb.run(np.concatenate(xs16), off16, 2)
+    want = 0.0
+    for x in xs16:
+        s = oracle.p16_stream()
+        r = s.func_wiener(x[:len(x) - len(x) % 160].astype(np.float32))
+        s.close()
+        want += float(r["out"].astype(np.float64).sum()) + float(r["gains"].astype(np.float64).sum())
+    assert abs(c - want) <= 50 + 1e-4 * abs(want)
+    rb = po.RefBench("resynth")
+    nf = [oracle.resynth_num_frames(len(x), 0) for x in xs16]
+    fo = np.concatenate([[0], np.cumsum(nf)]).astype(np.int64)
+    mask = (np.random.default_rng(1).random((int(fo[-1]), 64)) > 0.4).astype(np.float32)
+    _, c = rb.run(np.concatenate(xs16), off16, 2, mask, fo)
+    want = sum(float(oracle.resynth(x, mask[fo[u]:fo[u + 1]].copy(), 0)[0].astype(np.float64).sum()) for u, x in enumerate(xs16))
+    assert abs(c - want) <= 50
