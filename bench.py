@@ -1,18 +1,21 @@
 #!/usr/bin/env python
 """bench.py — audio-seconds per second (xRT) of the speech-enhancement hot path on B200.
 
-  python bench.py [--gpus N --steps K --warmup W]            our arm (CUDA, through the C ABI)
-  python bench.py --impl reference [...]                     the reference's own CPU code (oracle/_ref)
+  python bench.py [--gpus N --steps K --warmup W] [--workload p16|p8|resynth]      our arm (CUDA, through the C ABI)
+  python bench.py --impl reference [--workload p16|p8|resynth] [...]               the reference's own CPU code
 
-A "step" is one pass of the hot path over one batch of synthetic utterances.  Headline workload =
-BASELINE.json configs[1]: 10k synthetic 16 kHz noisy utterances (ragged 2-10 s) through the plugin
-NoiseSup (framed rfft + two-stage Wiener filter, etsi_denoise_mapping_func_Wiener) -> denoised stream,
-25 band gains per frame, frame-dropping flags.  The P8 NoiseSup+CompCeps path and the 64-sub IBM
-resynthesis are measured on smaller batches and reported under "other_workloads".
+A "step" is one pass of the hot path over one batch of synthetic utterances.  Headline workload (the default) =
+BASELINE.json configs[1]: 10k synthetic 16 kHz noisy utterances (ragged 2-10 s) through the plugin NoiseSup (framed
+rfft + two-stage Wiener filter, etsi_denoise_mapping_func_Wiener) -> denoised stream, 25 band gains per frame,
+frame-dropping flags.  The two paths BASELINE.json's metric names -- P8 ETSI NoiseSup+CompCeps (etsi_denoise + the
+CompCeps step) and the 64-sub IBM resynthesis (resyth_64sub_IBM) -- are measured in the same run with the same key set
+(value, e2e, roofline, cpu_baseline) under "workloads"; --workload makes one of them the headline.  Everything else on
+the path (feature chains, sub-band / IBM kernels, extract_Wiener chain) is under "other_workloads" (device-resident).
 
-Weak scaling: every rank (one per GPU) processes its own batch of the same size; there is no
-collective on the data path (utterances are independent).  torch is used for device memory, the
-stream/events and torch.distributed only.
+Weak scaling: every rank (one per GPU) processes its own batch of the same size; there is no collective on the data
+path (utterances are independent).  torch is used for device memory, the stream/events and torch.distributed only.
+The reference arm and the cpu_baseline legs time oracle/_ref (the reference's own sources compiled in place) through
+oracle/ref_bench.c: forked C workers over the in-memory batch, no Python in the timed region.
 """
 import argparse
 import json
@@ -39,7 +42,11 @@ def parse():
     ap.add_argument("--steps", type=int, default=5)
     ap.add_argument("--warmup", type=int, default=3)
     ap.add_argument("--impl", default="ours", choices=["ours", "reference"])
-    ap.add_argument("--utts", type=int, default=10000, help="utterances per GPU in the headline batch")
+    ap.add_argument("--workload", default="p16", choices=["p16", "p8", "resynth"],
+                    help="headline workload: p16 = configs[1] (default), p8 = ETSI NoiseSup+CompCeps, resynth = resyth_64sub_IBM")
+    ap.add_argument("--utts", type=int, default=10000, help="utterances per GPU in the p16 batch")
+    ap.add_argument("--gpu-map", default="stride", choices=["stride", "dense"],
+                    help="rank k -> GPU k * (visible / N) (stride: ranks spread over the box's PCIe root ports) or GPU k")
     ap.add_argument("--no-extra", action="store_true", help="skip the other_workloads section")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
@@ -514,48 +521,33 @@ def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
 # ------------------------------------------------------------------------------------------------
 # the reference's own CPU code (oracle/_ref, or the plain-C port when _ref is absent)
 # ------------------------------------------------------------------------------------------------
-_W = {}
+FS = {"p16": 16000, "p8": 8000, "resynth": 16000}
 
 
-def _cpu_init(kind):
+def cpu_leg(workload, samples, offsets, mask=None, frame_offsets=None, all_cores_s=4.0, one_core_s=3.0):
+    """The reference's CPU implementation (oracle/_ref, else the port) on a BOUNDED sample of the workload's own batch:
+    the first n utterances, n sized from a calibration pass so that the all-cores leg takes about all_cores_s seconds
+    of wall clock and the 1-worker leg about one_core_s.  Returns the cpu_baseline object."""
     from oracle import pyoracle
-    if kind == "reference":
-        _W["h"] = pyoracle.RefP16(fast=True)
-    else:
-        _W["h"] = pyoracle.Oracle(fast=True)
-    _W["kind"] = kind
+    rb = pyoracle.RefBench(workload)
+    cores = os.cpu_count() or 1
+    nu = len(offsets) - 1
+    fs = FS[workload]
 
+    def run(n, workers):
+        n = max(1, min(n, nu))
+        sec, _ = rb.run(samples, offsets[:n + 1], workers, mask, None if frame_offsets is None else frame_offsets[:n + 1])
+        return float(offsets[n]) / fs, sec, n
 
-def _cpu_one(x):
-    """One utterance through etsi_denoise_mapping_func_Wiener on a fresh thread instance."""
-    from oracle import pyoracle
-    xf = x.astype(np.float32)
-    if _W["kind"] == "reference":
-        h = _W["h"]
-        h.close()
-        h.h = h.L.ref_p16_create()
-        r = h.func_wiener(xf)
-    else:
-        s = _W["h"].p16_stream()
-        r = s.func_wiener(xf)
-        s.close()
-    return len(r["gains"])
-
-
-def cpu_p16(samples, offsets, n_utts, cores):
-    """Times the CPU implementation on the first n_utts utterances with `cores` worker processes."""
-    import multiprocessing as mp
-    from oracle import pyoracle
-    kind = "reference" if pyoracle.have_ref("libref_p16_fast.so") else "port"
-    xs = [samples[offsets[u]:offsets[u + 1]] for u in range(n_utts)]
-    audio_s = float(offsets[n_utts] - offsets[0]) / 16000.0
-    ctx = mp.get_context("fork")
-    with ctx.Pool(cores, initializer=_cpu_init, initargs=(kind,)) as pool:
-        pool.map(_cpu_one, xs[:cores])          # warm the workers (library load, table init)
-        t0 = time.perf_counter()
-        rows = pool.map(_cpu_one, xs, chunksize=max(1, n_utts // (cores * 8)))
-        dt = time.perf_counter() - t0
-    return dict(kind=kind, audio_s=audio_s, seconds=dt, rows=int(sum(rows)), cores=cores)
+    a0, t0, n0 = run(cores, cores)                        # calibration (also warms the page cache / library)
+    a_all, t_all, n_all = run(int(n0 * all_cores_s / max(t0, 1e-3)), cores)
+    a_one, t_one, n_one = run(int(n_all * (one_core_s / max(t_all, 1e-3)) / cores), 1)
+    return {"value": a_all / t_all, "unit": UNIT, "cores": cores, "kind": rb.kind,
+            "sample": "first %d utterances of the workload (%.0f audio-s) on %d forked C workers, %.2f s wall"
+                      % (n_all, a_all, cores, t_all),
+            "one_thread": {"value": a_one / t_one, "unit": UNIT, "cores": 1,
+                           "sample": "first %d utterances (%.0f audio-s), %.2f s wall" % (n_one, a_one, t_one)},
+            "library": os.path.relpath(rb.lib_path, ROOT)}
 
 
 METRIC = "audio-sec/sec (xRT) per B200 for NoiseSup+CompCeps & 64-sub IBM resynth, 1/2/4/8 GPU"
