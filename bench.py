@@ -207,34 +207,35 @@ def host_timed_steps(torch, dist, step, warmup, steps):
     return dist.max((t1 - t0) * 1e3)
 
 
-def ncu_capture(utts, alg_bytes):
-    """The committed ncu capture of the dominant kernel (profiles/r01_traffic.json), if it was taken on this
-    workload; None otherwise."""
+def ncu_capture(workload, alg_bytes):
+    """The committed ncu capture of the workload's dominant kernel(s) (profiles/traffic.json), if it was taken on this
+    workload size; None otherwise."""
     try:
-        with open(os.path.join(ROOT, "profiles", "r01_traffic.json")) as f:
-            t = json.load(f)
-        if t["workload_utts"] == utts and abs(t["algorithmic_bytes_per_launch"] - alg_bytes) <= 0.001 * alg_bytes:
+        with open(os.path.join(ROOT, "profiles", "traffic.json")) as f:
+            t = json.load(f)[workload]
+        if abs(t["algorithmic_bytes_per_launch"] - alg_bytes) <= 0.001 * alg_bytes:
             return t
     except (OSError, KeyError, ValueError):
         pass
     return None
 
 
-def measured_traffic(utts, alg_bytes):
-    """roofline.traffic: DRAM bytes per launch of the dominant kernel from that capture."""
-    t = ncu_capture(utts, alg_bytes)
-    return t["traffic_bytes"] if t else None
-
-
-def issue_bound(utts, alg_bytes, kernel_ms, sm_mhz, sm_count=148):
-    """What actually bounds the kernel: executed warp-instructions per launch (ncu) against the
-    issue slots the SMs offered during the live-timed launch (4 schedulers per SM, one instruction per clock)."""
-    t = ncu_capture(utts, alg_bytes)
-    if not t or not sm_mhz:
-        return None
-    slots = sm_count * 4 * sm_mhz * 1e6 * kernel_ms * 1e-3
-    return {"warp_instructions_per_launch": t["inst_executed"], "issue_slots_in_launch": slots,
-            "frac": t["inst_executed"] / slots}
+def roofline(workload, kernel, alg_bytes, kernel_ms, sm_mhz, sm_count=148):
+    """roofline object of one workload: ALGORITHMIC bytes per launch / live-timed kernel duration against the measured
+    HBM peak; traffic = DRAM bytes of the same launch from the committed ncu capture; issue_bound = executed
+    warp-instructions (ncu) against the issue slots the SMs offered during the live-timed launch (what actually bounds
+    these kernels)."""
+    hbm, src = peaks()
+    achieved = alg_bytes / (kernel_ms * 1e-3) / 1e9
+    t = ncu_capture(workload, alg_bytes)
+    r = {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
+         "traffic": t["traffic_bytes"] if t else None, "peak_source": src, "kernel": kernel, "kernel_ms": kernel_ms,
+         "algorithmic_bytes_per_launch": alg_bytes, "issue_bound": None}
+    if t and sm_mhz:
+        slots = sm_count * 4 * sm_mhz * 1e6 * kernel_ms * 1e-3
+        r["issue_bound"] = {"warp_instructions_per_launch": t["inst_executed"], "issue_slots_in_launch": slots,
+                            "frac": t["inst_executed"] / slots}
+    return r
 
 
 def dev(torch, a):
