@@ -312,9 +312,11 @@ def bench_p16(args, torch, api, ctx, dist, stream, first_u):
                 samples=samples, offsets=offsets)
 
 
-def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features=False):
+def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features=False, full=False):
     """P8: ETSI NoiseSup + CompCeps on 10 s 8 kHz utterances (C1-type work, batched); features=True runs the
-    whole feature chain (WaveProc -> CompCeps -> PostProc -> VAD, 15-column rows) behind NoiseSup."""
+    whole feature chain (WaveProc -> CompCeps -> PostProc -> VAD, 15-column rows) behind NoiseSup.
+    full=True (the metric's own path): also the end-to-end leg through se_etsi_denoise_batch with pinned HOST buffers
+    and the raw numbers run_ours() needs for value / e2e / roofline / cpu_baseline."""
     samples, offsets = make_corpus(first_u, n_utts, 8000, 0, 0, seconds=10.0)
     total = int(offsets[-1])
     co = np.zeros(n_utts + 1, np.int64)
@@ -337,16 +339,42 @@ def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features
     ctx.sync()
     ctx.reset_kernel_times()
     ctx.profiling(True)
-    ms = timed_steps(torch, dist, stream, step, 0, args.steps)
+    l0 = ctx.launch_count()
+    with ClockSampler(dist.local) as clk:
+        ms = timed_steps(torch, dist, stream, step, 0, args.steps)
+    launches = ctx.launch_count() - l0
     k_ms, k_n = ctx.kernel_time(api.K_NS_P8)
     ctx.profiling(False)
     audio_s = total / 8000.0
     hops = total // 80
     hbm, _ = peaks()
-    gbs = hops * (P8_BYTES_PER_HOP + (4 if features else 0)) / (k_ms / max(k_n, 1) * 1e-3) / 1e9
+    alg_bytes = hops * (P8_BYTES_PER_HOP + (4 if features else 0))
+    gbs = alg_bytes / (k_ms / max(k_n, 1) * 1e-3) / 1e9
     name = "P8 etsi NoiseSup+WaveProc+CompCeps+PostProc+VAD" if features else "P8 etsi NoiseSup+CompCeps"
-    return {"workload": "%s, %d x 10 s 8 kHz" % (name, n_utts), "xrt": audio_s * args.steps / (ms * 1e-3),
-            "ms_per_step": ms / args.steps, "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
+    out = {"workload": "%s, %d x 10 s 8 kHz" % (name, n_utts), "xrt": audio_s * args.steps / (ms * 1e-3),
+           "ms_per_step": ms / args.steps, "kernel_ms": k_ms / max(k_n, 1), "achieved_gbs": gbs, "frac": gbs / hbm}
+    if not full:
+        return out
+    # end to end: pinned host buffers through the same C-ABI call, H2D + D2H inside the timed region
+    rows_dev = d_nc.cpu().numpy()
+    h_in = pinned(api, samples)
+    h_den = api.PinnedArray(total, np.int16)
+    h_ceps = api.PinnedArray(int(co[-1]) * 14, np.float32)
+    h_nc = api.PinnedArray(n_utts, np.int32)
+
+    def step_e2e():
+        ctx.etsi_denoise_raw(h_in.ptr, offsets, n_utts, h_den.ptr, h_ceps.ptr, co, h_nc.ptr, mem=api.SE_MEM_HOST)
+
+    e2e_ms = host_timed_steps(torch, dist, step_e2e, 1, args.steps)
+    same = bool(np.array_equal(h_nc.array, rows_dev))
+    d2h = h_den.array.nbytes + h_ceps.array.nbytes + h_nc.array.nbytes
+    for q in (h_in, h_den, h_ceps, h_nc):
+        q.free()
+    del d_in, d_den, d_ceps, d_nc
+    torch.cuda.empty_cache()
+    return dict(name=out["workload"], audio_s=audio_s, ms=ms, launches=launches, k_ms=k_ms / max(k_n, 1), alg_bytes=alg_bytes,
+                kernel="ns_stream_kernel<8,int16>", e2e_ms=e2e_ms, h2d=samples.nbytes, d2h=d2h, clocks=clk.summary(),
+                e2e_matches_device=same, samples=samples, offsets=offsets, mask=None, frame_offsets=None)
 
 
 def bench_etsi16k(args, torch, api, ctx, dist, stream, first_u, n_utts=3000):
