@@ -306,10 +306,11 @@ def bench_p16(args, torch, api, ctx, dist, stream, first_u):
         p.free()
     del d_in, d_out, d_flags, d_gains, d_rows
     torch.cuda.empty_cache()
-    return dict(audio_s=audio_s, ms=ms, launches=launches, k_ms=k_ms, k_n=k_n, blocks=tb, rows=rows_total,
+    return dict(name=workload_name(args.utts), audio_s=audio_s, ms=ms, launches=launches, k_ms=k_ms / max(k_n, 1),
+                alg_bytes=tb * P16_BYTES_PER_BLOCK, kernel="ns_stream_kernel<16,int16>", blocks=tb, rows=rows_total,
                 e2e_ms=e2e_ms, feat_ms=feat_ms, feat_d2h=feat_d2h,
                 h2d=h2d, d2h=d2h, clocks=clk.summary(), e2e_matches_device=same,
-                samples=samples, offsets=offsets)
+                samples=samples, offsets=offsets, mask=None, frame_offsets=None)
 
 
 def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features=False, full=False):
@@ -512,8 +513,9 @@ def bench_extract_wiener(args, torch, api, ctx, dist, stream, first_u, n_utts=23
             "sub_band_audio_xrt": 64 * total / 16000.0 * steps / (ms * 1e-3), "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
-def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
-    """G64: resyth_64sub_IBM on 10 s 16 kHz utterances (BASELINE configs[2] shape)."""
+def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, full=False):
+    """G64: resyth_64sub_IBM on 10 s 16 kHz utterances (BASELINE configs[2] shape).  full=True adds the end-to-end leg
+    through se_resynth_batch with pinned HOST buffers and returns the raw numbers for run_ours()."""
     samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
     total = int(offsets[-1])
     nf = api.resynth_num_frames(160000, api.RESYNTH_IBM)
@@ -527,24 +529,48 @@ def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000):
         ctx.resynth_raw(d_in.data_ptr(), offsets, n_utts, d_mask.data_ptr(), fo, api.RESYNTH_IBM, 0, d_out.data_ptr(),
                         mem=api.SE_MEM_DEVICE)
 
-    w = min(args.warmup, 1)
+    w = min(args.warmup, 3 if full else 1)
     for _ in range(w):
         step()
     ctx.sync()
     ctx.reset_kernel_times()
     ctx.profiling(True)
-    steps = min(args.steps, 2)
-    ms = timed_steps(torch, dist, stream, step, 0, steps)
+    steps = args.steps if full else min(args.steps, 2)
+    l0 = ctx.launch_count()
+    with ClockSampler(dist.local) as clk:
+        ms = timed_steps(torch, dist, stream, step, 0, steps)
+    launches = ctx.launch_count() - l0
     f_ms, f_n = ctx.kernel_time(api.K_GT_FWD)
     b_ms, b_n = ctx.kernel_time(api.K_GT_BWD)
     ctx.profiling(False)
     audio_s = total / 16000.0
     hbm, _ = peaks()
     k = (f_ms + b_ms) / steps
-    gbs = total * G64_BYTES_PER_SAMPLE / (k * 1e-3) / 1e9
-    return {"workload": "G64 resyth_64sub_IBM, %d x 10 s 16 kHz" % n_utts, "xrt": audio_s * steps / (ms * 1e-3),
-            "ms_per_step": ms / steps, "kernel_ms": {"gt_fwd": f_ms / steps, "gt_bwd": b_ms / steps},
-            "achieved_gbs": gbs, "frac": gbs / hbm}
+    alg_bytes = int(total * G64_BYTES_PER_SAMPLE)
+    gbs = alg_bytes / (k * 1e-3) / 1e9
+    out = {"workload": "G64 resyth_64sub_IBM, %d x 10 s 16 kHz" % n_utts, "xrt": audio_s * steps / (ms * 1e-3),
+           "ms_per_step": ms / steps, "kernel_ms": {"gt_fwd": f_ms / steps, "gt_bwd": b_ms / steps},
+           "achieved_gbs": gbs, "frac": gbs / hbm}
+    if not full:
+        return out
+    ref_out = d_out.cpu().numpy()
+    h_in, h_mask = pinned(api, samples), pinned(api, mask)
+    h_out = api.PinnedArray(total, np.int16)
+
+    def step_e2e():
+        ctx.resynth_raw(h_in.ptr, offsets, n_utts, h_mask.ptr, fo, api.RESYNTH_IBM, 0, h_out.ptr, mem=api.SE_MEM_HOST)
+
+    e2e_ms = host_timed_steps(torch, dist, step_e2e, 1, steps)
+    same = bool(np.array_equal(h_out.array, ref_out))
+    h2d, d2h = samples.nbytes + mask.nbytes, h_out.array.nbytes
+    for q in (h_in, h_mask, h_out):
+        q.free()
+    del d_in, d_mask, d_out
+    torch.cuda.empty_cache()
+    return dict(name=out["workload"], audio_s=audio_s, ms=ms, steps=steps, launches=launches, k_ms=k, alg_bytes=alg_bytes,
+                kernel="gt_fwd_fast_kernel + gt_bwd_fast_kernel<IBM> (sum of the two launches)",
+                kernel_split={"gt_fwd": f_ms / steps, "gt_bwd": b_ms / steps}, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h,
+                clocks=clk.summary(), e2e_matches_device=same, samples=samples, offsets=offsets, mask=mask, frame_offsets=fo)
 
 
 # ------------------------------------------------------------------------------------------------
