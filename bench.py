@@ -135,11 +135,11 @@ def peaks():
 class Dist:
     """torch.distributed plumbing (barrier + max over ranks); a no-op at N=1 without torchrun."""
 
-    def __init__(self, torch, n_gpus):
+    def __init__(self, torch, n_gpus, device=None):
         self.torch = torch
         self.world = int(os.environ.get("WORLD_SIZE", "1"))
         self.rank = int(os.environ.get("RANK", "0"))
-        self.local = int(os.environ.get("LOCAL_RANK", "0"))
+        self.local = int(os.environ.get("LOCAL_RANK", "0")) if device is None else device    # CUDA device index of this rank
         self.on = self.world > 1
         if self.on:
             import torch.distributed as dist
@@ -207,6 +207,24 @@ def host_timed_steps(torch, dist, step, warmup, steps):
     return dist.max((t1 - t0) * 1e3)
 
 
+def e2e_timed(torch, dist, step, steps):
+    """End-to-end leg: (solo_ms, all_ms).  With several ranks, rank 0 first runs the same K steps ALONE while the others
+    wait (solo_ms: what one GPU reaches on this box when it has the host<->device links to itself), then all ranks run
+    them together (all_ms, max over ranks) -- so the line can state e2e_efficiency = e2e_N / (N * e2e_solo) from one run."""
+    solo = None
+    if dist.on:
+        if dist.rank == 0:
+            step()
+            torch.cuda.synchronize()
+            t0 = time.perf_counter()
+            for _ in range(steps):
+                step()
+            torch.cuda.synchronize()
+            solo = (time.perf_counter() - t0) * 1e3
+        dist.barrier()
+    return solo, host_timed_steps(torch, dist, step, 1, steps)
+
+
 def ncu_capture(workload, alg_bytes):
     """The committed ncu capture of the workload's dominant kernel(s) (profiles/traffic.json), if it was taken on this
     workload size; None otherwise."""
@@ -248,9 +266,9 @@ def pinned(api, a):
     return p
 
 
-def bench_p16(args, torch, api, ctx, dist, stream, first_u):
+def bench_p16(args, torch, api, ctx, dist, stream, first_u, corpus=None):
     """Headline: BASELINE configs[1]."""
-    samples, offsets = make_corpus(first_u, args.utts, 16000, 2.0, 10.0)
+    samples, offsets = corpus or make_corpus(first_u, args.utts, 16000, 2.0, 10.0)
     nu = args.utts
     bo = np.zeros(nu + 1, np.int64)
     bo[1:] = np.cumsum(np.diff(offsets) // 160)
@@ -291,7 +309,7 @@ def bench_p16(args, torch, api, ctx, dist, stream, first_u):
         ctx.p16_wiener_raw(h_in.ptr, 0, offsets, nu, h_out.ptr, h_flags.ptr, h_gains.ptr, h_rows.ptr, bo,
                            mem=api.SE_MEM_HOST)
 
-    e2e_ms = host_timed_steps(torch, dist, step_e2e, 1, args.steps)
+    solo_ms, e2e_ms = e2e_timed(torch, dist, step_e2e, args.steps)
     same = bool(np.array_equal(h_rows.array, d_rows.cpu().numpy()))
 
     # What extract_Wiener actually keeps (aurora_etsi_test.cpp:66-133 frees outData unused): gains + flags only.
@@ -308,17 +326,17 @@ def bench_p16(args, torch, api, ctx, dist, stream, first_u):
     torch.cuda.empty_cache()
     return dict(name=workload_name(args.utts), audio_s=audio_s, ms=ms, launches=launches, k_ms=k_ms / max(k_n, 1),
                 alg_bytes=tb * P16_BYTES_PER_BLOCK, kernel="ns_stream_kernel<16,int16>", blocks=tb, rows=rows_total,
-                e2e_ms=e2e_ms, feat_ms=feat_ms, feat_d2h=feat_d2h,
+                e2e_ms=e2e_ms, solo_ms=solo_ms, feat_ms=feat_ms, feat_d2h=feat_d2h,
                 h2d=h2d, d2h=d2h, clocks=clk.summary(), e2e_matches_device=same,
                 samples=samples, offsets=offsets, mask=None, frame_offsets=None)
 
 
-def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features=False, full=False):
+def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features=False, full=False, corpus=None):
     """P8: ETSI NoiseSup + CompCeps on 10 s 8 kHz utterances (C1-type work, batched); features=True runs the
     whole feature chain (WaveProc -> CompCeps -> PostProc -> VAD, 15-column rows) behind NoiseSup.
     full=True (the metric's own path): also the end-to-end leg through se_etsi_denoise_batch with pinned HOST buffers
     and the raw numbers run_ours() needs for value / e2e / roofline / cpu_baseline."""
-    samples, offsets = make_corpus(first_u, n_utts, 8000, 0, 0, seconds=10.0)
+    samples, offsets = corpus or make_corpus(first_u, n_utts, 8000, 0, 0, seconds=10.0)
     total = int(offsets[-1])
     co = np.zeros(n_utts + 1, np.int64)
     co[1:] = np.cumsum(np.diff(offsets) // 80 if features else np.maximum(np.diff(offsets) // 80 - 6, 0))
@@ -366,7 +384,7 @@ def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features
     def step_e2e():
         ctx.etsi_denoise_raw(h_in.ptr, offsets, n_utts, h_den.ptr, h_ceps.ptr, co, h_nc.ptr, mem=api.SE_MEM_HOST)
 
-    e2e_ms = host_timed_steps(torch, dist, step_e2e, 1, args.steps)
+    solo_ms, e2e_ms = e2e_timed(torch, dist, step_e2e, args.steps)
     same = bool(np.array_equal(h_nc.array, rows_dev))
     d2h = h_den.array.nbytes + h_ceps.array.nbytes + h_nc.array.nbytes
     for q in (h_in, h_den, h_ceps, h_nc):
@@ -374,7 +392,7 @@ def bench_p8(args, torch, api, ctx, dist, stream, first_u, n_utts=6000, features
     del d_in, d_den, d_ceps, d_nc
     torch.cuda.empty_cache()
     return dict(name=out["workload"], audio_s=audio_s, ms=ms, launches=launches, k_ms=k_ms / max(k_n, 1), alg_bytes=alg_bytes,
-                kernel="ns_stream_kernel<8,int16>", e2e_ms=e2e_ms, h2d=samples.nbytes, d2h=d2h, clocks=clk.summary(),
+                kernel="ns_stream_kernel<8,int16>", e2e_ms=e2e_ms, solo_ms=solo_ms, h2d=samples.nbytes, d2h=d2h, clocks=clk.summary(),
                 e2e_matches_device=same, samples=samples, offsets=offsets, mask=None, frame_offsets=None)
 
 
@@ -513,15 +531,21 @@ def bench_extract_wiener(args, torch, api, ctx, dist, stream, first_u, n_utts=23
             "sub_band_audio_xrt": 64 * total / 16000.0 * steps / (ms * 1e-3), "achieved_gbs": gbs, "frac": gbs / hbm}
 
 
-def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, full=False):
+def resynth_inputs(first_u, n_utts):
+    """configs[2]: n_utts x 10 s at 16 kHz + a random IBM (55 % of the T-F units on)."""
+    samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
+    nf = (160000 - 320) // 160 + 1                  # numFrame, resyth_64sub_IBM/cpp/main.cpp:110
+    fo = np.arange(n_utts + 1, dtype=np.int64) * nf
+    mask = (np.random.default_rng(first_u).random((n_utts * nf, 64)) > 0.45).astype(np.float32)
+    return samples, offsets, mask, fo
+
+
+def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, full=False, corpus=None):
     """G64: resyth_64sub_IBM on 10 s 16 kHz utterances (BASELINE configs[2] shape).  full=True adds the end-to-end leg
     through se_resynth_batch with pinned HOST buffers and returns the raw numbers for run_ours()."""
-    samples, offsets = make_corpus(first_u, n_utts, 16000, 0, 0, seconds=10.0)
+    samples, offsets, mask, fo = corpus or resynth_inputs(first_u, n_utts)
     total = int(offsets[-1])
-    nf = api.resynth_num_frames(160000, api.RESYNTH_IBM)
-    fo = np.arange(n_utts + 1, dtype=np.int64) * nf
-    rng = np.random.default_rng(first_u)
-    mask = (rng.random((n_utts * nf, 64)) > 0.45).astype(np.float32)
+    assert fo[1] == api.resynth_num_frames(160000, api.RESYNTH_IBM)
     d_in, d_mask = dev(torch, samples), dev(torch, mask)
     d_out = torch.empty(total, dtype=torch.int16, device="cuda")
 
@@ -560,7 +584,7 @@ def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, ful
     def step_e2e():
         ctx.resynth_raw(h_in.ptr, offsets, n_utts, h_mask.ptr, fo, api.RESYNTH_IBM, 0, h_out.ptr, mem=api.SE_MEM_HOST)
 
-    e2e_ms = host_timed_steps(torch, dist, step_e2e, 1, steps)
+    solo_ms, e2e_ms = e2e_timed(torch, dist, step_e2e, steps)
     same = bool(np.array_equal(h_out.array, ref_out))
     h2d, d2h = samples.nbytes + mask.nbytes, h_out.array.nbytes
     for q in (h_in, h_mask, h_out):
@@ -569,7 +593,7 @@ def bench_resynth(args, torch, api, ctx, dist, stream, first_u, n_utts=1000, ful
     torch.cuda.empty_cache()
     return dict(name=out["workload"], audio_s=audio_s, ms=ms, steps=steps, launches=launches, k_ms=k, alg_bytes=alg_bytes,
                 kernel="gt_fwd_fast_kernel + gt_bwd_fast_kernel<IBM> (sum of the two launches)",
-                kernel_split={"gt_fwd": f_ms / steps, "gt_bwd": b_ms / steps}, e2e_ms=e2e_ms, h2d=h2d, d2h=d2h,
+                kernel_split={"gt_fwd": f_ms / steps, "gt_bwd": b_ms / steps}, e2e_ms=e2e_ms, solo_ms=solo_ms, h2d=h2d, d2h=d2h,
                 clocks=clk.summary(), e2e_matches_device=same, samples=samples, offsets=offsets, mask=mask, frame_offsets=fo)
 
 
