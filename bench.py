@@ -638,30 +638,66 @@ def workload_name(utts):
             "framed rfft+NoiseSup features (etsi_denoise_mapping_func_Wiener)" % utts)
 
 
+P8_UTTS, RESYNTH_UTTS = 6000, 1000
+OFFS = {"p16": 0, "p8": 500000, "resynth": 700000}      # first synthetic utterance id of each workload
+
+
+def workload_label(w, args):
+    return {"p16": workload_name(args.utts), "p8": "P8 etsi NoiseSup+CompCeps, %d x 10 s 8 kHz" % P8_UTTS,
+            "resynth": "G64 resyth_64sub_IBM, %d x 10 s 16 kHz" % RESYNTH_UTTS}[w]
+
+
+def workload_corpus(w, args, first_u, count=None):
+    """(samples, offsets, mask, frame_offsets) of workload w (first `count` utterances; default = the whole batch)."""
+    if w == "p16":
+        return make_corpus(first_u + OFFS[w], count or args.utts, 16000, 2.0, 10.0) + (None, None)
+    if w == "p8":
+        return make_corpus(first_u + OFFS[w], count or P8_UTTS, 8000, 0, 0, seconds=10.0) + (None, None)
+    return resynth_inputs(first_u + OFFS[w], count or RESYNTH_UTTS)
+
+
 def run_reference(args):
-    """--impl reference: the reference's own CPU implementation, all host threads, bounded sample per step."""
+    """--impl reference: the reference's own CPU implementation of the chosen workload (oracle/_ref through
+    oracle/ref_bench.c), all host cores, each step a bounded sample of the workload (its first n utterances, n sized
+    so that a step takes about 3 s)."""
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
+    from oracle import pyoracle
+    w = args.workload
+    rb = pyoracle.RefBench(w)
     cores = os.cpu_count() or 1
-    n = max(cores * 32, 64)                        # utterances per step: a bounded sample of the workload
-    samples, offsets = make_corpus(0, n, 16000, 2.0, 10.0)
-    for _ in range(max(args.warmup, 0) and 1):
-        cpu_p16(samples, offsets, min(n, cores), cores)
+    fs = FS[w]
+    total_utts = {"p16": args.utts, "p8": P8_UTTS, "resynth": RESYNTH_UTTS}[w]
+    samples, offsets, mask, fo = workload_corpus(w, args, 0, min(total_utts, cores * {"p16": 96, "p8": 64, "resynth": 12}[w]))
+    nu = len(offsets) - 1
+
+    def run(n, workers):
+        n = max(1, min(n, nu))
+        sec, _ = rb.run(samples, offsets[:n + 1], workers, mask, None if fo is None else fo[:n + 1])
+        return float(offsets[n]) / fs, sec, n
+
+    a0, t0, n0 = run(cores, cores)                               # calibration
+    n = max(cores, min(nu, int(n0 * 3.0 / max(t0, 1e-3))))
+    for _ in range(min(args.warmup, 1)):
+        run(n, cores)
     t_total, audio = 0.0, 0.0
-    kind = "port"
     for _ in range(args.steps):
-        r = cpu_p16(samples, offsets, n, cores)
-        t_total += r["seconds"]
-        audio += r["audio_s"]
-        kind = r["kind"]
+        a, t, _n = run(n, cores)
+        t_total += t
+        audio += a
     v = audio / t_total
+    a1, t1, n1 = run(max(1, n // cores), 1)
     line = {"impl": "reference", "metric": METRIC, "value": v, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
             "warmup": args.warmup, "ms_per_step": t_total / args.steps * 1e3, "higher_is_better": True,
             "scaling": "weak", "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.utts), "sample": "%d utterances per step" % n},
-            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": kind,
-                             "sample": "first %d utterances of the workload per step, %d steps" % (n, args.steps)},
+            "config": {"workload": workload_label(w, args), "sample": "first %d utterances per step" % n},
+            "cpu_baseline": {"value": v, "unit": UNIT, "cores": cores, "kind": rb.kind,
+                             "sample": "first %d utterances of the workload per step (%.0f audio-s), %d steps, forked C workers"
+                                       % (n, audio / args.steps, args.steps),
+                             "one_thread": {"value": a1 / t1, "unit": UNIT, "cores": 1,
+                                            "sample": "first %d utterances, %.2f s wall" % (n1, t1)},
+                             "library": os.path.relpath(rb.lib_path, ROOT)},
             "e2e": {"value": v, "unit": UNIT, "h2d_bytes_per_step": 0, "d2h_bytes_per_step": 0}}
     emit(line)
 
