@@ -702,32 +702,83 @@ def run_reference(args):
     emit(line)
 
 
+def bench_c1(args, torch, api, ctx, first_u):
+    """configs[0]: ONE 10 s 8 kHz utterance through se_etsi_denoise_batch with host buffers (what the drop-in's
+    etsi_denoise + CompCeps step does per call): median wall-clock latency of 15 calls."""
+    x, off = make_corpus(first_u + OFFS["p8"], 1, 8000, 0, 0, seconds=10.0)
+    den = np.zeros(len(x), np.int16)
+    co = np.array([0, len(x) // 80 - 6], np.int64)
+    ceps = np.zeros((int(co[1]), 14), np.float32)
+    nc = np.zeros(1, np.int32)
+    ts = []
+    for _ in range(18):
+        t0 = time.perf_counter()
+        ctx.etsi_denoise_raw(x, off, 1, den, ceps, co, nc, mem=api.SE_MEM_HOST)
+        ts.append(time.perf_counter() - t0)
+    ms = float(np.median(ts[3:])) * 1e3
+    return {"workload": "configs[0]: etsi NoiseSup+CompCeps on one 10 s 8 kHz utterance, per-call latency (host buffers)",
+            "ms_per_call": ms, "value": 10.0 / (ms * 1e-3), "unit": UNIT,
+            "note": "one utterance = one warp: latency-bound by construction; throughput lives in the batch calls"}
+
+
+def assemble(w, r, args, dist, cpu):
+    """value / e2e / roofline / cpu_baseline of one workload from its raw numbers (all ranks call this: collectives)."""
+    steps = r.get("steps", args.steps)
+    audio_all = dist.sum(r["audio_s"])
+    e2e = audio_all * steps / (r["e2e_ms"] * 1e-3)
+    d = {"workload": r["name"], "value": audio_all * steps / (r["ms"] * 1e-3), "unit": UNIT,
+         "ms_per_step": r["ms"] / steps, "audio_s_per_gpu_per_step": r["audio_s"],
+         "roofline": roofline(w, r["kernel"], r["alg_bytes"], r["k_ms"], r["clocks"].get("sm_mhz")),
+         "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
+                 "ms_per_step": r["e2e_ms"] / steps, "matches_device_path": r["e2e_matches_device"],
+                 "host_link_gbs_per_gpu": (r["h2d"] + r["d2h"]) * steps / (r["e2e_ms"] * 1e-3) / 1e9},
+         "gpu_launches": r["launches"], "clocks": r["clocks"]}
+    if "kernel_split" in r:
+        d["roofline"]["kernel_ms_split"] = r["kernel_split"]
+    solo = dist.max(r["solo_ms"] or 0.0)              # rank 0's solo run, known to every rank after the reduction
+    if dist.on and solo > 0:
+        e2e_solo = r["audio_s"] * steps / (solo * 1e-3)
+        d["e2e"]["solo_one_gpu"] = {"value": e2e_solo, "unit": UNIT,
+                                    "note": "rank 0 alone on the same box, the other ranks idle, same run"}
+        d["e2e"]["e2e_efficiency"] = e2e / (args.gpus * e2e_solo)
+    if "feat_ms" in r:
+        d["e2e"]["features_only"] = {"value": audio_all * steps / (r["feat_ms"] * 1e-3), "unit": UNIT,
+                                     "ms_per_step": r["feat_ms"] / steps, "d2h_bytes_per_step": r["feat_d2h"],
+                                     "note": "same call with out_f32 = NULL: gains + flags only, which is all the "
+                                             "reference's extract_Wiener driver keeps (aurora_etsi_test.cpp:66-133)"}
+    if cpu:
+        d["cpu_baseline"] = cpu
+    return d
+
+
 def run_ours(args):
     import torch
     from speech_enhancement_b200 import api
     local = int(os.environ.get("LOCAL_RANK", "0"))
     rank = int(os.environ.get("RANK", "0"))
     first_u = rank * 1000003                        # every rank gets its own utterances (weak scaling)
+    order = [args.workload] + [w for w in ("p16", "p8", "resynth") if w != args.workload]
 
-    # CPU baseline first (rank 0, N=1 only), before any CUDA context exists in this process (fork-safe)
-    cpu = None
-    if rank == 0 and args.gpus == 1 and not args.no_cpu:
-        cores = os.cpu_count() or 1
-        n = max(cores * 64, 64)
-        s, o = make_corpus(first_u, n, 16000, 2.0, 10.0)
-        r = cpu_p16(s, o, n, cores)
-        cpu = {"value": r["audio_s"] / r["seconds"], "unit": UNIT, "cores": cores, "kind": r["kind"],
-               "sample": "first %d utterances of the workload (%.0f audio-s), %.1f s wall on %d worker processes"
-                         % (n, r["audio_s"], r["seconds"], cores)}
+    # inputs of the three workloads, and (rank 0, N = 1 only) the CPU baselines on the same batches -- before any CUDA
+    # context exists in this process: the CPU legs fork
+    corpora, cpu = {}, {}
+    if not args.profile_only:
+        for w in order:
+            corpora[w] = workload_corpus(w, args, first_u)
+            if rank == 0 and args.gpus == 1 and not args.no_cpu:
+                cpu[w] = cpu_leg(w, *corpora[w])
 
-    torch.cuda.set_device(local)
-    dist = Dist(torch, args.gpus)
+    # rank -> GPU: spread the ranks over the box (N = 2 -> GPUs 0 and 4 of 8, ...) unless --gpu-map dense
+    n_vis = torch.cuda.device_count()
+    stride = n_vis // args.gpus if (args.gpu_map == "stride" and args.gpus > 1 and n_vis >= args.gpus) else 1
+    device = local * max(stride, 1)
+    torch.cuda.set_device(device)
+    dist = Dist(torch, args.gpus, device)
     stream = torch.cuda.Stream()
-    ctx = api.Context(local)
+    ctx = api.Context(device)
     ctx.set_stream(stream.cuda_stream)
     if args.chunk_mb or args.chunk_utts:
         ctx.set_pipeline((args.chunk_mb or 512) << 20, args.chunk_utts or 1024)
-    hbm, peak_src = peaks()
 
     if args.profile_only:
         with torch.cuda.stream(stream):
@@ -737,42 +788,44 @@ def run_ours(args):
         ctx.close()
         dist.close()
         return
+    res, extra = {}, None
     with torch.cuda.stream(stream):
-        r = bench_p16(args, torch, api, ctx, dist, stream, first_u)
-        extra = None
+        for w in order:
+            c = corpora.pop(w)
+            if w == "p16":
+                r = bench_p16(args, torch, api, ctx, dist, stream, first_u, corpus=c[:2])
+            elif w == "p8":
+                r = bench_p8(args, torch, api, ctx, dist, stream, first_u + OFFS[w], n_utts=P8_UTTS, full=True, corpus=c[:2])
+            else:
+                r = bench_resynth(args, torch, api, ctx, dist, stream, first_u + OFFS[w], n_utts=RESYNTH_UTTS, full=True, corpus=c)
+            for k in ("samples", "offsets", "mask", "frame_offsets"):
+                r.pop(k, None)
+            res[w] = assemble(w, r, args, dist, cpu.get(w))
+            del c
+        c1 = bench_c1(args, torch, api, ctx, first_u) if args.gpus == 1 else None
         if not args.no_extra and args.gpus == 1:
-            extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000),
-                     bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000, features=True),
+            extra = [bench_p8(args, torch, api, ctx, dist, stream, first_u + 500000, features=True),
                      bench_etsi16k(args, torch, api, ctx, dist, stream, first_u + 600000),
-                     bench_resynth(args, torch, api, ctx, dist, stream, first_u + 700000),
                      bench_ibm(args, torch, api, ctx, dist, stream, first_u + 800000),
                      bench_subband(args, torch, api, ctx, dist, stream, first_u + 900000),
                      bench_extract_wiener(args, torch, api, ctx, dist, stream, first_u + 950000)]
-    audio_all = dist.sum(r["audio_s"])
-    value = audio_all * args.steps / (r["ms"] * 1e-3)
-    e2e = audio_all * args.steps / (r["e2e_ms"] * 1e-3)
-    k_avg_ms = r["k_ms"] / max(r["k_n"], 1)
-    alg_bytes = r["blocks"] * P16_BYTES_PER_BLOCK
-    achieved = alg_bytes / (k_avg_ms * 1e-3) / 1e9
-    line = {"metric": METRIC, "value": value, "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
-            "warmup": args.warmup, "ms_per_step": r["ms"] / args.steps, "higher_is_better": True, "scaling": "weak",
+    head = res[args.workload]
+    line = {"metric": METRIC, "value": head["value"], "unit": UNIT, "n_gpus": args.gpus, "steps": args.steps,
+            "warmup": args.warmup, "ms_per_step": head["ms_per_step"], "higher_is_better": True, "scaling": "weak",
             "vs_baseline": None, "dtype": "f32", "data": "synthetic",
-            "config": {"workload": workload_name(args.utts), "audio_s_per_gpu_per_step": r["audio_s"],
-                       "l2": "inputs larger than L2 (%.2f GB int16 per step)" % (r["h2d"] / 1e9),
-                       "parallelism": "utterance-sharded, %d rank(s), no collective" % args.gpus},
-            "roofline": {"bound": "hbm", "achieved": achieved, "peak": hbm, "unit": "GB/s", "frac": achieved / hbm,
-                         "traffic": measured_traffic(args.utts, alg_bytes), "peak_source": peak_src, "kernel": "ns_stream_kernel<16,int16>",
-                         "kernel_ms": k_avg_ms, "algorithmic_bytes_per_launch": alg_bytes,
-                         "issue_bound": issue_bound(args.utts, alg_bytes, k_avg_ms, r["clocks"].get("sm_mhz"))},
-            "e2e": {"value": e2e, "unit": UNIT, "h2d_bytes_per_step": r["h2d"], "d2h_bytes_per_step": r["d2h"],
-                    "ms_per_step": r["e2e_ms"] / args.steps, "matches_device_path": r["e2e_matches_device"],
-                    "features_only": {"value": audio_all * args.steps / (r["feat_ms"] * 1e-3), "unit": UNIT,
-                                      "ms_per_step": r["feat_ms"] / args.steps, "d2h_bytes_per_step": r["feat_d2h"],
-                                      "note": "same call with out_f32 = NULL: gains + flags only, which is all the "
-                                              "reference's extract_Wiener driver keeps (aurora_etsi_test.cpp:66-133)"}},
-            "gpu_launches": r["launches"], "clocks": r["clocks"]}
-    if cpu:
-        line["cpu_baseline"] = cpu
+            "config": {"workload": head["workload"], "audio_s_per_gpu_per_step": head["audio_s_per_gpu_per_step"],
+                       "l2": "inputs larger than L2 (%.2f GB per step)" % (head["e2e"]["h2d_bytes_per_step"] / 1e9),
+                       "parallelism": "utterance-sharded, %d rank(s), no collective" % args.gpus,
+                       "gpu_map": "rank k -> GPU %d*k of %d visible" % (max(stride, 1), n_vis)},
+            "roofline": head["roofline"], "e2e": head["e2e"], "gpu_launches": head["gpu_launches"], "clocks": head["clocks"]}
+    if "cpu_baseline" in head:
+        line["cpu_baseline"] = head["cpu_baseline"]
+    line["workloads"] = {w: res[w] for w in order[1:]}
+    if c1:
+        if "p8" in cpu:
+            c1["cpu_baseline"] = dict(cpu["p8"]["one_thread"], kind=cpu["p8"]["kind"],
+                                      note="reference etsi_denoise + CompCeps step on one core (batch of 10 s utterances)")
+        line["workloads"]["c1"] = c1
     if extra:
         line["other_workloads"] = extra
     if rank == 0:
