@@ -265,6 +265,23 @@ int64_t se_resynth_num_frames(int64_t n_samples, int mode);
 int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,
                      const float *mask, const int64_t *frame_offsets, int mode, int flags,
                      int16_t *out, int mem);
+/* resynth() for ONE utterance without any allocation in the call.  NO COUNTERPART IN THE REFERENCE: added
+ * for callers that cannot call cudaMalloc (code under CUDA graph capture, tight
+ * serving loops, harnesses that forbid it).  Same arithmetic, same work-item plan and therefore the same output, bit
+ * for bit, as se_resynth_batch on that utterance (mode / flags as there, SE_FLAG_EXACT and SE_FLAG_OUT_F32 included).
+ * d_samples (int16[n_samples]), d_mask (float[se_resynth_num_frames(n_samples, mode)][64]) and d_out (int16[n_samples],
+ * or float with SE_FLAG_OUT_F32) are DEVICE pointers on the context's GPU; the call is asynchronous on the context
+ * stream (se_ctx_set_stream / se_ctx_sync).  It calls no cudaMalloc, cudaFree or allocating library routine and copies
+ * nothing from the host: the [sample][64] float intermediate of the two gammatone passes and the work items (planned
+ * by a device kernel) live in a file-scope static __device__ array of 64 MiB that EVERY GPU which loads libse_b200.so
+ * holds until the process exits.  Limit: n_samples <= SE_RESYNTH_NOALLOC_MAX_SAMPLES (12.5 s at 16 kHz); longer
+ * utterances are rejected with SE_EINVAL and a message (use se_resynth_batch).  All calls on one GPU -- from any
+ * context, stream or thread -- share that one array: calls that OVERLAP on the GPU race and corrupt each other's
+ * output; issue them on one stream or order them with events.  The array keeps the last call's contents; nothing in it
+ * needs to start at zero (every element a call reads is written earlier in the same call). */
+#define SE_RESYNTH_NOALLOC_MAX_SAMPLES 200000
+int se_resynth_noalloc(se_ctx *ctx, const int16_t *d_samples, int64_t n_samples, const float *d_mask, int mode, int flags,
+                       int16_t *d_out);
 /* addnoise (enhancement_extract_subband_linux/cpp/extractwav.cpp:6-35): noise is scaled IN PLACE. */
 int se_addnoise_batch(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy,
                       const int64_t *offsets, int n_utts, int db, int mem);

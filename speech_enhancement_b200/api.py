@@ -77,6 +77,7 @@ def lib():
         L.se_subband_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, C.c_int, C.c_int]
         L.se_ibm_batch.argtypes = [_vp, _vp, _vp, _vp, C.c_int, _vp, _vp, _vp, C.c_int]
         L.se_resynth_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, C.c_int, C.c_int, _vp, C.c_int]
+        L.se_resynth_noalloc.argtypes = [_vp, _vp, C.c_int64, _vp, C.c_int, C.c_int, _vp]
         L.se_addnoise_batch.argtypes = [_vp, _vp, _vp, _vp, _vp, C.c_int, C.c_int, C.c_int]
         L.se_rfft_batch.argtypes = [_vp, _vp, C.c_int, C.c_int, C.c_int, C.c_int]
         L.se_gammatone_batch.argtypes = [_vp, _vp, _vp, _vp, C.c_int64, C.c_int, C.c_int, C.c_int]
@@ -234,6 +235,11 @@ class Context:
     def resynth_raw(self, samples, offsets, n_utts, mask, frame_offsets, mode, flags, out, mem=SE_MEM_HOST):
         _check(self.L.se_resynth_batch(self.h, _ptr(samples), _ptr(offsets), n_utts, _ptr(mask), _ptr(frame_offsets),
                                        mode, flags, _ptr(out), mem), "se_resynth_batch")
+
+    def resynth_noalloc_raw(self, d_samples, n_samples, d_mask, mode, flags, d_out):
+        """se_resynth_noalloc: device pointers only, nothing allocated, asynchronous on the context stream."""
+        _check(self.L.se_resynth_noalloc(self.h, _ptr(d_samples), int(n_samples), _ptr(d_mask), int(mode), int(flags),
+                                         _ptr(d_out)), "se_resynth_noalloc")
 
     def subband_raw(self, samples, offsets, n_utts, out, flags, mem=SE_MEM_HOST):
         _check(self.L.se_subband_batch(self.h, _ptr(samples), _ptr(offsets), n_utts, _ptr(out), flags, mem),

@@ -104,6 +104,22 @@ int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
     return leave(ctx, mem);
 }
 
+// No counterpart in the reference: added (se_b200.h).  Allocates nothing:
+// no cudaMalloc / cudaFree / staging / pinned arena -- device pointers in, device pointer out, fixed static scratch.
+int se_resynth_noalloc(se_ctx *ctx, const int16_t *d_samples, int64_t n_samples, const float *d_mask, int mode, int flags,
+                       int16_t *d_out)
+{
+    if (!ctx) { set_error("se_resynth_noalloc: NULL context"); return SE_EINVAL; }
+    std::lock_guard<std::recursive_mutex> guard(ctx->mu);
+    SE_CUDA(cudaSetDevice(ctx->device));
+    if (n_samples < 0 || mode < 0 || mode > 2 || (n_samples > 0 && (!d_samples || !d_mask || !d_out))) {
+        set_error("se_resynth_noalloc: bad arguments");
+        return SE_EINVAL;
+    }
+    if (n_samples == 0) return SE_OK;
+    return launch_resynth_noalloc(ctx, d_samples, n_samples, d_mask, mode, flags, d_out);
+}
+
 int se_addnoise_batch(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy,
                       const int64_t *offsets, int n_utts, int db, int mem)
 {

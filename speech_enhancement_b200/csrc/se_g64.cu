@@ -176,3 +176,4 @@ __global__ void __launch_bounds__(128) ibm_rows_kernel(const int16_t *pure64, co
 }  // namespace se
 
 #include "se_g64_resynth.cuh"
+#include "se_g64_noalloc.cuh"

@@ -206,6 +206,8 @@ int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *ch
 int launch_gammatone_coef(se_ctx *ctx, const float *in, float *out, const float *coef, int64_t n, int count, int flags);
 int launch_ibm_rows(se_ctx *ctx, const int16_t *pure64, const int16_t *noise64, const int64_t *offsets, int n_utts,
                     float *irm, uint64_t *bits, const int64_t *frame_offsets, int64_t total_frames);
+int launch_resynth_noalloc(se_ctx *ctx, const int16_t *d_samples, int64_t n, const float *d_mask, int mode, int flags,
+                           int16_t *d_out);
 int launch_addnoise(se_ctx *ctx, const int16_t *pure, int16_t *noise, int16_t *noisy, const int64_t *offsets,
                     int n_utts, int db);
 int upload_g64_tables(se_ctx *ctx);
