@@ -223,6 +223,11 @@ int  se_ns_stream_push(se_ns_stream *s, const float *in, int n_blocks, float *ou
                                FMA-contracted (faster, ~-120 dB relative difference)               */
 #define SE_FLAG_OUT_F32 2   /* se_resynth_batch: `out` is a float array that receives resynth_e[] before the
                                (short) cast (resyth_64sub_IBM/cpp/extractwav.cpp:109-122), for waveform-SNR checks */
+#define SE_FLAG_LATENCY 4   /* se_resynth_batch, default (non-EXACT) mode: cut every utterance into 2 048-sample
+                               time chunks instead of >= 1 s ones -- 8x more independent work items per utterance
+                               for 2.9x the arithmetic; for calls with a handful of utterances (the drop-in's
+                               resynth() with SE_B200_FAST=1 uses it).  Same accuracy bars as the default mode;
+                               the output is not bit-identical to a call without the flag                  */
 /* subbband (enhancement_extract_subband_linux/cpp/extractwav.cpp:36-97): int16 hair-cell output per
  * channel; out holds, for utterance u, 64 rows of len_u samples starting at 64*offsets[u]. */
 int se_subband_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets, int n_utts,

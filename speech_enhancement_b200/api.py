@@ -10,12 +10,14 @@ import os
 import numpy as np
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "lib", "libse_b200.so")
+# SE_B200_LIB: load another build of the same library (kernel A/B runs: tools/build_variants.sh)
+LIB_PATH = os.environ.get("SE_B200_LIB") or os.path.join(_HERE, "lib", "libse_b200.so")
 DROPIN_PATH = os.path.join(_HERE, "lib", "libse_b200_dropin.so")
 
 SE_MEM_HOST, SE_MEM_DEVICE = 0, 1
 SE_FLAG_EXACT = 1
 SE_FLAG_OUT_F32 = 2
+SE_FLAG_LATENCY = 4
 RESYNTH_IBM, RESYNTH_ORI, RESYNTH_1DNN = 0, 1, 2
 K_NS_P8, K_NS_P16, K_GT_FWD, K_GT_BWD, K_SUBBAND, K_IBM, K_ADDNOISE = range(7)
 KERNEL_NAMES = {K_NS_P8: "ns_p8", K_NS_P16: "ns_p16", K_GT_FWD: "gt_fwd", K_GT_BWD: "gt_bwd",
@@ -409,12 +411,13 @@ class Context:
                                               _ptr(rows), _ptr(bo), SE_MEM_HOST), "se_extract_wiener_batch")
         return [(gains[bo[u]:bo[u + 1]], flags[:, bo[u]:bo[u + 1]], int(rows[u])) for u in range(nu)]
 
-    def resynth(self, samples, offsets, mask, frame_offsets, mode, exact=True, f32=False):
+    def resynth(self, samples, offsets, mask, frame_offsets, mode, exact=True, f32=False, latency=False):
         samples = np.ascontiguousarray(samples, np.int16)
         mask = np.ascontiguousarray(mask, np.float32)
         out = np.zeros(len(samples), np.float32 if f32 else np.int16)
         self.resynth_raw(samples, _i64(offsets), len(offsets) - 1, mask, _i64(frame_offsets), mode,
-                         (SE_FLAG_EXACT if exact else 0) | (SE_FLAG_OUT_F32 if f32 else 0), out)
+                         (SE_FLAG_EXACT if exact else 0) | (SE_FLAG_OUT_F32 if f32 else 0) |
+                         (SE_FLAG_LATENCY if latency else 0), out)
         return out
 
     def addnoise(self, pure, noise, offsets, db):

@@ -193,6 +193,10 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
             } else {
                 b.samples = samples;
             }
+            if (in_elem == sizeof(int16_t)) {      // int16 input: the byte range the kernel's bulk-async prefetch may touch
+                b.bulk_lo = (const char *)b.samples;
+                b.bulk_hi = b.bulk_lo + in_elem * (uint64_t)(mem == SE_MEM_HOST ? hi[0] - lo[0] : offsets[n_utts]);
+            }
             for (int k = 0; k < n_outs; k++) {
                 const NsOut &o = outs[k];
                 if (!o.host) continue;

@@ -111,12 +111,7 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
         const int64_t n = h_offsets[u + 1] - h_offsets[u];
         if (n <= 0) continue;
         if (n > 0x7fffffff) { set_error("se_resynth_batch: utterance %d longer than 2^31 samples", u); return SE_EINVAL; }
-        // Time-chunk length of the default mode: every chunk pays 2 x kGtWarm samples of run-in, so long utterances get
-        // longer chunks -- a function of the utterance's own length only, so that its output does not depend on what
-        // else is in the batch (at least 4 chunks per utterance are kept for parallelism, at most 8 x kGtChunk each).
-        int64_t chunk = kGtChunk;
-        while (chunk < 8 * kGtChunk && n >= 8 * chunk) chunk *= 2;
-        const int64_t step = exact ? n : chunk;
+        const int64_t step = exact ? n : gt_chunk_len(n, a.flags);
         for (int64_t ca = 0; ca < n; ca += step) {
             GtItem it;
             it.sample_off = h_offsets[u];

@@ -43,11 +43,9 @@ __global__ void na_plan_kernel(GtItem *items, int n, int frames, int step, int e
 }
 
 // Host-side plan: chunk length, item count and scratch rows for an utterance of n samples (mirrors launch_resynth).
-static void na_plan_host(int64_t n, bool exact, int64_t *step, int *count, int64_t *rows)
+static void na_plan_host(int64_t n, bool exact, int flags, int64_t *step, int *count, int64_t *rows)
 {
-    int64_t chunk = kGtChunk;
-    while (chunk < 8 * kGtChunk && n >= 8 * chunk) chunk *= 2;
-    *step = exact ? n : chunk;
+    *step = exact ? n : gt_chunk_len(n, flags);
     *count = (int)((n + *step - 1) / *step);
     int64_t r = 0;
     for (int64_t a = 0; a < n; a += *step) {
@@ -82,7 +80,7 @@ int launch_resynth_noalloc(se_ctx *ctx, const int16_t *d_samples, int64_t n, con
     const bool exact = (flags & SE_FLAG_EXACT) != 0;
     int64_t step = 0, rows = 0;
     int count = 0;
-    na_plan_host(n, exact, &step, &count, &rows);
+    na_plan_host(n, exact, flags, &step, &count, &rows);
     if (n > SE_RESYNTH_NOALLOC_MAX_SAMPLES || rows > kNaMaxRows || count > kNaMaxItems) {
         set_error("se_resynth_noalloc: %lld samples exceed the fixed scratch (maximum %d samples per call; "
                   "use se_resynth_batch for longer utterances)", (long long)n, SE_RESYNTH_NOALLOC_MAX_SAMPLES);

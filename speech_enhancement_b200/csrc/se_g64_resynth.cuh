@@ -21,6 +21,20 @@ struct GtItem {
 };
 constexpr int kGtWarm = 2560;
 constexpr int kGtChunk = 16000;      // smallest time chunk; the host doubles it while enough work items remain
+constexpr int kGtChunkLatency = 2048; // SE_FLAG_LATENCY: chunk of a lone utterance (a multiple of the 64-sample tile)
+
+// Time-chunk length of the default mode.  Every chunk pays 2 x kGtWarm samples of run-in, so long utterances get longer
+// chunks -- a function of the utterance's own length (and the caller's flags) only, so that its output does not depend
+// on what else is in the batch (at least 4 chunks per utterance are kept for parallelism, at most 8 x kGtChunk each).
+// SE_FLAG_LATENCY trades throughput for latency: 2 048-sample chunks turn one 10 s utterance into 79 work items of
+// 7 168 + 4 608 filter steps instead of 10 items of 21 120 + 18 560, for 2.9x the arithmetic.
+static inline int64_t gt_chunk_len(int64_t n, int flags)
+{
+    if (flags & SE_FLAG_LATENCY) return kGtChunkLatency;
+    int64_t chunk = kGtChunk;
+    while (chunk < 8 * kGtChunk && n >= 8 * chunk) chunk *= 2;
+    return chunk;
+}
 
 // ---- pass 1: y1[n][c] = gammatone_c(x)[n] / midEar_c, channel-minor scratch (coalesced) ---------
 template <bool EXACT>

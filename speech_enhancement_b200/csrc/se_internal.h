@@ -27,6 +27,7 @@ struct NsDevTables {
     const float *sig_window;   // [frame]
     const float *fir_window;   // [9]  : ir_window[8..16]  (DoFilterWindowing uses the upper half only)
     const float *bankT;        // P8: [BANK_MAXLEN][32] transposed, zero padded; P16: float4 [25][32] (lane's 4 bins)
+    const float *bankR;        // P16: float4 [32][32]: (k, band) = the band's weights for bins 4k..4k+3 (bands 25..31: 0)
     const int *bank_start;     // [32]
     const int *bank_len;       // [32]
     const float *idctT;        // [25][16] : idctT[f*16+t] = idct[t][f], t<9
@@ -104,6 +105,10 @@ struct NsLaunch {
     int32_t *produced;           // optional per-block bitmask: 1 = shift output, 2 = stage 0 ran, 4 = skipped
     int zero_check;              // 0 none (DoNoiseSup), 1 leading frames only (DoAdvProcess), 2 anywhere (func_Wiener)
     float *spec_trace;           // optional [block][8][spec] spectral state per block (se_ns_spectra_batch)
+    // byte range of `samples` that bulk-async copies may touch ([bulk_lo, bulk_hi), both 0 = none): the kernel
+    // prefetches int16 input with cp.async.bulk, which moves whole 16-byte-aligned spans that can start up to 14 bytes
+    // before a block and end up to 16 bytes after it; blocks whose span leaves this range use plain loads
+    const char *bulk_lo, *bulk_hi;
     // work queue
     int *work_counter;           // device int, zeroed before launch
 };

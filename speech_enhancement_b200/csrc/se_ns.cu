@@ -57,19 +57,33 @@ template <> struct Prof<16> {     // function/.../aurora_etsi/NoiseSup.h:22-72
 
 constexpr int kTriRows = 32;     // max CompCeps triangle length (checked on the host)
 
+// Bulk-async input prefetch (se_ns_kernel.cuh): groups of int16 blocks in flight per warp and the bytes one of them
+// occupies (the group plus 16: the copy starts at the 16-byte boundary below the group's first sample).
+constexpr int kInSlots = 2;
+constexpr int kInGroupBytes = 640;                      // input bytes per copy: 4 blocks of 80 samples, 2 of 160
+constexpr int kInSlotBytes = kInGroupBytes + 16;
+
 template <int PROF> struct __align__(16) WarpMem {
     using P = Prof<PROF>;
+#ifdef SE_NS_EXACT
+    static constexpr bool kSpecScratch = true;       // W / melw: in-order sums of the exact mode, both profiles
+#else
+    static constexpr bool kSpecScratch = PROF == 8;  // the 16 kHz plugin profile keeps W and the mel gains in registers
+#endif
     float ring1[P::RB + 16];          // 8 guard samples either side, see ring_store()
     float ring2[P::RB + 16];
     float ring3[P::CEPS ? P::RB : 4];
     float prev[2 * P::NB * 32];       // previous-frame PSD of both stages, [stage][r][lane]
-    float2 Z[132];
-    float2 Z2[PROF == 16 ? 132 : 2];
+    float2 Z[kZ];                     // FFT-128 spectrum (zpad layout, 132 used) + its transposes (152)
+    float2 Z2[PROF == 16 ? kZ : 2];
     float raw[PROF == 16 ? 260 : 4];
-    float W[132];
-    float melw[32];
-    float fir[16];
+    float W[kSpecScratch ? 132 : 4];
+    float melw[kSpecScratch ? 32 : 4];
     float cold[PROF == 8 ? 16 : 4];   // P8: Scal fields touched once per block, parked here between their uses
+#ifndef SE_NS_NO_BULK
+    __align__(16) unsigned char in_stage[kInSlots][kInSlotBytes];   // cp.async.bulk destinations (int16 input blocks)
+    __align__(8) unsigned long long in_bar[kInSlots];               // their mbarriers
+#endif
 #ifdef SE_NS_EXACT
     float xf[PROF == 8 ? 256 : 512];  // the reference's in-place rfft array
     float sden[132], snoise[132];     // denSigSE / noiseSE of the current stage, for the in-order energy sums
@@ -84,17 +98,23 @@ template <int PROF> struct __align__(16) BlockMem {
     using P = Prof<PROF>;
     float win[P::FL];
     float2 twh[132];
+#if defined(SE_NS_BANK_T) && !defined(SE_NS_EXACT)
+    float bankT[PROF == 16 ? 32 * 32 * 4 : P::BANKROWS * 32];   // P16: NsDevTables::bankR (band-per-lane form)
+#else
     float bankT[PROF == 16 ? 25 * 32 * 4 : P::BANKROWS * 32];
+#endif
     int bank_start[32], bank_len[32];
-    float idctT[25 * 16];
+#ifdef SE_NS_EXACT
+    float idctT[25 * 16];             // the fast build reads the IDCT / window taps once, from global memory (lane_ic)
     float firwin[12];
+#endif
     // CompCeps tables (P8 only)
     float ham[P::CEPS ? 200 : 4];
     float triT[P::CEPS ? kTriRows * 32 : 4];
     int tri_start[32], tri_len[32];
     float dctT[P::CEPS ? 23 * 16 : 4];
 #ifdef SE_NS_CONST_SMEM
-    float lane_tw[15 * 32];      // FftTw of every lane, [field][lane]
+    float lane_tw[kTwFloats * 32];   // FftTw of every lane, [field][lane]
     float lane_ic[10 * 32];      // IdctRegs of every lane
     float lane_br[PROF == 8 ? 22 * 32 : 4];   // BankRegs taps of every lane: 10 mel + 12 CompCeps triangle taps
 #endif

@@ -1,7 +1,15 @@
 // Persistent fused NoiseSup kernel + host launchers.  Included by se_ns.cu.
 #pragma once
 
+#include "se_bulk.cuh"
+
 namespace SE_NSPACE {
+
+#ifdef SE_NS_NO_BULK
+constexpr bool kBulk = false;
+#else
+constexpr bool kBulk = true;
+#endif
 
 // warps (= concurrent utterances) per CTA; 2 CTAs per SM.  The feature-chain variant keeps more state live
 // per warp, so it trades occupancy (12 instead of 16 warps/SM) for 168 registers per thread.
@@ -24,11 +32,16 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
     const int tid = threadIdx.x, nt = blockDim.x;
     for (int i = tid; i < P::FL; i += nt) bm.win[i] = tb.sig_window[i];
     for (int i = tid; i < 129; i += nt) bm.twh[i] = reinterpret_cast<const float2 *>(tb.tw_half)[i];
-    for (int i = tid; i < (int)(sizeof(bm.bankT) / sizeof(float)); i += nt) bm.bankT[i] = tb.bankT[i];
+#if defined(SE_NS_BANK_T) && !defined(SE_NS_EXACT)
+    const float *bank_src = PROF == 16 ? tb.bankR : tb.bankT;
+#else
+    const float *bank_src = tb.bankT;
+#endif
+    for (int i = tid; i < (int)(sizeof(bm.bankT) / sizeof(float)); i += nt) bm.bankT[i] = bank_src[i];
     for (int i = tid; i < 32; i += nt) { bm.bank_start[i] = tb.bank_start[i]; bm.bank_len[i] = tb.bank_len[i]; }
+#ifdef SE_NS_EXACT
     for (int i = tid; i < 25 * 16; i += nt) bm.idctT[i] = tb.idctT[i];
     for (int i = tid; i < 9; i += nt) bm.firwin[i] = tb.fir_window[i];
-#ifdef SE_NS_EXACT
     if (tid == 0) { bm.rf.ops = tb.rf_ops; bm.rf.lvl = tb.rf_lvl; bm.rf.tw = tb.rf_tw; bm.rf.m = tb.rf_m; }
 #endif
     if constexpr (P::CEPS) {
@@ -76,7 +89,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     FftTw tw;
     fft_tw_init(tw, lane);
     IdctRegs ic;
-    idct_regs_init(ic, bm.idctT, bm.firwin, lane);
+    idct_regs_init(ic, tb.idctT, tb.fir_window, lane);
     BankRegs br;
     if constexpr (PROF == 8) bank_regs_init(br, bm, lane);
     else { br.mel_st = br.tri_st = 0; }
@@ -87,9 +100,18 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     }
     __syncthreads();
 #endif
-    for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;       // zero-weight taps may read past the spectrum
+    if constexpr (WarpMem<PROF>::kSpecScratch)
+        for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;   // zero-weight taps may read past the spectrum
     const float eps = tb.eps;
     const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
+    unsigned in_phase = 0;                 // bit s: parity the next wait on staging slot s uses (flips per completed wait)
+#ifndef SE_NS_NO_BULK
+    if (lane == 0) {
+        for (int k = 0; k < kInSlots; k++) se_bulk::mbar_init(&wm.in_bar[k], 1);
+        se_bulk::mbar_init_fence();
+    }
+    __syncwarp();
+#endif
 
     for (;;) {
         int u = 0;
@@ -169,29 +191,96 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         const int64_t ceps0 = a.ceps_offsets ? a.ceps_offsets[u] - a.ceps_base : 0;
         const int64_t ceps_cap = a.ceps_offsets ? a.ceps_offsets[u + 1] - a.ceps_offsets[u] : 0;
 
-        // ---- software prefetch of the next shift (strided: coalesced) -------------------------
-        // P8 keeps the prefetched samples in the input type and converts them one block later, when they are
-        // consumed (converting right after the load makes the warp wait for the load at once): -3 % on P8.
-        // P16 measured 1 % slower that way, so it converts at the load.
+        // ---- input ------------------------------------------------------------------------------
+        // int16 input: groups of kGroup blocks (640 bytes) are posted two groups ahead as ONE bulk-async copy each into
+        // this warp's two staging slots (se_bulk.cuh).  A copy starts at the 16-byte boundary below the group's first
+        // sample (`mis` samples earlier) and is kSpan bytes long; groups whose span would leave [bulk_lo, bulk_hi) -- at
+        // most the first and the last group of a buffer -- and the ragged last group of an utterance are staged with
+        // ordinary loads and stores instead, behind the same barrier, so the consumer is the same either way.
+        // float input (persistent streams, the plugin's float entry): software prefetch of the next block in registers.
+#ifdef SE_NS_BULK_ALL
+        constexpr bool BULK = kBulk && sizeof(IN_T) == 2;
+#else
+        // measured (B200, profiles/r02_kernel_ab.md): 160-sample blocks gain 1.3 % from it, the 80-sample blocks of the
+        // 8 kHz profile lose 1.7 % (their register prefetch converts at consumption and is cheaper than wait + LDS)
+        constexpr bool BULK = kBulk && sizeof(IN_T) == 2 && SIN == 160;
+#endif
+        constexpr int kGroup = kInGroupBytes / (SIN * 2);
+        constexpr int kSpan = kInGroupBytes + 16;
+        static_assert(kGroup * SIN * 2 == kInGroupBytes && kSpan == kInSlotBytes && kInSlots == 2, "staging slot layout");
+        const uintptr_t in_addr = reinterpret_cast<uintptr_t>(in);
+        const int mis = (int)(in_addr & 15) >> 1;
+        const char *span0 = reinterpret_cast<const char *>(in_addr & ~uintptr_t(15));
+        const int ngrp = (nblk + kGroup - 1) / kGroup;
         using NX_T = typename std::conditional<PROF == 8, IN_T, float>::type;
-        NX_T nx[NRI];
+        NX_T nx[BULK ? 1 : NRI];
+        (void)mis; (void)span0; (void)ngrp; (void)in_phase; (void)nx;       // unused in the instantiations without bulk input
+#ifndef SE_NS_NO_BULK
+        auto post_group = [&](int g) {
+            const int slot = g & 1;
+            const char *lo = span0 + (int64_t)g * kInGroupBytes;
+            const bool whole = (g + 1) * kGroup <= nblk && lo >= a.bulk_lo && lo + kSpan <= a.bulk_hi;
+            if (whole) {
+                if (lane == 0) se_bulk::bulk_g2s(wm.in_stage[slot], lo, kSpan, &wm.in_bar[slot]);
+            } else {
+                int16_t *sp = reinterpret_cast<int16_t *>(wm.in_stage[slot]) + mis;
+                const int cnt = (nblk - g * kGroup < kGroup ? nblk - g * kGroup : kGroup) * SIN;
+                for (int i = lane; i < cnt; i += 32) sp[i] = (int16_t)in[(int64_t)g * (kGroup * SIN) + i];
+                se_bulk::proxy_fence();
+                __syncwarp();
+                if (lane == 0) se_bulk::mbar_arrive(&wm.in_bar[slot]);
+            }
+        };
+#endif
+        if constexpr (BULK) {
+#ifndef SE_NS_NO_BULK
+            if (ngrp > 0) post_group(0);
+            if (ngrp > 1) post_group(1);
+#endif
+        } else {
+            // P8 keeps the prefetched samples in the input type and converts them one block later, when they are
+            // consumed (converting right after the load makes the warp wait for the load at once): -3 % on P8.
+            // P16 measured 1 % slower that way, so it converts at the load.
 #pragma unroll
-        for (int r = 0; r < NRI; r++) {
-            const int i = lane + 32 * r;
-            nx[r] = (nblk > 0 && i < SIN) ? NX_T(in[i]) : NX_T(0);
+            for (int r = 0; r < NRI; r++) {
+                const int i = lane + 32 * r;
+                nx[r] = (nblk > 0 && i < SIN) ? NX_T(in[i]) : NX_T(0);
+            }
         }
 
         for (int b = 0; b < nblk; b++) {
             float cur[NRI];
             float ss = 0.0f;
             bool nzl = false;
-#pragma unroll
-            for (int r = 0; r < NRI; r++) { cur[r] = to_f32(nx[r]); ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
-            if (b + 1 < nblk) {
+            if constexpr (BULK) {
+#ifndef SE_NS_NO_BULK
+                const int g = b / kGroup, k = b - g * kGroup, slot = g & 1;
+                if (k == 0) {                                  // first block of a group: its copy has landed?
+                    se_bulk::mbar_wait_warp(&wm.in_bar[slot], (in_phase >> slot) & 1u);
+                    in_phase ^= 1u << slot;
+                }
+                const int16_t *sp = reinterpret_cast<const int16_t *>(wm.in_stage[slot]) + mis + k * SIN;
 #pragma unroll
                 for (int r = 0; r < NRI; r++) {
                     const int i = lane + 32 * r;
-                    if (i < SIN) nx[r] = NX_T(in[(int64_t)(b + 1) * SIN + i]);
+                    cur[r] = (i < SIN) ? (float)sp[i] : 0.0f;
+                }
+                if (k == kGroup - 1 && g + 2 < ngrp) {
+                    __syncwarp();                              // every lane has read the slot: it can be refilled
+                    post_group(g + 2);
+                }
+#endif
+#pragma unroll
+                for (int r = 0; r < NRI; r++) { ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
+            } else {
+#pragma unroll
+                for (int r = 0; r < NRI; r++) { cur[r] = to_f32(nx[r]); ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
+                if (b + 1 < nblk) {
+#pragma unroll
+                    for (int r = 0; r < NRI; r++) {
+                        const int i = lane + 32 * r;
+                        if (i < SIN) nx[r] = NX_T(in[(int64_t)(b + 1) * SIN + i]);
+                    }
                 }
             }
             // zero-frame gate: DoAdvProcess (ParmInterface.c:244-250, leading frames only) /
@@ -347,9 +436,24 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 }
             } else {
                 if (a.out_f32) {
+#ifdef SE_NS_OUT_STAGED
+                    // through the (dead) PSD scratch so that the global stores are whole 128-byte lines
+                    float *so = wm.raw;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) so[i0 + t] = produced ? o[t] : 0.0f;
+                    __syncwarp();
+                    float *dst = a.out_f32 + obase;
+                    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
+                        for (int i = lane; i < P::S / 4; i += 32) reinterpret_cast<float4 *>(dst)[i] = reinterpret_cast<const float4 *>(so)[i];
+                    } else {
+                        for (int i = lane; i < P::S; i += 32) dst[i] = so[i];
+                    }
+#else
 #pragma unroll
                     for (int t = 0; t < P::CH; t++)
                         if (i0 + t < P::S) a.out_f32[obase + i0 + t] = produced ? o[t] : 0.0f;
+#endif
                 }
                 if (a.flags && lane == 0) {
                     int32_t *f = a.flags + blk0 + b;
@@ -450,7 +554,7 @@ __global__ void rfft_kernel(float *x, int n, int count, const RfPlanDev pl)
 #else
 __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
 {
-    __shared__ float2 Zs[4][132], Z2s[4][132];
+    __shared__ float2 Zs[4][kZ], Z2s[4][kZ];
     const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
     const int idx = blockIdx.x * 4 + warp;
     if (idx >= count) return;
@@ -460,11 +564,11 @@ __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
     fft_tw_init(tw, lane);
     float2 *Z = Zs[warp], *Z2 = Z2s[warp];
     if (n == 256) {
-        float2 v[4];
-        for (int j = 0; j < 4; j++) v[j] = reinterpret_cast<const float2 *>(p)[lane + 32 * j];
+        float2 v[1][4];
+        for (int j = 0; j < 4; j++) v[0][j] = reinterpret_cast<const float2 *>(p)[lane + 32 * j];
         __syncwarp();
-        fft128_warp(v, tw, lane);
-        fft128_store(v, Z, lane);
+        float2 *const zs[1] = {Z};
+        fft128_spectrum<1>(v, zs, tw, lane);
         __syncwarp();
         for (int k = lane; k <= 128; k += 32) {
             const float2 X = rsplit256(Z, k, twh[k]);
@@ -472,17 +576,15 @@ __global__ void rfft_kernel(float *x, int n, int count, const float *tw_half)
             if (k > 0 && k < 128) p[256 - k] = X.y;
         }
     } else {   // n == 512, m == 8 : the plugin's truncated schedule
-        float2 va[4], vw[4];
+        float2 v[2][4];
         for (int j = 0; j < 4; j++) {
             const float4 q = reinterpret_cast<const float4 *>(p)[lane + 32 * j];
-            va[j] = make_float2(q.x, q.z);
-            vw[j] = make_float2(q.y, q.w);
+            v[0][j] = make_float2(q.x, q.z);
+            v[1][j] = make_float2(q.y, q.w);
         }
         __syncwarp();
-        fft128_warp(va, tw, lane);
-        fft128_warp(vw, tw, lane);
-        fft128_store(va, Z, lane);
-        fft128_store(vw, Z2, lane);
+        float2 *const zs[2] = {Z, Z2};
+        fft128_spectrum<2>(v, zs, tw, lane);
         __syncwarp();
         for (int k = lane; k <= 128; k += 32) {
             const float2 A = rsplit256(Z, k, twh[k]);

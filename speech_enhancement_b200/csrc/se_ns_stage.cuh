@@ -13,22 +13,17 @@ struct IdctRegs { float c[9]; float firwin; };
 #ifdef SE_NS_CONST_SMEM
 __device__ __forceinline__ void lane_consts_store(float *tw_tab, float *ic_tab, const FftTw &t, const IdctRegs &ic, int lane)
 {
-    const float v[15] = {t.q1.x, t.q1.y, t.q2.x, t.q2.y, t.q3.x, t.q3.y, t.s16.x, t.s16.y, t.s8.x, t.s8.y,
-                         t.s4.x, t.s4.y, t.s2.x, t.s2.y, __uint_as_float(t.sign)};
+    float v[kTwFloats];
+    fft_tw_to_array(t, v);
 #pragma unroll
-    for (int i = 0; i < 15; i++) tw_tab[i * 32 + lane] = v[i];
+    for (int i = 0; i < kTwFloats; i++) tw_tab[i * 32 + lane] = v[i];
 #pragma unroll
     for (int i = 0; i < 9; i++) ic_tab[i * 32 + lane] = ic.c[i];
     ic_tab[9 * 32 + lane] = ic.firwin;
 }
 __device__ __forceinline__ FftTw lane_tw_load(const float *tab, int lane)
 {
-    FftTw t;
-    const float *p = tab + lane;
-    t.q1 = make_float2(p[0], p[32]);     t.q2 = make_float2(p[64], p[96]);    t.q3 = make_float2(p[128], p[160]);
-    t.s16 = make_float2(p[192], p[224]); t.s8 = make_float2(p[256], p[288]);  t.s4 = make_float2(p[320], p[352]);
-    t.s2 = make_float2(p[384], p[416]);  t.sign = __float_as_uint(p[448]);
-    return t;
+    return fft_tw_from_table(tab + lane);
 }
 #define SE_TW_LOCAL(bm, tw, lane) const FftTw tw##_l = lane_tw_load((bm).lane_tw, lane)
 #define SE_TW(tw) tw##_l
@@ -53,23 +48,23 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
 {
     using P = Prof<PROF>;
     if constexpr (PROF == 8) {
-        float2 v[4];
+        float2 v[1][4];
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             const int i2 = 2 * (lane + 32 * j);
-            v[j] = make_float2(0.0f, 0.0f);
+            v[0][j] = make_float2(0.0f, 0.0f);
             if (i2 < P::FL) {
                 const int pos = wrap<RB>(wpos + i2);
                 const float2 x = *reinterpret_cast<const float2 *>(ring + pos);
                 const float2 w = *reinterpret_cast<const float2 *>(bm.win + i2);
-                v[j] = make_float2(x.x * w.x, x.y * w.y);
+                v[0][j] = make_float2(x.x * w.x, x.y * w.y);
             }
         }
         {
             SE_TW_LOCAL(bm, tw, lane);
-            fft128_warp(v, SE_TW(tw), lane);
+            float2 *const zs[1] = {wm.Z};
+            fft128_spectrum<1>(v, zs, SE_TW(tw), lane);
         }
-        fft128_store(v, wm.Z, lane);
         __syncwarp();
         // FFTtoPSD, etsi/cpp/NoiseSup.c:249-270: |X|^2 on 129 bins, pair-averaged to 65
 #pragma unroll
@@ -90,27 +85,25 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
         // leaves in the array is A = rfft256(x[0::2]) in [0,256), B = rfft128(x[1::4]) in [256,384) and
         // C = rfft128(x[3::4]) in [384,512), each in the Re0..Re(n/2),Im(n/2-1)..Im1 layout; FFTtoPSD
         // then pairs element i with element 512-i.  Reproduced exactly, not "fixed".
-        float2 va[4], vw[4];
+        float2 v[2][4];       // [0]: z = x[0::4] + i x[2::4] (-> A), [1]: w = x[1::4] + i x[3::4] (-> B, C)
 #pragma unroll
         for (int j = 0; j < 4; j++) {
             const int i4 = 4 * (lane + 32 * j);
-            va[j] = make_float2(0.0f, 0.0f);
-            vw[j] = make_float2(0.0f, 0.0f);
+            v[0][j] = make_float2(0.0f, 0.0f);
+            v[1][j] = make_float2(0.0f, 0.0f);
             if (i4 < P::FL) {
                 const int pos = wrap<RB>(wpos + i4);
                 const float4 x = *reinterpret_cast<const float4 *>(ring + pos);
                 const float4 w = *reinterpret_cast<const float4 *>(bm.win + i4);
-                va[j] = make_float2(x.x * w.x, x.z * w.z);
-                vw[j] = make_float2(x.y * w.y, x.w * w.w);
+                v[0][j] = make_float2(x.x * w.x, x.z * w.z);
+                v[1][j] = make_float2(x.y * w.y, x.w * w.w);
             }
         }
         {
             SE_TW_LOCAL(bm, tw, lane);
-            fft128_warp(va, SE_TW(tw), lane);
-            fft128_warp(vw, SE_TW(tw), lane);
+            float2 *const zs[2] = {wm.Z, wm.Z2};
+            fft128_spectrum<2>(v, zs, SE_TW(tw), lane);
         }
-        fft128_store(va, wm.Z, lane);
-        fft128_store(vw, wm.Z2, lane);
         __syncwarp();
         float *raw = wm.raw;
 #pragma unroll
@@ -296,6 +289,25 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
 #pragma unroll
         for (int i = 0; i < kMelTaps; i++) mw = fmaf(wm.W[br.mel_st + i], SE_BR_MEL(bm, br, i, lane), mw);
     } else {
+#ifdef SE_NS_BANK_T
+        // dense 25 x 128, band per lane: the 128 gains go through shared memory (the PSD scratch is dead here) and lane
+        // j < 25 accumulates its own band over all of them -- a broadcast LDS.128 of four gains, a conflict-free LDS.128
+        // of the band's four weights, 4 FMAs -- with no cross-lane reduction at all
+        __syncwarp();
+#pragma unroll
+        for (int r = 0; r < 4; r++) wm.raw[lane + 32 * r] = W[r];
+        __syncwarp();
+        const float4 *bank4 = reinterpret_cast<const float4 *>(bm.bankT) + lane;
+        const float4 *w4 = reinterpret_cast<const float4 *>(wm.raw);
+        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
+#pragma unroll
+        for (int k = 0; k < 32; k++) {
+            const float4 c = bank4[k * 32];
+            const float4 w = w4[k];
+            a0 = fmaf(w.x, c.x, a0); a1 = fmaf(w.y, c.y, a1); a2 = fmaf(w.z, c.z, a2); a3 = fmaf(w.w, c.w, a3);
+        }
+        mw = (a0 + a1) + (a2 + a3);
+#else
         // dense 25 x 128: every lane multiplies its own 4 bins (registers) into 25 partial sums, then a
         // butterfly reduce-scatter leaves band j's total on lane j (31 shuffles instead of 25 x 5)
         float p[32];
@@ -318,6 +330,7 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
             }
         }
         mw = p[0];
+#endif
     }
     if (lane >= kMel) mw = 0.0f;
 
@@ -450,26 +463,26 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
 {
     constexpr int NBAND = HP16 ? 26 : 23;
     float e = 0.0f;
-    float2 v[4];
+    float2 v[1][4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
         const int i2 = 2 * (lane + 32 * j);
-        v[j] = make_float2(0.0f, 0.0f);
+        v[0][j] = make_float2(0.0f, 0.0f);
         if (i2 < 200) {
             const float dm1 = ld(i2 - 1);
             const float d0 = ld(i2);
             const float d1 = ld(i2 + 1);
             e += d0 * d0 + d1 * d1;
             // pre-emphasis 0.9 (:427-429) and Hamming (:434)
-            v[j] = make_float2((d0 - 0.9f * dm1) * bm.ham[i2], (d1 - 0.9f * d0) * bm.ham[i2 + 1]);
+            v[0][j] = make_float2((d0 - 0.9f * dm1) * bm.ham[i2], (d1 - 0.9f * d0) * bm.ham[i2 + 1]);
         }
     }
     e = warp_sum(e);
     {
         SE_TW_LOCAL(bm, tw, lane);
-        fft128_warp(v, SE_TW(tw), lane);
+        float2 *const zs[1] = {wm.Z};
+        fft128_spectrum<1>(v, zs, SE_TW(tw), lane);
     }
-    fft128_store(v, wm.Z, lane);
     __syncwarp();
     // power spectrum (:451-459), 129 bins, into wm.W
     float d0 = 0.0f, d1 = 0.0f, d2 = 0.0f;     // HP16: GetBandsForDecoding16k, bins 66..76 | 78..96 | 98..128

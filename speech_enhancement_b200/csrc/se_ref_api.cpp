@@ -44,7 +44,8 @@ se_ctx *default_ctx(const char *who)
 
 // The sub-band adapters default to the bit-exact kernels (one serial work item per utterance).  SE_B200_FAST=1 selects
 // the time-chunked default-mode kernels instead (int16 within 1 LSB of the reference, >= 60 dB; ~20x lower latency for
-// a lone 10 s resynthesis).
+// a lone 10 s resynthesis); every adapter call carries ONE utterance, so resynthesis also asks for the short chunks of
+// SE_FLAG_LATENCY.
 int g64_flags()
 {
     static const int fast = [] { const char *e = std::getenv("SE_B200_FAST"); return e && e[0] == '1'; }();
@@ -427,7 +428,8 @@ SE_EXPORT int se_resynth(const short *wav, long n, float *mask, int num_frame, i
     if (!ctx) return SE_ENODEVICE;
     if (n <= 0) return SE_OK;
     const int64_t off[2] = {0, n}, fo[2] = {0, num_frame};
-    int rc = report("se_resynth", se_resynth_batch(ctx, wav, off, 1, mask, fo, mode, g64_flags(), out, SE_MEM_HOST));
+    const int flags = g64_flags() ? g64_flags() : SE_FLAG_LATENCY;
+    int rc = report("se_resynth", se_resynth_batch(ctx, wav, off, 1, mask, fo, mode, flags, out, SE_MEM_HOST));
     if (rc == SE_OK && mode == SE_RESYNTH_IBM && mask)
         for (long i = 0; i < (long)num_frame * 64; i++)
             if (mask[i] > 0.5f) mask[i] = 1.0f;                       // resyth_64sub_IBM/cpp/extractwav.cpp:99

@@ -162,3 +162,9 @@ def test_resynth_time_chunked_default_mode(ctx, oracle, mode):
     assert snr_db(ref_i16, got) >= 60.0
     exact = ctx.resynth(x, [0, n], m, [0, nf], mode, exact=True)
     assert np.array_equal(exact, ref_i16)
+    # SE_FLAG_LATENCY: 2 048-sample chunks (26 work items here instead of 4), same bars, float stream included
+    lat = ctx.resynth(x, [0, n], m, [0, nf], mode, exact=False, latency=True)
+    d = np.abs(lat.astype(np.int32) - ref_i16.astype(np.int32))
+    assert d.max() <= 1, "latency chunks: max |d| = %d LSB at %d" % (d.max(), int(d.argmax()))
+    lat_f = ctx.resynth(x, [0, n], m, [0, nf], mode, exact=False, f32=True, latency=True)
+    assert snr_db(ref_f32, lat_f) >= 60.0

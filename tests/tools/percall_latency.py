@@ -52,6 +52,10 @@ rows.append(("subbband (64 rows, exact)", med(lambda: D.se_subband(x16.ctypes.da
              med(lambda: rs.subband(x16), 2)))
 rows.append(("resynth IBM (exact)", med(lambda: D.se_resynth(x16.ctypes.data, 160000, mask.ctypes.data, nf, 0, out16.ctypes.data)),
              med(lambda: rr.resynth(x16, mask), 2)))
+with api.Context(0) as ctx:
+    fo = [0, nf]
+    rows.append(("resynth IBM, default mode (1 s chunks), se_resynth_batch", med(lambda: ctx.resynth(x16, [0, 160000], mask, fo, 0, exact=False)), None))
+    rows.append(("resynth IBM, SE_FLAG_LATENCY (2 048-sample chunks)", med(lambda: ctx.resynth(x16, [0, 160000], mask, fo, 0, exact=False, latency=True)), None))
 rows.append(("make_single_IBM incl. both subbband passes", med(lambda: D.se_single_ibm(clean.ctypes.data, noise.ctypes.data, 160000, irm.ctypes.data, ibm.ctypes.data)),
              None))
 print("| call (one 10 s utterance) | drop-in on the GPU, ms | reference on one host core, ms |")
