@@ -51,6 +51,7 @@ def lib():
         L.se_ctx_profiling.argtypes = [_vp, C.c_int]
         L.se_ctx_set_pipeline.argtypes = [_vp, C.c_uint64, C.c_int]
         L.se_ctx_set_feature_flush.argtypes = [_vp, C.c_int]
+        L.se_ctx_set_ns_pipeline.argtypes = [_vp, C.c_int]
         L.se_ctx_set_exact.argtypes = [_vp, C.c_int]
         L.se_extract_wiener_batch.argtypes = [_vp, _vp, _vp, C.c_int, _vp, _vp, _vp, _vp, C.c_int]
         L.se_ctx_kernel_time.argtypes = [_vp, C.c_int, C.POINTER(C.c_double), C.POINTER(C.c_int64)]
@@ -307,6 +308,10 @@ class Context:
         self.etsi_features_raw(samples, offsets, nu, feat, fo, rows, den)
         per_utt = [feat[fo[u]:fo[u] + rows[u]] for u in range(nu)]
         return (per_utt, den) if denoised else per_utt
+
+    def set_ns_pipeline(self, mode):
+        """0: kernel chosen by batch size, 1: one warp per utterance, 2: one CTA per utterance (pipelined warps)."""
+        _check(self.L.se_ctx_set_ns_pipeline(self.h, int(mode)), "se_ctx_set_ns_pipeline")
 
     def set_feature_flush(self, enable):
         """FlushAdvProcess at the end of every utterance of the feature-chain calls (6 more rows)."""

@@ -319,6 +319,7 @@ int se_ctx_create(int device, se_ctx **out)
     ctx->chunk_bytes = 512ull << 20;
     ctx->chunk_min_utts = 1024;
     ctx->feature_flush = 0;
+    ctx->ns_pipeline = 0;
     ctx->bounce = nullptr;
     ctx->bounce_cap = ctx->bounce_used = 0;
     ctx->profiling = 0;
@@ -390,6 +391,13 @@ int se_ctx_set_exact(se_ctx *ctx, int enable)
 {
     if (!ctx) return SE_EINVAL;
     ctx->exact = enable ? 1 : 0;
+    return SE_OK;
+}
+
+int se_ctx_set_ns_pipeline(se_ctx *ctx, int mode)
+{
+    if (!ctx || mode < 0 || mode > 2) return SE_EINVAL;
+    ctx->ns_pipeline = mode;
     return SE_OK;
 }
 

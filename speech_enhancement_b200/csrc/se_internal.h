@@ -150,6 +150,7 @@ struct se_ctx {
     uint64_t chunk_bytes;       // SE_MEM_HOST pipelining: target I/O bytes per chunk
     int chunk_min_utts;         // ... and the fewest utterances worth a launch of their own
     int feature_flush;          // se_ctx_set_feature_flush: the feature-chain calls append FlushAdvProcess's 6 rows
+    int ns_pipeline;            // se_ctx_set_ns_pipeline: 0 auto, 1 never, 2 always (se_ns_pipe.cuh)
     // tables
     se::NsTables h_p8, h_p16;
     se::RfftPlan h_rf8, h_rf16;

@@ -676,6 +676,12 @@ __global__ void __launch_bounds__(128) comp_ceps_kernel(const float *frames, flo
     }
 }
 
+}  // namespace SE_NSPACE
+#ifndef SE_NS_EXACT
+#include "se_ns_pipe.cuh"
+#endif
+namespace SE_NSPACE {
+
 // ------------------------------------------------------------------------------------------------
 // host launchers
 // ------------------------------------------------------------------------------------------------
@@ -690,6 +696,12 @@ template <int PROF, typename IN_T, int FEAT = 0>
 static int launch_ns(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid)
 {
     if (a.n_utts <= 0) return SE_OK;
+#ifndef SE_NS_EXACT
+    if constexpr (FEAT == 0) {      // few utterances: one CTA per utterance, a block's work pipelined over its warps
+        int rc = SE_OK;
+        if (try_ns_pipe<PROF, IN_T>(ctx, a, tb, kid, &rc)) return rc;
+    }
+#endif
     const size_t smem = ns_smem_bytes<PROF, FEAT>();
     auto kern = ns_stream_kernel<PROF, IN_T, FEAT>;
     SE_CUDA(cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem));

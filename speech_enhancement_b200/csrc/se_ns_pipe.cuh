@@ -1,0 +1,426 @@
+// Pipelined NoiseSup kernel for SMALL batches: one CTA per utterance, the work of one block spread over 4-5 warps.
+// Included by se_ns.cu (fast arithmetic only).
+//
+// The batch kernel (se_ns_kernel.cuh) gives an utterance one warp, so a lone 10 s utterance is 1 000 strictly serial
+// block iterations of ~4.5 us (8 kHz) / ~6.5 us (16 kHz): twice a CPU core, and the ramp of every host-buffer chunk.
+// The recursion is serial in TIME, but inside one block iteration the parts form a chain that can be software-pipelined
+// over blocks:
+//
+//   warp 0  input -> ring1, zero-frame gate, window + FFT + PSD of stage 0     (depends on the input only: runs ahead)
+//   warp 1  stage 0: VAD, FilterCalc, filter bank, frame-dropping statistics, IDCT, 17-tap FIR   -> stage-0 output
+//   warp 2  stage-0 output -> ring2, window + FFT + PSD of stage 1
+//   warp 3  stage 1: FilterCalc, filter bank, gain factorisation, IDCT, FIR, DC filter, outputs
+//   warp 4  (8 kHz profile) CompCeps on the denoised stream
+//
+// Each warp keeps PRIVATE copies of the sample rings it reads (warp 1 and warp 3 re-store the blocks they receive), so the
+// only shared data are four small FIFOs of kPipeDepth entries in shared memory, handed over with mbarriers (full / empty
+// per slot).  Every role consumes and produces exactly one entry per input block, in order.  The arithmetic is the batch
+// kernel's own device functions (frame_psd, ns_stage_rest, dc_offset, comp_ceps), so the outputs are bit-identical to
+// the batch kernel's; the launcher picks this kernel when the batch is too small to fill the GPU with one warp per
+// utterance (se_ctx_set_ns_pipeline overrides).
+#pragma once
+
+namespace SE_NSPACE {
+
+constexpr int kPipeDepth = 4;
+template <int PROF> struct PipeWarps { static constexpr int value = PROF == 8 ? 5 : 4; };
+
+template <int PROF> struct __align__(16) PipeMem {
+    using P = Prof<PROF>;
+    struct __align__(16) EntA { float x[P::S]; float psd[P::NB * 32]; int process, run, pad0, pad1; };
+    struct __align__(16) EntB {
+        float x[P::S];
+        int process, ran0, var, spec, mel, nb_speech, nb_frame0, flag_vad;
+        float den_en0, den_en1, den_en2, pad;
+    };
+    struct __align__(16) EntC { float psd[P::NB * 32]; int run, pad0, pad1, pad2; };
+    struct __align__(16) EntD { float x[P::S]; int produced, nb_out2, pad0, pad1; };
+    EntA a[kPipeDepth];
+    EntB b[kPipeDepth];
+    EntC c[kPipeDepth];
+    EntD d[kPipeDepth];
+    unsigned long long full[4][kPipeDepth], empty[4][kPipeDepth];
+};
+
+// consumer / producer sides of one FIFO slot; entry k lives in slot k % depth, round k / depth
+__device__ __forceinline__ void pipe_wait_full(unsigned long long *full, unsigned k)
+{
+    se_bulk::mbar_wait_warp(&full[k & (kPipeDepth - 1)], (k / kPipeDepth) & 1u);
+}
+__device__ __forceinline__ void pipe_wait_empty(unsigned long long *empty, unsigned k)
+{
+    se_bulk::mbar_wait_warp(&empty[k & (kPipeDepth - 1)], ((k / kPipeDepth) & 1u) ^ 1u);
+}
+// every lane's shared-memory accesses to the slot are done: one arrival by lane 0
+__device__ __forceinline__ void pipe_signal(unsigned long long *bars, unsigned k, int lane)
+{
+    __syncwarp();
+    if (lane == 0) se_bulk::mbar_arrive(&bars[k & (kPipeDepth - 1)]);
+}
+
+template <int PROF, typename IN_T>
+__global__ void __launch_bounds__(PipeWarps<PROF>::value * 32, 2)
+ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
+{
+    using P = Prof<PROF>;
+    constexpr int NW = PipeWarps<PROF>::value;
+    extern __shared__ __align__(16) unsigned char smem_raw[];
+    BlockMem<PROF> &bm = *reinterpret_cast<BlockMem<PROF> *>(smem_raw);
+    WarpMem<PROF> *wms = reinterpret_cast<WarpMem<PROF> *>(smem_raw + ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)));
+    PipeMem<PROF> &pm = *reinterpret_cast<PipeMem<PROF> *>(wms + NW);
+    const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+    WarpMem<PROF> &wm = wms[warp];
+
+    load_block_tables<PROF>(bm, tb, cc);
+    if (threadIdx.x == 0) {
+        const int consumers[4] = {1, 2, 1, 1};
+        for (int f = 0; f < 4; f++)
+            for (int k = 0; k < kPipeDepth; k++) {
+                se_bulk::mbar_init(&pm.full[f][k], 1);
+                se_bulk::mbar_init(&pm.empty[f][k], consumers[f]);
+            }
+        se_bulk::mbar_init_fence();
+    }
+    __syncthreads();
+    FftTw tw;
+    fft_tw_init(tw, lane);
+    IdctRegs ic;
+    idct_regs_init(ic, tb.idctT, tb.fir_window, lane);
+    BankRegs br;
+    if constexpr (PROF == 8) bank_regs_init(br, bm, lane);
+    else { br.mel_st = br.tri_st = 0; }
+#ifdef SE_NS_CONST_SMEM
+    if (warp == 0) {
+        lane_consts_store(bm.lane_tw, bm.lane_ic, tw, ic, lane);
+        if constexpr (PROF == 8) bank_regs_store(bm.lane_br, br, lane);
+    }
+    __syncthreads();
+#endif
+    if constexpr (WarpMem<PROF>::kSpecScratch)
+        for (int i = lane; i < 132; i += 32) wm.W[i] = 0.0f;
+    const float eps = tb.eps;
+    const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
+    unsigned kbase = 0;                      // FIFO entry index of block 0 of the current utterance (same on every warp)
+
+    for (int q = blockIdx.x; q < a.n_utts; q += gridDim.x) {
+        int u = a.utt_begin + q;
+        if (a.order) u = a.order[u];
+        const int64_t off0 = a.offsets[u] - a.sample_base;
+        const int64_t n = a.offsets[u + 1] - a.offsets[u];
+        const int nblk = (int)(n / P::S);
+        const IN_T *in = all + off0;
+        const int64_t blk0 = a.block_offsets ? a.block_offsets[u] - a.block_base : 0;
+        const int64_t tr0 = a.trace_offsets ? a.trace_offsets[u] - a.trace_base : 0;
+        const int64_t ceps0 = a.ceps_offsets ? a.ceps_offsets[u] - a.ceps_base : 0;
+        const int64_t ceps_cap = a.ceps_offsets ? a.ceps_offsets[u + 1] - a.ceps_offsets[u] : 0;
+
+        // every role starts the utterance from the reference's initial state (DoNoiseSupInit); a role only ever touches
+        // its own part of it
+        Scal s;
+        scal_init(s);
+        float noise[P::NB], den[P::NB];      // this role's stage: noiseSE / denSigSE of its bins
+#pragma unroll
+        for (int r = 0; r < P::NB; r++) {
+            noise[r] = eps;
+            den[r] = 0.0f;
+            wm.prev[r * 32 + lane] = 0.0f;
+            wm.prev[(P::NB + r) * 32 + lane] = 0.0f;
+        }
+        for (int i = lane; i < P::RB + 16; i += 32) { wm.ring1[i] = 0.0f; wm.ring2[i] = 0.0f; }
+        if (P::CEPS)
+            for (int i = lane; i < P::RB; i += 32) wm.ring3[i] = 0.0f;
+        SE_COLD(cold_fd_store(wm.cold, s));
+        SE_COLD(cold_gf_store(wm.cold, s));
+        float *ring1 = wm.ring1 + 8, *ring2 = wm.ring2 + 8;
+        __syncwarp();
+
+        if (warp == 0) {
+            // ---- input, zero-frame gate, stage-0 PSD -------------------------------------------------------------
+            IN_T nx[P::NR];
+#pragma unroll
+            for (int r = 0; r < P::NR; r++) {
+                const int i = lane + 32 * r;
+                nx[r] = (nblk > 0 && i < P::S) ? in[i] : IN_T(0);
+            }
+            for (int b = 0; b < nblk; b++) {
+                float cur[P::NR];
+                float ss = 0.0f;
+                bool nzl = false;
+#pragma unroll
+                for (int r = 0; r < P::NR; r++) { cur[r] = to_f32(nx[r]); ss += cur[r] * cur[r]; nzl |= (cur[r] != 0.0f); }
+                if (b + 1 < nblk) {
+#pragma unroll
+                    for (int r = 0; r < P::NR; r++) {
+                        const int i = lane + 32 * r;
+                        if (i < P::S) nx[r] = in[(int64_t)(b + 1) * P::S + i];
+                    }
+                }
+                bool process = true;
+                if (a.zero_check) {
+                    bool nonzero;
+                    if (sizeof(IN_T) == 2) nonzero = __any_sync(0xffffffffu, nzl);
+                    else nonzero = !(warp_sum(ss) < 1.0f);
+                    if (a.zero_check == 1) { process = nonzero || (s.onset != 0); if (process) s.onset = 1; }
+                    else process = nonzero;
+                }
+                const unsigned k = kbase + b;
+                pipe_wait_empty(pm.empty[0], k);
+                typename PipeMem<PROF>::EntA &e = pm.a[k & (kPipeDepth - 1)];
+                bool run = false;
+                if (process) {
+                    const int slot = s.nb_in1 & 3;
+#pragma unroll
+                    for (int r = 0; r < P::NR; r++) {
+                        const int i = lane + 32 * r;
+                        if (i < P::S) { ring_store<PROF>(ring1, slot, i, cur[r]); e.x[i] = cur[r]; }
+                    }
+                    s.nb_in1++;
+                    __syncwarp();
+                    run = s.nb_in1 - s.nb_in2 > 2;
+                    if (run) {
+                        float psd[P::NB];
+                        frame_psd<PROF>(wm, bm, tw, lane, ring1, (s.nb_in1 & 3) * P::S + P::ANA, psd);
+#pragma unroll
+                        for (int r = 0; r < P::NB; r++) e.psd[r * 32 + lane] = psd[r];
+                        s.nb_in2++;
+                    }
+                }
+                if (lane == 0) { e.process = process ? 1 : 0; e.run = run ? 1 : 0; }
+                pipe_signal(pm.full[0], k, lane);
+            }
+        } else if (warp == 1) {
+            // ---- stage 0 without its PSD ---------------------------------------------------------------------------
+            for (int b = 0; b < nblk; b++) {
+                const unsigned k = kbase + b;
+                pipe_wait_full(pm.full[0], k);
+                const typename PipeMem<PROF>::EntA &e = pm.a[k & (kPipeDepth - 1)];
+                const bool process = e.process != 0, run = e.run != 0;
+                float psd[P::NB];
+                if (process) {
+                    const int slot = s.nb_in1 & 3;
+#pragma unroll
+                    for (int r = 0; r < P::NR; r++) {
+                        const int i = lane + 32 * r;
+                        if (i < P::S) ring_store<PROF>(ring1, slot, i, e.x[i]);
+                    }
+                    s.nb_in1++;
+                }
+#pragma unroll
+                for (int r = 0; r < P::NB; r++) psd[r] = run ? e.psd[r * 32 + lane] : 0.0f;
+                pipe_signal(pm.empty[0], k, lane);             // the entry is in this warp's ring / registers now
+                float o[P::CH];
+                StageFlags fl = {0, 0, 0};
+                if (run) ns_stage_rest<PROF>(wm, bm, ic, br, lane, s, noise, den, eps, 0, psd, o, fl, nullptr, nullptr);
+                pipe_wait_empty(pm.empty[1], k);
+                typename PipeMem<PROF>::EntB &eb = pm.b[k & (kPipeDepth - 1)];
+                if (run) {
+                    const int i0 = lane * P::CH;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) eb.x[i0 + t] = o[t];
+                }
+                if (lane == 0) {
+                    eb.process = process ? 1 : 0; eb.ran0 = run ? 1 : 0;
+                    eb.var = fl.var; eb.spec = fl.spec; eb.mel = fl.mel;
+                    eb.nb_speech = s.nb_speech; eb.nb_frame0 = s.nb_frame0; eb.flag_vad = s.flag_vad;
+                    eb.den_en0 = s.den_en0; eb.den_en1 = s.den_en1; eb.den_en2 = s.den_en2;
+                }
+                pipe_signal(pm.full[1], k, lane);
+            }
+        } else if (warp == 2) {
+            // ---- stage-0 output -> ring2, stage-1 PSD ----------------------------------------------------------------
+            for (int b = 0; b < nblk; b++) {
+                const unsigned k = kbase + b;
+                pipe_wait_full(pm.full[1], k);
+                const typename PipeMem<PROF>::EntB &eb = pm.b[k & (kPipeDepth - 1)];
+                const bool ran0 = eb.ran0 != 0;
+                if (ran0) {
+                    const int slot = s.nb_in2 & 3, i0 = lane * P::CH;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) ring_store<PROF>(ring2, slot, i0 + t, eb.x[i0 + t]);
+                    s.nb_in2++;
+                }
+                pipe_signal(pm.empty[1], k, lane);
+                const bool run = ran0 && (s.nb_in2 - s.nb_out2 > 2);
+                pipe_wait_empty(pm.empty[2], k);
+                typename PipeMem<PROF>::EntC &ec = pm.c[k & (kPipeDepth - 1)];
+                if (run) {
+                    float psd[P::NB];
+                    frame_psd<PROF>(wm, bm, tw, lane, ring2, (s.nb_in2 & 3) * P::S + P::ANA, psd);
+#pragma unroll
+                    for (int r = 0; r < P::NB; r++) ec.psd[r * 32 + lane] = psd[r];
+                    s.nb_out2++;
+                }
+                if (lane == 0) ec.run = run ? 1 : 0;
+                pipe_signal(pm.full[2], k, lane);
+            }
+        } else if (warp == 3) {
+            // ---- stage 1 without its PSD, DC filter, outputs -----------------------------------------------------------
+            for (int b = 0; b < nblk; b++) {
+                const unsigned k = kbase + b;
+                pipe_wait_full(pm.full[1], k);
+                const typename PipeMem<PROF>::EntB &eb = pm.b[k & (kPipeDepth - 1)];
+                const bool process = eb.process != 0, ran0 = eb.ran0 != 0;
+                StageFlags fl = {eb.var, eb.spec, eb.mel};
+                s.nb_speech = eb.nb_speech; s.nb_frame0 = eb.nb_frame0; s.flag_vad = eb.flag_vad;
+                s.den_en0 = eb.den_en0; s.den_en1 = eb.den_en1; s.den_en2 = eb.den_en2;
+                if constexpr (PROF == 8) { wm.cold[8] = s.den_en0; wm.cold[9] = s.den_en1; wm.cold[10] = s.den_en2; }
+                if (ran0) {
+                    const int slot = s.nb_in2 & 3, i0 = lane * P::CH;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) ring_store<PROF>(ring2, slot, i0 + t, eb.x[i0 + t]);
+                    s.nb_in2++;
+                }
+                pipe_signal(pm.empty[1], k, lane);
+                pipe_wait_full(pm.full[2], k);
+                const typename PipeMem<PROF>::EntC &ec = pm.c[k & (kPipeDepth - 1)];
+                const bool run = ec.run != 0;
+                float psd[P::NB];
+#pragma unroll
+                for (int r = 0; r < P::NB; r++) psd[r] = run ? ec.psd[r * 32 + lane] : 0.0f;
+                pipe_signal(pm.empty[2], k, lane);
+                float o[P::CH];
+                bool produced = false;
+                if (run) {
+                    float *grow = (PROF == 16 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
+                    StageFlags fl1 = {0, 0, 0};
+                    ns_stage_rest<PROF>(wm, bm, ic, br, lane, s, noise, den, eps, 1, psd, o, fl1, grow, nullptr);
+                    s.n_rows++;
+                    produced = true;
+                    dc_offset<PROF>(o, s, lane);
+                }
+                const int64_t obase = off0 + (int64_t)b * P::S;
+                const int i0 = lane * P::CH;
+                if constexpr (PROF == 8) {
+                    // denoised shift -> CompCeps warp, then coalesced int16 / float stores (as the batch kernel)
+                    pipe_wait_empty(pm.empty[3], k);
+                    typename PipeMem<PROF>::EntD &ed = pm.d[k & (kPipeDepth - 1)];
+                    float *stage_out = wm.W;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) {
+                            const float v = produced ? o[t] : 0.0f;
+                            stage_out[i0 + t] = v;
+                            ed.x[i0 + t] = v;
+                        }
+                    if (lane == 0) { ed.produced = produced ? 1 : 0; ed.nb_out2 = s.nb_out2; }
+                    pipe_signal(pm.full[3], k, lane);          // (its __syncwarp also orders the stage_out reads below)
+                    if (a.den_i16) {
+                        for (int i = lane; i < P::S / 2; i += 32) {
+                            const float2 f = *reinterpret_cast<const float2 *>(stage_out + 2 * i);
+                            short2 qv;
+                            qv.x = (short)__float2int_rz(f.x);
+                            qv.y = (short)__float2int_rz(f.y);
+                            if ((reinterpret_cast<uintptr_t>(a.den_i16 + obase) & 3) == 0) *reinterpret_cast<short2 *>(a.den_i16 + obase + 2 * i) = qv;
+                            else { a.den_i16[obase + 2 * i] = qv.x; a.den_i16[obase + 2 * i + 1] = qv.y; }
+                        }
+                    }
+                    if (a.den_f32)
+                        for (int i = lane; i < P::S; i += 32) a.den_f32[obase + i] = stage_out[i];
+                    if (a.vad_trace && lane == 0) {
+                        unsigned char t = 128;
+                        if (process)
+                            t = (unsigned char)((s.flag_vad ? 1 : 0) | (fl.var << 1) | (fl.spec << 2) | (fl.mel << 3) |
+                                                ((s.nb_speech > 4 ? 1 : 0) << 4) | (ran0 ? 32 : 0) | (produced ? 64 : 0));
+                        a.vad_trace[tr0 + b] = t;
+                    }
+                    __syncwarp();
+                } else {
+                    if (a.out_f32) {
+#pragma unroll
+                        for (int t = 0; t < P::CH; t++)
+                            if (i0 + t < P::S) a.out_f32[obase + i0 + t] = produced ? o[t] : 0.0f;
+                    }
+                    if (a.flags && lane == 0) {
+                        int32_t *f = a.flags + blk0 + b;
+                        const int64_t T = a.total_blocks;
+                        f[0 * T] = ran0 ? fl.var : 0;
+                        f[1 * T] = ran0 ? fl.spec : 0;
+                        f[2 * T] = ran0 ? fl.mel : 0;
+                        f[3 * T] = ran0 ? (s.nb_speech > 4 ? 1 : 0) : 0;
+                        f[4 * T] = (ran0 || produced) ? s.nb_frame0 : 0;
+                    }
+                }
+            }
+            // tail (len % S): the reference leaves it untouched; the batch API defines it as 0
+            if (PROF == 8) {
+                for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) {
+                    if (a.den_i16) a.den_i16[off0 + i] = 0;
+                    if (a.den_f32) a.den_f32[off0 + i] = 0.0f;
+                }
+            } else if (a.out_f32) {
+                for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
+            }
+            if (lane == 0 && a.n_rows) a.n_rows[u] = s.n_rows;
+        } else {
+            // ---- CompCeps on the third denoised shift onwards (8 kHz profile) --------------------------------------------
+            if constexpr (PROF == 8) {
+                for (int b = 0; b < nblk; b++) {
+                    const unsigned k = kbase + b;
+                    pipe_wait_full(pm.full[3], k);
+                    const typename PipeMem<PROF>::EntD &ed = pm.d[k & (kPipeDepth - 1)];
+                    const bool produced = ed.produced != 0;
+                    const int nb_out2 = ed.nb_out2;
+                    if (produced) {
+                        const int nb3 = ((nb_out2 - 1) & 3) * P::S;
+                        for (int i = lane; i < P::S; i += 32) wm.ring3[nb3 + i] = ed.x[i];
+                    }
+                    pipe_signal(pm.empty[3], k, lane);
+                    if (produced && a.ceps && nb_out2 >= 3) {
+                        const int m = nb_out2 - 3;
+                        if (m < ceps_cap) comp_ceps(wm, bm, tw, br, lane, (m & 3) * P::S, a.ceps + (ceps0 + m) * 14);
+                        s.n_ceps = m + 1;
+                    }
+                }
+                if (lane == 0 && a.n_ceps) a.n_ceps[u] = s.n_ceps;
+            }
+        }
+        kbase += (unsigned)nblk;
+        __syncwarp();
+    }
+}
+
+template <int PROF> static size_t pipe_smem_bytes()
+{
+    return ((sizeof(BlockMem<PROF>) + 15) & ~size_t(15)) + PipeWarps<PROF>::value * sizeof(WarpMem<PROF>) + sizeof(PipeMem<PROF>);
+}
+
+// CTAs of the pipelined kernel the GPU holds at once (0: cannot run)
+template <int PROF, typename IN_T> static int pipe_capacity(se_ctx *ctx)
+{
+    const size_t smem = pipe_smem_bytes<PROF>();
+    auto kern = ns_pipe_kernel<PROF, IN_T>;
+    if (cudaFuncSetAttribute(kern, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    int per_sm = 0;
+    if (cudaOccupancyMaxActiveBlocksPerMultiprocessor(&per_sm, kern, PipeWarps<PROF>::value * 32, smem) != cudaSuccess) { cudaGetLastError(); return 0; }
+    return per_sm * ctx->sm_count;
+}
+
+template <int PROF, typename IN_T>
+static int launch_ns_pipe(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid, int capacity)
+{
+    const size_t smem = pipe_smem_bytes<PROF>();
+    int blocks = a.n_utts < capacity ? a.n_utts : capacity;
+    prof_begin(ctx, kid);
+    ns_pipe_kernel<PROF, IN_T><<<blocks, PipeWarps<PROF>::value * 32, smem, ctx->cur->stream>>>(a, tb, ctx->d_cc);
+    prof_end(ctx, kid);
+    SE_CUDA(cudaGetLastError());
+    return SE_OK;
+}
+
+// The pipelined kernel serves plain batch launches (no persistent state, feature chain or traces) whose utterances all
+// get a CTA of their own at once; ctx->ns_pipeline: 0 = that rule, 1 = never, 2 = whenever it is able to.
+template <int PROF, typename IN_T>
+static bool try_ns_pipe(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, int kid, int *rc)
+{
+    if (ctx->ns_pipeline == 1 || a.state || a.features || a.spec_trace || a.produced || a.n_utts <= 0) return false;
+    const int cap = pipe_capacity<PROF, IN_T>(ctx);
+    if (cap <= 0) return false;
+    if (ctx->ns_pipeline != 2 && a.n_utts > cap) return false;
+    *rc = launch_ns_pipe<PROF, IN_T>(ctx, a, tb, kid, cap);
+    return true;
+}
+
+}  // namespace SE_NSPACE

@@ -217,23 +217,20 @@ __device__ __forceinline__ void bank_regs_store(float *tab /*[22][32]*/, const B
 #endif
 
 #ifndef SE_NS_EXACT
-// One Wiener-filter stage (fstage is warp-uniform at run time: both stages share one copy of the code,
-// which halves the kernel's instruction footprint).
+// One Wiener-filter stage after its PSD is known (fstage is warp-uniform at run time in the batch kernel: both stages
+// share one copy of the code, which halves the kernel's instruction footprint).  psd[r] = PSD bin lane + 32 r of the
+// frame (frame_psd).  Split from the PSD so that the pipelined single-utterance kernel (se_ns_pipe.cuh) can compute
+// the two on different warps.
 template <int PROF>
-__device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, const IdctRegs &ic,
-                                         const BankRegs &br, int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
-                                         float eps, const int fstage, float (&o)[Prof<PROF>::CH], StageFlags &fl,
-                                         float *gains_row, float *spec_trace, float *psd_keep = nullptr)
+__device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const IdctRegs &ic,
+                                              const BankRegs &br, int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
+                                              float eps, const int fstage, const float (&psd)[Prof<PROF>::NB], float (&o)[Prof<PROF>::CH],
+                                              StageFlags &fl, float *gains_row, float *spec_trace)
 {
     using P = Prof<PROF>;
     float *ring = fstage == 0 ? wm.ring1 + 8 : wm.ring2 + 8;
     const int cnt = fstage == 0 ? s.nb_in1 : s.nb_in2;   // blocks written to this ring so far
-    const int slot_old = cnt & 3;                        // buffer[0..S)      = prvFrame
     const int cur_base = ((cnt + 1) & 3) * P::S;         // buffer[S..2S)     = curFrame
-
-    float psd[P::NB];
-    frame_psd<PROF>(wm, bm, tw, lane, ring, slot_old * P::S + P::ANA, psd);
-    if (psd_keep) { psd_keep[0] = psd[1]; psd_keep[1] = psd[2]; }      // 16 kHz mode: bins 32..64 of this frame
 
     // VAD (stage 0 only looks at the signal)
     float frame_sq = 0.0f;
@@ -403,6 +400,22 @@ __device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF>
         s.nb_out2++;
     }
     __syncwarp();
+}
+
+// One whole stage on one warp: windowed frame -> PSD -> the rest.
+template <int PROF>
+__device__ __forceinline__ void ns_stage(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const FftTw &tw, const IdctRegs &ic,
+                                         const BankRegs &br, int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
+                                         float eps, const int fstage, float (&o)[Prof<PROF>::CH], StageFlags &fl,
+                                         float *gains_row, float *spec_trace, float *psd_keep = nullptr)
+{
+    using P = Prof<PROF>;
+    const float *ring = fstage == 0 ? wm.ring1 + 8 : wm.ring2 + 8;
+    const int cnt = fstage == 0 ? s.nb_in1 : s.nb_in2;
+    float psd[P::NB];
+    frame_psd<PROF>(wm, bm, tw, lane, ring, (cnt & 3) * P::S + P::ANA, psd);   // buffer[0..S) = prvFrame = slot cnt & 3
+    if (psd_keep) { psd_keep[0] = psd[1]; psd_keep[1] = psd[2]; }      // 16 kHz mode: bins 32..64 of this frame
+    ns_stage_rest<PROF>(wm, bm, ic, br, lane, s, noise, den, eps, fstage, psd, o, fl, gains_row, spec_trace);
 }
 
 // DCOffsetFil (NoiseSup.c:182-198) over one shift, chunk-per-lane layout, as a warp scan of the
