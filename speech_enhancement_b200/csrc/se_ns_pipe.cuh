@@ -1,55 +1,86 @@
-// Pipelined NoiseSup kernel for SMALL batches: one CTA per utterance, the work of one block spread over 4-5 warps.
+// Pipelined NoiseSup kernel for SMALL batches: one CTA per utterance, the work of one block spread over 5-6 warps.
 // Included by se_ns.cu (fast arithmetic only).
 //
 // The batch kernel (se_ns_kernel.cuh) gives an utterance one warp, so a lone 10 s utterance is 1 000 strictly serial
-// block iterations of ~4.5 us (8 kHz) / ~6.5 us (16 kHz): twice a CPU core, and the ramp of every host-buffer chunk.
+// block iterations of ~5 us (8 kHz) / ~6.5 us (16 kHz): twice a CPU core, and the ramp of every host-buffer chunk.
 // The recursion is serial in TIME, but inside one block iteration the parts form a chain that can be software-pipelined
 // over blocks:
 //
-//   warp 0  input -> ring1, zero-frame gate, window + FFT + PSD of stage 0     (depends on the input only: runs ahead)
-//   warp 1  stage 0: VAD, FilterCalc, filter bank, frame-dropping statistics, IDCT, 17-tap FIR   -> stage-0 output
-//   warp 2  stage-0 output -> ring2, window + FFT + PSD of stage 1
-//   warp 3  stage 1: FilterCalc, filter bank, gain factorisation, IDCT, FIR, DC filter, outputs
-//   warp 4  (8 kHz profile) CompCeps on the denoised stream
+//   warp 0  input -> ring1, zero-frame gate, frame energy, window + FFT + PSD of stage 0   (input only: runs ahead)
+//   warp 1  stage-0 recursion: VAD, FilterCalc, mel / Gamma bank, denoised-energy history, IDCT   -> 9 filter taps
+//   warp 2  17-tap FIR of stage 0 over its own ring1 -> ring2, window + FFT + PSD of stage 1
+//   warp 3  stage-1 recursion: noise update, FilterCalc, bank, gain factorisation, IDCT           -> 9 filter taps
+//   warp 4  frame-dropping statistics of stage 0, FIR of stage 1 over its own ring2, DC filter, every output
+//   warp 5  (8 kHz profile) CompCeps on the denoised stream
 //
-// Each warp keeps PRIVATE copies of the sample rings it reads (warp 1 and warp 3 re-store the blocks they receive), so the
-// only shared data are four small FIFOs of kPipeDepth entries in shared memory, handed over with mbarriers (full / empty
-// per slot).  Every role consumes and produces exactly one entry per input block, in order.  The arithmetic is the batch
-// kernel's own device functions (frame_psd, ns_stage_rest, dc_offset, comp_ceps), so the outputs are bit-identical to
-// the batch kernel's; the launcher picks this kernel when the batch is too small to fill the GPU with one warp per
-// utterance (se_ctx_set_ns_pipeline overrides).
+// Every warp keeps PRIVATE copies of what it reads repeatedly (warps 0 and 2 each hold ring1, warps 2 and 4 each ring2),
+// so the only shared data are six small FIFOs of kPipeDepth entries in shared memory, handed over with mbarriers (full /
+// empty per slot).  Every role consumes and produces exactly one entry per input block, in order.  The arithmetic is the
+// batch kernel's own device functions (frame_psd, ns_stage_rest, fd_stats, apply_fir, dc_offset, comp_ceps), so the
+// outputs are bit-identical to the batch kernel's; the launcher picks this kernel when the batch is too small to fill
+// the GPU with one warp per utterance (se_ctx_set_ns_pipeline overrides).
 #pragma once
 
 namespace SE_NSPACE {
 
-constexpr int kPipeDepth = 4;
-template <int PROF> struct PipeWarps { static constexpr int value = PROF == 8 ? 5 : 4; };
+#ifndef SE_PIPE_DEPTH
+#define SE_PIPE_DEPTH 4
+#endif
+constexpr int kPipeDepth = SE_PIPE_DEPTH;      // entries per FIFO (a power of two)
+template <int PROF> struct PipeWarps { static constexpr int value = PROF == 8 ? 6 : 5; };
+constexpr int kPipeFifos = 6;
+// FIFO index: producer -> consumer(s)
+enum { kFA = 0,   // warp 0 -> 1, 2 : input block, stage-0 PSD, frame energy
+       kFB = 1,   // warp 1 -> 2, 4 : stage-0 filter taps, lane partials for the statistics, VAD state
+       kFC = 2,   // warp 2 -> 3    : stage-1 PSD, denoised-energy history
+       kFE = 3,   // warp 2 -> 4    : stage-0 output block
+       kFD = 4,   // warp 3 -> 4    : stage-1 filter taps
+       kFF = 5 }; // warp 4 -> 5    : denoised block (8 kHz profile)
 
 template <int PROF> struct __align__(16) PipeMem {
     using P = Prof<PROF>;
-    struct __align__(16) EntA { float x[P::S]; float psd[P::NB * 32]; int process, run, pad0, pad1; };
+    struct __align__(16) EntA { float x[P::S]; float psd[P::NB * 32]; float frame_sq; int process, run, pad0; };
     struct __align__(16) EntB {
-        float x[P::S];
-        int process, ran0, var, spec, mel, nb_speech, nb_frame0, flag_vad;
-        float den_en0, den_en1, den_en2, pad;
+        float h[12], wsum[32], wsq[32], mw[32];
+        int process, ran0, nb_speech, nb_frame0, flag_vad, pad0, pad1, pad2;
+        float den_en0, den_en1, den_en2, pad3;
     };
-    struct __align__(16) EntC { float psd[P::NB * 32]; int run, pad0, pad1, pad2; };
-    struct __align__(16) EntD { float x[P::S]; int produced, nb_out2, pad0, pad1; };
+    struct __align__(16) EntC { float psd[P::NB * 32]; int run, pad0; float den_en0, den_en1, den_en2, pad1, pad2, pad3; };
+    struct __align__(16) EntE { float x[P::S]; int ran0, pad0, pad1, pad2; };
+    struct __align__(16) EntD { float h[12]; int run, pad0, pad1, pad2; };
+    struct __align__(16) EntF { float x[P::S]; int produced, nb_out2, pad0, pad1; };
     EntA a[kPipeDepth];
     EntB b[kPipeDepth];
     EntC c[kPipeDepth];
+    EntE e[kPipeDepth];
     EntD d[kPipeDepth];
-    unsigned long long full[4][kPipeDepth], empty[4][kPipeDepth];
+    EntF f[kPipeDepth];
+    unsigned long long full[kPipeFifos][kPipeDepth], empty[kPipeFifos][kPipeDepth];
 };
 
+// -DSE_PIPE_STATS (a measurement build, tools/build_variants.sh): cycles every role spends waiting for its input
+// (full) and for room in its output (empty), summed over the launch; read back with se_debug_pipe_stats().
+#ifdef SE_PIPE_STATS
+__device__ unsigned long long g_pipe_stats[8][4];
+#define SE_PIPE_T0 const long long t0__ = clock64()
+#define SE_PIPE_ACC(i) pipe_wait_cycles[i] += clock64() - t0__
+#else
+#define SE_PIPE_T0
+#define SE_PIPE_ACC(i)
+#endif
+
 // consumer / producer sides of one FIFO slot; entry k lives in slot k % depth, round k / depth
-__device__ __forceinline__ void pipe_wait_full(unsigned long long *full, unsigned k)
+__device__ __forceinline__ void pipe_wait_full(unsigned long long *full, unsigned k, long long *pipe_wait_cycles)
 {
+    SE_PIPE_T0;
     se_bulk::mbar_wait_warp(&full[k & (kPipeDepth - 1)], (k / kPipeDepth) & 1u);
+    SE_PIPE_ACC(0);
 }
-__device__ __forceinline__ void pipe_wait_empty(unsigned long long *empty, unsigned k)
+__device__ __forceinline__ void pipe_wait_empty(unsigned long long *empty, unsigned k, long long *pipe_wait_cycles)
 {
+    SE_PIPE_T0;
     se_bulk::mbar_wait_warp(&empty[k & (kPipeDepth - 1)], ((k / kPipeDepth) & 1u) ^ 1u);
+    SE_PIPE_ACC(1);
 }
 // every lane's shared-memory accesses to the slot are done: one arrival by lane 0
 __device__ __forceinline__ void pipe_signal(unsigned long long *bars, unsigned k, int lane)
@@ -73,8 +104,8 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 
     load_block_tables<PROF>(bm, tb, cc);
     if (threadIdx.x == 0) {
-        const int consumers[4] = {1, 2, 1, 1};
-        for (int f = 0; f < 4; f++)
+        const int consumers[kPipeFifos] = {2, 2, 1, 1, 1, 1};
+        for (int f = 0; f < kPipeFifos; f++)
             for (int k = 0; k < kPipeDepth; k++) {
                 se_bulk::mbar_init(&pm.full[f][k], 1);
                 se_bulk::mbar_init(&pm.empty[f][k], consumers[f]);
@@ -101,6 +132,11 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     const float eps = tb.eps;
     const IN_T *all = reinterpret_cast<const IN_T *>(a.samples);
     unsigned kbase = 0;                      // FIFO entry index of block 0 of the current utterance (same on every warp)
+    long long wait_cycles[2] = {0, 0};
+    (void)wait_cycles;
+#ifdef SE_PIPE_STATS
+    const long long t_start = clock64();
+#endif
 
     for (int q = blockIdx.x; q < a.n_utts; q += gridDim.x) {
         int u = a.utt_begin + q;
@@ -134,8 +170,9 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         float *ring1 = wm.ring1 + 8, *ring2 = wm.ring2 + 8;
         __syncwarp();
 
+        constexpr int SL = kPipeDepth - 1;
         if (warp == 0) {
-            // ---- input, zero-frame gate, stage-0 PSD -------------------------------------------------------------
+            // ---- input, zero-frame gate, frame energy, stage-0 PSD -----------------------------------------------------
             IN_T nx[P::NR];
 #pragma unroll
             for (int r = 0; r < P::NR; r++) {
@@ -164,8 +201,8 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     else process = nonzero;
                 }
                 const unsigned k = kbase + b;
-                pipe_wait_empty(pm.empty[0], k);
-                typename PipeMem<PROF>::EntA &e = pm.a[k & (kPipeDepth - 1)];
+                pipe_wait_empty(pm.empty[kFA], k, wait_cycles);
+                typename PipeMem<PROF>::EntA &e = pm.a[k & SL];
                 bool run = false;
                 if (process) {
                     const int slot = s.nb_in1 & 3;
@@ -182,21 +219,56 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         frame_psd<PROF>(wm, bm, tw, lane, ring1, (s.nb_in1 & 3) * P::S + P::ANA, psd);
 #pragma unroll
                         for (int r = 0; r < P::NB; r++) e.psd[r * 32 + lane] = psd[r];
+                        const float fsq = frame_energy<PROF>(ring1, ((s.nb_in1 + 1) & 3) * P::S, lane);
+                        if (lane == 0) e.frame_sq = fsq;
                         s.nb_in2++;
                     }
                 }
                 if (lane == 0) { e.process = process ? 1 : 0; e.run = run ? 1 : 0; }
-                pipe_signal(pm.full[0], k, lane);
+                pipe_signal(pm.full[kFA], k, lane);
             }
         } else if (warp == 1) {
-            // ---- stage 0 without its PSD ---------------------------------------------------------------------------
+            // ---- stage-0 recursion -> filter taps ---------------------------------------------------------------------
             for (int b = 0; b < nblk; b++) {
                 const unsigned k = kbase + b;
-                pipe_wait_full(pm.full[0], k);
-                const typename PipeMem<PROF>::EntA &e = pm.a[k & (kPipeDepth - 1)];
+                pipe_wait_full(pm.full[kFA], k, wait_cycles);
+                const typename PipeMem<PROF>::EntA &e = pm.a[k & SL];
                 const bool process = e.process != 0, run = e.run != 0;
                 float psd[P::NB];
-                if (process) {
+#pragma unroll
+                for (int r = 0; r < P::NB; r++) psd[r] = run ? e.psd[r * 32 + lane] : 0.0f;
+                StageSplit sp;
+                sp.frame_sq = run ? e.frame_sq : 0.0f;
+                pipe_signal(pm.empty[kFA], k, lane);
+                if (process) s.nb_in1++;
+                float o[P::CH];
+                StageFlags fl = {0, 0, 0};
+                if (run) ns_stage_rest<PROF, true>(wm, bm, ic, br, lane, s, noise, den, eps, 0, psd, o, fl, nullptr, nullptr, &sp);
+                pipe_wait_empty(pm.empty[kFB], k, wait_cycles);
+                typename PipeMem<PROF>::EntB &eb = pm.b[k & SL];
+                if (run) {
+                    eb.wsum[lane] = sp.wsum_part;
+                    eb.wsq[lane] = sp.wsq_part;
+                    eb.mw[lane] = sp.mw;
+                    if (lane == 0) {
+#pragma unroll
+                        for (int t = 0; t < 9; t++) eb.h[t] = sp.h[t];
+                    }
+                }
+                if (lane == 0) {
+                    eb.process = process ? 1 : 0; eb.ran0 = run ? 1 : 0;
+                    eb.nb_speech = s.nb_speech; eb.nb_frame0 = s.nb_frame0; eb.flag_vad = s.flag_vad;
+                    eb.den_en0 = s.den_en0; eb.den_en1 = s.den_en1; eb.den_en2 = s.den_en2;
+                }
+                pipe_signal(pm.full[kFB], k, lane);
+            }
+        } else if (warp == 2) {
+            // ---- stage-0 FIR over a private ring1 -> ring2, stage-1 PSD ---------------------------------------------------
+            for (int b = 0; b < nblk; b++) {
+                const unsigned k = kbase + b;
+                pipe_wait_full(pm.full[kFA], k, wait_cycles);
+                const typename PipeMem<PROF>::EntA &e = pm.a[k & SL];
+                if (e.process != 0) {
                     const int slot = s.nb_in1 & 3;
 #pragma unroll
                     for (int r = 0; r < P::NR; r++) {
@@ -205,46 +277,31 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     }
                     s.nb_in1++;
                 }
-#pragma unroll
-                for (int r = 0; r < P::NB; r++) psd[r] = run ? e.psd[r * 32 + lane] : 0.0f;
-                pipe_signal(pm.empty[0], k, lane);             // the entry is in this warp's ring / registers now
-                float o[P::CH];
-                StageFlags fl = {0, 0, 0};
-                if (run) ns_stage_rest<PROF>(wm, bm, ic, br, lane, s, noise, den, eps, 0, psd, o, fl, nullptr, nullptr);
-                pipe_wait_empty(pm.empty[1], k);
-                typename PipeMem<PROF>::EntB &eb = pm.b[k & (kPipeDepth - 1)];
-                if (run) {
-                    const int i0 = lane * P::CH;
-#pragma unroll
-                    for (int t = 0; t < P::CH; t++)
-                        if (i0 + t < P::S) eb.x[i0 + t] = o[t];
-                }
-                if (lane == 0) {
-                    eb.process = process ? 1 : 0; eb.ran0 = run ? 1 : 0;
-                    eb.var = fl.var; eb.spec = fl.spec; eb.mel = fl.mel;
-                    eb.nb_speech = s.nb_speech; eb.nb_frame0 = s.nb_frame0; eb.flag_vad = s.flag_vad;
-                    eb.den_en0 = s.den_en0; eb.den_en1 = s.den_en1; eb.den_en2 = s.den_en2;
-                }
-                pipe_signal(pm.full[1], k, lane);
-            }
-        } else if (warp == 2) {
-            // ---- stage-0 output -> ring2, stage-1 PSD ----------------------------------------------------------------
-            for (int b = 0; b < nblk; b++) {
-                const unsigned k = kbase + b;
-                pipe_wait_full(pm.full[1], k);
-                const typename PipeMem<PROF>::EntB &eb = pm.b[k & (kPipeDepth - 1)];
+                pipe_signal(pm.empty[kFA], k, lane);
+                pipe_wait_full(pm.full[kFB], k, wait_cycles);
+                const typename PipeMem<PROF>::EntB &eb = pm.b[k & SL];
                 const bool ran0 = eb.ran0 != 0;
+                float h[9];
+#pragma unroll
+                for (int t = 0; t < 9; t++) h[t] = eb.h[t];
+                const float de0 = eb.den_en0, de1 = eb.den_en1, de2 = eb.den_en2;
+                pipe_signal(pm.empty[kFB], k, lane);
+                pipe_wait_empty(pm.empty[kFE], k, wait_cycles);
+                typename PipeMem<PROF>::EntE &ee = pm.e[k & SL];
                 if (ran0) {
+                    float o[P::CH];
+                    apply_fir<PROF>(ring1, ((s.nb_in1 + 1) & 3) * P::S, h, lane, o);
                     const int slot = s.nb_in2 & 3, i0 = lane * P::CH;
 #pragma unroll
                     for (int t = 0; t < P::CH; t++)
-                        if (i0 + t < P::S) ring_store<PROF>(ring2, slot, i0 + t, eb.x[i0 + t]);
+                        if (i0 + t < P::S) { ring_store<PROF>(ring2, slot, i0 + t, o[t]); ee.x[i0 + t] = o[t]; }
                     s.nb_in2++;
                 }
-                pipe_signal(pm.empty[1], k, lane);
+                if (lane == 0) ee.ran0 = ran0 ? 1 : 0;
+                pipe_signal(pm.full[kFE], k, lane);            // (its __syncwarp also orders the ring2 stores before the PSD)
                 const bool run = ran0 && (s.nb_in2 - s.nb_out2 > 2);
-                pipe_wait_empty(pm.empty[2], k);
-                typename PipeMem<PROF>::EntC &ec = pm.c[k & (kPipeDepth - 1)];
+                pipe_wait_empty(pm.empty[kFC], k, wait_cycles);
+                typename PipeMem<PROF>::EntC &ec = pm.c[k & SL];
                 if (run) {
                     float psd[P::NB];
                     frame_psd<PROF>(wm, bm, tw, lane, ring2, (s.nb_in2 & 3) * P::S + P::ANA, psd);
@@ -252,42 +309,76 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     for (int r = 0; r < P::NB; r++) ec.psd[r * 32 + lane] = psd[r];
                     s.nb_out2++;
                 }
-                if (lane == 0) ec.run = run ? 1 : 0;
-                pipe_signal(pm.full[2], k, lane);
+                if (lane == 0) { ec.run = run ? 1 : 0; ec.den_en0 = de0; ec.den_en1 = de1; ec.den_en2 = de2; }
+                pipe_signal(pm.full[kFC], k, lane);
             }
         } else if (warp == 3) {
-            // ---- stage 1 without its PSD, DC filter, outputs -----------------------------------------------------------
+            // ---- stage-1 recursion -> filter taps (and the gains row of the 16 kHz profile) --------------------------------
             for (int b = 0; b < nblk; b++) {
                 const unsigned k = kbase + b;
-                pipe_wait_full(pm.full[1], k);
-                const typename PipeMem<PROF>::EntB &eb = pm.b[k & (kPipeDepth - 1)];
-                const bool process = eb.process != 0, ran0 = eb.ran0 != 0;
-                StageFlags fl = {eb.var, eb.spec, eb.mel};
-                s.nb_speech = eb.nb_speech; s.nb_frame0 = eb.nb_frame0; s.flag_vad = eb.flag_vad;
-                s.den_en0 = eb.den_en0; s.den_en1 = eb.den_en1; s.den_en2 = eb.den_en2;
-                if constexpr (PROF == 8) { wm.cold[8] = s.den_en0; wm.cold[9] = s.den_en1; wm.cold[10] = s.den_en2; }
-                if (ran0) {
-                    const int slot = s.nb_in2 & 3, i0 = lane * P::CH;
-#pragma unroll
-                    for (int t = 0; t < P::CH; t++)
-                        if (i0 + t < P::S) ring_store<PROF>(ring2, slot, i0 + t, eb.x[i0 + t]);
-                    s.nb_in2++;
-                }
-                pipe_signal(pm.empty[1], k, lane);
-                pipe_wait_full(pm.full[2], k);
-                const typename PipeMem<PROF>::EntC &ec = pm.c[k & (kPipeDepth - 1)];
+                pipe_wait_full(pm.full[kFC], k, wait_cycles);
+                const typename PipeMem<PROF>::EntC &ec = pm.c[k & SL];
                 const bool run = ec.run != 0;
                 float psd[P::NB];
 #pragma unroll
                 for (int r = 0; r < P::NB; r++) psd[r] = run ? ec.psd[r * 32 + lane] : 0.0f;
-                pipe_signal(pm.empty[2], k, lane);
+                s.den_en0 = ec.den_en0; s.den_en1 = ec.den_en1; s.den_en2 = ec.den_en2;
+                pipe_signal(pm.empty[kFC], k, lane);
+                if constexpr (PROF == 8) { wm.cold[8] = s.den_en0; wm.cold[9] = s.den_en1; wm.cold[10] = s.den_en2; }
+                StageSplit sp;
+                if (run) {
+                    float o[P::CH];
+                    StageFlags fl1 = {0, 0, 0};
+                    float *grow = (PROF == 16 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
+                    ns_stage_rest<PROF, true>(wm, bm, ic, br, lane, s, noise, den, eps, 1, psd, o, fl1, grow, nullptr, &sp);
+                    s.n_rows++;
+                }
+                pipe_wait_empty(pm.empty[kFD], k, wait_cycles);
+                typename PipeMem<PROF>::EntD &ed = pm.d[k & SL];
+                if (lane == 0) {
+                    if (run) {
+#pragma unroll
+                        for (int t = 0; t < 9; t++) ed.h[t] = sp.h[t];
+                    }
+                    ed.run = run ? 1 : 0;
+                }
+                pipe_signal(pm.full[kFD], k, lane);
+            }
+            if (lane == 0 && a.n_rows) a.n_rows[u] = s.n_rows;
+        } else if (warp == 4) {
+            // ---- frame-dropping statistics, stage-1 FIR over a private ring2, DC filter, outputs -----------------------------
+            for (int b = 0; b < nblk; b++) {
+                const unsigned k = kbase + b;
+                pipe_wait_full(pm.full[kFB], k, wait_cycles);
+                const typename PipeMem<PROF>::EntB &eb = pm.b[k & SL];
+                const bool process = eb.process != 0, ran0 = eb.ran0 != 0;
+                s.nb_speech = eb.nb_speech; s.nb_frame0 = eb.nb_frame0; s.flag_vad = eb.flag_vad;
+                const float wsum = eb.wsum[lane], wsq = eb.wsq[lane], mw = eb.mw[lane];
+                pipe_signal(pm.empty[kFB], k, lane);
+                StageFlags fl = {0, 0, 0};
+                if (ran0) fd_stats<PROF>(wm, s, wsum, wsq, mw, fl);
+                pipe_wait_full(pm.full[kFE], k, wait_cycles);
+                const typename PipeMem<PROF>::EntE &ee = pm.e[k & SL];
+                if (ran0) {
+                    const int slot = s.nb_in2 & 3, i0 = lane * P::CH;
+#pragma unroll
+                    for (int t = 0; t < P::CH; t++)
+                        if (i0 + t < P::S) ring_store<PROF>(ring2, slot, i0 + t, ee.x[i0 + t]);
+                    s.nb_in2++;
+                }
+                pipe_signal(pm.empty[kFE], k, lane);
+                pipe_wait_full(pm.full[kFD], k, wait_cycles);
+                const typename PipeMem<PROF>::EntD &ed = pm.d[k & SL];
+                const bool run = ed.run != 0;
+                float h[9];
+#pragma unroll
+                for (int t = 0; t < 9; t++) h[t] = ed.h[t];
+                pipe_signal(pm.empty[kFD], k, lane);
                 float o[P::CH];
                 bool produced = false;
                 if (run) {
-                    float *grow = (PROF == 16 && a.gains) ? a.gains + (blk0 + s.n_rows) * kMel : nullptr;
-                    StageFlags fl1 = {0, 0, 0};
-                    ns_stage_rest<PROF>(wm, bm, ic, br, lane, s, noise, den, eps, 1, psd, o, fl1, grow, nullptr);
-                    s.n_rows++;
+                    apply_fir<PROF>(ring2, ((s.nb_in2 + 1) & 3) * P::S, h, lane, o);
+                    s.nb_out2++;
                     produced = true;
                     dc_offset<PROF>(o, s, lane);
                 }
@@ -295,18 +386,18 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 const int i0 = lane * P::CH;
                 if constexpr (PROF == 8) {
                     // denoised shift -> CompCeps warp, then coalesced int16 / float stores (as the batch kernel)
-                    pipe_wait_empty(pm.empty[3], k);
-                    typename PipeMem<PROF>::EntD &ed = pm.d[k & (kPipeDepth - 1)];
+                    pipe_wait_empty(pm.empty[kFF], k, wait_cycles);
+                    typename PipeMem<PROF>::EntF &ef = pm.f[k & SL];
                     float *stage_out = wm.W;
 #pragma unroll
                     for (int t = 0; t < P::CH; t++)
                         if (i0 + t < P::S) {
                             const float v = produced ? o[t] : 0.0f;
                             stage_out[i0 + t] = v;
-                            ed.x[i0 + t] = v;
+                            ef.x[i0 + t] = v;
                         }
-                    if (lane == 0) { ed.produced = produced ? 1 : 0; ed.nb_out2 = s.nb_out2; }
-                    pipe_signal(pm.full[3], k, lane);          // (its __syncwarp also orders the stage_out reads below)
+                    if (lane == 0) { ef.produced = produced ? 1 : 0; ef.nb_out2 = s.nb_out2; }
+                    pipe_signal(pm.full[kFF], k, lane);        // (its __syncwarp also orders the stage_out reads below)
                     if (a.den_i16) {
                         for (int i = lane; i < P::S / 2; i += 32) {
                             const float2 f = *reinterpret_cast<const float2 *>(stage_out + 2 * i);
@@ -353,21 +444,20 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             } else if (a.out_f32) {
                 for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
             }
-            if (lane == 0 && a.n_rows) a.n_rows[u] = s.n_rows;
         } else {
             // ---- CompCeps on the third denoised shift onwards (8 kHz profile) --------------------------------------------
             if constexpr (PROF == 8) {
                 for (int b = 0; b < nblk; b++) {
                     const unsigned k = kbase + b;
-                    pipe_wait_full(pm.full[3], k);
-                    const typename PipeMem<PROF>::EntD &ed = pm.d[k & (kPipeDepth - 1)];
-                    const bool produced = ed.produced != 0;
-                    const int nb_out2 = ed.nb_out2;
+                    pipe_wait_full(pm.full[kFF], k, wait_cycles);
+                    const typename PipeMem<PROF>::EntF &ef = pm.f[k & SL];
+                    const bool produced = ef.produced != 0;
+                    const int nb_out2 = ef.nb_out2;
                     if (produced) {
                         const int nb3 = ((nb_out2 - 1) & 3) * P::S;
-                        for (int i = lane; i < P::S; i += 32) wm.ring3[nb3 + i] = ed.x[i];
+                        for (int i = lane; i < P::S; i += 32) wm.ring3[nb3 + i] = ef.x[i];
                     }
-                    pipe_signal(pm.empty[3], k, lane);
+                    pipe_signal(pm.empty[kFF], k, lane);
                     if (produced && a.ceps && nb_out2 >= 3) {
                         const int m = nb_out2 - 3;
                         if (m < ceps_cap) comp_ceps(wm, bm, tw, br, lane, (m & 3) * P::S, a.ceps + (ceps0 + m) * 14);
@@ -380,6 +470,14 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         kbase += (unsigned)nblk;
         __syncwarp();
     }
+#ifdef SE_PIPE_STATS
+    if (lane == 0) {
+        atomicAdd(&g_pipe_stats[warp][0], (unsigned long long)wait_cycles[0]);
+        atomicAdd(&g_pipe_stats[warp][1], (unsigned long long)wait_cycles[1]);
+        atomicAdd(&g_pipe_stats[warp][2], (unsigned long long)(clock64() - t_start));
+        atomicAdd(&g_pipe_stats[warp][3], 1ull);
+    }
+#endif
 }
 
 template <int PROF> static size_t pipe_smem_bytes()
@@ -424,3 +522,15 @@ static bool try_ns_pipe(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, i
 }
 
 }  // namespace SE_NSPACE
+
+#ifdef SE_PIPE_STATS
+extern "C" int se_debug_pipe_stats(unsigned long long *out32, int reset)
+{
+    if (cudaMemcpyFromSymbol(out32, SE_NSPACE::g_pipe_stats, sizeof(unsigned long long) * 32) != cudaSuccess) return -1;
+    if (reset) {
+        unsigned long long z[32] = {0};
+        cudaMemcpyToSymbol(SE_NSPACE::g_pipe_stats, z, sizeof z);
+    }
+    return 0;
+}
+#endif

@@ -221,11 +221,68 @@ __device__ __forceinline__ void bank_regs_store(float *tab /*[22][32]*/, const B
 // share one copy of the code, which halves the kernel's instruction footprint).  psd[r] = PSD bin lane + 32 r of the
 // frame (frame_psd).  Split from the PSD so that the pipelined single-utterance kernel (se_ns_pipe.cuh) can compute
 // the two on different warps.
+// SPLIT (the pipelined kernel's two "recursion" warps): the frame energy comes in through `sp`, the frame-dropping
+// statistics (fd_stats) and the FIR (apply_fir) run on other warps -- `sp` takes what they need: the lane partials of
+// the gain sums, the mel gains and the 9 filter taps.  Same expressions, same order, as the whole-stage form.
+struct StageSplit { float frame_sq, wsum_part, wsq_part, mw, h[9]; };
+
+// sum of squares of curFrame (the VAD's frame energy, stage 0)
+template <int PROF> __device__ __forceinline__ float frame_energy(const float *ring, int cur_base, int lane)
+{
+    using P = Prof<PROF>;
+    float frame_sq = 0.0f;
+#pragma unroll
+    for (int r = 0; r < P::NR; r++) {
+        const int i = lane + 32 * r;
+        if (i < P::S) { const float x = ring[cur_base + i]; frame_sq += x * x; }
+    }
+    return warp_sum(frame_sq);
+}
+
+// ApplyWF, NoiseSup.c:324-340: 17-tap symmetric FIR over curFrame with prv/next context
 template <int PROF>
+__device__ __forceinline__ void apply_fir(const float *ring, int cur_base, const float (&h)[9], int lane, float (&o)[Prof<PROF>::CH])
+{
+    using P = Prof<PROF>;
+    float x[P::CH + 16];
+    const int i0 = lane * P::CH;
+    const float *xin = ring + cur_base + i0 - 8;        // guard samples make this window contiguous
+#pragma unroll
+    for (int d = 0; d < P::CH + 16; d++) x[d] = xin[d];
+#pragma unroll
+    for (int t = 0; t < P::CH; t++) {
+        float acc = 0.0f;
+#pragma unroll
+        for (int j = -8; j <= 8; j++) acc += h[j < 0 ? -j : j] * x[t + 8 - j];
+        o[t] = acc;
+    }
+}
+
+// frame-dropping VAD statistics of stage 0 (NoiseSup.c:1268-1281, SpeechQVar / SpeechQSpec / SpeechQMel) from the lane
+// partials of the gain sums and the mel gains (0 on lanes >= 25); s.nb_frame0 is the stage-0 frame counter
+template <int PROF>
+__device__ __forceinline__ void fd_stats(WarpMem<PROF> &wm, Scal &s, float wsum, float wsq, float mw, StageFlags &fl)
+{
+    using P = Prof<PROF>;
+    wsum = warp_sum(wsum);
+    wsq = warp_sum(wsq);
+    SE_COLD(cold_fd_load(s, wm.cold));
+    fl.var = q_var(s, wsum, wsq, P::QVAR);
+    const float te = warp_sum(mw);
+    s.fd_spec_val = (float)((double)(te * te) - 3.0);
+    fl.spec = q_spec(s);
+    const float w1 = __shfl_sync(0xffffffffu, mw, 1), w2 = __shfl_sync(0xffffffffu, mw, 2),
+                w3 = __shfl_sync(0xffffffffu, mw, 3);
+    s.fd_mel_val1 = (float)((double)__fadd_rn(__fadd_rn(w1, w2), w3) / 3.0);
+    fl.mel = q_mel(s);
+    SE_COLD(cold_fd_store(wm.cold, s));
+}
+
+template <int PROF, bool SPLIT = false>
 __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<PROF> &bm, const IdctRegs &ic,
                                               const BankRegs &br, int lane, Scal &s, float (&noise)[Prof<PROF>::NB], float (&den)[Prof<PROF>::NB],
                                               float eps, const int fstage, const float (&psd)[Prof<PROF>::NB], float (&o)[Prof<PROF>::CH],
-                                              StageFlags &fl, float *gains_row, float *spec_trace)
+                                              StageFlags &fl, float *gains_row, float *spec_trace, StageSplit *sp = nullptr)
 {
     using P = Prof<PROF>;
     float *ring = fstage == 0 ? wm.ring1 + 8 : wm.ring2 + 8;
@@ -235,12 +292,8 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
     // VAD (stage 0 only looks at the signal)
     float frame_sq = 0.0f;
     if (fstage == 0) {
-#pragma unroll
-        for (int r = 0; r < P::NR; r++) {
-            const int i = lane + 32 * r;
-            if (i < P::S) { const float x = ring[cur_base + i]; frame_sq += x * x; }
-        }
-        frame_sq = warp_sum(frame_sq);
+        if constexpr (SPLIT) frame_sq = sp->frame_sq;
+        else frame_sq = frame_energy<PROF>(ring, cur_base, lane);
     }
     vad_ns(s, fstage, frame_sq);
     const int nbf = (int)(short)(fstage == 0 ? s.nb_frame0 : s.nb_frame1);   // Q2: read through int16
@@ -272,11 +325,16 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
         }
     }
     if (fstage == 0) {
-        wsum = warp_sum(wsum);
-        wsq = warp_sum(wsq);
-        SE_COLD(cold_fd_load(s, wm.cold));
-        fl.var = q_var(s, wsum, wsq, P::QVAR);
-        SE_COLD(cold_fd_store(wm.cold, s));
+        if constexpr (SPLIT) {
+            sp->wsum_part = wsum;
+            sp->wsq_part = wsq;
+        } else {
+            wsum = warp_sum(wsum);
+            wsq = warp_sum(wsq);
+            SE_COLD(cold_fd_load(s, wm.cold));
+            fl.var = q_var(s, wsum, wsq, P::QVAR);
+            SE_COLD(cold_fd_store(wm.cold, s));
+        }
     }
 
     // DoMelFB (etsi/cpp/MelProc.c:82-104) / DoGamma (aurora_etsi/MelProc.cpp:119-141, ignores StartingPoint)
@@ -331,7 +389,15 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
     }
     if (lane >= kMel) mw = 0.0f;
 
-    if (fstage == 0) {
+    if (SPLIT && fstage == 0) {
+        sp->mw = mw;
+        // DoGainFact stage 0, NoiseSup.c:593-599
+        SE_COLD(cold_gf_load(s, wm.cold));
+        s.den_en0 = s.den_en1;
+        s.den_en1 = s.den_en2;
+        s.den_en2 = warp_sum(den_sum);
+        SE_COLD(cold_gf_store(wm.cold, s));
+    } else if (fstage == 0) {
         // frame-dropping VAD statistics, NoiseSup.c:1268-1281
         const float te = warp_sum(mw);
         SE_COLD(cold_fd_load(s, wm.cold));
@@ -376,19 +442,16 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
         for (int t = 0; t < 9; t++) h[t] = __shfl_sync(0xffffffffu, acc, t);
     }
 
-    // ApplyWF, NoiseSup.c:324-340: 17-tap symmetric FIR over curFrame with prv/next context
-    float x[P::CH + 16];
-    const int i0 = lane * P::CH;
-    const float *xin = ring + cur_base + i0 - 8;        // guard samples make this window contiguous
+    if constexpr (SPLIT) {
 #pragma unroll
-    for (int d = 0; d < P::CH + 16; d++) x[d] = xin[d];
-#pragma unroll
-    for (int t = 0; t < P::CH; t++) {
-        float acc = 0.0f;
-#pragma unroll
-        for (int j = -8; j <= 8; j++) acc += h[j < 0 ? -j : j] * x[t + 8 - j];
-        o[t] = acc;
+        for (int t = 0; t < 9; t++) sp->h[t] = h[t];
+        if (fstage == 0) s.nb_in2++;
+        else s.nb_out2++;
+        __syncwarp();
+        return;
     }
+    apply_fir<PROF>(ring, cur_base, h, lane, o);
+    const int i0 = lane * P::CH;
 
     if (fstage == 0) {
         const int slot = s.nb_in2 & 3;
