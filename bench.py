@@ -721,7 +721,8 @@ def bench_c1(args, torch, api, ctx, first_u):
     ms = float(np.median(ts[3:])) * 1e3
     return {"workload": "configs[0]: etsi NoiseSup+CompCeps on one 10 s 8 kHz utterance, per-call latency (host buffers)",
             "ms_per_call": ms, "value": 10.0 / (ms * 1e-3), "unit": UNIT,
-            "note": "one utterance = one warp: latency-bound by construction; throughput lives in the batch calls"}
+            "note": "one utterance = one CTA of the pipelined kernel (csrc/se_ns_pipe.cuh: a block's work over six warps); "
+                    "the recursion is serial in time, so this is a latency figure -- throughput lives in the batch calls"}
 
 
 def assemble(w, r, args, dist, cpu):

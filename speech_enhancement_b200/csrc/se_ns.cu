@@ -31,6 +31,7 @@
 namespace se_exact { using namespace se; }
 #endif
 #include "se_warp_fft.cuh"
+#include "se_tmem.cuh"
 
 namespace SE_NSPACE {
 
@@ -100,9 +101,13 @@ template <int PROF> struct __align__(16) BlockMem {
     float2 twh[132];
 #if defined(SE_NS_BANK_T) && !defined(SE_NS_EXACT)
     float bankT[PROF == 16 ? 32 * 32 * 4 : P::BANKROWS * 32];   // P16: NsDevTables::bankR (band-per-lane form)
+#elif defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
+    float bankT[PROF == 16 ? 4 : P::BANKROWS * 32];             // P16: the Gamma bank lives in tensor memory (se_tmem.cuh)
 #else
     float bankT[PROF == 16 ? 25 * 32 * 4 : P::BANKROWS * 32];
 #endif
+    uint32_t tmem_base;               // P16 with SE_NS_BANK_TMEM: this CTA's tensor-memory allocation (kBankTmemCols columns)
+    uint32_t tmem_pad[3];
     int bank_start[32], bank_len[32];
 #ifdef SE_NS_EXACT
     float idctT[25 * 16];             // the fast build reads the IDCT / window taps once, from global memory (lane_ic)

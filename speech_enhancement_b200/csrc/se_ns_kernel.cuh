@@ -85,6 +85,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         for (int i = threadIdx.x; i < 26 * 16; i += blockDim.x) hb.dct26T[i] = cc.dct26T[i];
     }
     __syncthreads();
+    bank_tmem_setup<PROF>(bm, tb.bankT);
 
     FftTw tw;
     fft_tw_init(tw, lane);
@@ -531,6 +532,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         }
         __syncwarp();
     }
+    bank_tmem_release<PROF>(bm);
 }
 
 // ------------------------------------------------------------------------------------------------

@@ -113,6 +113,7 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         se_bulk::mbar_init_fence();
     }
     __syncthreads();
+    bank_tmem_setup<PROF>(bm, tb.bankT);
     FftTw tw;
     fft_tw_init(tw, lane);
     IdctRegs ic;
@@ -470,6 +471,7 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         kbase += (unsigned)nblk;
         __syncwarp();
     }
+    bank_tmem_release<PROF>(bm);
 #ifdef SE_PIPE_STATS
     if (lane == 0) {
         atomicAdd(&g_pipe_stats[warp][0], (unsigned long long)wait_cycles[0]);

@@ -144,8 +144,10 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
         for (int r = 0; r < P::NB; r++) {
             const int b = lane + 32 * r;
             psd[r] = 0.0f;
-            if (b < 128) psd[r] = (raw[2 * b] + raw[2 * b + 1]) * 0.5f;
-            else if (b == 128) psd[r] = raw[256];
+            if (b < 128) {
+                const float2 e = *reinterpret_cast<const float2 *>(raw + 2 * b);    // one 8-byte load: half the wavefronts
+                psd[r] = (e.x + e.y) * 0.5f;
+            } else if (b == 128) psd[r] = raw[256];
         }
     }
 }
@@ -153,6 +155,46 @@ __device__ __forceinline__ void frame_psd(WarpMem<PROF> &wm, const BlockMem<PROF
 #endif  // !SE_NS_EXACT
 
 struct StageFlags { int var, spec, mel; };
+
+// Gamma bank of the 16 kHz plugin profile in tensor memory (SE_NS_BANK_TMEM): column 4 j + r of lane l (in every lane
+// quadrant) = weight of band j for bin l + 32 r -- the float4 the shared-memory version reads at bank4[j * 32 + l].
+// Called by every thread of the CTA, which must have at least four warps; pairs with bank_tmem_release at kernel end.
+constexpr uint32_t kBankTmemCols = 128;
+template <int PROF> __device__ __forceinline__ void bank_tmem_setup(BlockMem<PROF> &bm, const float *bank_global)
+{
+#if defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
+    if constexpr (PROF == 16) {
+        const int lane = threadIdx.x & 31, warp = threadIdx.x >> 5;
+        if (warp == 0) se_tmem::alloc(&bm.tmem_base, kBankTmemCols);
+        se_tmem::fence_before_sync();
+        __syncthreads();
+        se_tmem::fence_after_sync();
+        if (warp < 4) {
+            const float4 *g = reinterpret_cast<const float4 *>(bank_global);
+            const uint32_t taddr = se_tmem::warp_addr(bm.tmem_base, warp, 0);
+            for (int j = 0; j < kMel; j++) {
+                const float4 c = g[j * 32 + lane];
+                se_tmem::st4(taddr + 4 * j, c.x, c.y, c.z, c.w);
+            }
+            se_tmem::wait_st();
+        }
+        se_tmem::fence_before_sync();
+        __syncthreads();
+        se_tmem::fence_after_sync();
+    }
+#endif
+}
+template <int PROF> __device__ __forceinline__ void bank_tmem_release(BlockMem<PROF> &bm)
+{
+#if defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
+    if constexpr (PROF == 16) {
+        se_tmem::fence_before_sync();
+        __syncthreads();
+        se_tmem::fence_after_sync();
+        if ((threadIdx.x >> 5) == 0) se_tmem::dealloc(bm.tmem_base, kBankTmemCols);
+    }
+#endif
+}
 
 // Sample rings: 4 shifts of history per stage, stored with 8 guard samples on either side (a copy of the
 // other end) so the 17-tap filter reads its S+16 window with plain contiguous addresses.
@@ -366,12 +408,32 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
         // dense 25 x 128: every lane multiplies its own 4 bins (registers) into 25 partial sums, then a
         // butterfly reduce-scatter leaves band j's total on lane j (31 shuffles instead of 25 x 5)
         float p[32];
+#if defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
+        // the lane's 100 weights come from its row of tensor memory (bank_tmem_setup), two bands per load: the
+        // shared-memory pipe, which bounds this kernel, no longer carries them
+        const uint32_t taddr = se_tmem::warp_addr(bm.tmem_base, (int)(threadIdx.x >> 5), 0);
+#pragma unroll
+        for (int j = 0; j + 1 < kMel; j += 2) {
+            uint32_t c[8];
+            se_tmem::ld8(taddr + 4 * j, c);
+            se_tmem::wait_ld8(c);
+            p[j] = W[0] * __uint_as_float(c[0]) + W[1] * __uint_as_float(c[1]) + W[2] * __uint_as_float(c[2]) + W[3] * __uint_as_float(c[3]);
+            p[j + 1] = W[0] * __uint_as_float(c[4]) + W[1] * __uint_as_float(c[5]) + W[2] * __uint_as_float(c[6]) + W[3] * __uint_as_float(c[7]);
+        }
+        {
+            uint32_t c[4];
+            se_tmem::ld4(taddr + 4 * (kMel - 1), c);
+            se_tmem::wait_ld4(c);
+            p[kMel - 1] = W[0] * __uint_as_float(c[0]) + W[1] * __uint_as_float(c[1]) + W[2] * __uint_as_float(c[2]) + W[3] * __uint_as_float(c[3]);
+        }
+#else
         const float4 *bank4 = reinterpret_cast<const float4 *>(bm.bankT);
 #pragma unroll
         for (int j = 0; j < kMel; j++) {
             const float4 c = bank4[j * 32 + lane];
             p[j] = W[0] * c.x + W[1] * c.y + W[2] * c.z + W[3] * c.w;
         }
+#endif
 #pragma unroll
         for (int j = kMel; j < 32; j++) p[j] = 0.0f;
 #pragma unroll

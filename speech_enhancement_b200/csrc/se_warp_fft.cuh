@@ -157,10 +157,29 @@ __device__ __forceinline__ void fft_tw_to_array(const FftTw &t, float (&v)[kTwFl
 __device__ __forceinline__ FftTw fft_tw_from_table(const float *p /* tab + lane, stride 32 */)
 {
     FftTw t;
+#ifdef SE_FFT_TW_DERIVE
+    // Measured and NOT adopted: load the two base twiddles and the sign, derive the squares / cubes and select the
+    // constant last-pass twiddles -- 14 fewer shared-memory wavefronts per frame (the pipe that bounds these kernels):
+    // P16 -0.6 %, P8 -1.5 %, but the 2-ulp twiddles double the FFT's rounding noise and the cepstra of speech with
+    // digital-silence runs (tests/test_gpu_fuzz.py, kind 6) leave their bar.  Parity first.
+    t.q1 = make_float2(p[0], p[32]);
+    t.p1 = make_float2(p[192], p[224]);
+    t.sgn = p[576];
+    t.q2 = cmul(t.q1, t.q1);
+    t.q3 = cmul(t.q2, t.q1);
+    t.p2 = cmul(t.p1, t.p1);
+    t.p3 = cmul(t.p2, t.p1);
+    const bool odd = t.sgn < 0.0f;
+    const float h = 0.70710678118654752440f;
+    t.r1 = make_float2(odd ? h : 1.0f, odd ? -h : 0.0f);
+    t.r2 = make_float2(odd ? 0.0f : 1.0f, odd ? -1.0f : 0.0f);
+    t.r3 = make_float2(odd ? -h : 1.0f, odd ? -h : 0.0f);
+#else
     t.q1 = make_float2(p[0], p[32]);     t.q2 = make_float2(p[64], p[96]);    t.q3 = make_float2(p[128], p[160]);
     t.p1 = make_float2(p[192], p[224]);  t.p2 = make_float2(p[256], p[288]);  t.p3 = make_float2(p[320], p[352]);
     t.r1 = make_float2(p[384], p[416]);  t.r2 = make_float2(p[448], p[480]);  t.r3 = make_float2(p[512], p[544]);
     t.sgn = p[576];
+#endif
     return t;
 }
 
