@@ -788,7 +788,8 @@ def run_ours(args):
         with torch.cuda.stream(stream):
             fn = {"p16": bench_p16, "p8": bench_p8, "resynth": bench_resynth, "ibm": bench_ibm, "subband": lambda *a: bench_subband(*a, n_utts=int(os.environ.get("SE_SUB_UTTS", "1000")), seconds=float(os.environ.get("SE_SUB_SEC", "5"))),
                   "p8feat": lambda *a: bench_p8(*a, features=True), "etsi16k": bench_etsi16k, "wiener": bench_extract_wiener}[args.profile_only]
-            emit(fn(args, torch, api, ctx, dist, stream, first_u + 500000))
+            # p16: the same corpus as the default run's headline launch (profiles/traffic.json is keyed on its bytes)
+            emit(fn(args, torch, api, ctx, dist, stream, first_u if args.profile_only == "p16" else first_u + 500000))
         ctx.close()
         dist.close()
         return
