@@ -47,6 +47,7 @@ def parse():
     ap.add_argument("--utts", type=int, default=10000, help="utterances per GPU in the p16 batch")
     ap.add_argument("--gpu-map", default="stride", choices=["stride", "dense"],
                     help="rank k -> GPU k * (visible / N) (stride: ranks spread over the box's PCIe root ports) or GPU k")
+    ap.add_argument("--exact", action="store_true", help="NoiseSup family in the exact arithmetic mode (se_ctx_set_exact); for --profile-only runs")
     ap.add_argument("--no-extra", action="store_true", help="skip the other_workloads section")
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
@@ -781,6 +782,8 @@ def run_ours(args):
     stream = torch.cuda.Stream()
     ctx = api.Context(device)
     ctx.set_stream(stream.cuda_stream)
+    if args.exact:
+        ctx.set_exact(True)
     if args.chunk_mb or args.chunk_utts:
         ctx.set_pipeline((args.chunk_mb or 512) << 20, args.chunk_utts or 1024)
 
