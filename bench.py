@@ -52,6 +52,7 @@ def parse():
     ap.add_argument("--no-cpu", action="store_true", help="skip the cpu_baseline leg")
     ap.add_argument("--chunk-mb", type=int, default=0, help="override the SE_MEM_HOST pipeline chunk size (MiB)")
     ap.add_argument("--chunk-utts", type=int, default=0, help="override the pipeline's minimum utterances per chunk")
+    ap.add_argument("--pipe-mode", type=int, default=-1, help="se_ctx_set_pipeline_lead bits (A/B): 1 lead chunk, 2 upload ahead")
     ap.add_argument("--profile-only", default="", choices=["", "p16", "p8", "p8feat", "etsi16k", "resynth", "ibm", "subband", "wiener"],
                     help="run just one of the other_workloads (for ncu) and print its dict")
     return ap.parse_args()
@@ -784,6 +785,8 @@ def run_ours(args):
     ctx.set_stream(stream.cuda_stream)
     if args.exact:
         ctx.set_exact(True)
+    if args.pipe_mode >= 0:
+        ctx.set_pipeline_lead(args.pipe_mode)
     if args.chunk_mb or args.chunk_utts:
         ctx.set_pipeline((args.chunk_mb or 512) << 20, args.chunk_utts or 1024)
 

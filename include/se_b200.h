@@ -57,6 +57,14 @@ int  se_ctx_sync(se_ctx *ctx);
  * enough to keep the persistent warps busy); H2D, kernels and D2H of successive chunks overlap.
  * Results do not depend on the chunking (utterances are independent). */
 int  se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts);
+/* Two refinements of that pipeline for the NoiseSup calls, as bits of `mode` (default 3):
+ *   1  the call opens with a small first chunk -- as many utterances as the single-utterance kernel
+ *      (se_ctx_set_ns_pipeline) runs at once -- so results start flowing back after ~2 ms instead of after the batch
+ *      kernel's per-utterance latency;
+ *   2  the inputs of ALL chunks are uploaded back to back on a stream of their own, ahead of the kernels, instead of
+ *      chunk by chunk between the downloads: the upload engine finishes early and the download engine, which bounds
+ *      the call, runs the rest of it alone (host links are slower with both directions busy). */
+int  se_ctx_set_pipeline_lead(se_ctx *ctx, int mode);
 /* FlushAdvProcess (etsi/cpp/ParmInterface.c:347-355 -> DoVADFlush, VAD.c:342-431): with enable != 0,
  * se_etsi_features_batch and se_etsi16k_features_batch end every utterance the way the ETSI driver loop
  * `while (FlushAdvProcess(FeatureBuffer, fe)) write` does: SE_FEATURE_FLUSH_ROWS more rows leave the VAD's 7-frame

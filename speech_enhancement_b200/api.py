@@ -50,6 +50,7 @@ def lib():
         L.se_ctx_set_scratch_limit.argtypes = [_vp, C.c_uint64]
         L.se_ctx_profiling.argtypes = [_vp, C.c_int]
         L.se_ctx_set_pipeline.argtypes = [_vp, C.c_uint64, C.c_int]
+        L.se_ctx_set_pipeline_lead.argtypes = [_vp, C.c_int]
         L.se_ctx_set_feature_flush.argtypes = [_vp, C.c_int]
         L.se_ctx_set_ns_pipeline.argtypes = [_vp, C.c_int]
         L.se_ctx_set_exact.argtypes = [_vp, C.c_int]
@@ -187,6 +188,10 @@ class Context:
 
     def set_scratch_limit(self, nbytes):
         _check(self.L.se_ctx_set_scratch_limit(self.h, int(nbytes)), "se_ctx_set_scratch_limit")
+
+    def set_pipeline_lead(self, mode):
+        """bits: 1 = small first chunk on the pipelined kernel, 2 = inputs of all chunks uploaded ahead (default 3)"""
+        _check(self.L.se_ctx_set_pipeline_lead(self.h, int(mode)), "se_ctx_set_pipeline_lead")
 
     def set_pipeline(self, chunk_bytes, min_utts):
         _check(self.L.se_ctx_set_pipeline(self.h, int(chunk_bytes), int(min_utts)), "se_ctx_set_pipeline")

@@ -274,6 +274,7 @@ static int ctx_init_device(se_ctx *ctx)
     SE_CUDA(cudaGetDeviceProperties(&prop, device));
     ctx->sm_count = prop.multiProcessorCount;
     SE_CUDA(cudaStreamCreateWithFlags(&ctx->own_stream, cudaStreamNonBlocking));
+    SE_CUDA(cudaStreamCreateWithFlags(&ctx->up_stream, cudaStreamNonBlocking));
     ctx->lanes[0].stream = ctx->own_stream;
     for (int l = 0; l < kLanes; l++) {
         if (l > 0) SE_CUDA(cudaStreamCreateWithFlags(&ctx->lanes[l].stream, cudaStreamNonBlocking));
@@ -318,6 +319,8 @@ int se_ctx_create(int device, se_ctx **out)
     ctx->scratch_limit = 48ull << 30;
     ctx->chunk_bytes = 512ull << 20;
     ctx->chunk_min_utts = 1024;
+    ctx->chunk_lead = 3;
+    ctx->up_stream = nullptr;
     ctx->feature_flush = 0;
     ctx->ns_pipeline = 0;
     ctx->bounce = nullptr;
@@ -353,6 +356,8 @@ void se_ctx_destroy(se_ctx *ctx)
     if (ctx->bounce) cudaFreeHost(ctx->bounce);
     for (auto &e : ctx->pending) { cudaEventDestroy(e.a); cudaEventDestroy(e.b); }
     if (ctx->own_stream) cudaStreamDestroy(ctx->own_stream);
+    if (ctx->up_stream) cudaStreamDestroy(ctx->up_stream);
+    for (cudaEvent_t e : ctx->up_events) cudaEventDestroy(e);
     delete ctx;
 }
 
@@ -384,6 +389,13 @@ int se_ctx_set_pipeline(se_ctx *ctx, uint64_t chunk_bytes, int min_utts)
     if (!ctx || chunk_bytes == 0 || min_utts < 1) return SE_EINVAL;
     ctx->chunk_bytes = chunk_bytes;
     ctx->chunk_min_utts = min_utts;
+    return SE_OK;
+}
+
+int se_ctx_set_pipeline_lead(se_ctx *ctx, int enable)
+{
+    if (!ctx || enable < 0 || enable > 3) return SE_EINVAL;
+    ctx->chunk_lead = enable;
     return SE_OK;
 }
 

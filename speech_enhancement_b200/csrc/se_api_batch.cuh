@@ -8,7 +8,7 @@ namespace se {
 enum {
     kSlotOffsets = 0, kSlotOffsets2 = 1, kSlotOffsets3 = 2, kSlotIn = 3, kSlotIn2 = 4,
     kSlotOut = 5, kSlotOut2 = 6, kSlotOut3 = 7, kSlotOut4 = 8, kSlotOut5 = 9, kSlotOut6 = 10,
-    kSlotGain = 15
+    kSlotInAll = 13, kSlotGain = 15
 };
 
 // offsets / frame-offset arrays are HOST arrays in both memory modes: upload a device copy.
@@ -133,8 +133,23 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
         const uint64_t by_bytes = io_bytes / ctx->chunk_bytes, by_utts = (uint64_t)n_utts / (uint64_t)ctx->chunk_min_utts;
         n_chunks = (int)std::max<uint64_t>(1, std::min<uint64_t>(std::min(by_bytes, by_utts), 32));
     }
-    std::vector<int32_t> first(n_chunks + 1), order(n_utts);
-    SE_TRY(se_shard_plan(offsets, n_utts, n_chunks, first.data()));
+    // Pipelined batches open with a SMALL chunk: as many utterances as the single-utterance kernel (se_ns_pipe.cuh) runs at
+    // once.  It finishes a 10 s utterance in ~1.6 ms where the batch kernel's one warp needs 5-6.5 ms, so the D2H engine --
+    // the bottleneck of the whole call -- starts ~10 ms earlier.  Results do not depend on the chunking.
+    int lead = 0;
+    if (n_chunks > 1 && !ctx->exact && (ctx->chunk_lead & 1)) {
+        const int cap = ns_pipe_capacity(ctx, profile, a);
+        if (cap > 0 && n_utts >= 4 * cap) lead = cap;
+    }
+    std::vector<int32_t> first(n_chunks + 1 + (lead ? 1 : 0)), order(n_utts);
+    if (lead) {
+        first[0] = 0;
+        SE_TRY(se_shard_plan(offsets + lead, n_utts - lead, n_chunks, first.data() + 1));
+        for (int c = 1; c <= n_chunks + 1; c++) first[c] += lead;
+        n_chunks++;
+    } else {
+        SE_TRY(se_shard_plan(offsets, n_utts, n_chunks, first.data()));
+    }
     for (int u = 0; u < n_utts; u++) order[u] = u;
     for (int c = 0; c < n_chunks; c++)
         std::stable_sort(order.begin() + first[c], order.begin() + first[c + 1], [&](int32_t x, int32_t y) {
@@ -171,6 +186,29 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
         trace.push_back({e, c, what});
     };
     mark(-1, "start");
+    // upload-ahead: every chunk's input goes up back to back on ctx->up_stream into ONE staging array that mirrors the
+    // caller's; chunk c's lane waits for event c.  The upload engine is done early, and the download engine -- the
+    // bottleneck of the call -- has the host link to itself for the rest of it.
+    const bool ahead = mem == SE_MEM_HOST && n_chunks > 1 && (ctx->chunk_lead & 2);
+    void *d_in_all = nullptr;
+    if (ahead) {
+        SE_TRY(ensure_stage(ctx, kSlotInAll, in_elem * (uint64_t)offsets[n_utts], &d_in_all));
+        while ((int)ctx->up_events.size() < n_chunks) {
+            cudaEvent_t e;
+            SE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ctx->up_events.push_back(e);
+        }
+        for (int c = 0; c < n_chunks; c++) {
+            const uint64_t b0 = in_elem * (uint64_t)offsets[first[c]], b1 = in_elem * (uint64_t)offsets[first[c + 1]];
+            if (b1 > b0)
+                SE_CUDA(cudaMemcpyAsync((char *)d_in_all + b0, (const char *)samples + b0, b1 - b0, cudaMemcpyHostToDevice, ctx->up_stream));
+            SE_CUDA(cudaEventRecord(ctx->up_events[c], ctx->up_stream));
+            if (tracing) {
+                cudaEvent_t e;
+                if (cudaEventCreate(&e) == cudaSuccess) { cudaEventRecord(e, ctx->up_stream); trace.push_back({e, c, "h2d"}); }
+            }
+        }
+    }
     int rc = SE_OK;
     for (int c = 0; c < n_chunks && rc == SE_OK; c++) {
         const int u0 = first[c], u1 = first[c + 1];
@@ -188,14 +226,20 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
                 b.sample_base = lo[0];
                 if (profile == 8) { b.ceps_base = lo[1]; b.trace_base = lo[2]; } else b.block_base = lo[1];
                 b.total_blocks = hi[1] - lo[1];
-                SE_TRY(stage_in(ctx, kSlotIn, (const char *)samples + in_elem * (uint64_t)lo[0],
-                                in_elem * (uint64_t)(hi[0] - lo[0]), mem, &b.samples));
+                if (ahead) {
+                    SE_CUDA(cudaStreamWaitEvent(ctx->cur->stream, ctx->up_events[c], 0));
+                    b.samples = d_in_all;
+                    b.in_shift = lo[0];
+                } else {
+                    SE_TRY(stage_in(ctx, kSlotIn, (const char *)samples + in_elem * (uint64_t)lo[0],
+                                    in_elem * (uint64_t)(hi[0] - lo[0]), mem, &b.samples));
+                }
             } else {
                 b.samples = samples;
             }
             if (in_elem == sizeof(int16_t)) {      // int16 input: the byte range the kernel's bulk-async prefetch may touch
                 b.bulk_lo = (const char *)b.samples;
-                b.bulk_hi = b.bulk_lo + in_elem * (uint64_t)(mem == SE_MEM_HOST ? hi[0] - lo[0] : offsets[n_utts]);
+                b.bulk_hi = b.bulk_lo + in_elem * (uint64_t)(mem == SE_MEM_HOST && !ahead ? hi[0] - lo[0] : offsets[n_utts]);
             }
             for (int k = 0; k < n_outs; k++) {
                 const NsOut &o = outs[k];
@@ -205,7 +249,7 @@ static int ns_batch_run(se_ctx *ctx, int profile, NsLaunch a, const void *sample
                 else d_out[k] = o.host;          // device arrays are written in place (caller zeroes nothing)
                 set_field(b, o.field, d_out[k]);
             }
-            mark(c, "h2d");
+            if (!ahead) mark(c, "h2d");
             SE_TRY(ctx->exact ? (profile == 8 ? se_exact::launch_ns_p8(ctx, b) : se_exact::launch_ns_p16(ctx, b))
                                : (profile == 8 ? launch_ns_p8(ctx, b) : launch_ns_p16(ctx, b)));
             mark(c, "kernel");

@@ -82,6 +82,7 @@ struct NsLaunch {
     // a launch may cover a chunk of the batch whose data pointers address chunk-local staging buffers:
     // element index = global offset - base
     int64_t sample_base, block_base, ceps_base, trace_base;
+    int64_t in_shift;            // added to the INPUT index only: `samples` may address the whole batch while the outputs are chunk-local
     // P8 outputs
     int16_t *den_i16;
     float *den_f32;
@@ -149,6 +150,10 @@ struct se_ctx {
     se_lane *cur;               // lane the launch helpers currently target
     uint64_t chunk_bytes;       // SE_MEM_HOST pipelining: target I/O bytes per chunk
     int chunk_min_utts;         // ... and the fewest utterances worth a launch of their own
+    int chunk_lead;             // se_ctx_set_pipeline_lead bits: 1 = small first chunk on the pipelined kernel, 2 = all chunks'
+                                // inputs uploaded back to back on up_stream ahead of the kernels (default 3)
+    cudaStream_t up_stream;     // upload stream of the SE_MEM_HOST pipeline
+    std::vector<cudaEvent_t> up_events;   // chunk c's input has arrived
     int feature_flush;          // se_ctx_set_feature_flush: the feature-chain calls append FlushAdvProcess's 6 rows
     int ns_pipeline;            // se_ctx_set_ns_pipeline: 0 auto, 1 never, 2 always (se_ns_pipe.cuh)
     // tables
@@ -191,6 +196,7 @@ void prof_end(se_ctx *ctx, int k);
 // kernel launchers
 int launch_ns_p8(se_ctx *ctx, const NsLaunch &a);
 int launch_ns_p16(se_ctx *ctx, const NsLaunch &a);
+int ns_pipe_capacity(se_ctx *ctx, int profile, const NsLaunch &a);
 int launch_rfft(se_ctx *ctx, float *x, int n, int m, int count);
 int launch_qmf_split(se_ctx *ctx, const int16_t *x, int64_t n, int count, float *lp, float *hp);
 int launch_wave_proc(se_ctx *ctx, float *frames, int count);

@@ -125,7 +125,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         const int64_t off0 = a.offsets[u] - a.sample_base;
         const int64_t n = a.offsets[u + 1] - a.offsets[u];
         const int nblk = (int)(n / SIN);
-        const IN_T *in = all + off0;
+        const IN_T *in = all + off0 + a.in_shift;
 
         // ---- stream state -------------------------------------------------------------------
         Scal s;

@@ -145,7 +145,7 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
         const int64_t off0 = a.offsets[u] - a.sample_base;
         const int64_t n = a.offsets[u + 1] - a.offsets[u];
         const int nblk = (int)(n / P::S);
-        const IN_T *in = all + off0;
+        const IN_T *in = all + off0 + a.in_shift;
         const int64_t blk0 = a.block_offsets ? a.block_offsets[u] - a.block_base : 0;
         const int64_t tr0 = a.trace_offsets ? a.trace_offsets[u] - a.trace_base : 0;
         const int64_t ceps0 = a.ceps_offsets ? a.ceps_offsets[u] - a.ceps_base : 0;
@@ -521,6 +521,15 @@ static bool try_ns_pipe(se_ctx *ctx, const NsLaunch &a, const NsDevTables &tb, i
     if (ctx->ns_pipeline != 2 && a.n_utts > cap) return false;
     *rc = launch_ns_pipe<PROF, IN_T>(ctx, a, tb, kid, cap);
     return true;
+}
+
+// Utterances a launch with these arguments would run on the pipelined kernel at once (0: it would not use it); lets the
+// host-buffer pipeline cut a first chunk of exactly that size, whose results start flowing back after ~2 ms.
+int ns_pipe_capacity(se_ctx *ctx, int profile, const NsLaunch &a)
+{
+    if (ctx->ns_pipeline == 1 || a.state || a.features || a.spec_trace || a.produced) return 0;
+    if (profile == 8) return a.is_f32 ? pipe_capacity<8, float>(ctx) : pipe_capacity<8, int16_t>(ctx);
+    return a.is_f32 ? pipe_capacity<16, float>(ctx) : pipe_capacity<16, int16_t>(ctx);
 }
 
 }  // namespace SE_NSPACE
