@@ -8,10 +8,12 @@
 // Mapping.  The per-frame recursion (noise PSD, decision-directed gain, VAD, gain factorisation) is
 // strictly serial in time, so parallelism comes from utterances: a persistent grid of warps pulls
 // utterance indices from an atomic queue.  Inside a warp: lane l owns PSD bins {l, l+32, ...} in
-// registers (noise / denoised / previous-PSD state for both stages), the FFT is an in-register
-// shuffle FFT (se_warp_fft.cuh), the 4-block sample history of both stages lives in per-warp shared
-// memory rings, filter banks / IDCT / windows are CTA-shared tables in shared memory.  HBM traffic is
-// exactly the algorithmic minimum: each input sample is read once, each output written once.
+// registers (noise / denoised / previous-PSD state for both stages), the FFT-128 runs as three
+// in-register radix-4 passes with two shared-memory transposes (se_warp_fft.cuh), the 4-block sample
+// history of both stages lives in per-warp shared memory rings, filter banks / IDCT / windows are
+// CTA-shared tables in shared memory, int16 input arrives through bulk-async copies (se_bulk.cuh).
+// HBM traffic is exactly the algorithmic minimum: each input sample is read once, each output written
+// once.  Batches too small for that mapping get one CTA per utterance instead (se_ns_pipe.cuh).
 #include <type_traits>
 // Per-lane loop-invariant constants (FFT twiddles, IDCT taps, mel / CompCeps triangle taps) live in shared memory
 // ([field][lane], conflict-free) and are reloaded at their use sites instead of holding ~25-45 registers through the

@@ -11,8 +11,9 @@ constexpr bool kBulk = false;
 constexpr bool kBulk = true;
 #endif
 
-// warps (= concurrent utterances) per CTA; 2 CTAs per SM.  The feature-chain variant keeps more state live
-// per warp, so it trades occupancy (12 instead of 16 warps/SM) for 168 registers per thread.
+// warps (= concurrent utterances) per CTA; 2 CTAs per SM.  NoiseSup and the 8 kHz feature chain run 8 warps at 128
+// registers; the 16 kHz-mode variant keeps more state live per warp and trades occupancy (6 warps per CTA, 12 per SM)
+// for 157 registers per thread.
 #ifndef SE_NS_WARPS
 #define SE_NS_WARPS 8
 #endif

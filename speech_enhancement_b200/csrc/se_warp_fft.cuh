@@ -1,5 +1,6 @@
-// In-warp 128-point complex FFT held in registers (4 points per lane) with shuffle butterflies, and
-// the real-FFT split helpers built on it.  Replaces the reference's in-place split-radix rfft
+// In-warp 128-point complex FFT held in registers (4 points per lane): radix-4 passes in registers with
+// lane <-> point transposes through shared memory (default) or shuffle butterflies (-DSE_FFT_SHFL, the
+// round-1 form), and the real-FFT split helpers built on it.  Replaces the reference's in-place split-radix rfft
 // (etsi/cpp/rfft.c:45-180) for the sizes the hot path uses:
 //   * 256-point real FFT  (P8 NoiseSup, CompCeps)          = one complex FFT-128 + split
 //   * the plugin's truncated rfft(x,512,8)   = rfft256(x[0::2]) ++ rfft128(x[1::4]) ++

@@ -83,3 +83,27 @@ def test_lone_utterance_default_rule_against_the_oracle(ctx, oracle):
     d = np.abs(got["den_i16"].astype(np.int32) - ref["den_i16"].astype(np.int32))
     assert d.max() <= 1
     assert ceps_err(ref["ceps"], got["ceps"][:len(ref["ceps"])]).max() <= 1e-4
+
+
+def test_host_pipeline_lead_chunk_and_upload_ahead(ctx):
+    """SE_MEM_HOST calls cut the batch into chunks; the first one is sized for the pipelined kernel and every chunk's
+    input is uploaded ahead on its own stream (se_ctx_set_pipeline_lead bits 1 and 2).  None of that may change a bit."""
+    rng = np.random.default_rng(11)
+    lens = [int(v) for v in rng.integers(0, 1800, 1400)]
+    x8, off8 = _batch(8000, 80, lens, 12000)
+    x16, off16 = _batch(16000, 160, [2 * v for v in lens], 15000)
+    ref8 = ctx.etsi_denoise(x8, off8, ceps=True, den_f32=True, trace=True)          # one chunk (default sizes)
+    ref16 = ctx.p16_wiener(x16, off16)
+    try:
+        ctx.set_pipeline(256 << 10, 64)                                              # many small chunks
+        for mode in (0, 1, 2, 3):
+            ctx.set_pipeline_lead(mode)
+            got8 = ctx.etsi_denoise(x8, off8, ceps=True, den_f32=True, trace=True)
+            for k in ("den_i16", "den_f32", "ceps", "n_ceps", "trace"):
+                assert np.array_equal(ref8[k], got8[k]), (mode, k)
+            got16 = ctx.p16_wiener(x16, off16)
+            for k in ("out", "flags", "gains", "n_rows"):
+                assert np.array_equal(ref16[k], got16[k]), (mode, k)
+    finally:
+        ctx.set_pipeline(512 << 20, 1024)
+        ctx.set_pipeline_lead(3)

@@ -1,6 +1,8 @@
-"""Smallest run of every kernel, for compute-sanitizer (one tool per gpurun call; the tool is closed on the shared pool
-this round was built on, so the last clean memcheck / racecheck runs predate the 16 kHz-mode, flush and extract_Wiener
-entry points -- those are covered by the parity tests only):
+"""Smallest run of every kernel, for compute-sanitizer (one tool per gpurun call).  Both NoiseSup kernels are driven
+explicitly: the batch kernel (with its bulk-async input staging) and the pipelined single-utterance kernel (mbarrier
+FIFOs), and the chunked host-buffer pipeline with its lead chunk and upload stream.  compute-sanitizer is closed on the
+shared pool these rounds were built on ("runs under it have left GPUs needing a reset"), so the new kernels are covered by
+the bit-identity tests between the two kernels and by the parity tests only; run these where the tool is available:
     compute-sanitizer --tool memcheck  python tools/sanitize_small.py
     compute-sanitizer --tool racecheck python tools/sanitize_small.py
 """
@@ -14,10 +16,19 @@ from speech_enhancement_b200 import api, synth  # noqa: E402
 
 with api.Context(0) as ctx:
     s8, o8 = synth.corpus(0, 5, 8000, min_s=0.2, max_s=0.5)
-    r = ctx.etsi_denoise(s8, o8, ceps=True, den_f32=True, trace=True)
     s16, o16 = synth.corpus(10, 5, 16000, min_s=0.2, max_s=0.5)
-    r = ctx.p16_wiener(s16, o16)
-    r = ctx.p16_wiener(s16.astype(np.float32), o16)
+    for mode in (1, 2):                       # 1: one warp per utterance, 2: one CTA per utterance (pipelined warps)
+        ctx.set_ns_pipeline(mode)
+        r = ctx.etsi_denoise(s8, o8, ceps=True, den_f32=True, trace=True)
+        r = ctx.p16_wiener(s16, o16)
+        r = ctx.p16_wiener(s16.astype(np.float32), o16)
+        r = ctx.p16_wiener(s16[3:], np.maximum(o16 - 3, 0))        # input not 16-byte aligned: bulk copies start below it
+    ctx.set_ns_pipeline(0)
+    if os.environ.get("SE_SANITIZE_CHUNKS", "1") == "1":            # host-buffer pipeline: lead chunk + upload stream
+        sl, ol = synth.corpus(50, 1300, 8000, min_s=0.02, max_s=0.06)
+        ctx.set_pipeline(64 << 10, 64)
+        ctx.etsi_denoise(sl, ol, ceps=True)
+        ctx.set_pipeline(512 << 20, 1024)
     st = ctx.ns_stream(16)
     st.push(s16[:1600].astype(np.float32)); st.push(s16[1600:3200].astype(np.float32)); st.close()
     st = ctx.ns_stream(8)
@@ -41,6 +52,7 @@ with api.Context(0) as ctx:
         m = np.random.default_rng(mode).random((int(fo[-1]), 64)).astype(np.float32)
         for exact in (True, False):
             ctx.resynth(xx, off, m, fo, mode, exact=exact)
+        ctx.resynth(xx, off, m, fo, mode, exact=False, latency=True)
     ctx.subband(x[:3000], [0, 3000], exact=True)
     ctx.subband(x[:3000], [0, 3000], exact=False)
     ctx.ibm(clean[:3000], noise[:3000], [0, 3000])
