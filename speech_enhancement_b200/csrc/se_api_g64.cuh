@@ -92,14 +92,33 @@ int se_resynth_batch(se_ctx *ctx, const int16_t *samples, const int64_t *offsets
     void *d_out = nullptr;
     SE_TRY(upload_offsets(ctx, kSlotOffsets, offsets, n_utts + 1, &a.offsets));
     SE_TRY(stage_in(ctx, kSlotIn, samples, sizeof(int16_t) * total, mem, &d_in));
-    SE_TRY(stage_in(ctx, kSlotIn2, mask, sizeof(float) * 64 * frames, mem, &d_mask));
+    // The mask (1.6x the bytes of the samples) is only read by the reversed pass: host callers get it uploaded on the
+    // context's upload stream while the forward pass runs.
+    cudaEvent_t mask_ready = nullptr;
+    if (mem == SE_MEM_HOST && frames > 0) {
+        void *dm = nullptr;
+        SE_TRY(ensure_stage(ctx, kSlotIn2, sizeof(float) * 64 * frames, &dm));
+        if (ctx->up_events.empty()) {
+            cudaEvent_t e;
+            SE_CUDA(cudaEventCreateWithFlags(&e, cudaEventDisableTiming));
+            ctx->up_events.push_back(e);
+        }
+        SE_CUDA(cudaEventRecord(ctx->cur->done, ctx->cur->stream));         // the samples go up first, undisturbed
+        SE_CUDA(cudaStreamWaitEvent(ctx->up_stream, ctx->cur->done, 0));
+        SE_CUDA(cudaMemcpyAsync(dm, mask, sizeof(float) * 64 * frames, cudaMemcpyHostToDevice, ctx->up_stream));
+        SE_CUDA(cudaEventRecord(ctx->up_events[0], ctx->up_stream));
+        mask_ready = ctx->up_events[0];
+        d_mask = dm;
+    } else {
+        SE_TRY(stage_in(ctx, kSlotIn2, mask, sizeof(float) * 64 * frames, mem, &d_mask));
+    }
     const uint64_t out_elem = (flags & SE_FLAG_OUT_F32) ? sizeof(float) : sizeof(int16_t);
     SE_TRY(stage_out(ctx, kSlotOut, out, out_elem * total, mem, false, &d_out));
     a.samples = (const int16_t *)d_in;
     a.utt_begin = 0;
     a.utt_count = n_utts;
     a.flags = flags;
-    SE_TRY(launch_resynth(ctx, a, offsets, (const float *)d_mask, frame_offsets, mode, (int16_t *)d_out));
+    SE_TRY(launch_resynth(ctx, a, offsets, (const float *)d_mask, frame_offsets, mode, (int16_t *)d_out, mask_ready));
     SE_TRY(stage_out_copy(ctx, out, d_out, out_elem * total, mem));
     return leave(ctx, mem);
 }

@@ -73,7 +73,7 @@ static void launch_bwd(se_ctx *ctx, int mode, int count, const float *Y, const G
 // h_offsets / h_frame_offsets: host copies (work items are planned on the host and grouped against the
 // scratch limit: one group = one forward + one reversed launch).
 int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, const float *mask,
-                   const int64_t *h_frame_offsets, int mode, int16_t *out)
+                   const int64_t *h_frame_offsets, int mode, int16_t *out, cudaEvent_t mask_ready)
 {
     float *out_f = (a.flags & SE_FLAG_OUT_F32) ? reinterpret_cast<float *>(out) : nullptr;
     const bool exact = (a.flags & SE_FLAG_EXACT) != 0;
@@ -97,6 +97,7 @@ int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, co
         if (exact) gt_fwd_kernel<true><<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
         else gt_fwd_fast_kernel<<<count, 64, 0, ctx->cur->stream>>>(a.samples, it, Y);
         prof_end(ctx, SE_K_GT_FWD);
+        if (mask_ready) SE_CUDA(cudaStreamWaitEvent(ctx->cur->stream, mask_ready, 0));   // the mask upload ran beside the forward pass
         prof_begin(ctx, SE_K_GT_BWD);
         if (exact) launch_bwd<true>(ctx, mode, count, Y, it, mask, out, out_f);
         else if (mode == SE_RESYNTH_IBM) gt_bwd_fast_kernel<SE_RESYNTH_IBM><<<count, 64, 0, ctx->cur->stream>>>(Y, it, mask, out, out_f);

@@ -211,8 +211,9 @@ struct G64Launch {
 };
 int launch_subband(se_ctx *ctx, const G64Launch &a, int16_t *out);
 int launch_ibm(se_ctx *ctx, const G64Launch &a, float *irm, uint64_t *bits, const int64_t *frame_offsets);
+// mask_ready (optional): recorded on another stream once `mask` is on the device; only the reversed pass waits for it
 int launch_resynth(se_ctx *ctx, const G64Launch &a, const int64_t *h_offsets, const float *mask,
-                   const int64_t *h_frame_offsets, int mode, int16_t *out);
+                   const int64_t *h_frame_offsets, int mode, int16_t *out, cudaEvent_t mask_ready = nullptr);
 int launch_gammatone(se_ctx *ctx, const float *in, float *out, const int32_t *channel, int64_t n, int count,
                      int flags);
 int launch_gammatone_coef(se_ctx *ctx, const float *in, float *out, const float *coef, int64_t n, int count, int flags);
