@@ -59,14 +59,6 @@ static int upload_ns(se_ctx *ctx, const NsTables &h, NsDevTables &d, int bank_ro
         }
     }
     if ((rc = upload(ctx, bankT.data(), bankT.size(), &d.bankT))) return rc;
-    d.bankR = nullptr;
-    if (bank_rows == 128) {
-        std::vector<float> bankR((size_t)32 * 32 * 4, 0.0f);
-        for (int k = 0; k < 32; k++)
-            for (int j = 0; j < kMel; j++)
-                for (int r = 0; r < 4; r++) bankR[((size_t)k * 32 + j) * 4 + r] = h.bank[(size_t)j * h.bank_w + 4 * k + r];
-        if ((rc = upload(ctx, bankR.data(), bankR.size(), &d.bankR))) return rc;
-    }
     if ((rc = upload(ctx, st, 32, &d.bank_start))) return rc;
     if ((rc = upload(ctx, ln, 32, &d.bank_len))) return rc;
     std::vector<float> idctT(25 * 16, 0.0f);

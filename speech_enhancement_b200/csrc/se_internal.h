@@ -27,7 +27,6 @@ struct NsDevTables {
     const float *sig_window;   // [frame]
     const float *fir_window;   // [9]  : ir_window[8..16]  (DoFilterWindowing uses the upper half only)
     const float *bankT;        // P8: [BANK_MAXLEN][32] transposed, zero padded; P16: float4 [25][32] (lane's 4 bins)
-    const float *bankR;        // P16: float4 [32][32]: (k, band) = the band's weights for bins 4k..4k+3 (bands 25..31: 0)
     const int *bank_start;     // [32]
     const int *bank_len;       // [32]
     const float *idctT;        // [25][16] : idctT[f*16+t] = idct[t][f], t<9

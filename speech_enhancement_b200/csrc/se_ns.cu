@@ -101,9 +101,7 @@ template <int PROF> struct __align__(16) BlockMem {
     using P = Prof<PROF>;
     float win[P::FL];
     float2 twh[132];
-#if defined(SE_NS_BANK_T) && !defined(SE_NS_EXACT)
-    float bankT[PROF == 16 ? 32 * 32 * 4 : P::BANKROWS * 32];   // P16: NsDevTables::bankR (band-per-lane form)
-#elif defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
+#if defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
     float bankT[PROF == 16 ? 4 : P::BANKROWS * 32];             // P16: the Gamma bank lives in tensor memory (se_tmem.cuh)
 #else
     float bankT[PROF == 16 ? 25 * 32 * 4 : P::BANKROWS * 32];

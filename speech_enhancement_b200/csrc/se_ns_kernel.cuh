@@ -33,12 +33,7 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
     const int tid = threadIdx.x, nt = blockDim.x;
     for (int i = tid; i < P::FL; i += nt) bm.win[i] = tb.sig_window[i];
     for (int i = tid; i < 129; i += nt) bm.twh[i] = reinterpret_cast<const float2 *>(tb.tw_half)[i];
-#if defined(SE_NS_BANK_T) && !defined(SE_NS_EXACT)
-    const float *bank_src = PROF == 16 ? tb.bankR : tb.bankT;
-#else
-    const float *bank_src = tb.bankT;
-#endif
-    for (int i = tid; i < (int)(sizeof(bm.bankT) / sizeof(float)); i += nt) bm.bankT[i] = bank_src[i];
+    for (int i = tid; i < (int)(sizeof(bm.bankT) / sizeof(float)); i += nt) bm.bankT[i] = tb.bankT[i];
     for (int i = tid; i < 32; i += nt) { bm.bank_start[i] = tb.bank_start[i]; bm.bank_len[i] = tb.bank_len[i]; }
 #ifdef SE_NS_EXACT
     for (int i = tid; i < 25 * 16; i += nt) bm.idctT[i] = tb.idctT[i];
@@ -438,24 +433,9 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                 }
             } else {
                 if (a.out_f32) {
-#ifdef SE_NS_OUT_STAGED
-                    // through the (dead) PSD scratch so that the global stores are whole 128-byte lines
-                    float *so = wm.raw;
-#pragma unroll
-                    for (int t = 0; t < P::CH; t++)
-                        if (i0 + t < P::S) so[i0 + t] = produced ? o[t] : 0.0f;
-                    __syncwarp();
-                    float *dst = a.out_f32 + obase;
-                    if ((reinterpret_cast<uintptr_t>(dst) & 15) == 0) {
-                        for (int i = lane; i < P::S / 4; i += 32) reinterpret_cast<float4 *>(dst)[i] = reinterpret_cast<const float4 *>(so)[i];
-                    } else {
-                        for (int i = lane; i < P::S; i += 32) dst[i] = so[i];
-                    }
-#else
 #pragma unroll
                     for (int t = 0; t < P::CH; t++)
                         if (i0 + t < P::S) a.out_f32[obase + i0 + t] = produced ? o[t] : 0.0f;
-#endif
                 }
                 if (a.flags && lane == 0) {
                     int32_t *f = a.flags + blk0 + b;

@@ -386,25 +386,6 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
 #pragma unroll
         for (int i = 0; i < kMelTaps; i++) mw = fmaf(wm.W[br.mel_st + i], SE_BR_MEL(bm, br, i, lane), mw);
     } else {
-#ifdef SE_NS_BANK_T
-        // dense 25 x 128, band per lane: the 128 gains go through shared memory (the PSD scratch is dead here) and lane
-        // j < 25 accumulates its own band over all of them -- a broadcast LDS.128 of four gains, a conflict-free LDS.128
-        // of the band's four weights, 4 FMAs -- with no cross-lane reduction at all
-        __syncwarp();
-#pragma unroll
-        for (int r = 0; r < 4; r++) wm.raw[lane + 32 * r] = W[r];
-        __syncwarp();
-        const float4 *bank4 = reinterpret_cast<const float4 *>(bm.bankT) + lane;
-        const float4 *w4 = reinterpret_cast<const float4 *>(wm.raw);
-        float a0 = 0.0f, a1 = 0.0f, a2 = 0.0f, a3 = 0.0f;
-#pragma unroll
-        for (int k = 0; k < 32; k++) {
-            const float4 c = bank4[k * 32];
-            const float4 w = w4[k];
-            a0 = fmaf(w.x, c.x, a0); a1 = fmaf(w.y, c.y, a1); a2 = fmaf(w.z, c.z, a2); a3 = fmaf(w.w, c.w, a3);
-        }
-        mw = (a0 + a1) + (a2 + a3);
-#else
         // dense 25 x 128: every lane multiplies its own 4 bins (registers) into 25 partial sums, then a
         // butterfly reduce-scatter leaves band j's total on lane j (31 shuffles instead of 25 x 5)
         float p[32];
@@ -447,7 +428,6 @@ __device__ __forceinline__ void ns_stage_rest(WarpMem<PROF> &wm, const BlockMem<
             }
         }
         mw = p[0];
-#endif
     }
     if (lane >= kMel) mw = 0.0f;
 
