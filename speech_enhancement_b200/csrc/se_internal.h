@@ -127,7 +127,10 @@ struct GtDevTables {
 // One in-order pipeline lane: a stream with its own staging buffers and work-queue counter.  Lane 0
 // is the context's visible stream (se_ctx_set_stream); lanes 1.. exist so that SE_MEM_HOST calls can
 // overlap H2D, kernels and D2H of successive utterance chunks.
-constexpr int kLanes = 3;
+#ifndef SE_LANES
+#define SE_LANES 3
+#endif
+constexpr int kLanes = SE_LANES;
 struct se_lane {
     cudaStream_t stream;
     int *d_work_counter;
