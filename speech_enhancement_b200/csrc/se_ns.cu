@@ -101,10 +101,14 @@ template <int PROF> struct __align__(16) BlockMem {
     using P = Prof<PROF>;
     float win[P::FL];
     float2 twh[132];
-#if defined(SE_NS_BANK_TMEM) && !defined(SE_NS_EXACT)
-    float bankT[PROF == 16 ? 4 : P::BANKROWS * 32];             // P16: the Gamma bank lives in tensor memory (se_tmem.cuh)
-#else
+    // the 8 kHz profile's sparse banks are read once, from global memory, into per-lane taps (lane_br): only the exact
+    // build walks them in shared memory
+#ifdef SE_NS_EXACT
     float bankT[PROF == 16 ? 25 * 32 * 4 : P::BANKROWS * 32];
+#elif defined(SE_NS_BANK_TMEM)
+    float bankT[4];                                              // P16: the Gamma bank lives in tensor memory (se_tmem.cuh)
+#else
+    float bankT[PROF == 16 ? 25 * 32 * 4 : 4];
 #endif
     uint32_t tmem_base;               // P16 with SE_NS_BANK_TMEM: this CTA's tensor-memory allocation (kBankTmemCols columns)
     uint32_t tmem_pad[3];
@@ -115,7 +119,11 @@ template <int PROF> struct __align__(16) BlockMem {
 #endif
     // CompCeps tables (P8 only)
     float ham[P::CEPS ? 200 : 4];
+#ifdef SE_NS_EXACT
     float triT[P::CEPS ? kTriRows * 32 : 4];
+#else
+    float triT[4];
+#endif
     int tri_start[32], tri_len[32];
     float dctT[P::CEPS ? 23 * 16 : 4];
 #ifdef SE_NS_CONST_SMEM

@@ -42,7 +42,7 @@ template <int PROF> __device__ __forceinline__ void load_block_tables(BlockMem<P
 #endif
     if constexpr (P::CEPS) {
         for (int i = tid; i < 200; i += nt) bm.ham[i] = cc.hamming[i];
-        for (int i = tid; i < kTriRows * 32; i += nt) bm.triT[i] = cc.triT[i];
+        for (int i = tid; i < (int)(sizeof(bm.triT) / sizeof(float)); i += nt) bm.triT[i] = cc.triT[i];
         for (int i = tid; i < 32; i += nt) { bm.tri_start[i] = cc.tri_start[i]; bm.tri_len[i] = cc.tri_len[i]; }
         for (int i = tid; i < 23 * 16; i += nt) bm.dctT[i] = cc.dctT[i];
     }
@@ -88,7 +88,7 @@ ns_stream_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     IdctRegs ic;
     idct_regs_init(ic, tb.idctT, tb.fir_window, lane);
     BankRegs br;
-    if constexpr (PROF == 8) bank_regs_init(br, bm, lane);
+    if constexpr (PROF == 8) bank_regs_init(br, tb, cc, lane);
     else { br.mel_st = br.tri_st = 0; }
 #ifdef SE_NS_CONST_SMEM
     if (warp == 0) {
@@ -641,7 +641,7 @@ __global__ void __launch_bounds__(128) comp_ceps_kernel(const float *frames, flo
     FftTw tw;
     fft_tw_init(tw, lane);
     BankRegs br;
-    bank_regs_init(br, bm, lane);
+    bank_regs_init(br, tb, cc, lane);
 #ifdef SE_NS_CONST_SMEM
     {
         IdctRegs ic0 = {};

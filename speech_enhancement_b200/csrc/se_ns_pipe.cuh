@@ -119,7 +119,7 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
     IdctRegs ic;
     idct_regs_init(ic, tb.idctT, tb.fir_window, lane);
     BankRegs br;
-    if constexpr (PROF == 8) bank_regs_init(br, bm, lane);
+    if constexpr (PROF == 8) bank_regs_init(br, tb, cc, lane);
     else { br.mel_st = br.tri_st = 0; }
 #ifdef SE_NS_CONST_SMEM
     if (warp == 0) {

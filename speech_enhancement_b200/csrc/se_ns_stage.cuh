@@ -231,17 +231,18 @@ struct BankRegs {
     float mel[kMelTaps], tri[kTriTaps];
 };
 
-__device__ __forceinline__ void bank_regs_init(BankRegs &br, const BlockMem<8> &bm, int lane)
+__device__ __forceinline__ void bank_regs_init(BankRegs &br, const NsDevTables &tb, const CcDevTables &cc, int lane)
 {
-    br.mel_st = bm.bank_start[lane];
-    const int ml = bm.bank_len[lane];
+    // once per kernel, straight from the global tables (tb.bankT: [tap][32 bands], cc.triT likewise)
+    br.mel_st = tb.bank_start[lane];
+    const int ml = tb.bank_len[lane];
 #pragma unroll
-    for (int i = 0; i < kMelTaps; i++) br.mel[i] = (i < ml) ? bm.bankT[i * 32 + lane] : 0.0f;
+    for (int i = 0; i < kMelTaps; i++) br.mel[i] = (i < ml) ? tb.bankT[i * 32 + lane] : 0.0f;
     const int band = lane < 23 ? lane : lane - 9, t0 = lane < 23 ? 0 : kTriTaps;
-    br.tri_st = bm.tri_start[band] + t0;
-    const int tl = bm.tri_len[band];
+    br.tri_st = cc.tri_start[band] + t0;
+    const int tl = cc.tri_len[band];
 #pragma unroll
-    for (int i = 0; i < kTriTaps; i++) br.tri[i] = (t0 + i < tl) ? bm.triT[(t0 + i) * 32 + band] : 0.0f;
+    for (int i = 0; i < kTriTaps; i++) br.tri[i] = (t0 + i < tl) ? cc.triT[(t0 + i) * 32 + band] : 0.0f;
 }
 #ifdef SE_NS_CONST_SMEM
 __device__ __forceinline__ void bank_regs_store(float *tab /*[22][32]*/, const BankRegs &br, int lane)
