@@ -255,6 +255,12 @@ def roofline(workload, kernel, alg_bytes, kernel_ms, sm_mhz, sm_count=148):
         slots = sm_count * 4 * sm_mhz * 1e6 * kernel_ms * 1e-3
         r["issue_bound"] = {"warp_instructions_per_launch": t["inst_executed"], "issue_slots_in_launch": slots,
                             "frac": t["inst_executed"] / slots}
+    if t and sm_mhz and t.get("shared_wavefronts"):
+        # the resource that actually binds the NoiseSup kernels: LDS / STS / SHFL wavefronts (ncu) against
+        # one wavefront per SM and clock during the live-timed launch
+        cycles = sm_count * sm_mhz * 1e6 * kernel_ms * 1e-3
+        r["shared_memory_pipe"] = {"wavefronts_per_launch": t["shared_wavefronts"], "wavefront_slots_in_launch": cycles,
+                                   "frac": t["shared_wavefronts"] / cycles}
     return r
 
 
