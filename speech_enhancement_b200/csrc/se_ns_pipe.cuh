@@ -1,4 +1,4 @@
-// Pipelined NoiseSup kernel for SMALL batches: one CTA per utterance, the work of one block spread over 5-6 warps.
+// Pipelined NoiseSup kernel for SMALL batches: one CTA per utterance, the work of one block spread over 5-8 warps.
 // Included by se_ns.cu (fast arithmetic only).
 //
 // The batch kernel (se_ns_kernel.cuh) gives an utterance one warp, so a lone 10 s utterance is 1 000 strictly serial
@@ -10,11 +10,13 @@
 //   warp 1  stage-0 recursion: VAD, FilterCalc, mel / Gamma bank, denoised-energy history, IDCT   -> 9 filter taps
 //   warp 2  17-tap FIR of stage 0 over its own ring1 -> ring2, window + FFT + PSD of stage 1
 //   warp 3  stage-1 recursion: noise update, FilterCalc, bank, gain factorisation, IDCT           -> 9 filter taps
-//   warp 4  frame-dropping statistics of stage 0, FIR of stage 1 over its own ring2, DC filter, every output
-//   warp 5  (8 kHz profile) CompCeps on the denoised stream
+//   warp 4  FIR of stage 1 over its own ring2, DC filter, every output (16 kHz profile: also the statistics of warp 7)
+//   warp 5  (8 kHz profile) CompCeps, first half: ring3, pre-emphasis, Hamming, FFT, power spectrum
+//   warp 6  (8 kHz profile) CompCeps, second half: mel triangles, log, DCT, the cepstral row
+//   warp 7  (8 kHz profile) frame-dropping statistics of stage 0 (three reductions + the double-precision SpeechQ recursions)
 //
 // Every warp keeps PRIVATE copies of what it reads repeatedly (warps 0 and 2 each hold ring1, warps 2 and 4 each ring2),
-// so the only shared data are six small FIFOs of kPipeDepth entries in shared memory, handed over with mbarriers (full /
+// so the only shared data are six to eight small FIFOs of kPipeDepth entries in shared memory, handed over with mbarriers (full /
 // empty per slot).  Every role consumes and produces exactly one entry per input block, in order.  The arithmetic is the
 // batch kernel's own device functions (frame_psd, ns_stage_rest, fd_stats, apply_fir, dc_offset, comp_ceps), so the
 // outputs are bit-identical to the batch kernel's; the launcher picks this kernel when the batch is too small to fill
@@ -27,15 +29,17 @@ namespace SE_NSPACE {
 #define SE_PIPE_DEPTH 4
 #endif
 constexpr int kPipeDepth = SE_PIPE_DEPTH;      // entries per FIFO (a power of two)
-template <int PROF> struct PipeWarps { static constexpr int value = PROF == 8 ? 6 : 5; };
-constexpr int kPipeFifos = 6;
+template <int PROF> struct PipeWarps { static constexpr int value = PROF == 8 ? 8 : 5; };
+constexpr int kPipeFifos = 8;
 // FIFO index: producer -> consumer(s)
 enum { kFA = 0,   // warp 0 -> 1, 2 : input block, stage-0 PSD, frame energy
-       kFB = 1,   // warp 1 -> 2, 4 : stage-0 filter taps, lane partials for the statistics, VAD state
+       kFB = 1,   // warp 1 -> 2 and 7 (8 kHz) / 4 (16 kHz): stage-0 filter taps, lane partials for the statistics, VAD state
        kFC = 2,   // warp 2 -> 3    : stage-1 PSD, denoised-energy history
-       kFE = 3,   // warp 2 -> 4    : stage-0 output block
+       kFE = 3,   // warp 2 -> 4    : stage-0 output block, VAD state
        kFD = 4,   // warp 3 -> 4    : stage-1 filter taps
-       kFF = 5 }; // warp 4 -> 5    : denoised block (8 kHz profile)
+       kFF = 5,   // warp 4 -> 5    : denoised block (8 kHz profile)
+       kFG = 6,   // warp 7 -> 4    : frame-dropping flags (8 kHz profile)
+       kFH = 7 }; // warp 5 -> 6    : power spectrum and frame energy (8 kHz profile)
 
 template <int PROF> struct __align__(16) PipeMem {
     using P = Prof<PROF>;
@@ -46,15 +50,19 @@ template <int PROF> struct __align__(16) PipeMem {
         float den_en0, den_en1, den_en2, pad3;
     };
     struct __align__(16) EntC { float psd[P::NB * 32]; int run, pad0; float den_en0, den_en1, den_en2, pad1, pad2, pad3; };
-    struct __align__(16) EntE { float x[P::S]; int ran0, pad0, pad1, pad2; };
+    struct __align__(16) EntE { float x[P::S]; int process, ran0, nb_speech, nb_frame0, flag_vad, pad0, pad1, pad2; };
     struct __align__(16) EntD { float h[12]; int run, pad0, pad1, pad2; };
     struct __align__(16) EntF { float x[P::S]; int produced, nb_out2, pad0, pad1; };
+    struct __align__(16) EntG { int var, spec, mel, pad; };
+    struct __align__(16) EntH { float pw[132]; float e; int compute, count, m; };
     EntA a[kPipeDepth];
     EntB b[kPipeDepth];
     EntC c[kPipeDepth];
     EntE e[kPipeDepth];
     EntD d[kPipeDepth];
     EntF f[kPipeDepth];
+    EntG g[PROF == 8 ? kPipeDepth : 1];
+    EntH h[PROF == 8 ? kPipeDepth : 1];
     unsigned long long full[kPipeFifos][kPipeDepth], empty[kPipeFifos][kPipeDepth];
 };
 
@@ -104,7 +112,7 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 
     load_block_tables<PROF>(bm, tb, cc);
     if (threadIdx.x == 0) {
-        const int consumers[kPipeFifos] = {2, 2, 1, 1, 1, 1};
+        const int consumers[kPipeFifos] = {2, 2, 1, 1, 1, 1, 1, 1};
         for (int f = 0; f < kPipeFifos; f++)
             for (int k = 0; k < kPipeDepth; k++) {
                 se_bulk::mbar_init(&pm.full[f][k], 1);
@@ -286,6 +294,7 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
 #pragma unroll
                 for (int t = 0; t < 9; t++) h[t] = eb.h[t];
                 const float de0 = eb.den_en0, de1 = eb.den_en1, de2 = eb.den_en2;
+                const int m_process = eb.process, m_nbs = eb.nb_speech, m_nbf = eb.nb_frame0, m_vad = eb.flag_vad;
                 pipe_signal(pm.empty[kFB], k, lane);
                 pipe_wait_empty(pm.empty[kFE], k, wait_cycles);
                 typename PipeMem<PROF>::EntE &ee = pm.e[k & SL];
@@ -298,7 +307,10 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         if (i0 + t < P::S) { ring_store<PROF>(ring2, slot, i0 + t, o[t]); ee.x[i0 + t] = o[t]; }
                     s.nb_in2++;
                 }
-                if (lane == 0) ee.ran0 = ran0 ? 1 : 0;
+                if (lane == 0) {
+                    ee.process = m_process; ee.ran0 = ran0 ? 1 : 0;
+                    ee.nb_speech = m_nbs; ee.nb_frame0 = m_nbf; ee.flag_vad = m_vad;
+                }
                 pipe_signal(pm.full[kFE], k, lane);            // (its __syncwarp also orders the ring2 stores before the PSD)
                 const bool run = ran0 && (s.nb_in2 - s.nb_out2 > 2);
                 pipe_wait_empty(pm.empty[kFC], k, wait_cycles);
@@ -350,16 +362,20 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             // ---- frame-dropping statistics, stage-1 FIR over a private ring2, DC filter, outputs -----------------------------
             for (int b = 0; b < nblk; b++) {
                 const unsigned k = kbase + b;
-                pipe_wait_full(pm.full[kFB], k, wait_cycles);
-                const typename PipeMem<PROF>::EntB &eb = pm.b[k & SL];
-                const bool process = eb.process != 0, ran0 = eb.ran0 != 0;
-                s.nb_speech = eb.nb_speech; s.nb_frame0 = eb.nb_frame0; s.flag_vad = eb.flag_vad;
-                const float wsum = eb.wsum[lane], wsq = eb.wsq[lane], mw = eb.mw[lane];
-                pipe_signal(pm.empty[kFB], k, lane);
                 StageFlags fl = {0, 0, 0};
-                if (ran0) fd_stats<PROF>(wm, s, wsum, wsq, mw, fl);
+                if constexpr (PROF != 8) {                     // 16 kHz profile: the statistics run here (8 kHz: warp 7)
+                    pipe_wait_full(pm.full[kFB], k, wait_cycles);
+                    const typename PipeMem<PROF>::EntB &eb = pm.b[k & SL];
+                    const bool r0 = eb.ran0 != 0;
+                    s.nb_frame0 = eb.nb_frame0;
+                    const float wsum = eb.wsum[lane], wsq = eb.wsq[lane], mw = eb.mw[lane];
+                    pipe_signal(pm.empty[kFB], k, lane);
+                    if (r0) fd_stats<PROF>(wm, s, wsum, wsq, mw, fl);
+                }
                 pipe_wait_full(pm.full[kFE], k, wait_cycles);
                 const typename PipeMem<PROF>::EntE &ee = pm.e[k & SL];
+                const bool process = ee.process != 0, ran0 = ee.ran0 != 0;
+                s.nb_speech = ee.nb_speech; s.nb_frame0 = ee.nb_frame0; s.flag_vad = ee.flag_vad;
                 if (ran0) {
                     const int slot = s.nb_in2 & 3, i0 = lane * P::CH;
 #pragma unroll
@@ -411,6 +427,12 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                     }
                     if (a.den_f32)
                         for (int i = lane; i < P::S; i += 32) a.den_f32[obase + i] = stage_out[i];
+                    {                                          // this block's frame-dropping flags, from warp 7
+                        pipe_wait_full(pm.full[kFG], k, wait_cycles);
+                        const typename PipeMem<PROF>::EntG &eg = pm.g[k & SL];
+                        fl.var = eg.var; fl.spec = eg.spec; fl.mel = eg.mel;
+                        pipe_signal(pm.empty[kFG], k, lane);
+                    }
                     if (a.vad_trace && lane == 0) {
                         unsigned char t = 128;
                         if (process)
@@ -445,8 +467,8 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
             } else if (a.out_f32) {
                 for (int64_t i = (int64_t)nblk * P::S + lane; i < n; i += 32) a.out_f32[off0 + i] = 0.0f;
             }
-        } else {
-            // ---- CompCeps on the third denoised shift onwards (8 kHz profile) --------------------------------------------
+        } else if (warp == 5) {
+            // ---- CompCeps, first half (8 kHz profile): ring3, pre-emphasis, Hamming, FFT, power spectrum ------------------------
             if constexpr (PROF == 8) {
                 for (int b = 0; b < nblk; b++) {
                     const unsigned k = kbase + b;
@@ -459,13 +481,68 @@ ns_pipe_kernel(const NsLaunch a, const NsDevTables tb, const CcDevTables cc)
                         for (int i = lane; i < P::S; i += 32) wm.ring3[nb3 + i] = ef.x[i];
                     }
                     pipe_signal(pm.empty[kFF], k, lane);
-                    if (produced && a.ceps && nb_out2 >= 3) {
-                        const int m = nb_out2 - 3;
-                        if (m < ceps_cap) comp_ceps(wm, bm, tw, br, lane, (m & 3) * P::S, a.ceps + (ceps0 + m) * 14);
-                        s.n_ceps = m + 1;
+                    const bool count = produced && a.ceps && nb_out2 >= 3;       // third denoised shift onwards
+                    const int m = nb_out2 - 3;
+                    const bool compute = count && m < ceps_cap;
+                    float e = 0.0f, d0, d1, d2;
+                    if (compute) {
+                        const float *d = wm.ring3;
+                        const int base = (m & 3) * P::S;
+                        comp_ceps_front(wm, bm, tw, lane, [&](int i) { return d[wrap<P::RB>(base + i)]; }, e, d0, d1, d2);
                     }
+                    pipe_wait_empty(pm.empty[kFH], k, wait_cycles);
+                    typename PipeMem<PROF>::EntH &eh = pm.h[k & SL];
+                    if (compute) {
+#pragma unroll
+                        for (int r = 0; r < 4; r++) eh.pw[lane + 32 * r] = wm.W[lane + 32 * r];
+                        if (lane == 0) eh.pw[128] = wm.W[128];
+                    }
+                    if (lane == 0) { eh.e = e; eh.compute = compute ? 1 : 0; eh.count = count ? 1 : 0; eh.m = m; }
+                    pipe_signal(pm.full[kFH], k, lane);
+                }
+            }
+        } else if (warp == 6) {
+            // ---- CompCeps, second half (8 kHz profile): mel triangles, log, DCT ------------------------------------------------
+            if constexpr (PROF == 8) {
+                for (int b = 0; b < nblk; b++) {
+                    const unsigned k = kbase + b;
+                    pipe_wait_full(pm.full[kFH], k, wait_cycles);
+                    const typename PipeMem<PROF>::EntH &eh = pm.h[k & SL];
+                    const bool compute = eh.compute != 0, count = eh.count != 0;
+                    const int m = eh.m;
+                    const float e = eh.e;
+                    if (compute) {
+#pragma unroll
+                        for (int r = 0; r < 4; r++) wm.W[lane + 32 * r] = eh.pw[lane + 32 * r];
+                        if (lane == 0) wm.W[128] = eh.pw[128];
+                    }
+                    pipe_signal(pm.empty[kFH], k, lane);       // (its __syncwarp orders the wm.W stores before the triangles)
+                    if (compute) {
+                        const float out = comp_ceps_back(wm, bm, br, lane, e, 0.0f, 0.0f, 0.0f);
+                        if (lane < 14) a.ceps[(ceps0 + m) * 14 + lane] = out;
+                    }
+                    if (count) s.n_ceps = m + 1;
                 }
                 if (lane == 0 && a.n_ceps) a.n_ceps[u] = s.n_ceps;
+            }
+        } else {
+            // ---- frame-dropping statistics of stage 0 (8 kHz profile) -----------------------------------------------------------
+            if constexpr (PROF == 8) {
+                for (int b = 0; b < nblk; b++) {
+                    const unsigned k = kbase + b;
+                    pipe_wait_full(pm.full[kFB], k, wait_cycles);
+                    const typename PipeMem<PROF>::EntB &eb = pm.b[k & SL];
+                    const bool ran0 = eb.ran0 != 0;
+                    s.nb_frame0 = eb.nb_frame0;
+                    const float wsum = eb.wsum[lane], wsq = eb.wsq[lane], mw = eb.mw[lane];
+                    pipe_signal(pm.empty[kFB], k, lane);
+                    StageFlags fl = {0, 0, 0};
+                    if (ran0) fd_stats<PROF>(wm, s, wsum, wsq, mw, fl);
+                    pipe_wait_empty(pm.empty[kFG], k, wait_cycles);
+                    typename PipeMem<PROF>::EntG &eg = pm.g[k & SL];
+                    if (lane == 0) { eg.var = fl.var; eg.spec = fl.spec; eg.mel = fl.mel; }
+                    pipe_signal(pm.full[kFG], k, lane);
+                }
             }
         }
         kbase += (unsigned)nblk;

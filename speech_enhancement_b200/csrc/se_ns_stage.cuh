@@ -576,24 +576,25 @@ template <int PROF> __device__ __forceinline__ void dc_offset(float (&o)[Prof<PR
 // spectrum shape + 30 % spectrally-subtracted HP energies, both delayed 3 frames) after the 23 mel bands, DCT over
 // 26 bands, HP energy added to logE.  dct_t: [bands][16] transposed DCT; code9 / hp3: lane-distributed oldest
 // entries of the code and HP-band delay lines (lanes 0..8 / 0..2).
+// First half (the pipelined kernel runs the halves on two warps): pre-emphasis, Hamming, FFT, power spectrum into wm.W[0..128];
+// `e` = frame energy, d0..d2 = the 16 kHz mode's decoding-band sums (lane partials).
 template <bool HP16 = false, class LD>
-__device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, LD ld,
-                                                const float *dct26T = nullptr, float code9 = 0.0f, float hp3 = 0.0f)
+__device__ __forceinline__ void comp_ceps_front(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, int lane, LD ld,
+                                                float &e, float &d0, float &d1, float &d2)
 {
-    constexpr int NBAND = HP16 ? 26 : 23;
-    float e = 0.0f;
+    e = 0.0f;
     float2 v[1][4];
 #pragma unroll
     for (int j = 0; j < 4; j++) {
         const int i2 = 2 * (lane + 32 * j);
         v[0][j] = make_float2(0.0f, 0.0f);
         if (i2 < 200) {
-            const float dm1 = ld(i2 - 1);
-            const float d0 = ld(i2);
-            const float d1 = ld(i2 + 1);
-            e += d0 * d0 + d1 * d1;
+            const float sm1 = ld(i2 - 1);
+            const float s0 = ld(i2);
+            const float s1 = ld(i2 + 1);
+            e += s0 * s0 + s1 * s1;
             // pre-emphasis 0.9 (:427-429) and Hamming (:434)
-            v[0][j] = make_float2((d0 - 0.9f * dm1) * bm.ham[i2], (d1 - 0.9f * d0) * bm.ham[i2 + 1]);
+            v[0][j] = make_float2((s0 - 0.9f * sm1) * bm.ham[i2], (s1 - 0.9f * s0) * bm.ham[i2 + 1]);
         }
     }
     e = warp_sum(e);
@@ -604,7 +605,7 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
     }
     __syncwarp();
     // power spectrum (:451-459), 129 bins, into wm.W
-    float d0 = 0.0f, d1 = 0.0f, d2 = 0.0f;     // HP16: GetBandsForDecoding16k, bins 66..76 | 78..96 | 98..128
+    d0 = d1 = d2 = 0.0f;                       // HP16: GetBandsForDecoding16k, bins 66..76 | 78..96 | 98..128
 #pragma unroll
     for (int r = 0; r < 4; r++) {
         const int k = lane + 32 * r;
@@ -623,6 +624,15 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
         if constexpr (HP16) d2 += xk.x * xk.x;
     }
     __syncwarp();
+}
+
+// Second half: mel triangles over wm.W, log, DCT; returns this lane's coefficient.
+template <bool HP16 = false>
+__device__ __forceinline__ float comp_ceps_back(WarpMem<8> &wm, const BlockMem<8> &bm, const BankRegs &br, int lane, float e,
+                                               float d0, float d1, float d2, const float *dct26T = nullptr, float code9 = 0.0f,
+                                               float hp3 = 0.0f)
+{
+    constexpr int NBAND = HP16 ? 26 : 23;
     // 23 mel triangles (DoMelFB, MelProc.c:82-104), ln with floor (:509-513)
     float fb = 0.0f;
 #pragma unroll
@@ -679,6 +689,15 @@ __device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8
     }
     __syncwarp();
     return out;
+}
+
+template <bool HP16 = false, class LD>
+__device__ __forceinline__ float comp_ceps_core(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, LD ld,
+                                                const float *dct26T = nullptr, float code9 = 0.0f, float hp3 = 0.0f)
+{
+    float e, d0, d1, d2;
+    comp_ceps_front<HP16>(wm, bm, tw, lane, ld, e, d0, d1, d2);
+    return comp_ceps_back<HP16>(wm, bm, br, lane, e, d0, d1, d2, dct26T, code9, hp3);
 }
 
 __device__ __forceinline__ void comp_ceps(WarpMem<8> &wm, const BlockMem<8> &bm, const FftTw &tw, const BankRegs &br, int lane, int base,

@@ -39,7 +39,7 @@ with api.Context(0) as ctx:
             ctx.sync()
             L.se_debug_pipe_stats(buf, 1)
             v = np.array(list(buf), np.float64).reshape(8, 4)
-            for w in range(6 if prof == 8 else 5):
+            for w in range(8 if prof == 8 else 5):
                 tot = v[w, 2]
                 print("P%d warp %d: total %.0f cycles, waiting for input %.1f %%, for output room %.1f %%, busy %.1f %% (%.0f cycles per block)"
                       % (prof, w, tot, 100 * v[w, 0] / tot, 100 * v[w, 1] / tot, 100 * (tot - v[w, 0] - v[w, 1]) / tot,
