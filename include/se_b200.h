@@ -75,9 +75,9 @@ int  se_ctx_set_pipeline_lead(se_ctx *ctx, int mode);
 int  se_ctx_set_feature_flush(se_ctx *ctx, int enable);
 /* Kernel choice of se_etsi_denoise_batch / se_p16_wiener_batch (no counterpart in the reference, whose etsi_denoise /
  * func_Wiener are one serial loop per call -- etsi/cpp/AdvFrontEnd.c:125-210, aurora_etsi/NoiseSup.cpp:1140-1407):
- * batches too small to give every SM its warps run on a kernel that spreads ONE utterance over a CTA of 4-5 warps
- * (input + stage-0 PSD | stage 0 | stage-1 PSD | stage 1 + outputs | CompCeps, software-pipelined over blocks) --
- * ~3x lower latency for a lone utterance, bit-identical results.  mode 0 (default): chosen by batch size;
+ * batches too small to give every SM its warps run on a kernel that spreads ONE utterance over a CTA of 5-8 warps
+ * (input + stage-0 PSD | stage-0 recursion | FIR + stage-1 PSD | stage-1 recursion | FIR + outputs | CompCeps halves |
+ * statistics, software-pipelined over blocks) -- 3-4x lower latency for a lone utterance, bit-identical results.  mode 0 (default): chosen by batch size;
  * 1: always the one-warp-per-utterance batch kernel; 2: the pipelined kernel whenever it is able to run. */
 int  se_ctx_set_ns_pipeline(se_ctx *ctx, int mode);
 /* Arithmetic mode of the NoiseSup family (se_etsi_denoise_batch, se_etsi_features_batch, se_etsi16k_features_batch,
